@@ -1,0 +1,86 @@
+"""ctypes binding of libfdsm.so (include/fdsm.h).  No torch types cross this boundary: only raw
+device pointers, sizes, scalars and the cudaStream_t handle.
+
+There is NO CPU fallback: if the shared library is missing or a tensor is not a CUDA fp32 tensor
+the call raises.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libfdsm.so")
+
+ROW_X, ROW_PLUS, ROW_MINUS = 1, 2, 4
+
+_f32p = C.c_void_p
+_i64 = C.c_int64
+_i32 = C.c_int32
+_u64 = C.c_uint64
+_f32 = C.c_float
+_stream = C.c_void_p
+
+
+class StackArgs(C.Structure):
+    """Mirror of `fdsm_stack_args` (include/fdsm.h)."""
+    _fields_ = [
+        ("x", _f32p), ("ldx", _i64),
+        ("dir", _f32p), ("lddir", _i64),
+        ("normalize_dir", _i32), ("dir_scale", _f32),
+        ("noise", _f32p), ("ldnoise", _i64),
+        ("sigma", _f32p), ("labels", C.c_void_p),
+        ("perturb_input", _i32), ("dot_mode", _i32),
+        ("out", _f32p), ("ldout", _i64),
+        ("row_mask", _i32),
+        ("v_out", _f32p), ("ldv", _i64),
+        ("dot_out", _f32p),
+        ("seed", _u64), ("offset", _u64), ("row0", _u64),
+        ("B", _i64), ("D", _i64),
+    ]
+
+
+# name -> (restype, argtypes); must list every symbol include/fdsm.h declares
+PROTOTYPES = {
+    "fdsm_version": (C.c_int, []),
+    "fdsm_last_error_string": (C.c_char_p, []),
+    "fdsm_device_supported": (C.c_int, []),
+    "fdsm_stack": (C.c_int, [C.POINTER(StackArgs), _stream]),
+    "fdsm_direction": (C.c_int, [_f32p, _i64, _f32p, _i64, _i64, _i64, _f32, _u64, _u64, _u64, _stream]),
+    "fdsm_philox_normal": (C.c_int, [_f32p, _i64, _i64, _i64, _i32, _u64, _u64, _u64, _stream]),
+    "fdsm_combine_energy_fwd": (C.c_int, [_f32p, _i64, _i32, _f32, _f32, _i32, _f32p, _f32p, _stream]),
+    "fdsm_combine_energy_bwd": (C.c_int, [_f32p, _i64, _i32, _f32, _f32, _i32, _f32p, _f32p, _stream]),
+    "fdsm_combine_dsm_fwd": (C.c_int, [_f32p, _f32p, _f32p, _i64, _f32, _f32, _f32, _f32p, _f32p, _stream]),
+    "fdsm_combine_dsm_bwd": (C.c_int, [_f32p, _f32p, _f32p, _i64, _f32, _f32, _f32, _f32p, _f32p, _stream]),
+    "fdsm_combine_score": (C.c_int, [_f32p, _i64, _f32p, _i64, _f32p, C.c_void_p, _f32, _i64, _i64, _f32, _i32,
+                                     _f32p, _f32p, _f32p, _f32p, _i64, _stream]),
+}
+
+_lib = None
+
+
+class FdsmError(RuntimeError):
+    pass
+
+
+def load():
+    """Load libfdsm.so (once) and bind every prototype.  Raises if the library is not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise FdsmError(
+            f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(or `make -C fd-scorematching_b200/csrc`).  There is no CPU/PyTorch fallback.")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in PROTOTYPES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is missing
+        fn.restype, fn.argtypes = res, args
+    if lib.fdsm_version() != 1:
+        raise FdsmError(f"libfdsm ABI version {lib.fdsm_version()} != 1")
+    _lib = lib
+    return lib
+
+
+def check(rc, what=""):
+    if rc != 0:
+        msg = load().fdsm_last_error_string()
+        raise FdsmError(f"{what} failed (rc={rc}): {msg.decode() if msg else ''}")

@@ -1,0 +1,248 @@
+"""Drop-in FD score-matching losses: the reference's call signatures over the sm_100a kernels.
+
+Each adapter keeps the reference function's name, argument order, defaults and error behaviour
+(file:line cited per function, relative to the reference repo).  Generic mode: kernels (1)+(2)
+build the stacked batch, the caller's network (any callable) runs in PyTorch, kernel (4) turns the
+outputs into the loss and feeds the analytic gradient back into autograd.  When the network is one
+of our fused MLP energies (``mlp.FusedEnergyMLP``) its forward/backward are the tcgen05 GEMMs.
+
+Extra keyword-only arguments (``u=``, ``dsm_noise=``) inject the random draws the reference takes
+from the global generator, in its RNG order, for parity tests; without them the draws come from
+the in-kernel Philox streams (``ops.manual_seed``).
+"""
+import math
+
+import torch
+
+from . import ops
+from ._lib import ROW_MINUS, ROW_PLUS, ROW_X
+
+
+class Flags:
+    """Stand-in for DeepEBM's process-global ``Utils.flags.FLAGS`` (Utils/flags.py:27-77), which
+    the reference's DeepEBM losses read directly (loss_train.py:6,97-98,213-215)."""
+    batch_size = None   # None -> samples.shape[0]
+    esm_eps = 0.05      # configs/default.yaml:28
+    loss_coe = 1e-4     # configs/default.yaml:24
+
+
+FLAGS = Flags()
+
+
+def _flat(samples):
+    if samples.dim() < 2:
+        raise ValueError("samples must have a batch dimension and at least one data dimension")
+    B = samples.shape[0]
+    return samples.reshape(B, -1), B, int(samples[0].numel()) if B > 0 else int(math.prod(samples.shape[1:]))
+
+
+def _check_particles(n_particles, what):
+    if n_particles != 1:
+        # the reference multiplies a (n_particles*B,) loss by a (B,) sigma vector: shape error for != 1
+        raise RuntimeError(f"{what}: only n_particles=1 is shape-correct in the reference "
+                           "(ncsn/losses/sliced_sm.py:205, ncsnv2/losses/dsm.py:131)")
+
+
+# ------------------------------------------------------------------------------------------------
+# energy form
+# ------------------------------------------------------------------------------------------------
+def _fd_energy(energy_net, x2, *, v=None, u=None, eps, scale, c1=2.0, mean=True, rows3=True, detach=False,
+               mode=0, want_per_sample=False):
+    B, D = x2.shape
+    mask = (ROW_X | ROW_PLUS | ROW_MINUS) if rows3 else (ROW_X | ROW_PLUS)
+    if v is not None:
+        stacked, _, _ = ops.stack(x2, row_mask=mask, scale=1.0, direction=v, normalize=False)
+    else:
+        stacked, _, _ = ops.stack(x2, row_mask=mask, scale=eps, direction=u, normalize=True)
+    if detach:
+        with torch.no_grad():
+            E = energy_net(stacked)
+            return ops.CombineEnergy.apply(E, B, mode, float(c1), float(scale), mean, want_per_sample)
+    E = energy_net(stacked)
+    return ops.CombineEnergy.apply(E, B, mode, float(c1), float(scale), mean, want_per_sample)
+
+
+def efficient_score_matching_conjugate(energy_net, samples, noise=None, eps=0.1, noise_type="sphere", detach=False,
+                                       *, u=None):
+    """FD-SSM, energy form -- SSM/losses/efficient_sm.py:47-73.  ``noise`` (already-normalised v) is
+    the reference's own injection hook; ``noise_type`` is ignored there and here."""
+    dim = samples.shape[1]
+    return _fd_energy(energy_net, samples, v=noise, u=u, eps=eps, scale=dim / eps ** 2, detach=detach)[0]
+
+
+def single_efficient_score_matching(energy_net, samples, eps=0.01, noise_type="sphere", *, u=None):
+    """One-sided 2-point FD -- SSM/losses/efficient_sm.py:7-24 (sum of d^2+4d, no /eps^2)."""
+    if noise_type != "sphere":
+        raise NotImplementedError("only noise_type='sphere' is implemented on the CUDA path "
+                                  "(efficient_sm.py:10-11 'radermacher' is not part of the hot path)")
+    x2 = samples.reshape(samples.shape[0], -1)
+    return _fd_energy(energy_net, x2, u=u, eps=eps, scale=1.0, mean=False, rows3=False, mode=1)[0]
+
+
+def MLE_efficient_score_matching_conjugate(energy_net, samples, eps=0.01, mle_ratio=10, noise_type="sphere", *, u=None):
+    """SSM/losses/efficient_sm.py:101-123: c1 = mle_ratio, summed, no /eps^2."""
+    if noise_type != "sphere":
+        raise NotImplementedError("only noise_type='sphere' is implemented on the CUDA path")
+    x2 = samples.reshape(samples.shape[0], -1)
+    return _fd_energy(energy_net, x2, u=u, eps=eps, scale=1.0, c1=mle_ratio, mean=False)[0]
+
+
+def ssm_fd(energy, samples, *, eps=None, batch_size=None, u=None):
+    """DeepEBM FD-SSM -- DeepEBM/ESM/loss_train.py:212-234 (no *D factor; eps=FLAGS.esm_eps;
+    samples.view(FLAGS.batch_size, dim))."""
+    eps = FLAGS.esm_eps if eps is None else eps
+    bs = batch_size or FLAGS.batch_size or samples.shape[0]
+    x2 = samples.reshape(bs, -1)
+    if u is not None:
+        u = u.reshape(bs, -1)
+    return _fd_energy(energy, x2, u=u, eps=eps, scale=1.0 / eps ** 2)[0]
+
+
+def ssm_fd_nop(energy, samples, *, eps=None, batch_size=None, u=None):
+    """Timing-ablation twin with three separate forwards -- loss_train.py:237-255.  Same stacked
+    build; the three row blocks are handed to the network one at a time."""
+    eps = FLAGS.esm_eps if eps is None else eps
+    bs = batch_size or FLAGS.batch_size or samples.shape[0]
+    x2 = samples.reshape(bs, -1)
+    if u is not None:
+        u = u.reshape(bs, -1)
+    stacked, _, _ = ops.stack(x2, row_mask=7, scale=eps, direction=u, normalize=True)
+    E = torch.cat([energy(stacked[:bs]), energy(stacked[bs:2 * bs]), energy(stacked[2 * bs:])], 0)
+    return ops.CombineEnergy.apply(E, bs, 0, 2.0, 1.0 / eps ** 2, True, False)[0]
+
+
+# ------------------------------------------------------------------------------------------------
+# DSM energy form
+# ------------------------------------------------------------------------------------------------
+def _fd_dsm(energy_net, x2, sigma_b, *, eps_scale, alpha, beta, gamma, weight_by_sigma, perturb, dot_mode, u, dsm_noise,
+            separate=False):
+    B, D = x2.shape
+    stacked, _, dot = ops.stack(x2, row_mask=ROW_PLUS | ROW_MINUS, scale=eps_scale, direction=u, normalize=True,
+                                noise=dsm_noise, sigma=sigma_b, perturb=perturb, dot_mode=dot_mode, want_dot=True)
+    if separate:
+        E = torch.cat([energy_net(stacked[:B]), energy_net(stacked[B:])], 0)
+    else:
+        E = energy_net(stacked)
+    return ops.CombineDsm.apply(E, dot, sigma_b if weight_by_sigma else None, B, float(alpha), float(beta), float(gamma))
+
+
+def dsm_fd(energy_net, samples, sigma=1, eps=0.001, *, u=None, dsm_noise=None):
+    """FD-DSM -- SSM/losses/efficient_sm.py:27-44.  RNG order: DSM noise, then direction."""
+    B, dim = samples.shape[0], samples.shape[1]
+    sig = torch.full((B,), float(sigma), device=samples.device, dtype=torch.float32)
+    return _fd_dsm(energy_net, samples, sig, eps_scale=eps * dim ** 0.5, alpha=sigma ** 2 * 0.5, beta=1.0,
+                   gamma=1.0 / (2.0 * eps ** 2), weight_by_sigma=False, perturb=True, dot_mode=0, u=u, dsm_noise=dsm_noise)
+
+
+def dsm_tracetrick_FD(energy_net, samples, sigma=1, eps=0.1, *, u=None, dsm_noise=None):
+    """SSM/losses/dsm.py:122-141.  As in the reference the stacked input perturbs ``samples``, not the
+    noised input (:131)."""
+    B, dim = samples.shape[0], samples.shape[-1]
+    sig = torch.full((B,), float(sigma), device=samples.device, dtype=torch.float32)
+    return _fd_dsm(energy_net, samples, sig, eps_scale=eps, alpha=sigma ** 2, beta=2.0, gamma=dim / (8.0 * eps * eps),
+                   weight_by_sigma=False, perturb=False, dot_mode=0, u=u, dsm_noise=dsm_noise)
+
+
+def mdsm_fd(energy, x_real, sigmas, sigma02, dim, *, eps=None, batch_size=None, loss_coe=None, u=None, dsm_noise=None,
+            _separate=False):
+    """FD multiscale DSM -- DeepEBM/ESM/loss_train.py:96-118; sigmas is the (B,1) per-batch-position
+    schedule of train_dsm.py:50-57."""
+    eps = FLAGS.esm_eps if eps is None else eps
+    coe = FLAGS.loss_coe if loss_coe is None else loss_coe
+    bs = batch_size or FLAGS.batch_size or x_real.shape[0]
+    x2 = x_real.reshape(bs, dim)
+    sig = sigmas.reshape(-1).to(torch.float32)
+    if sig.numel() != bs:
+        raise RuntimeError(f"sigmas has {sig.numel()} entries for batch size {bs}")
+    if u is not None:
+        u = u.reshape(bs, dim)
+    if dsm_noise is not None:
+        dsm_noise = dsm_noise.reshape(bs, dim)
+    return _fd_dsm(energy, x2, sig, eps_scale=eps, alpha=0.5, beta=1.0 / sigma02, gamma=coe / eps ** 2 * dim,
+                   weight_by_sigma=True, perturb=True, dot_mode=1, u=u, dsm_noise=dsm_noise, separate=_separate)
+
+
+def mdsm_fd_nop(energy, x_real, sigmas, sigma02, dim, **kw):
+    """loss_train.py:151-170: two separate forwards."""
+    return mdsm_fd(energy, x_real, sigmas, sigma02, dim, _separate=True, **kw)
+
+
+# ------------------------------------------------------------------------------------------------
+# score-net form
+# ------------------------------------------------------------------------------------------------
+def _fd_score(scorenet, samples, *, eps_dir, k, sigma_table=None, labels=None, power=2.0, projected=False, u=None,
+              dsm_noise=None, hook=None):
+    x2, B, D = _flat(samples)
+    if u is not None:
+        u = u.reshape(B, D)
+    if dsm_noise is not None:
+        dsm_noise = dsm_noise.reshape(B, D)
+    sig = sigma_table.to(torch.float32).contiguous() if sigma_table is not None else None
+    stacked, v, _ = ops.stack(x2, row_mask=ROW_PLUS | ROW_MINUS, scale=eps_dir, direction=u, normalize=True,
+                              noise=dsm_noise, sigma=sig, labels=labels, perturb=True, want_v=True)
+    cat_input = stacked.view(2 * B, *samples.shape[1:])
+    if labels is not None:
+        out = scorenet(cat_input, torch.cat([labels, labels], 0))
+    else:
+        out = scorenet(cat_input)
+    loss, per = ops.CombineScore.apply(out, v, sig, labels, float(power), B, D, float(k), projected, True)
+    if hook is not None:
+        hook(per, labels)
+    return loss
+
+
+def esm_scorenet_VR(scorenet, samples, eps=0.1, *, u=None):
+    """FD-SSMVR for score nets -- SSM/losses/efficient_sm.py:76-98 (dim = samples.shape[-1])."""
+    dim = samples.shape[-1]
+    return _fd_score(scorenet, samples, eps_dir=eps, k=dim / (2 * eps * eps), u=u)
+
+
+def ncsn_anneal_ESM_scorenet_VR(scorenet, samples, labels, sigmas, n_particles=1, eps=0.1, *, u=None, dsm_noise=None):
+    """ncsn annealed FD-SSMVR -- ncsn/losses/sliced_sm.py:174-207 (constant 32*32*3 hard-coded at
+    :202, sigma^2 weighting :205)."""
+    _check_particles(n_particles, "anneal_ESM_scorenet_VR")
+    return _fd_score(scorenet, samples, eps_dir=eps, k=(32. * 32. * 3.) / (2. * eps * eps), sigma_table=sigmas,
+                     labels=labels, power=2.0, u=u, dsm_noise=dsm_noise)
+
+
+def ncsn_anneal_ESM_scorenet(scorenet, samples, labels, sigmas, n_particles=1, *, u=None, dsm_noise=None):
+    """ncsn annealed FD-SSM (non-VR) -- ncsn/losses/sliced_sm.py:210-240 (eps fixed 0.1, no /eps^2)."""
+    _check_particles(n_particles, "anneal_ESM_scorenet")
+    return _fd_score(scorenet, samples, eps_dir=0.1, k=0.0, sigma_table=sigmas, labels=labels, power=2.0,
+                     projected=True, u=u, dsm_noise=dsm_noise)
+
+
+def anneal_ESM_scorenet_VR(scorenet, samples, sigmas, labels=None, anneal_power=2.0, hook=None, n_particles=1, eps=0.1,
+                           *, u=None, dsm_noise=None):
+    """ncsnv2 annealed FD-SSMVR -- ncsnv2/losses/dsm.py:77-136 (data_dim = prod(shape[1:]), labels
+    drawn inside when None, sigma**anneal_power, hook(per_sample, labels))."""
+    _check_particles(n_particles, "anneal_ESM_scorenet_VR")
+    data_dim = int(math.prod(samples.shape[1:]))
+    if labels is None:
+        labels = torch.randint(0, len(sigmas), (samples.shape[0],), device=samples.device)
+    return _fd_score(scorenet, samples, eps_dir=eps, k=data_dim / (2.0 * eps * eps), sigma_table=sigmas, labels=labels,
+                     power=anneal_power, u=u, dsm_noise=dsm_noise, hook=hook)
+
+
+# ------------------------------------------------------------------------------------------------
+# unified entry point (BASELINE.json: "(model, samples, n_particles, eps, sigma)")
+# ------------------------------------------------------------------------------------------------
+def fd_loss(model, samples, n_particles=1, eps=0.1, sigma=None, *, mode="ssm", labels=None, sigmas=None, noise=None,
+            u=None, dsm_noise=None, anneal_power=2.0, hook=None, sigma02=0.01, loss_coe=1e-4):
+    """mode: 'ssm' (a1), 'ssm_deepebm' (a7), 'dsm' (a3, needs sigma), 'mdsm' (a9, sigma = per-sample
+    schedule), 'ssmvr_score' (a4), 'anneal_ssmvr' (a13, needs sigmas)."""
+    _check_particles(n_particles, f"fd_loss[{mode}]")
+    if mode == "ssm":
+        return efficient_score_matching_conjugate(model, samples.reshape(samples.shape[0], -1), noise=noise, eps=eps, u=u)
+    if mode == "ssm_deepebm":
+        return ssm_fd(model, samples, eps=eps, u=u)
+    if mode == "dsm":
+        return dsm_fd(model, samples, sigma=1 if sigma is None else sigma, eps=eps, u=u, dsm_noise=dsm_noise)
+    if mode == "mdsm":
+        return mdsm_fd(model, samples, sigma, sigma02, int(math.prod(samples.shape[1:])), eps=eps, loss_coe=loss_coe,
+                       u=u, dsm_noise=dsm_noise)
+    if mode == "ssmvr_score":
+        return esm_scorenet_VR(model, samples, eps=eps, u=u)
+    if mode == "anneal_ssmvr":
+        return anneal_ESM_scorenet_VR(model, samples, sigmas, labels, anneal_power, hook, 1, eps, u=u, dsm_noise=dsm_noise)
+    raise ValueError(f"unknown mode {mode!r}")

@@ -1,0 +1,265 @@
+"""Tensor-level wrappers of the libfdsm kernels and the autograd Functions around kernel (4).
+
+PyTorch is plumbing here: it owns device memory and streams; every computation below is a call
+through the C ABI (``_lib``).  No fallback path exists.
+"""
+import ctypes as C
+import threading
+
+import torch
+
+from . import _lib
+from ._lib import ROW_MINUS, ROW_PLUS, ROW_X, StackArgs, check
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _req(t, name, dtype=torch.float32):
+    if t is None:
+        return None
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise _lib.FdsmError(f"{name} must be a CUDA tensor (no CPU fallback); got "
+                             f"{type(t).__name__}{'' if not isinstance(t, torch.Tensor) else ' on ' + str(t.device)}")
+    if t.dtype != dtype:
+        raise TypeError(f"{name} must be {dtype}, got {t.dtype} (the hot path computes in fp32)")
+    return t
+
+
+def _rows(t, name):
+    """(B, D) row-major view with unit inner stride; returns (tensor, ld)."""
+    if t.dim() != 2:
+        raise ValueError(f"{name} must be 2-D, got shape {tuple(t.shape)}")
+    if t.shape[0] > 1 and t.shape[1] > 0 and (t.stride(1) != 1 or t.stride(0) < t.shape[1]):
+        t = t.contiguous()
+    if t.shape[1] > 0 and t.stride(1) != 1:
+        t = t.contiguous()
+    ld = t.stride(0) if t.shape[0] > 1 else max(t.shape[1], 1)
+    return t, ld
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else None
+
+
+# --------------------------------------------------------------------------------------------
+# Philox state: (seed, offset).  Every production-mode draw consumes one offset.
+# --------------------------------------------------------------------------------------------
+class _Rng(threading.local):
+    seed = 0x5EED_F05D
+    offset = 0
+    row0 = 0
+
+
+_rng = _Rng()
+
+
+def manual_seed(seed, offset=0):
+    """Seed the Philox streams used when no noise is injected."""
+    _rng.seed, _rng.offset = int(seed) & (2 ** 64 - 1), int(offset)
+
+
+def set_row_offset(row0):
+    """Global index of this rank's first sample (rank*B_local), so a sharded batch draws exactly
+    what the un-sharded batch would."""
+    _rng.row0 = int(row0)
+
+
+def next_draw():
+    o = _rng.offset
+    _rng.offset += 1
+    return _rng.seed, o, _rng.row0
+
+
+# --------------------------------------------------------------------------------------------
+# kernels (1)+(2)
+# --------------------------------------------------------------------------------------------
+def stack(x, *, row_mask, scale, direction=None, normalize=True, noise=None, sigma=None, labels=None,
+          perturb=True, dot_mode=0, want_v=False, want_dot=False, draw=None, out=None):
+    """Fused direction sampling + normalisation + stacked-batch build (fdsm_stack).
+
+    x: (B, D) fp32 CUDA.  Returns (stacked (rows*B, D) | None, v (B, D) | None, dot (B,) | None)."""
+    lib = _lib.load()
+    x = _req(x, "samples")
+    x, ldx = _rows(x, "samples")
+    B, D = x.shape
+    a = StackArgs()
+    a.x, a.ldx = _ptr(x), ldx
+    keep = [x]
+    if direction is not None:
+        direction, ldd = _rows(_req(direction, "direction"), "direction")
+        if direction.shape != x.shape:
+            raise ValueError(f"direction shape {tuple(direction.shape)} != samples {tuple(x.shape)}")
+        a.dir, a.lddir = _ptr(direction), ldd
+        keep.append(direction)
+    a.normalize_dir, a.dir_scale = int(bool(normalize)), float(scale)
+    if sigma is not None:
+        sigma = _req(sigma, "sigma").contiguous().view(-1)
+        a.sigma = _ptr(sigma)
+        keep.append(sigma)
+        if labels is not None:
+            labels = _req(labels, "labels", torch.int64).contiguous()
+            if labels.numel() != B:
+                raise ValueError("labels must have one entry per sample")
+            a.labels = _ptr(labels)
+            keep.append(labels)
+        elif sigma.numel() != B:
+            raise ValueError(f"per-sample sigma must have B={B} entries, got {sigma.numel()}")
+        if noise is not None:
+            noise, ldn = _rows(_req(noise, "noise"), "noise")
+            if noise.shape != x.shape:
+                raise ValueError("noise shape != samples shape")
+            a.noise, a.ldnoise = _ptr(noise), ldn
+            keep.append(noise)
+    a.perturb_input, a.dot_mode = int(bool(perturb)), int(dot_mode)
+    rows = bin(row_mask & 7).count("1")
+    if rows:
+        if out is None:
+            out = torch.empty((rows * B, D), device=x.device, dtype=torch.float32)
+        a.out, a.ldout = _ptr(out), (out.stride(0) if out.shape[0] > 1 else max(D, 1))
+    a.row_mask = row_mask
+    v = dot = None
+    if want_v:
+        v = torch.empty((B, D), device=x.device, dtype=torch.float32)
+        a.v_out, a.ldv = _ptr(v), max(D, 1)
+    if want_dot:
+        dot = torch.empty((B,), device=x.device, dtype=torch.float32)
+        a.dot_out = _ptr(dot)
+    seed, offset, row0 = draw if draw is not None else next_draw()
+    a.seed, a.offset, a.row0 = seed, offset, row0
+    a.B, a.D = B, D
+    check(lib.fdsm_stack(C.byref(a), _stream()), "fdsm_stack")
+    return out, v, dot
+
+
+def direction(B, D, scale, *, u=None, device=None, draw=None):
+    """Kernel (1) alone: v = scale*u/||u|| with u injected or Philox."""
+    lib = _lib.load()
+    if u is not None:
+        u, ldu = _rows(_req(u, "u"), "u")
+        device = u.device
+    v = torch.empty((B, D), device=device, dtype=torch.float32)
+    seed, offset, row0 = draw if draw is not None else next_draw()
+    check(lib.fdsm_direction(_ptr(u), ldu if u is not None else 0, _ptr(v), max(D, 1), B, D, float(scale), seed,
+                             offset, row0, _stream()), "fdsm_direction")
+    return v
+
+
+def philox_normal(B, D, stream_id, seed, offset, row0=0, device="cuda"):
+    lib = _lib.load()
+    out = torch.empty((B, D), device=device, dtype=torch.float32)
+    check(lib.fdsm_philox_normal(_ptr(out), max(D, 1), B, D, stream_id, seed, offset, row0, _stream()),
+          "fdsm_philox_normal")
+    return out
+
+
+# --------------------------------------------------------------------------------------------
+# kernel (4): autograd Functions
+# --------------------------------------------------------------------------------------------
+class CombineEnergy(torch.autograd.Function):
+    """loss = scale * reduce_b[(E2-E3)^2/8 - E2 - E3 + c1*E1]  (mode 0) / sum(d^2+4d) (mode 1)."""
+
+    @staticmethod
+    def forward(ctx, E, B, mode, c1, scale, mean, want_per_sample):
+        lib = _lib.load()
+        E = _req(E, "energy output").contiguous().view(-1)
+        rows = 3 if mode == 0 else 2
+        if E.numel() != rows * B:
+            raise ValueError(f"energy net returned {E.numel()} values for a stacked batch of {rows * B} rows")
+        loss = torch.empty((), device=E.device, dtype=torch.float32)
+        per = torch.empty((B,), device=E.device, dtype=torch.float32) if want_per_sample else None
+        check(lib.fdsm_combine_energy_fwd(_ptr(E), B, mode, c1, scale, int(mean), _ptr(per), _ptr(loss), _stream()),
+              "fdsm_combine_energy_fwd")
+        ctx.save_for_backward(E)
+        ctx.cfg = (B, mode, c1, scale, int(mean))
+        if want_per_sample:
+            ctx.mark_non_differentiable(per)
+            return loss, per
+        return loss, None
+
+    @staticmethod
+    def backward(ctx, gout, _gper):
+        lib = _lib.load()
+        (E,) = ctx.saved_tensors
+        B, mode, c1, scale, mean = ctx.cfg
+        gout = gout.contiguous().float()
+        dE = torch.empty_like(E)
+        check(lib.fdsm_combine_energy_bwd(_ptr(E), B, mode, c1, scale, mean, _ptr(gout), _ptr(dE), _stream()),
+              "fdsm_combine_energy_bwd")
+        return dE, None, None, None, None, None, None
+
+
+class CombineDsm(torch.autograd.Function):
+    """loss = gamma*mean_b[(alpha*(E2-E1) + beta*dot_b)^2 / sigma_b^2]."""
+
+    @staticmethod
+    def forward(ctx, E, dot, sigma_b, B, alpha, beta, gamma):
+        lib = _lib.load()
+        E = _req(E, "energy output").contiguous().view(-1)
+        if E.numel() != 2 * B:
+            raise ValueError(f"energy net returned {E.numel()} values for a stacked batch of {2 * B} rows")
+        loss = torch.empty((), device=E.device, dtype=torch.float32)
+        check(lib.fdsm_combine_dsm_fwd(_ptr(E), _ptr(dot), _ptr(sigma_b), B, alpha, beta, gamma, None, _ptr(loss),
+                                       _stream()), "fdsm_combine_dsm_fwd")
+        ctx.save_for_backward(E, dot, sigma_b)
+        ctx.cfg = (B, alpha, beta, gamma)
+        return loss
+
+    @staticmethod
+    def backward(ctx, gout):
+        lib = _lib.load()
+        E, dot, sigma_b = ctx.saved_tensors
+        B, alpha, beta, gamma = ctx.cfg
+        gout = gout.contiguous().float()
+        dE = torch.empty_like(E)
+        check(lib.fdsm_combine_dsm_bwd(_ptr(E), _ptr(dot), _ptr(sigma_b), B, alpha, beta, gamma, _ptr(gout), _ptr(dE),
+                                       _stream()), "fdsm_combine_dsm_bwd")
+        return dE, None, None, None, None, None, None
+
+
+class CombineScore(torch.autograd.Function):
+    """loss = mean_b w_b * sum_d[(s1+s2)^2/8 + (s1-s2) v k]  (or the projected non-VR form)."""
+
+    @staticmethod
+    def forward(ctx, s, v, sigma, labels, power, B, D, k, projected, want_per_sample):
+        lib = _lib.load()
+        s2d = _req(s, "score output").reshape(2 * B, D) if s.numel() == 2 * B * D else None
+        if s2d is None:
+            raise ValueError(f"score net returned shape {tuple(s.shape)}; expected 2B*D = {2 * B * D} elements")
+        s2d, lds = _rows(s2d, "score output")
+        loss = torch.empty((), device=s.device, dtype=torch.float32)
+        per = torch.empty((B,), device=s.device, dtype=torch.float32)
+        check(lib.fdsm_combine_score(_ptr(s2d), lds, _ptr(v), max(D, 1), _ptr(sigma), _ptr(labels), power, B, D, k,
+                                     int(projected), None, _ptr(per), _ptr(loss), None, 0, _stream()),
+              "fdsm_combine_score(fwd)")
+        ctx.save_for_backward(s2d, v, sigma, labels)
+        ctx.cfg = (power, B, D, k, int(projected), tuple(s.shape), lds)
+        ctx.mark_non_differentiable(per)
+        return loss, per
+
+    @staticmethod
+    def backward(ctx, gout, _gper):
+        lib = _lib.load()
+        s2d, v, sigma, labels = ctx.saved_tensors
+        power, B, D, k, projected, shape, lds = ctx.cfg
+        gout = gout.contiguous().float()
+        ds = torch.empty((2 * B, D), device=s2d.device, dtype=torch.float32)
+        check(lib.fdsm_combine_score(_ptr(s2d), lds, _ptr(v), max(D, 1), _ptr(sigma), _ptr(labels), power, B, D, k,
+                                     projected, _ptr(gout), None, None, _ptr(ds), max(D, 1), _stream()),
+              "fdsm_combine_score(bwd)")
+        return ds.view(shape), None, None, None, None, None, None, None, None, None
+
+
+def combine_score_fused(s2d, v, *, k, sigma=None, labels=None, power=2.0, projected=False):
+    """Single-pass fwd+bwd (root loss, upstream grad 1): returns (loss, per_sample, ds)."""
+    lib = _lib.load()
+    s2d, lds = _rows(_req(s2d, "score output"), "score output")
+    B, D = v.shape
+    loss = torch.empty((), device=s2d.device, dtype=torch.float32)
+    per = torch.empty((B,), device=s2d.device, dtype=torch.float32)
+    ds = torch.empty((2 * B, D), device=s2d.device, dtype=torch.float32)
+    check(lib.fdsm_combine_score(_ptr(s2d), lds, _ptr(v), max(D, 1), _ptr(sigma), _ptr(labels), float(power), B, D,
+                                 float(k), int(projected), None, _ptr(per), _ptr(loss), _ptr(ds), max(D, 1),
+                                 _stream()), "fdsm_combine_score(fused)")
+    return loss, per, ds

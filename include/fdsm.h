@@ -1,0 +1,137 @@
+/* libfdsm -- C ABI of the B200-native FD score-matching hot path.
+ *
+ * The reference (taufikxu/FD-ScoreMatching) is pure Python/PyTorch and has NO FFI layer: its
+ * boundary is the Python call `loss = f(net, samples, ...)`.  This header is the
+ * C-ABI a maintainer binds (ctypes stub in INTEGRATION.md) to replace the torch op sequences
+ * cited on each entry point (paths relative to the reference repo root).
+ *
+ * Conventions (all entry points):
+ *   - plain pointers + sizes; every pointer is a DEVICE pointer unless named `h_*`;
+ *   - the caller owns every buffer including workspaces; the library never allocates or frees
+ *     device memory and keeps no pointer after return;
+ *   - all work is enqueued on `stream` (a cudaStream_t passed as void*); no host sync, no host
+ *     read of device data => CUDA-graph capturable;
+ *   - return 0 on success, <0 for argument errors, >0 = cudaError_t; message via
+ *     fdsm_last_error_string() (thread-local);
+ *   - row-major fp32 matrices with an explicit leading dimension `ld*` in elements;
+ *   - 128-bit vector path when D%4==0, ld%4==0 and 16-byte aligned bases; scalar path otherwise
+ *     (D=11 of config 1).
+ */
+#ifndef FDSM_H_
+#define FDSM_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FDSM_ABI_VERSION 1
+
+#define FDSM_OK 0
+#define FDSM_ERR_INVALID_ARGUMENT (-1)
+#define FDSM_ERR_UNSUPPORTED (-2)
+
+typedef void* fdsm_stream_t; /* cudaStream_t */
+
+int fdsm_version(void);
+const char* fdsm_last_error_string(void);
+/* 1 if the current device is compute capability 10.x (the only target), else 0. */
+int fdsm_device_supported(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Kernels (1)+(2): direction sampling + per-sample L2 normalisation + stacked-batch build.
+ *
+ * Replaces   u = randn_like(x); v = u / ||u||_2 * eps; cat([x, x+v, x-v])            or
+ *            n = randn_like(x); xt = x + sigma_b*n; u = ...; cat([xt+v, xt-v])
+ * at SSM/losses/efficient_sm.py:9-16,28-37,53-59,79-84,105-112; SSM/losses/dsm.py:124-132;
+ * DeepEBM/ESM/loss_train.py:101-107,217-222; ncsn/losses/sliced_sm.py:175-188,211-224;
+ * ncsnv2/losses/dsm.py:92-113.
+ * ------------------------------------------------------------------------------------------ */
+#define FDSM_ROW_X 1     /* emit base row          (x or xt)   */
+#define FDSM_ROW_PLUS 2  /* emit base + v                       */
+#define FDSM_ROW_MINUS 4 /* emit base - v                       */
+
+typedef struct fdsm_stack_args {
+  const float* x;        /* (B, D) samples; may be NULL iff row_mask == 0                       */
+  int64_t ldx;
+  const float* dir;      /* injected direction (B, D), or NULL => Philox stream 0                */
+  int64_t lddir;
+  int32_t normalize_dir; /* 1: v = dir/||dir||*dir_scale (dir is raw u); 0: v = dir as given     */
+  float dir_scale;       /* eps (times sqrt(D) for dsm_fd, efficient_sm.py:33-35)                */
+  const float* noise;    /* injected unit-Gaussian DSM noise n (B, D), or NULL => Philox stream 1;
+                            only used when `sigma` != NULL                                       */
+  int64_t ldnoise;
+  const float* sigma;    /* per-sample sigma (B) -- or the sigma table when `labels` != NULL;
+                            NULL => no DSM noise                                                 */
+  const int64_t* labels; /* optional (B): sigma_b = sigma[labels[b]] (ncsn/ncsnv2)               */
+  int32_t perturb_input; /* 1: base = x + sigma_b*n; 0: base = x (dsm_tracetrick_FD, dsm.py:131) */
+  int32_t dot_mode;      /* dot_out: 0 = sum_d v*(sigma_b*n) (efficient_sm.py:41, dsm.py:137);
+                                     1 = sum_d v*((x+sigma_b*n)-x) (loss_train.py:112)            */
+  float* out;            /* (popcount(row_mask)*B, D) stacked rows in X,PLUS,MINUS order; may be
+                            NULL iff row_mask == 0                                               */
+  int64_t ldout;
+  int32_t row_mask;
+  float* v_out;          /* optional (B, D): the normalised direction v                          */
+  int64_t ldv;
+  float* dot_out;        /* optional (B)                                                         */
+  uint64_t seed;         /* Philox key                                                           */
+  uint64_t offset;       /* Philox draw counter (step)                                           */
+  uint64_t row0;         /* global index of local row 0 (rank*B_local): shards draw what the
+                            un-sharded batch would                                               */
+  int64_t B, D;
+} fdsm_stack_args;
+
+int fdsm_stack(const fdsm_stack_args* args, fdsm_stream_t stream);
+
+/* Kernel (1) alone: v = eps_scale * u/||u||, u ~ Philox N(0,I) (dir == NULL) or injected. */
+int fdsm_direction(const float* dir, int64_t lddir, float* v, int64_t ldv, int64_t B, int64_t D, float scale,
+                   uint64_t seed, uint64_t offset, uint64_t row0, fdsm_stream_t stream);
+
+/* Raw Philox N(0,1) draws of a stream (0 = direction, 1 = DSM noise), no normalisation: what the
+ * fused kernels consume internally; exposed for the statistical / bit-exactness tests. */
+int fdsm_philox_normal(float* out, int64_t ld, int64_t B, int64_t D, int32_t stream_id, uint64_t seed,
+                       uint64_t offset, uint64_t row0, fdsm_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Kernel (4): central-difference combine, forward and analytic backward.
+ * ------------------------------------------------------------------------------------------ */
+/* Energy form.  E = energy(stacked) (3B) [mode 0] or (2B) [mode 1].
+ *   mode 0: per_b = (E2-E3)^2/8 - E2 - E3 + c1*E1        efficient_sm.py:61-71,113-121;
+ *                                                         loss_train.py:225-232
+ *   mode 1: d = E1-E2; per_b = d^2 + 4d                   efficient_sm.py:21-22
+ *   loss = scale * (mean ? mean_b : sum_b) per_b ; per_sample (optional) = scale*per_b
+ * bwd: dE = gout[0] * dloss/dE   (gout: device scalar, NULL => 1)                           */
+int fdsm_combine_energy_fwd(const float* E, int64_t B, int32_t mode, float c1, float scale, int32_t mean,
+                            float* per_sample, float* loss, fdsm_stream_t stream);
+int fdsm_combine_energy_bwd(const float* E, int64_t B, int32_t mode, float c1, float scale, int32_t mean,
+                            const float* gout, float* dE, fdsm_stream_t stream);
+
+/* DSM energy form.  E = energy([xt+v, xt-v]) (2B); logp = -E.
+ *   r_b = alpha*(E[B+b]-E[b]) + beta*dot_b ; per_b = r_b^2 * cw_b ; loss = gamma*mean_b per_b
+ *   cw_b = 1/sigma_b^2 when inv_sigma2 != NULL (sigma_b = inv_sigma2[b]), else 1.
+ *   loss_train.py:109-117 (alpha .5, beta 1/sigma0^2, gamma loss_coe*D/eps^2);
+ *   efficient_sm.py:39-43 (alpha sigma^2/2, beta 1, gamma 1/(2 eps^2));
+ *   SSM/losses/dsm.py:132-139 (alpha sigma^2, beta 2, gamma D/(8 eps^2)).                    */
+int fdsm_combine_dsm_fwd(const float* E, const float* dot, const float* sigma_b, int64_t B, float alpha, float beta,
+                         float gamma, float* per_sample, float* loss, fdsm_stream_t stream);
+int fdsm_combine_dsm_bwd(const float* E, const float* dot, const float* sigma_b, int64_t B, float alpha, float beta,
+                         float gamma, const float* gout, float* dE, fdsm_stream_t stream);
+
+/* Score-net form.  s = scorenet([x+v, x-v]) viewed (2B, D); v (B, D).
+ *   projected=0: per_b = w_b * sum_d[(s1+s2)^2/8 + (s1-s2)*v*k]     efficient_sm.py:86-96,
+ *                ncsn/losses/sliced_sm.py:192-205, ncsnv2/losses/dsm.py:118-131
+ *   projected=1: per_b = w_b * sum_d[((s1+s2)*v)^2/8 + (s1-s2)*v/2] ncsn/losses/sliced_sm.py:234-238
+ *   w_b = sigma[labels[b]]^power when sigma != NULL (labels NULL => sigma[b]), else 1.
+ *   loss = mean_b per_b.  `ds` (2B, D, optional) = gout[0] * dloss/ds  (gout NULL => 1).
+ *   Any of per_sample / loss may be NULL (backward-only call); ds NULL => forward only;
+ *   both given => the fused fwd+bwd single pass (20*D bytes per sample).                     */
+int fdsm_combine_score(const float* s, int64_t lds, const float* v, int64_t ldv, const float* sigma,
+                       const int64_t* labels, float power, int64_t B, int64_t D, float k, int32_t projected,
+                       const float* gout, float* per_sample, float* loss, float* ds, int64_t ldds,
+                       fdsm_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FDSM_H_ */

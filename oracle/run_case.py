@@ -1,0 +1,60 @@
+"""Run the oracle restatement (oracle/fd_losses.py) on a built case (oracle/cases.py).
+TEST INFRASTRUCTURE."""
+import math
+
+import torch
+
+from . import fd_losses as F
+
+
+def directions(c):
+    """Per-function direction scaling (see fd_losses.sphere_direction)."""
+    fn, eps, u = c["fn"], c["eps"], c["u"]
+    if fn == "a3":
+        return F.sphere_direction(u, eps, math.sqrt(c["D"]))
+    if fn == "a12":
+        return F.sphere_direction(u, 0.1)  # eps hard-coded, ncsn/losses/sliced_sm.py:220
+    return F.sphere_direction(u, eps)
+
+
+def oracle_loss(c, net=None):
+    net = net or c["net"]
+    fn, x, eps, D, B = c["fn"], c["x"], c["eps"], c["D"], c["B"]
+    v = directions(c)
+    if fn == "a1":
+        return F.fd_ssm(net, x, v, D / eps ** 2)
+    if fn == "a7":
+        xf = x.reshape(B, -1)
+        return F.fd_ssm(net, xf, v.reshape(B, -1), 1.0 / eps ** 2)
+    if fn == "a8":
+        return F.fd_ssm_nop(net, x.reshape(B, -1), v.reshape(B, -1), 1.0 / eps ** 2)
+    if fn == "a2":
+        return F.fd_one_sided(net, x, v)
+    if fn == "a5":
+        return F.fd_ssm(net, x, v, 1.0, c1=c["mle_ratio"], reduce="sum")
+    if fn == "a3":
+        return F.fd_dsm(net, x, c["n"] * c["sigma"], v, c["sigma"], eps)
+    if fn == "a6":
+        return F.dsm_tracetrick_fd(net, x, c["n"] * c["sigma"], v, c["sigma"], eps)
+    if fn == "a4":
+        return F.fd_ssmvr_score(net, x, v, eps)
+    if fn in ("a9", "a10"):
+        return F.mdsm_fd(net, x, c["n"], v, c["sig_b"], c["sigma02"], eps, c["loss_coe"], nop=fn == "a10")
+    if fn == "a11":
+        return F.anneal_fd_ssmvr(net, x, c["n"], v, c["labels"], c["sigmas"], eps, 32. * 32. * 3., 2.0)
+    if fn == "a12":
+        return F.anneal_fd_ssmvr(net, x, c["n"], v, c["labels"], c["sigmas"], 0.1, 0.0, 2.0, projected=True)
+    if fn == "a13":
+        return F.anneal_fd_ssmvr(net, x, c["n"], v, c["labels"], c["sigmas"], eps, float(D), c["anneal_power"])
+    raise KeyError(fn)
+
+
+def loss_and_grad(c, net=None):
+    net = net or c["net"]
+    for p in net.parameters():
+        p.grad = None
+    loss = oracle_loss(c, net)
+    loss.backward()
+    g = torch.cat([(p.grad if p.grad is not None else torch.zeros_like(p)).reshape(-1)
+                   for p in net.parameters()])
+    return loss.detach(), g

@@ -1,0 +1,72 @@
+"""CPU suite, part 2: the C-ABI library loads and exports every symbol include/fdsm.h declares,
+and the host-side adapters mirror the reference's argument/error behaviour.  No compute calls."""
+import ctypes
+import os
+import re
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _header_symbols():
+    names = set()
+    for fn in os.listdir(os.path.join(ROOT, "include")):
+        if fn.endswith(".h"):
+            txt = open(os.path.join(ROOT, "include", fn)).read()
+            txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+            names |= set(re.findall(r"\b(fdsm_[a-z0-9_]+)\s*\(", txt))
+    return names
+
+
+def test_library_exports_every_declared_symbol(fdsm):
+    lib = fdsm._lib.load()
+    syms = _header_symbols()
+    assert len(syms) >= 10
+    for s in syms:
+        assert hasattr(lib, s), f"libfdsm.so does not export {s}"
+    assert syms == set(fdsm._lib.PROTOTYPES), "ctypes prototype table out of sync with include/*.h"
+    assert lib.fdsm_version() == 1
+
+
+def test_stack_args_struct_matches_header(fdsm):
+    """Field order of the ctypes mirror == field order of the C struct."""
+    txt = open(os.path.join(ROOT, "include", "fdsm.h")).read()
+    body = txt[txt.index("typedef struct fdsm_stack_args {"):txt.index("} fdsm_stack_args;")]
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    fields = []
+    for decl in body.split("{", 1)[1].split(";"):
+        decl = decl.strip()
+        if not decl:
+            continue
+        for part in decl.split(","):
+            fields.append(re.findall(r"([A-Za-z_0-9]+)\s*$", part.strip())[0])
+    assert fields == [f[0] for f in fdsm._lib.StackArgs._fields_]
+
+
+def test_no_cpu_fallback(fdsm):
+    """CPU tensors are refused loudly: the product has no CPU path."""
+    x = torch.randn(4, 8)
+    with pytest.raises(fdsm._lib.FdsmError):
+        fdsm.efficient_score_matching_conjugate(lambda z: z.sum(-1), x)
+
+
+def test_reference_error_behaviour(fdsm):
+    x = torch.randn(4, 3, 8, 8)
+    with pytest.raises(RuntimeError):  # reference is only shape-correct for n_particles=1
+        fdsm.anneal_ESM_scorenet_VR(lambda z, y: z, x, torch.ones(3), n_particles=2)
+    with pytest.raises(NotImplementedError):
+        fdsm.single_efficient_score_matching(lambda z: z.sum(-1), torch.randn(4, 8), noise_type="radermacher")
+    with pytest.raises(ValueError):
+        fdsm.fd_loss(lambda z: z, x, mode="nope")
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "fd-scorematching_b200")
+    for dp, _, fns in os.walk(pkg):
+        for fn in fns:
+            if fn.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
+                txt = open(os.path.join(dp, fn)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", txt, flags=re.M), f"{fn} imports oracle/"
+                assert "/root/reference" not in txt
