@@ -1,0 +1,297 @@
+#!/usr/bin/env python
+"""Benchmark of the FD-SSM training hot path (BASELINE.json metric "FD-SSM train samples/sec").
+
+Workload (N=1 and per rank for N>1, weak scaling): BASELINE.json configs[1] -- DeepEBM `ssm_fd`
+(eps 0.05) on the 784-200-200-200 quadratic-head energy MLP (`MLP_Quadratic_MNIST`, nsoftplus),
+synthetic MNIST-shaped batch B=4096 x 784 ~ U[0,1]+N(0,0.005^2), Adam(lr 1e-5, betas .9/.95),
+grad-norm clip 0.1.  One step = stack build -> network fwd -> combine -> backward -> all-reduce ->
+clip -> Adam (DeepEBM/train_ssm.py:63-69).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Prints ONE JSON line (see the task contract): value (device-resident inputs), e2e (host buffers,
+H2D + D2H inside the timed region), roofline of the dominant kernel, cpu_baseline.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+B_PER_GPU, D, HID, NHID, EPS = 4096, 784, 200, 3, 0.05
+LR, BETAS, CLIP = 1e-5, (0.9, 0.95), 0.1
+POOL = 16  # rotating device batches: 16 x 12.85 MB = 205 MB > 126 MB L2
+WORKLOAD = "cfg2: DeepEBM ssm_fd, MLP_Quadratic_MNIST(nsoftplus) 784-200-200-200, B=4096/GPU, D=784, Adam+clip"
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d, "measured"
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.proc, self.lines, self.index = None, [], index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=lambda: [self.lines.append(l) for l in self.proc.stdout], daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for l in self.lines:
+            f = [x.strip() for x in l.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def synth_batch(gen, n, device):
+    x = torch.rand(n, D, generator=gen, device=device)
+    return x + 0.005 * torch.randn(n, D, generator=gen, device=device)   # train_ssm.py:62
+
+
+# ---------------------------------------------------------------------------------------------------
+# CPU baseline: the oracle port (torch CPU restatement of the reference's ssm_fd + model) on host cores
+# ---------------------------------------------------------------------------------------------------
+def cpu_step_fn(batch):
+    from oracle import fd_losses, nets
+    torch.manual_seed(1234)
+    net = nets.init_from_numpy(nets.QuadraticMLP(D, HID, NHID, "nsoftplus"), 1234)
+    opt = torch.optim.Adam(net.parameters(), lr=LR, betas=BETAS)
+    g = torch.Generator().manual_seed(1234)
+    xs = [synth_batch(g, batch, "cpu") for _ in range(2)]
+
+    def step(i):
+        x = xs[i % 2]
+        u = torch.randn_like(x)
+        v = fd_losses.sphere_direction(u, EPS)
+        loss = fd_losses.fd_ssm(net, x, v, 1.0 / EPS ** 2)
+        opt.zero_grad()
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(net.parameters(), CLIP)
+        opt.step()
+        return loss
+    return step
+
+
+def cpu_baseline(budget_s=12.0):
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    step = cpu_step_fn(B_PER_GPU)
+    for i in range(3):
+        step(i)
+    t0, n = time.perf_counter(), 0
+    while True:
+        step(n)
+        n += 1
+        dt = time.perf_counter() - t0
+        if dt > budget_s or n >= 200:
+            break
+    return {"value": B_PER_GPU * n / dt, "unit": "samples/s", "cores": cores, "kind": "port",
+            "sample": f"{n} full steps of the cfg2 workload (B={B_PER_GPU}, D={D}) on torch-CPU oracle port, "
+                      f"{dt:.1f}s, {cores} threads"}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path (oracle port: the reference is Python and cannot travel)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    step = cpu_step_fn(B_PER_GPU)
+    for i in range(args.warmup):
+        step(i)
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        step(i)
+    dt = time.perf_counter() - t0
+    v = B_PER_GPU * args.steps / dt
+    print(json.dumps({
+        "impl": "reference", "metric": "fd_ssm_train_samples_per_sec", "value": v, "unit": "samples/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "note": "CPU arm runs one rank's batch (B=4096) per step on all host threads"},
+        "cpu_baseline": {"value": v, "unit": "samples/s", "cores": cores, "kind": "port",
+                         "sample": f"{args.steps} steps of B={B_PER_GPU}"},
+        "e2e": {"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+# ---------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--network", default="auto", choices=["auto", "fused", "torch"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch.distributed as dist
+    import fdsm_b200 as fdsm
+    from fdsm_b200 import ops
+    from fdsm_b200.train import FDSSMTrainer
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    if not fdsm._lib.load().fdsm_device_supported():
+        raise SystemExit("bench.py: needs a compute-capability 10.x GPU (no fallback path)")
+    torch.backends.cuda.matmul.allow_tf32 = False
+
+    use_fused = args.network in ("auto", "fused") and hasattr(fdsm, "mlp")
+    if args.network == "fused" and not use_fused:
+        raise SystemExit("fused MLP path not built")
+    if use_fused:
+        net = fdsm.mlp.FusedEnergyMLP(D, HID, NHID, act="nsoftplus", head="quadratic", device=dev, seed=1234)
+        network = "fused tcgen05 3xTF32 MLP (ours)"
+    else:
+        from oracle import nets as onets   # definition + deterministic init only; runs on the GPU through torch
+        net = onets.init_from_numpy(onets.QuadraticMLP(D, HID, NHID, "nsoftplus"), 1234).to(dev)
+        network = "torch nn.Linear (cuBLAS fp32) between our FD kernels"
+    tr = FDSSMTrainer(net, eps=EPS, lr=LR, betas=BETAS, clip=CLIP, seed=1234)
+
+    gen = torch.Generator(device=dev).manual_seed(1234 + rank)
+    pool = [synth_batch(gen, B_PER_GPU, dev) for _ in range(POOL)]
+    host = [p.cpu().pin_memory() for p in pool[:4]]
+    loss_host = torch.zeros((), pin_memory=True)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- value: device-resident inputs ---------------------------------------------------------------
+    for i in range(args.warmup):
+        tr.step(pool[i % POOL])
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = ops.LAUNCHES if hasattr(ops, "LAUNCHES") else 0
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    kev = []   # events around the dominant kernel of each step
+    if hasattr(ops, "PROFILE_HOOK"):
+        ops.PROFILE_HOOK = kev
+    e0.record()
+    for i in range(args.steps):
+        tr.step(pool[i % POOL])
+    e1.record()
+    barrier()
+    if hasattr(ops, "PROFILE_HOOK"):
+        ops.PROFILE_HOOK = None
+    launches = (ops.LAUNCHES - l0) if hasattr(ops, "LAUNCHES") else None
+    ms = e0.elapsed_time(e1)
+    t = torch.tensor([ms], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t)
+    value = B_PER_GPU * world * args.steps / (ms * 1e-3)
+
+    # ---- e2e: host buffers through the public API, H2D + D2H inside the timed region -----------------
+    for i in range(max(3, args.warmup // 2)):
+        tr.step_from_host(host[i % 4], loss_host)
+    barrier()
+    e0.record()
+    for i in range(args.steps):
+        tr.step_from_host(host[i % 4], loss_host)
+    e1.record()
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_ms = float(t)
+    clocks = sampler.stop() if rank == 0 else None
+    final_loss = float(loss_host)
+
+    # ---- roofline of the dominant kernel of OUR path, timed live with CUDA events ---------------------
+    pk, pk_kind = peaks()
+    roof = tr.net.roofline(kev, pk, pk_kind) if use_fused and hasattr(tr.net, "roofline") else None
+    if roof is None:
+        # generic mode: the dominant kernel of ours is the fused direction+stack build (HBM-bound)
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+        for i in range(3):
+            ops.stack(pool[i % POOL], row_mask=7, scale=EPS)
+        torch.cuda.synchronize()
+        outbuf = [torch.empty(3 * B_PER_GPU, D, device=dev) for _ in range(4)]   # 4 x 38.5 MB rotating outputs
+        for i, (a, b) in enumerate(ev):
+            a.record()
+            ops.stack(pool[i % POOL], row_mask=7, scale=EPS, out=outbuf[i % 4])
+            b.record()
+        torch.cuda.synchronize()
+        kms = sorted(a.elapsed_time(b) for a, b in ev)
+        kavg = sum(kms) / len(kms)
+        alg = 16.0 * D * B_PER_GPU   # R x (4D) + W 3 rows (12D) bytes per sample, SURVEY.md §8d
+        ach = alg / (kavg * 1e-3) / 1e9
+        roof = {"kernel": "fdsm_stack (Philox direction + L2 norm + [x,x+v,x-v] build)", "bound": "hbm",
+                "achieved": ach, "peak": pk["hbm_gbs"], "peak_kind": pk_kind + " (burst copy)", "unit": "GB/s",
+                "frac": ach / pk["hbm_gbs"], "traffic": None, "algorithmic_bytes_per_launch": alg,
+                "avg_launch_us": kavg * 1e3, "median_launch_us": kms[len(kms) // 2] * 1e3}
+
+    if rank == 0:
+        out = {
+            "metric": "fd_ssm_train_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "global_batch": B_PER_GPU * world, "network": network,
+                       "l2_policy": f"inputs larger than L2: rotating pool of {POOL} device batches (205 MB)",
+                       "parallelism": f"dp{world}"},
+            "e2e": {"value": B_PER_GPU * world * args.steps / (e2e_ms * 1e-3), "unit": "samples/s",
+                    "h2d_bytes_per_step": B_PER_GPU * D * 4, "d2h_bytes_per_step": 4,
+                    "ms_per_step": e2e_ms / args.steps, "api": "FDSSMTrainer.step_from_host (pinned host batch)"},
+            "gpu_launches": launches, "final_loss": final_loss, "clocks": clocks, "roofline": roof,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            out["cpu_baseline"] = cpu_baseline()
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

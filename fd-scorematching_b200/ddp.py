@@ -1,0 +1,73 @@
+"""Data-parallel plumbing: one process per GPU, batch sharded by rank, exactly one all-reduce of
+the flat fp32 gradient bucket per step.  Replaces the reference's single-process
+``nn.DataParallel`` (DeepEBM/train_ssm.py:33-34, ncsn/runners/anneal_runner.py:116,
+ncsnv2/runners/ncsn_esm_runner.py:67), which re-broadcasts parameters and gathers outputs to GPU 0
+every step.  Works with the NCCL backend on GPUs and with gloo on CPU (host-logic tests).
+"""
+import torch
+import torch.distributed as dist
+
+
+class FlatParams:
+    """Re-homes a module's parameters (and their gradients) into two flat fp32 buffers so that the
+    gradient all-reduce, the global-norm clip and the optimizer each touch ONE contiguous tensor."""
+
+    def __init__(self, module):
+        params = [p for p in module.parameters() if p.requires_grad]
+        if not params:
+            raise ValueError("module has no trainable parameters")
+        dev, dt = params[0].device, params[0].dtype
+        # 16-byte align every tensor inside the bucket (128-bit loads in the kernels)
+        offs, n = [], 0
+        for p in params:
+            offs.append(n)
+            n += (p.numel() + 3) // 4 * 4
+        self.flat = torch.zeros(n, device=dev, dtype=dt)
+        self.grad = torch.zeros(n, device=dev, dtype=dt)
+        self.params, self.offsets = params, offs
+        for p, o in zip(params, offs):
+            self.flat[o:o + p.numel()].copy_(p.data.reshape(-1))
+            p.data = self.flat[o:o + p.numel()].view_as(p)
+            p.grad = self.grad[o:o + p.numel()].view_as(p)
+        self.numel = n
+
+    def zero_grad(self):
+        self.grad.zero_()
+        for p, o in zip(self.params, self.offsets):  # autograd may have re-pointed .grad
+            if p.grad is None or p.grad.data_ptr() != self.grad.data_ptr() + 4 * o:
+                p.grad = self.grad[o:o + p.numel()].view_as(p)
+
+
+def is_distributed():
+    return dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+
+
+def shard_range(global_batch, rank=None, world=None):
+    """Rank r owns samples [r*b, (r+1)*b) of the global batch; all rows of a sample stay on one rank."""
+    rank = dist.get_rank() if rank is None else rank
+    world = dist.get_world_size() if world is None else world
+    if global_batch % world:
+        raise ValueError(f"global batch {global_batch} not divisible by world size {world}")
+    b = global_batch // world
+    return rank * b, (rank + 1) * b
+
+
+def shard_sigmas(sigmas, rank=None, world=None):
+    """DeepEBM's sigma schedule is positional within the GLOBAL batch (train_dsm.py:50-57): a shard takes
+    its slice, it does not re-linspace (SURVEY.md §7 hard part 7)."""
+    lo, hi = shard_range(sigmas.shape[0], rank, world)
+    return sigmas[lo:hi]
+
+
+def allreduce_mean_(flat_grad):
+    """The step's single collective: sum over ranks, pre-scaled by 1/world (loss is a per-rank mean)."""
+    if not is_distributed():
+        return None
+    flat_grad.mul_(1.0 / dist.get_world_size())
+    return dist.all_reduce(flat_grad, op=dist.ReduceOp.SUM, async_op=False)
+
+
+def broadcast_params_(flat):
+    """Once, at step 0.  Replicas then stay bit-identical because they apply identical averaged grads."""
+    if is_distributed():
+        dist.broadcast(flat, src=0)

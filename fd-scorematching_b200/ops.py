@@ -12,6 +12,15 @@ from . import _lib
 from ._lib import ROW_MINUS, ROW_PLUS, ROW_X, StackArgs, check
 
 
+LAUNCHES = 0          # kernels launched through the C ABI by this process (bench.py "gpu_launches")
+PROFILE_HOOK = None   # bench.py: list collecting (start, end) CUDA events around the dominant kernel
+
+
+def _count(n):
+    global LAUNCHES
+    LAUNCHES += n
+
+
 def _stream():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
@@ -129,7 +138,7 @@ def stack(x, *, row_mask, scale, direction=None, normalize=True, noise=None, sig
     seed, offset, row0 = draw if draw is not None else next_draw()
     a.seed, a.offset, a.row0 = seed, offset, row0
     a.B, a.D = B, D
-    check(lib.fdsm_stack(C.byref(a), _stream()), "fdsm_stack")
+    _count(1); check(lib.fdsm_stack(C.byref(a), _stream()), "fdsm_stack")
     return out, v, dot
 
 
@@ -141,7 +150,7 @@ def direction(B, D, scale, *, u=None, device=None, draw=None):
         device = u.device
     v = torch.empty((B, D), device=device, dtype=torch.float32)
     seed, offset, row0 = draw if draw is not None else next_draw()
-    check(lib.fdsm_direction(_ptr(u), ldu if u is not None else 0, _ptr(v), max(D, 1), B, D, float(scale), seed,
+    _count(1); check(lib.fdsm_direction(_ptr(u), ldu if u is not None else 0, _ptr(v), max(D, 1), B, D, float(scale), seed,
                              offset, row0, _stream()), "fdsm_direction")
     return v
 
@@ -149,7 +158,7 @@ def direction(B, D, scale, *, u=None, device=None, draw=None):
 def philox_normal(B, D, stream_id, seed, offset, row0=0, device="cuda"):
     lib = _lib.load()
     out = torch.empty((B, D), device=device, dtype=torch.float32)
-    check(lib.fdsm_philox_normal(_ptr(out), max(D, 1), B, D, stream_id, seed, offset, row0, _stream()),
+    _count(1); check(lib.fdsm_philox_normal(_ptr(out), max(D, 1), B, D, stream_id, seed, offset, row0, _stream()),
           "fdsm_philox_normal")
     return out
 
@@ -169,7 +178,7 @@ class CombineEnergy(torch.autograd.Function):
             raise ValueError(f"energy net returned {E.numel()} values for a stacked batch of {rows * B} rows")
         loss = torch.empty((), device=E.device, dtype=torch.float32)
         per = torch.empty((B,), device=E.device, dtype=torch.float32) if want_per_sample else None
-        check(lib.fdsm_combine_energy_fwd(_ptr(E), B, mode, c1, scale, int(mean), _ptr(per), _ptr(loss), _stream()),
+        _count(1); check(lib.fdsm_combine_energy_fwd(_ptr(E), B, mode, c1, scale, int(mean), _ptr(per), _ptr(loss), _stream()),
               "fdsm_combine_energy_fwd")
         ctx.save_for_backward(E)
         ctx.cfg = (B, mode, c1, scale, int(mean))
@@ -185,7 +194,7 @@ class CombineEnergy(torch.autograd.Function):
         B, mode, c1, scale, mean = ctx.cfg
         gout = gout.contiguous().float()
         dE = torch.empty_like(E)
-        check(lib.fdsm_combine_energy_bwd(_ptr(E), B, mode, c1, scale, mean, _ptr(gout), _ptr(dE), _stream()),
+        _count(1); check(lib.fdsm_combine_energy_bwd(_ptr(E), B, mode, c1, scale, mean, _ptr(gout), _ptr(dE), _stream()),
               "fdsm_combine_energy_bwd")
         return dE, None, None, None, None, None, None
 
@@ -200,7 +209,7 @@ class CombineDsm(torch.autograd.Function):
         if E.numel() != 2 * B:
             raise ValueError(f"energy net returned {E.numel()} values for a stacked batch of {2 * B} rows")
         loss = torch.empty((), device=E.device, dtype=torch.float32)
-        check(lib.fdsm_combine_dsm_fwd(_ptr(E), _ptr(dot), _ptr(sigma_b), B, alpha, beta, gamma, None, _ptr(loss),
+        _count(1); check(lib.fdsm_combine_dsm_fwd(_ptr(E), _ptr(dot), _ptr(sigma_b), B, alpha, beta, gamma, None, _ptr(loss),
                                        _stream()), "fdsm_combine_dsm_fwd")
         ctx.save_for_backward(E, dot, sigma_b)
         ctx.cfg = (B, alpha, beta, gamma)
@@ -213,7 +222,7 @@ class CombineDsm(torch.autograd.Function):
         B, alpha, beta, gamma = ctx.cfg
         gout = gout.contiguous().float()
         dE = torch.empty_like(E)
-        check(lib.fdsm_combine_dsm_bwd(_ptr(E), _ptr(dot), _ptr(sigma_b), B, alpha, beta, gamma, _ptr(gout), _ptr(dE),
+        _count(1); check(lib.fdsm_combine_dsm_bwd(_ptr(E), _ptr(dot), _ptr(sigma_b), B, alpha, beta, gamma, _ptr(gout), _ptr(dE),
                                        _stream()), "fdsm_combine_dsm_bwd")
         return dE, None, None, None, None, None, None
 
@@ -230,7 +239,7 @@ class CombineScore(torch.autograd.Function):
         s2d, lds = _rows(s2d, "score output")
         loss = torch.empty((), device=s.device, dtype=torch.float32)
         per = torch.empty((B,), device=s.device, dtype=torch.float32)
-        check(lib.fdsm_combine_score(_ptr(s2d), lds, _ptr(v), max(D, 1), _ptr(sigma), _ptr(labels), power, B, D, k,
+        _count(2); check(lib.fdsm_combine_score(_ptr(s2d), lds, _ptr(v), max(D, 1), _ptr(sigma), _ptr(labels), power, B, D, k,
                                      int(projected), None, _ptr(per), _ptr(loss), None, 0, _stream()),
               "fdsm_combine_score(fwd)")
         ctx.save_for_backward(s2d, v, sigma, labels)
@@ -245,7 +254,7 @@ class CombineScore(torch.autograd.Function):
         power, B, D, k, projected, shape, lds = ctx.cfg
         gout = gout.contiguous().float()
         ds = torch.empty((2 * B, D), device=s2d.device, dtype=torch.float32)
-        check(lib.fdsm_combine_score(_ptr(s2d), lds, _ptr(v), max(D, 1), _ptr(sigma), _ptr(labels), power, B, D, k,
+        _count(1); check(lib.fdsm_combine_score(_ptr(s2d), lds, _ptr(v), max(D, 1), _ptr(sigma), _ptr(labels), power, B, D, k,
                                      projected, _ptr(gout), None, None, _ptr(ds), max(D, 1), _stream()),
               "fdsm_combine_score(bwd)")
         return ds.view(shape), None, None, None, None, None, None, None, None, None
@@ -259,7 +268,7 @@ def combine_score_fused(s2d, v, *, k, sigma=None, labels=None, power=2.0, projec
     loss = torch.empty((), device=s2d.device, dtype=torch.float32)
     per = torch.empty((B,), device=s2d.device, dtype=torch.float32)
     ds = torch.empty((2 * B, D), device=s2d.device, dtype=torch.float32)
-    check(lib.fdsm_combine_score(_ptr(s2d), lds, _ptr(v), max(D, 1), _ptr(sigma), _ptr(labels), float(power), B, D,
+    _count(2); check(lib.fdsm_combine_score(_ptr(s2d), lds, _ptr(v), max(D, 1), _ptr(sigma), _ptr(labels), float(power), B, D,
                                  float(k), int(projected), None, _ptr(per), _ptr(loss), _ptr(ds), max(D, 1),
                                  _stream()), "fdsm_combine_score(fused)")
     return loss, per, ds

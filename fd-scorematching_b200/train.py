@@ -1,0 +1,67 @@
+"""Training-step driver for the FD-SSM / FD-DSM hot loop (DeepEBM/train_ssm.py:60-70):
+loss -> zero_grad -> backward -> clip_grad_norm_ -> Adam step, data-parallel over ranks.
+
+This is the call a user makes (`bench.py`'s e2e leg goes through `step_from_host`)."""
+import torch
+
+from . import ddp, losses, ops
+
+
+class FDSSMTrainer:
+    def __init__(self, net, *, eps=0.05, lr=1e-5, betas=(0.9, 0.95), clip=0.1, loss="ssm_fd", seed=1234):
+        self.net = net
+        self.eps, self.clip, self.loss_name = eps, clip, loss
+        self.fused = hasattr(net, "fd_ssm_step")       # mlp.FusedEnergyMLP: kernels (1)-(4) + Adam in CUDA
+        if self.fused:
+            self.flat = net.flat_params()
+            net.configure_optimizer(lr=lr, betas=betas, clip=clip)
+        else:
+            self.flat = ddp.FlatParams(net)
+            self.opt = torch.optim.Adam([self.flat.flat], lr=lr, betas=betas, fused=self.flat.flat.is_cuda)
+            self.flat.flat.grad = self.flat.grad
+        ddp.broadcast_params_(self.flat.flat)
+        rank = torch.distributed.get_rank() if ddp.is_distributed() else 0
+        ops.manual_seed(seed)
+        self._rank = rank
+        self._copy_stream = None
+        self._staged = None
+
+    # -- one optimisation step on a device-resident batch ------------------------------------------
+    def step(self, x):
+        B = x.shape[0]
+        ops.set_row_offset(self._rank * B)
+        if self.fused:
+            return self.net.fd_ssm_step(x, eps=self.eps, allreduce=ddp.allreduce_mean_)
+        self.flat.zero_grad()
+        loss = losses.ssm_fd(self.net, x, eps=self.eps, batch_size=B)
+        loss.backward()
+        ddp.allreduce_mean_(self.flat.grad)
+        if self.clip is not None:
+            # clip_grad_norm_ on the flat bucket: one norm kernel, no host sync
+            nrm = torch.linalg.vector_norm(self.flat.grad)
+            self.flat.grad.mul_(torch.clamp(self.clip / (nrm + 1e-6), max=1.0))
+        self.opt.step()
+        return loss.detach()
+
+    # -- end-to-end: host batch in pinned memory -> loss on the host --------------------------------
+    def step_from_host(self, x_host, loss_host):
+        """H2D copy of this step's batch (pinned -> device, on a side stream, double-buffered against the
+        previous step's compute), the step, and an async D2H read of the loss into `loss_host` (pinned)."""
+        cur = torch.cuda.current_stream()
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream()
+            self._bufs = [torch.empty_like(x_host, device="cuda") for _ in range(2)]
+            self._evt = [torch.cuda.Event() for _ in range(2)]
+            self._free = [torch.cuda.Event() for _ in range(2)]
+            self._i = 0
+        i = self._i
+        self._i ^= 1
+        with torch.cuda.stream(self._copy_stream):
+            self._copy_stream.wait_event(self._free[i])      # previous consumer of this buffer is done
+            self._bufs[i].copy_(x_host, non_blocking=True)
+            self._evt[i].record(self._copy_stream)
+        cur.wait_event(self._evt[i])
+        loss = self.step(self._bufs[i])
+        self._free[i].record(cur)
+        loss_host.copy_(loss, non_blocking=True)
+        return loss_host
