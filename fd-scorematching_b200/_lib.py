@@ -38,6 +38,17 @@ class StackArgs(C.Structure):
     ]
 
 
+class GemmArgs(C.Structure):
+    """Mirror of `fdsm_gemm_args` (include/fdsm.h)."""
+    _fields_ = [
+        ("a_hi", _f32p), ("a_lo", _f32p), ("lda", _i64), ("a_major", _i32),
+        ("b_hi", _f32p), ("b_lo", _f32p), ("ldb", _i64), ("b_major", _i32),
+        ("M", _i64), ("N", _i64), ("K", _i64),
+        ("passes", _i32), ("splits", _i32), ("tile_n", _i32),
+        ("out", _f32p), ("ldo", _i64), ("split_stride", _i64),
+    ]
+
+
 # name -> (restype, argtypes); must list every symbol include/fdsm.h declares
 PROTOTYPES = {
     "fdsm_version": (C.c_int, []),
@@ -52,6 +63,8 @@ PROTOTYPES = {
     "fdsm_combine_dsm_bwd": (C.c_int, [_f32p, _f32p, _f32p, _i64, _f32, _f32, _f32, _f32p, _f32p, _stream]),
     "fdsm_combine_score": (C.c_int, [_f32p, _i64, _f32p, _i64, _f32p, C.c_void_p, _f32, _i64, _i64, _f32, _i32,
                                      _f32p, _f32p, _f32p, _f32p, _i64, _stream]),
+    "fdsm_tf32_split": (C.c_int, [_f32p, _i64, _i64, _i64, _f32p, _f32p, _i64, _i64, _i32, _stream]),
+    "fdsm_tc_gemm": (C.c_int, [C.POINTER(GemmArgs), _stream]),
 }
 
 _lib = None

@@ -22,7 +22,7 @@ int cuda_status(cudaError_t e, const char* what);
 
 #define FDSM_LAUNCH_CHECK(what) return ::fdsm::cuda_status(cudaGetLastError(), what)
 
-static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+__host__ __device__ static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 int sm_count();
 
 // ---- Philox4x32-10 (Salmon et al. 2011), counter-based --------------------------------------

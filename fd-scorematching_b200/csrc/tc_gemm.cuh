@@ -1,0 +1,298 @@
+// Kernel (3): the energy-MLP dense layers as tcgen05/TMEM GEMMs fed by TMA (sm_100a).
+//
+//   D[M x N] = sum_k A[m,k] * B[n,k]        (fp32 in, fp32 accumulate in TMEM)
+//
+// The reference's nn.Linear is true-fp32 SGEMM (DeepEBM/ESM/models.py:932-955 under torch's
+// allow_tf32=False); tcgen05 has no fp32 MMA kind, so operands arrive PRE-SPLIT into TF32 hi/lo
+// halves (x = hi + lo, written by the producing kernel's epilogue) and each k-step issues
+// hi*hi + hi*lo + lo*hi ("3xTF32", ~fp32 product accuracy).  passes=1 issues hi*hi only.
+//
+// One 128 x BN output tile per CTA (BN <= 256), optional split-K over gridDim.z.  Warp roles:
+// warp 0 = TMA producer, warp 1 = MMA issuer, warp 2 = TMEM allocator, warps 4..7 = epilogue
+// (TMEM -> registers -> fused epilogue -> global).  BK = 32 fp32 = one 128-byte swizzle row.
+#pragma once
+#include <cuda.h>
+
+#include "fdsm_common.cuh"
+#include "tc_ptx.cuh"
+
+namespace fdsm {
+namespace tc {
+
+constexpr int BM = 128;            // UMMA M
+constexpr int BK = 32;             // fp32 elements per k-block (128 B)
+constexpr int UMMA_K = 8;          // tf32: 32 B per instruction
+constexpr int A_TILE_BYTES = BM * BK * 4;    // 16 KB
+constexpr int B_TILE_BYTES = 256 * BK * 4;   // 32 KB (max BN)
+constexpr int kThreads = 256;
+constexpr int TMEM_COLS = 256;
+
+enum Major : int { MAJOR_K = 0, MAJOR_MN = 1 };
+enum Act : int { ACT_NONE = 0, ACT_SOFTPLUS = 1, ACT_NSOFTPLUS = 2, ACT_ELU = 3 };
+enum Epi : int {
+  EPI_STORE = 0,       // out_hi[z][m][n] = D           (plain fp32; split-K partials indexed by blockIdx.z)
+  EPI_ACT_SPLIT = 1,   // h = act(D) -> hi/lo ; col N := 1 (bias column of the next layer) ; cols (N, out_cols) := 0
+  EPI_HEAD = 2,        // h = act(D) -> out_hi (fp32) ; E = (h.w1+b1)(h.w2+b2) + h^2.wq + bq -> e_out, l1_out, l2_out
+  EPI_DACT_SPLIT = 3,  // g = D * act'(aux) -> hi/lo ; cols [N, out_cols) := 0
+};
+
+struct alignas(64) GemmParams {
+  CUtensorMap ta_hi, ta_lo, tb_hi, tb_lo;
+  int M, N, K;              // logical sizes (rows of D, valid columns of D, contraction length)
+  int BN;                   // UMMA N (multiple of 16, <= 256, >= N - n0 for the last tile)
+  int a_major, b_major;
+  int passes;               // 1 or 3
+  int epi, act;
+  float* out_hi; float* out_lo; long long ldo; long long split_stride; int out_cols;
+  const float* aux_hi; const float* aux_lo; long long ldaux;     // EPI_DACT_SPLIT: H of the previous layer
+  const float* head_w;      // EPI_HEAD: [w1(N) | b1 | w2(N) | b2 | wq(N) | bq] = the reference's ln1, ln2, lq parameters
+  float* e_out; float* l1_out; float* l2_out;
+};
+
+__device__ __forceinline__ float act_fwd(int act, float z) {
+  switch (act) {
+    case ACT_SOFTPLUS: return z > 20.f ? z : log1pf(expf(z));                       // nn.Softplus(beta=1, threshold=20)
+    case ACT_NSOFTPLUS: return (z > 20.f ? z : log1pf(expf(z))) - 0.69314718055994531f;  // models.py:19-28
+    case ACT_ELU: return z > 0.f ? z : expm1f(z);
+    default: return z;
+  }
+}
+// derivative expressed through the stored activation h = act(z)
+__device__ __forceinline__ float act_bwd_from_h(int act, float h) {
+  switch (act) {
+    case ACT_SOFTPLUS: return 1.f - expf(-h);          // sigmoid(z) = 1 - exp(-softplus(z))
+    case ACT_NSOFTPLUS: return 1.f - 0.5f * expf(-h);  // softplus = h + ln2
+    case ACT_ELU: return h > 0.f ? 1.f : h + 1.f;
+    default: return 1.f;
+  }
+}
+
+struct SmemLayout {
+  // dynamic smem (1024-byte aligned): per stage [A_hi | A_lo | B_hi | B_lo]
+  static __host__ __device__ constexpr int stage_bytes(int passes) {
+    return (passes == 3 ? 2 : 1) * (A_TILE_BYTES + B_TILE_BYTES);
+  }
+  static __host__ __device__ constexpr int stages(int passes) { return passes == 3 ? 2 : 4; }
+  static __host__ __device__ constexpr int total(int passes) { return stages(passes) * stage_bytes(passes) + 1024 + 256; }
+};
+
+template <int PASSES>
+__global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant__ GemmParams p) {
+  using namespace ptx;
+  constexpr int STAGES = SmemLayout::stages(PASSES);
+  constexpr int STAGE_BYTES = SmemLayout::stage_bytes(PASSES);
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  uint8_t* gen = smem_raw + (base - raw);
+  const uint32_t bars = base + STAGES * STAGE_BYTES;              // full[STAGES], empty[STAGES], tmem_full, tmem_ptr
+  volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(gen + STAGES * STAGE_BYTES + 8 * (2 * STAGES + 1));
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (STAGES + s); };
+  const uint32_t tmem_full_bar = bars + 8u * (2 * STAGES);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * BM, n0 = blockIdx.y * p.BN;
+  const int kblocks = (p.K + BK - 1) / BK;
+  const int kb0 = (int)((long long)kblocks * blockIdx.z / gridDim.z);
+  const int kb1 = (int)((long long)kblocks * (blockIdx.z + 1) / gridDim.z);
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&p.ta_hi);
+    prefetch_tensormap(&p.tb_hi);
+    if (PASSES == 3) {
+      prefetch_tensormap(&p.ta_lo);
+      prefetch_tensormap(&p.tb_lo);
+    }
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc(smem_u32((const void*)tmem_ptr_smem), TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    // ===== TMA producer ===========================================================================
+    if (lane == 0) {
+      const int b_boxes_mn = (p.BN + 31) / 32;
+      const uint32_t tx = (uint32_t)(PASSES == 3 ? 2 : 1) *
+                          (uint32_t)(A_TILE_BYTES + (p.b_major == MAJOR_K ? p.BN * BK * 4 : b_boxes_mn * 32 * BK * 4));
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(empty_bar(stage), phase ^ 1u);
+        const uint32_t sa = base + stage * STAGE_BYTES;
+        const uint32_t fb = full_bar(stage);
+        mbar_arrive_expect_tx(fb, tx);
+        const int k0 = kb * BK;
+#pragma unroll
+        for (int h = 0; h < (PASSES == 3 ? 2 : 1); ++h) {
+          const void* ta = h ? (const void*)&p.ta_lo : (const void*)&p.ta_hi;
+          const void* tb = h ? (const void*)&p.tb_lo : (const void*)&p.tb_hi;
+          const uint32_t a_dst = sa + h * A_TILE_BYTES;
+          const uint32_t b_dst = sa + (PASSES == 3 ? 2 : 1) * A_TILE_BYTES + h * B_TILE_BYTES;
+          if (p.a_major == MAJOR_K) {
+            tma_load_2d(a_dst, ta, fb, k0, m0);                     // box {32 k, 128 rows}
+          } else {
+            for (int i = 0; i < BM / 32; ++i) tma_load_2d(a_dst + i * 4096, ta, fb, m0 + 32 * i, k0);  // box {32 m, 32 k}
+          }
+          if (p.b_major == MAJOR_K) {
+            tma_load_2d(b_dst, tb, fb, k0, n0);                     // box {32 k, BN rows}
+          } else {
+            for (int i = 0; i < b_boxes_mn; ++i) tma_load_2d(b_dst + i * 4096, tb, fb, n0 + 32 * i, k0);
+          }
+        }
+        if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (one thread) ================================================================
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_tf32(BM, p.BN, p.a_major, p.b_major);
+      // per-UMMA_K advance of the descriptor start address: 32 B inside the swizzle row (K-major) or
+      // one 8-row k-group = 1024 B (MN-major)
+      const uint32_t a_lbo = p.a_major == MAJOR_K ? 16u : 4096u, b_lbo = p.b_major == MAJOR_K ? 16u : 4096u;
+      const uint32_t a_step = p.a_major == MAJOR_K ? 32u : 1024u, b_step = p.b_major == MAJOR_K ? 32u : 1024u;
+      const uint32_t a_sbo = p.a_major == MAJOR_K ? 1024u : 512u, b_sbo = p.b_major == MAJOR_K ? 1024u : 512u;
+      const uint32_t a_lay = p.a_major == MAJOR_K ? 2u : 1u, b_lay = p.b_major == MAJOR_K ? 2u : 1u;
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(full_bar(stage), phase);
+        tc_fence_after();
+        const uint32_t sa = base + stage * STAGE_BYTES;
+        const uint32_t a_hi = sa, a_lo = sa + A_TILE_BYTES;
+        const uint32_t b_hi = sa + (PASSES == 3 ? 2 : 1) * A_TILE_BYTES, b_lo = b_hi + B_TILE_BYTES;
+#pragma unroll
+        for (int k8 = 0; k8 < BK / UMMA_K; ++k8) {
+          const uint64_t dah = make_smem_desc(a_hi + k8 * a_step, a_lbo, a_sbo, a_lay);
+          const uint64_t dbh = make_smem_desc(b_hi + k8 * b_step, b_lbo, b_sbo, b_lay);
+          mma_tf32_ss(tmem_base, dah, dbh, idesc, (kb > kb0 || k8 > 0) ? 1u : 0u);
+          if (PASSES == 3) {
+            const uint64_t dal = make_smem_desc(a_lo + k8 * a_step, a_lbo, a_sbo, a_lay);
+            const uint64_t dbl = make_smem_desc(b_lo + k8 * b_step, b_lbo, b_sbo, b_lay);
+            mma_tf32_ss(tmem_base, dah, dbl, idesc, 1u);
+            mma_tf32_ss(tmem_base, dal, dbh, idesc, 1u);
+          }
+        }
+        tc_commit(empty_bar(stage));                    // smem slot free once these MMAs have read it
+        if (kb == kb1 - 1) tc_commit(tmem_full_bar);    // accumulator complete
+        if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+      }
+    }
+  } else if (warp >= 4) {
+    // ===== epilogue: TMEM -> registers -> fused op -> global ======================================
+    const int q = warp & 3;                      // TMEM lane quarter this warp may read
+    const int row = m0 + q * 32 + lane;
+    const bool row_ok = row < p.M;
+    const bool have_acc = kb1 > kb0;
+    if (have_acc) {
+      mbar_wait(tmem_full_bar, 0);
+      tc_fence_after();
+    }
+    float l1 = 0.f, l2 = 0.f, lq = 0.f;
+    const int ncols_out = (p.epi == EPI_STORE || p.epi == EPI_HEAD) ? min(p.N - n0, p.BN) : (p.out_cols - n0);
+    for (int c0 = 0; c0 < ncols_out; c0 += 32) {
+      float v[32];
+      if (have_acc && c0 < p.BN) {
+        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = 0.f;
+      }
+      const int nvalid = p.N - n0 - c0;          // columns [0, nvalid) of this chunk are real outputs
+      if (p.epi == EPI_STORE) {
+        if (row_ok) {
+          float* o = p.out_hi + (long long)blockIdx.z * p.split_stride + (long long)row * p.ldo + n0 + c0;
+          if (nvalid >= 32 && ((p.ldo | (n0 + c0)) & 3) == 0 && aligned16(p.out_hi)) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 4) *reinterpret_cast<float4*>(o + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if (i < nvalid) o[i] = v[i];
+          }
+        }
+      } else if (p.epi == EPI_HEAD) {
+        const float* w1 = p.head_w;
+        const float* w2 = p.head_w + p.N + 1;
+        const float* wq = p.head_w + 2 * (p.N + 1);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const int c = n0 + c0 + i;
+          float h = 0.f;
+          if (i < nvalid) {
+            h = act_fwd(p.act, v[i]);
+            l1 = fmaf(h, __ldg(w1 + c), l1);
+            l2 = fmaf(h, __ldg(w2 + c), l2);
+            lq = fmaf(h * h, __ldg(wq + c), lq);
+          }
+          v[i] = h;
+        }
+        if (row_ok) {
+          float* o = p.out_hi + (long long)row * p.ldo + n0 + c0;
+#pragma unroll
+          for (int i = 0; i < 32; i += 4)
+            if (c0 + i < p.out_cols) *reinterpret_cast<float4*>(o + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+        }
+      } else {
+        // EPI_ACT_SPLIT / EPI_DACT_SPLIT: hi/lo rows of the next GEMM's operand, padded to out_cols
+        float hi[32], lo[32];
+        const float* ah = p.aux_hi ? p.aux_hi + (long long)row * p.ldaux + n0 + c0 : nullptr;
+        const float* al = p.aux_lo ? p.aux_lo + (long long)row * p.ldaux + n0 + c0 : nullptr;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          float y = 0.f;
+          if (i < nvalid) {
+            if (p.epi == EPI_ACT_SPLIT) {
+              y = act_fwd(p.act, v[i]);
+            } else if (row_ok) {
+              float h = __ldg(ah + i);
+              if (al) h += __ldg(al + i);
+              y = v[i] * act_bwd_from_h(p.act, h);
+            }
+          } else if (i == nvalid && p.epi == EPI_ACT_SPLIT) {
+            y = 1.f;                              // bias column of the next layer's augmented input
+          }
+          tf32_split(y, hi[i], lo[i]);
+        }
+        if (row_ok) {
+          float* oh = p.out_hi + (long long)row * p.ldo + n0 + c0;
+          float* ol = p.out_lo + (long long)row * p.ldo + n0 + c0;
+#pragma unroll
+          for (int i = 0; i < 32; i += 4) {
+            if (c0 + i < ncols_out) {
+              *reinterpret_cast<float4*>(oh + i) = make_float4(hi[i], hi[i + 1], hi[i + 2], hi[i + 3]);
+              *reinterpret_cast<float4*>(ol + i) = make_float4(lo[i], lo[i + 1], lo[i + 2], lo[i + 3]);
+            }
+          }
+        }
+      }
+    }
+    if (p.epi == EPI_HEAD && row_ok) {
+      const float b1 = __ldg(p.head_w + p.N), b2 = __ldg(p.head_w + 2 * p.N + 1), bq = __ldg(p.head_w + 3 * p.N + 2);
+      l1 += b1;
+      l2 += b2;
+      p.e_out[row] = fmaf(l1, l2, lq + bq);     // ln1(h)*ln2(h) + lq(h^2)   models.py:338,954
+      p.l1_out[row] = l1;
+      p.l2_out[row] = l2;
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+}  // namespace tc
+}  // namespace fdsm

@@ -1,0 +1,93 @@
+// Host side of the tcgen05 GEMM: TMA tensor-map encoding and launch.
+#pragma once
+#include <cudaTypedefs.h>
+
+#include <mutex>
+
+#include "tc_gemm.cuh"
+
+namespace fdsm {
+namespace tc {
+
+// cuTensorMapEncodeTiled through the runtime's driver-entry-point lookup (no -lcuda link dependency)
+inline PFN_cuTensorMapEncodeTiled_v12000 encode_fn() {
+  static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+  });
+  return fn;
+}
+
+// Row-major fp32 matrix [rows x cols] with leading dimension ld (elements); box = {32 cols, box_rows}; 128-byte swizzle;
+// out-of-bounds elements read as zero.
+// `mn_major` operands (contraction index = row) use the 32-byte-atom flavour of the 128-byte swizzle: the only
+// shared-memory layout tcgen05 accepts for MN-major 32-bit operands.
+inline int make_tmap(CUtensorMap* m, const float* ptr, long long rows, long long cols, long long ld, int box_rows,
+                     bool mn_major, const char* what) {
+  auto fn = encode_fn();
+  if (!fn) {
+    set_error("cuTensorMapEncodeTiled entry point not available");
+    return FDSM_ERR_UNSUPPORTED;
+  }
+  FDSM_REQUIRE(ptr && aligned16(ptr), "%s: operand pointer must be non-NULL and 16-byte aligned", what);
+  FDSM_REQUIRE(ld % 4 == 0 && ld >= cols, "%s: leading dimension %lld must be a multiple of 4 and >= %lld", what, ld, cols);
+  FDSM_REQUIRE(box_rows >= 1 && box_rows <= 256, "%s: box rows %d out of range", what, box_rows);
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
+  cuuint32_t box[2] = {32, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("%s: cuTensorMapEncodeTiled failed (CUresult %d)", what, (int)r);
+    return FDSM_ERR_INVALID_ARGUMENT;
+  }
+  return FDSM_OK;
+}
+
+struct Operand {
+  const float* hi; const float* lo; long long ld; int major;   // MAJOR_K: [R x K] row-major; MAJOR_MN: [K x R] row-major
+};
+
+// Fills the tensor maps + sizes of `p` and launches.  `p` must already carry the epilogue fields.
+inline int launch_gemm(GemmParams& p, const Operand& A, const Operand& B, int M, int N, int K, int BN, int passes,
+                       int splits, cudaStream_t st) {
+  FDSM_REQUIRE(passes == 1 || passes == 3, "tc_gemm: passes must be 1 or 3");
+  FDSM_REQUIRE(M > 0 && N > 0 && K > 0, "tc_gemm: empty problem (M=%d N=%d K=%d)", M, N, K);
+  FDSM_REQUIRE(BN % 16 == 0 && BN >= 16 && BN <= 256, "tc_gemm: BN=%d must be a multiple of 16 in [16, 256]", BN);
+  FDSM_REQUIRE(passes == 1 || (A.lo && B.lo), "tc_gemm: 3-pass mode needs the lo halves");
+  const int kblocks = (K + BK - 1) / BK;
+  FDSM_REQUIRE(splits >= 1 && splits <= kblocks, "tc_gemm: splits=%d must be in [1, %d]", splits, kblocks);
+  p.M = M; p.N = N; p.K = K; p.BN = BN; p.a_major = A.major; p.b_major = B.major; p.passes = passes;
+  int rc;
+  for (int h = 0; h < (passes == 3 ? 2 : 1); ++h) {
+    CUtensorMap* ta = h ? &p.ta_lo : &p.ta_hi;
+    CUtensorMap* tb = h ? &p.tb_lo : &p.tb_hi;
+    if (A.major == MAJOR_K) rc = make_tmap(ta, h ? A.lo : A.hi, M, K, A.ld, BM, false, "tc_gemm A");
+    else rc = make_tmap(ta, h ? A.lo : A.hi, K, M, A.ld, BK, true, "tc_gemm A");
+    if (rc) return rc;
+    if (B.major == MAJOR_K) rc = make_tmap(tb, h ? B.lo : B.hi, N, K, B.ld, BN, false, "tc_gemm B");
+    else rc = make_tmap(tb, h ? B.lo : B.hi, K, N, B.ld, BK, true, "tc_gemm B");
+    if (rc) return rc;
+  }
+  dim3 grid((M + BM - 1) / BM, (N + BN - 1) / BN, splits);
+  const int smem = SmemLayout::total(passes);
+  static std::once_flag once;
+  std::call_once(once, [] {
+    cudaFuncSetAttribute(gemm_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SmemLayout::total(1));
+    cudaFuncSetAttribute(gemm_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, SmemLayout::total(3));
+  });
+  if (passes == 3) gemm_kernel<3><<<grid, kThreads, smem, st>>>(p);
+  else gemm_kernel<1><<<grid, kThreads, smem, st>>>(p);
+  FDSM_LAUNCH_CHECK("tc_gemm");
+}
+
+}  // namespace tc
+}  // namespace fdsm

@@ -272,3 +272,35 @@ def combine_score_fused(s2d, v, *, k, sigma=None, labels=None, power=2.0, projec
                                  float(k), int(projected), None, _ptr(per), _ptr(loss), _ptr(ds), max(D, 1),
                                  _stream()), "fdsm_combine_score(fused)")
     return loss, per, ds
+
+
+# --------------------------------------------------------------------------------------------
+# kernel (3) building blocks: TF32 hi/lo split and the tcgen05 GEMM
+# --------------------------------------------------------------------------------------------
+def tf32_split(x, out_cols=None, ones_col=False, want_lo=True):
+    """(hi, lo) with x = hi + lo, both TF32-representable; rows padded to `out_cols` columns (multiple of 4),
+    column x.shape[1] set to 1 when `ones_col` (bias column of an augmented operand)."""
+    lib = _lib.load()
+    x, ldx = _rows(_req(x, "x"), "x")
+    R, Cc = x.shape
+    oc = out_cols if out_cols is not None else (Cc + int(ones_col) + 3) // 4 * 4
+    hi = torch.empty((R, oc), device=x.device, dtype=torch.float32)
+    lo = torch.empty((R, oc), device=x.device, dtype=torch.float32) if want_lo else None
+    _count(1); check(lib.fdsm_tf32_split(_ptr(x), ldx, R, Cc, _ptr(hi), _ptr(lo), oc, oc, int(ones_col), _stream()),
+                     "fdsm_tf32_split")
+    return hi, lo
+
+
+def tc_gemm(a_hi, a_lo, b_hi, b_lo, M, N, K, *, a_major=0, b_major=0, passes=3, splits=1, tile_n=0):
+    """D[M,N] = sum_k A[m,k] B[n,k] on the tensor cores (fdsm_tc_gemm).  Operands are the pre-split hi/lo
+    halves; major 0: stored [rows, K]; major 1: stored [K, rows].  Returns (splits, M, N) partials."""
+    lib = _lib.load()
+    out = torch.empty((splits, M, N), device=a_hi.device, dtype=torch.float32)
+    g = _lib.GemmArgs()
+    g.a_hi, g.a_lo, g.lda, g.a_major = _ptr(a_hi), _ptr(a_lo), a_hi.stride(0), a_major
+    g.b_hi, g.b_lo, g.ldb, g.b_major = _ptr(b_hi), _ptr(b_lo), b_hi.stride(0), b_major
+    g.M, g.N, g.K = M, N, K
+    g.passes, g.splits, g.tile_n = passes, splits, tile_n
+    g.out, g.ldo, g.split_stride = _ptr(out), N, M * N
+    _count(1); check(lib.fdsm_tc_gemm(C.byref(g), _stream()), "fdsm_tc_gemm")
+    return out

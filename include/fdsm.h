@@ -131,6 +131,35 @@ int fdsm_combine_score(const float* s, int64_t lds, const float* v, int64_t ldv,
                        const float* gout, float* per_sample, float* loss, float* ds, int64_t ldds,
                        fdsm_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Kernel (3) building blocks: TF32 hi/lo operand split and the tcgen05/TMEM GEMM fed by TMA.
+ *
+ * Replaces the cuBLAS fp32 SGEMMs behind nn.Linear in the energy MLPs
+ * (DeepEBM/ESM/models.py:129-160,932-955; SSM/models/dkef.py:442-461).  tcgen05 has no fp32 MMA
+ * kind: operands are pre-split x = hi + lo (both TF32-representable) and passes=3 issues
+ * hi*hi + hi*lo + lo*hi per k-step (fp32-grade products, fp32 accumulation in TMEM).
+ * ------------------------------------------------------------------------------------------ */
+/* out_hi/out_lo[r,c] = split(in[r,c]) (c < cols); column `cols` := 1 if ones_col (bias column of an
+ * augmented operand) ; remaining columns up to out_cols := 0.  out_lo may be NULL (hi only). */
+int fdsm_tf32_split(const float* in, int64_t ldin, int64_t rows, int64_t cols, float* out_hi, float* out_lo,
+                    int64_t ldo, int64_t out_cols, int32_t ones_col, fdsm_stream_t stream);
+
+typedef struct fdsm_gemm_args {
+  /* D[M x N] = sum_k A[m,k] * B[n,k]
+   * major 0 (K-major):  operand stored [rows x K] row-major (K contiguous, as nn.Linear.weight)
+   * major 1 (MN-major): operand stored [K x rows] row-major (rows contiguous)                  */
+  const float* a_hi; const float* a_lo; int64_t lda; int32_t a_major;
+  const float* b_hi; const float* b_lo; int64_t ldb; int32_t b_major;
+  int64_t M, N, K;
+  int32_t passes;        /* 1: hi*hi (plain TF32) ; 3: 3xTF32                                      */
+  int32_t splits;        /* split-K: partial s is written at out + s*split_stride (caller reduces) */
+  int32_t tile_n;        /* UMMA N (multiple of 16, <= 256); 0 = auto                              */
+  float* out; int64_t ldo; int64_t split_stride;
+} fdsm_gemm_args;
+
+/* 16-byte aligned bases and ld % 4 == 0 required (TMA); out-of-range rows/columns read as zero. */
+int fdsm_tc_gemm(const fdsm_gemm_args* args, fdsm_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
