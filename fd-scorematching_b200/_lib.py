@@ -35,6 +35,7 @@ class StackArgs(C.Structure):
         ("dot_out", _f32p),
         ("seed", _u64), ("offset", _u64), ("row0", _u64),
         ("B", _i64), ("D", _i64),
+        ("out_lo", _f32p),
     ]
 
 
@@ -47,6 +48,11 @@ class GemmArgs(C.Structure):
         ("passes", _i32), ("splits", _i32), ("tile_n", _i32),
         ("out", _f32p), ("ldo", _i64), ("split_stride", _i64),
     ]
+
+
+class MlpDesc(C.Structure):
+    """Mirror of `fdsm_mlp_desc` (include/fdsm.h)."""
+    _fields_ = [("in_dim", _i32), ("hidden", _i32), ("n_hidden", _i32), ("act", _i32), ("head", _i32), ("passes", _i32)]
 
 
 # name -> (restype, argtypes); must list every symbol include/fdsm.h declares
@@ -65,6 +71,10 @@ PROTOTYPES = {
                                      _f32p, _f32p, _f32p, _f32p, _i64, _stream]),
     "fdsm_tf32_split": (C.c_int, [_f32p, _i64, _i64, _i64, _f32p, _f32p, _i64, _i64, _i32, _stream]),
     "fdsm_tc_gemm": (C.c_int, [C.POINTER(GemmArgs), _stream]),
+    "fdsm_mlp_sizes": (C.c_int, [C.POINTER(MlpDesc), _i64, C.POINTER(_i64), C.POINTER(_i64), C.POINTER(_i64)]),
+    "fdsm_mlp_prepare": (C.c_int, [C.POINTER(MlpDesc), _i64, _f32p, _f32p, _stream]),
+    "fdsm_mlp_forward": (C.c_int, [C.POINTER(MlpDesc), _f32p, _f32p, _i64, _f32p, _f32p, _f32p, _stream]),
+    "fdsm_mlp_backward": (C.c_int, [C.POINTER(MlpDesc), _f32p, _f32p, _i64, _f32p, _f32p, _f32p, _f32p, _i32, _stream]),
 }
 
 _lib = None
@@ -87,8 +97,8 @@ def load():
     for name, (res, args) in PROTOTYPES.items():
         fn = getattr(lib, name)  # AttributeError if the symbol is missing
         fn.restype, fn.argtypes = res, args
-    if lib.fdsm_version() != 1:
-        raise FdsmError(f"libfdsm ABI version {lib.fdsm_version()} != 1")
+    if lib.fdsm_version() != 2:
+        raise FdsmError(f"libfdsm ABI version {lib.fdsm_version()} != 2")
     _lib = lib
     return lib
 

@@ -8,6 +8,7 @@
 // longer than 4*MAXC*256 elements take the re-generate path (Philox is counter-based, so pass 2
 // recomputes exactly the numbers pass 1 reduced).
 #include "fdsm_common.cuh"
+#include "tc_ptx.cuh"
 
 namespace fdsm {
 namespace {
@@ -63,6 +64,20 @@ __device__ __forceinline__ float4 raw_noise(const fdsm_stack_args& a, int64_t b,
   return mask_tail(philox_normal4(a.seed, a.offset, STREAM_NOISE, a.row0 + (uint64_t)b, (uint32_t)j), j, (int)a.D);
 }
 
+// one stacked row chunk: plain fp32, or TF32 hi/lo halves when the batch feeds the tensor-core MLP
+template <bool VEC>
+__device__ __forceinline__ void store_row(const fdsm_stack_args& a, int64_t r, int j, int D, float4 v) {
+  if (a.out_lo) {
+    float4 hi, lo;
+    ptx::tf32_split(v.x, hi.x, lo.x); ptx::tf32_split(v.y, hi.y, lo.y);
+    ptx::tf32_split(v.z, hi.z, lo.z); ptx::tf32_split(v.w, hi.w, lo.w);
+    store4<VEC>(a.out + r * a.ldout, j, D, hi);
+    store4<VEC>(a.out_lo + r * a.ldout, j, D, lo);
+  } else {
+    store4<VEC>(a.out + r * a.ldout, j, D, v);
+  }
+}
+
 __device__ __forceinline__ float sumsq(float4 d) { return d.x * d.x + d.y * d.y + d.z * d.z + d.w * d.w; }
 
 // v = d / nrm * scale with the reference's rounding sequence (division, then multiply).
@@ -113,7 +128,6 @@ __global__ void __launch_bounds__(kBlock) stack_kernel(const fdsm_stack_args a) 
       float sig = 0.f;
       if (a.sigma) sig = a.labels ? __ldg(a.sigma + __ldg(a.labels + b)) : __ldg(a.sigma + b);
       const float* xrow = a.x ? a.x + b * a.ldx : nullptr;
-      float* o0 = a.out;
       auto emit = [&](int j, float4 dc) {
         const float4 v = need_norm ? normalise(dc, nrm, a.dir_scale) : dc;
         float4 base = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -134,19 +148,19 @@ __global__ void __launch_bounds__(kBlock) stack_kernel(const fdsm_stack_args a) 
         }
         int r = 0;
         if (a.row_mask & FDSM_ROW_X) {
-          store4<VEC>(o0 + ((int64_t)r * a.B + b) * a.ldout, j, D, base);
+          store_row<VEC>(a, (int64_t)r * a.B + b, j, D, base);
           ++r;
         }
         if (a.row_mask & FDSM_ROW_PLUS) {
-          store4<VEC>(o0 + ((int64_t)r * a.B + b) * a.ldout, j, D,
-                      make_float4(__fadd_rn(base.x, v.x), __fadd_rn(base.y, v.y), __fadd_rn(base.z, v.z),
-                                  __fadd_rn(base.w, v.w)));
+          store_row<VEC>(a, (int64_t)r * a.B + b, j, D,
+                         make_float4(__fadd_rn(base.x, v.x), __fadd_rn(base.y, v.y), __fadd_rn(base.z, v.z),
+                                     __fadd_rn(base.w, v.w)));
           ++r;
         }
         if (a.row_mask & FDSM_ROW_MINUS) {
-          store4<VEC>(o0 + ((int64_t)r * a.B + b) * a.ldout, j, D,
-                      make_float4(__fsub_rn(base.x, v.x), __fsub_rn(base.y, v.y), __fsub_rn(base.z, v.z),
-                                  __fsub_rn(base.w, v.w)));
+          store_row<VEC>(a, (int64_t)r * a.B + b, j, D,
+                         make_float4(__fsub_rn(base.x, v.x), __fsub_rn(base.y, v.y), __fsub_rn(base.z, v.z),
+                                     __fsub_rn(base.w, v.w)));
         }
         if (a.v_out) store4<VEC>(a.v_out + b * a.ldv, j, D, v);
       };
@@ -160,7 +174,15 @@ __global__ void __launch_bounds__(kBlock) stack_kernel(const fdsm_stack_args a) 
         for (int j = t; j < nchunk; j += G) emit(j, raw_direction<VEC>(a, b, j));
       }
     }
-    (void)nrows;
+    if (a.out_lo && active) {   // GEMM padding columns [D, ldout): ones column then zeros
+      for (int r = 0; r < nrows; ++r) {
+        const int64_t row = (int64_t)r * a.B + b;
+        for (int c = D + t; c < (int)a.ldout; c += G) {
+          a.out[row * a.ldout + c] = c == D ? 1.f : 0.f;
+          a.out_lo[row * a.ldout + c] = 0.f;
+        }
+      }
+    }
     if (a.dot_out) {  // uniform branch
       dot = group_sum<G>(dot, red);
       if (active && t == 0) a.dot_out[b] = dot;
@@ -213,10 +235,11 @@ extern "C" int fdsm_stack(const fdsm_stack_args* args, fdsm_stream_t stream) {
   FDSM_REQUIRE(!(a.sigma && a.noise) || a.ldnoise >= a.D, "fdsm_stack: ldnoise < D");
   FDSM_REQUIRE(!a.dot_out || a.sigma, "fdsm_stack: dot_out needs sigma (DSM noise)");
   FDSM_REQUIRE(!a.labels || a.sigma, "fdsm_stack: labels given without a sigma table");
+  FDSM_REQUIRE(!a.out_lo || (a.out && a.ldout > a.D), "fdsm_stack: out_lo needs out and ldout > D (room for the ones column)");
 
   bool vec = (a.D % 4 == 0);
   auto ok = [&](const float* p, int64_t ld) { return !p || (aligned16(p) && ld % 4 == 0); };
-  vec = vec && ok(a.x, a.ldx) && ok(a.dir, a.lddir) && ok(a.out, a.ldout) && ok(a.v_out, a.ldv) &&
+  vec = vec && ok(a.x, a.ldx) && ok(a.dir, a.lddir) && ok(a.out, a.ldout) && ok(a.out_lo, a.ldout) && ok(a.v_out, a.ldv) &&
         (!a.sigma || ok(a.noise, a.ldnoise));
 
   const int64_t nchunk = (a.D + 3) / 4;

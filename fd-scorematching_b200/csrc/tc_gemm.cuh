@@ -46,6 +46,7 @@ struct alignas(64) GemmParams {
   float* out_hi; float* out_lo; long long ldo; long long split_stride; int out_cols;
   const float* aux_hi; const float* aux_lo; long long ldaux;     // EPI_DACT_SPLIT: H of the previous layer
   const float* head_w;      // EPI_HEAD: [w1(N) | b1 | w2(N) | b2 | wq(N) | bq] = the reference's ln1, ln2, lq parameters
+  int head_mode;            // 1: quadratic head ; 0: linear head [w(N) | b]
   float* e_out; float* l1_out; float* l2_out;
 };
 
@@ -199,7 +200,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       tc_fence_after();
     }
     float l1 = 0.f, l2 = 0.f, lq = 0.f;
-    const int ncols_out = (p.epi == EPI_STORE || p.epi == EPI_HEAD) ? min(p.N - n0, p.BN) : (p.out_cols - n0);
+    const bool last_tile = n0 + p.BN >= p.N;   // the tile that also writes the padding columns [N, out_cols)
+    const int ncols_out = (p.epi == EPI_STORE || p.epi == EPI_HEAD) ? min(p.N - n0, p.BN)
+                                                                     : (last_tile ? p.out_cols - n0 : p.BN);
     for (int c0 = 0; c0 < ncols_out; c0 += 32) {
       float v[32];
       if (have_acc && c0 < p.BN) {
@@ -212,7 +215,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       if (p.epi == EPI_STORE) {
         if (row_ok) {
           float* o = p.out_hi + (long long)blockIdx.z * p.split_stride + (long long)row * p.ldo + n0 + c0;
-          if (nvalid >= 32 && ((p.ldo | (n0 + c0)) & 3) == 0 && aligned16(p.out_hi)) {
+          if (nvalid >= 32 && ((p.ldo | (n0 + c0) | (blockIdx.z ? p.split_stride : 0)) & 3) == 0 && aligned16(p.out_hi)) {
 #pragma unroll
             for (int i = 0; i < 32; i += 4) *reinterpret_cast<float4*>(o + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
           } else {
@@ -232,8 +235,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
           if (i < nvalid) {
             h = act_fwd(p.act, v[i]);
             l1 = fmaf(h, __ldg(w1 + c), l1);
-            l2 = fmaf(h, __ldg(w2 + c), l2);
-            lq = fmaf(h * h, __ldg(wq + c), lq);
+            if (p.head_mode) {
+              l2 = fmaf(h, __ldg(w2 + c), l2);
+              lq = fmaf(h * h, __ldg(wq + c), lq);
+            }
           }
           v[i] = h;
         }
@@ -278,10 +283,12 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       }
     }
     if (p.epi == EPI_HEAD && row_ok) {
-      const float b1 = __ldg(p.head_w + p.N), b2 = __ldg(p.head_w + 2 * p.N + 1), bq = __ldg(p.head_w + 3 * p.N + 2);
+      const float b1 = __ldg(p.head_w + p.N);
+      const float b2 = p.head_mode ? __ldg(p.head_w + 2 * p.N + 1) : 0.f, bq = p.head_mode ? __ldg(p.head_w + 3 * p.N + 2) : 0.f;
       l1 += b1;
       l2 += b2;
-      p.e_out[row] = fmaf(l1, l2, lq + bq);     // ln1(h)*ln2(h) + lq(h^2)   models.py:338,954
+      // quadratic head ln1(h)*ln2(h) + lq(h^2) (models.py:338,954) or a plain Linear(H,1) head (head_mode 0)
+      p.e_out[row] = p.head_mode ? fmaf(l1, l2, lq + bq) : l1;
       p.l1_out[row] = l1;
       p.l2_out[row] = l2;
     }

@@ -85,7 +85,7 @@ def next_draw():
 # kernels (1)+(2)
 # --------------------------------------------------------------------------------------------
 def stack(x, *, row_mask, scale, direction=None, normalize=True, noise=None, sigma=None, labels=None,
-          perturb=True, dot_mode=0, want_v=False, want_dot=False, draw=None, out=None):
+          perturb=True, dot_mode=0, want_v=False, want_dot=False, draw=None, out=None, out_lo=None):
     """Fused direction sampling + normalisation + stacked-batch build (fdsm_stack).
 
     x: (B, D) fp32 CUDA.  Returns (stacked (rows*B, D) | None, v (B, D) | None, dot (B,) | None)."""
@@ -126,7 +126,11 @@ def stack(x, *, row_mask, scale, direction=None, normalize=True, noise=None, sig
     if rows:
         if out is None:
             out = torch.empty((rows * B, D), device=x.device, dtype=torch.float32)
-        a.out, a.ldout = _ptr(out), (out.stride(0) if out.shape[0] > 1 else max(D, 1))
+        a.out, a.ldout = _ptr(out), (out.stride(0) if out.shape[0] > 1 else max(out.shape[1], 1))
+        if out_lo is not None:
+            if out_lo.shape != out.shape or out_lo.stride() != out.stride():
+                raise ValueError("out_lo must have the shape and strides of out")
+            a.out_lo = _ptr(out_lo)
     a.row_mask = row_mask
     v = dot = None
     if want_v:

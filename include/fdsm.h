@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define FDSM_ABI_VERSION 1
+#define FDSM_ABI_VERSION 2
 
 #define FDSM_OK 0
 #define FDSM_ERR_INVALID_ARGUMENT (-1)
@@ -80,6 +80,9 @@ typedef struct fdsm_stack_args {
   uint64_t row0;         /* global index of local row 0 (rank*B_local): shards draw what the
                             un-sharded batch would                                               */
   int64_t B, D;
+  float* out_lo;         /* optional: when set, `out` receives the TF32 hi half and `out_lo` the lo half of every
+                            stacked row (x = hi + lo), and columns [D, ldout) are written as the GEMM padding:
+                            column D = 1 (folded bias), the rest 0 -- the operand format of fdsm_mlp_forward      */
 } fdsm_stack_args;
 
 int fdsm_stack(const fdsm_stack_args* args, fdsm_stream_t stream);
@@ -159,6 +162,44 @@ typedef struct fdsm_gemm_args {
 
 /* 16-byte aligned bases and ld % 4 == 0 required (TMA); out-of-range rows/columns read as zero. */
 int fdsm_tc_gemm(const fdsm_gemm_args* args, fdsm_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Kernel (3): the energy MLP (forward + backward) as tcgen05 GEMM launches with fused epilogues.
+ *
+ * Replaces the torch modules MLP_Quadratic_MNIST / MLP_Quadratic (DeepEBM/ESM/models.py:129-160,
+ * 932-955: AF(fc_k(.)) x n_hidden, E = ln1(h)*ln2(h) + lq(h^2)) and the config-1 3-layer Softplus
+ * MLP with a Linear(H,1) head (SSM/models/dkef.py:442-461 shape), and their autograd backward.
+ *
+ * Parameters and gradients: ONE flat fp32 vector, tightly packed in the reference's
+ * named_parameters() order (fc1.weight[H,D], fc1.bias[H], ..., then ln1.weight[H], ln1.bias,
+ * ln2.weight[H], ln2.bias, lq.weight[H], lq.bias -- or out.weight[H], out.bias for head = 0).
+ * The input rows arrive as the TF32 hi/lo halves of the augmented batch [rows x in_ld]
+ * (column in_dim = 1, the folded bias; remaining padding 0): exactly what fdsm_stack writes when
+ * `out_lo` is set.  All scratch lives in the caller's workspace.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct fdsm_mlp_desc {
+  int32_t in_dim;    /* D                                                         */
+  int32_t hidden;    /* H (<= 256)                                                */
+  int32_t n_hidden;  /* number of fc layers (3 for MLP_Quadratic_MNIST)           */
+  int32_t act;       /* 1 softplus, 2 softplus - ln2 (NormalizedSoftplus), 3 ELU  */
+  int32_t head;      /* 1 quadratic head, 0 Linear(H,1)                           */
+  int32_t passes;    /* 3 = 3xTF32 (fp32-grade), 1 = plain TF32                   */
+} fdsm_mlp_desc;
+
+/* Sizes for `rows` stacked input rows: parameter count, workspace floats, padded input leading dim. */
+int fdsm_mlp_sizes(const fdsm_mlp_desc* desc, int64_t rows, int64_t* n_params, int64_t* workspace_floats,
+                   int64_t* in_ld);
+/* Once per optimizer step: flat parameters -> augmented transposed TF32 hi/lo weights (in workspace). */
+int fdsm_mlp_prepare(const fdsm_mlp_desc* desc, int64_t rows, const float* params, float* workspace,
+                     fdsm_stream_t stream);
+/* energy[rows] = E(x); keeps the activations needed by the backward in the workspace. */
+int fdsm_mlp_forward(const fdsm_mlp_desc* desc, const float* x_hi, const float* x_lo, int64_t rows,
+                     const float* params, float* workspace, float* energy, fdsm_stream_t stream);
+/* grads (flat, same layout as params) (+)= dL/dparams given dE[rows] = dL/dE; needs the workspace of the
+ * matching forward.  Deterministic (fixed-order split-K reduction) except the 3(H+1) head sums (atomics). */
+int fdsm_mlp_backward(const fdsm_mlp_desc* desc, const float* x_hi, const float* x_lo, int64_t rows,
+                      const float* params, float* workspace, const float* dE, float* grads, int32_t accumulate,
+                      fdsm_stream_t stream);
 
 #ifdef __cplusplus
 }
