@@ -36,6 +36,7 @@ class StackArgs(C.Structure):
         ("seed", _u64), ("offset", _u64), ("row0", _u64),
         ("B", _i64), ("D", _i64),
         ("out_lo", _f32p),
+        ("offset_dev", C.c_void_p),
     ]
 
 
@@ -71,6 +72,9 @@ PROTOTYPES = {
                                      _f32p, _f32p, _f32p, _f32p, _i64, _stream]),
     "fdsm_tf32_split": (C.c_int, [_f32p, _i64, _i64, _i64, _f32p, _f32p, _i64, _i64, _i32, _stream]),
     "fdsm_tc_gemm": (C.c_int, [C.POINTER(GemmArgs), _stream]),
+    "fdsm_grad_sumsq": (C.c_int, [_f32p, _i64, _f32p, C.c_void_p, _stream]),
+    "fdsm_adam_step": (C.c_int, [_f32p, _f32p, _f32p, _f32p, _i64, _f32, _f32p, _f32, _f32, _f32, _f32, _f32p, C.c_void_p,
+                                 _stream]),
     "fdsm_mlp_sizes": (C.c_int, [C.POINTER(MlpDesc), _i64, C.POINTER(_i64), C.POINTER(_i64), C.POINTER(_i64)]),
     "fdsm_mlp_prepare": (C.c_int, [C.POINTER(MlpDesc), _i64, _f32p, _f32p, _stream]),
     "fdsm_mlp_forward": (C.c_int, [C.POINTER(MlpDesc), _f32p, _f32p, _i64, _f32p, _f32p, _f32p, _stream]),

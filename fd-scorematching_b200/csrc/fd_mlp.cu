@@ -36,6 +36,7 @@ struct Layout {
   long long h_last;                 // H_L fp32 [rows x npad]
   long long dz_hi[2], dz_lo[2];     // ping-pong dZ hi/lo [rows x npad]
   long long l1, l2;                 // per-row head dot products
+  long long head_acc;               // fp64 accumulators of the head-parameter gradients (3(H+1) doubles)
   long long partial;                // split-K partials
   long long total;
   int splits[16];
@@ -92,6 +93,7 @@ inline int make_layout(const fdsm_mlp_desc* d, long long rows, Layout& y) {
   }
   y.l1 = take(rows);
   y.l2 = take(rows);
+  y.head_acc = take(2ll * 3 * (y.H + 1));
   y.partial = take(max_partial);
   y.total = w;
   return FDSM_OK;
@@ -128,12 +130,14 @@ __global__ void __launch_bounds__(256) prep_weights_kernel(const float* __restri
 
 // ---- head backward: dE -> dZ_L (hi/lo) and the head parameter gradients -----------------------------------
 // dH[r,j] = g (l2 w1[j] + l1 w2[j] + 2 wq[j] h)   (quadratic)   |   g w[j]   (linear);   dZ = dH * act'(h)
-constexpr int HB_ROWS = 64;
+// The head-parameter sums cancel heavily across the x / x+v / x-v rows of a sample (dE = 2c, c(q-1), c(-q-1)), so they
+// are accumulated in fp64 (registers, then fp64 atomics into `acc`) and rounded to fp32 once by head_finish_kernel.
+constexpr int HB_ROWS = 32;
 __global__ void __launch_bounds__(256) head_bwd_kernel(const float* __restrict__ hlast, int ldh, const float* __restrict__ dE,
                                                        const float* __restrict__ l1v, const float* __restrict__ l2v,
                                                        const float* __restrict__ head_w, int H, int npad, long long rows,
                                                        int act, int head, float* __restrict__ dz_hi, float* __restrict__ dz_lo,
-                                                       float* __restrict__ ghead) {
+                                                       double* __restrict__ acc) {
   const int j = threadIdx.x;
   const long long r0 = (long long)blockIdx.x * HB_ROWS;
   const bool col = j < H;
@@ -142,23 +146,24 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(const float* __restrict__
     w1 = head_w[j];
     if (head) { w2 = head_w[H + 1 + j]; wq = head_w[2 * (H + 1) + j]; }
   }
-  float a1 = 0.f, a2 = 0.f, aq = 0.f, sb1 = 0.f, sb2 = 0.f, sbq = 0.f;
+  double a1 = 0., a2 = 0., aq = 0., sb1 = 0., sb2 = 0., sbq = 0.;
+#pragma unroll 4
   for (int i = 0; i < HB_ROWS; ++i) {
     const long long r = r0 + i;
     if (r >= rows) break;
-    const float g = dE[r];
+    const float g = __ldg(dE + r);
     float dz = 0.f;
     if (col) {
-      const float h = hlast[r * ldh + j];
+      const float h = __ldg(hlast + r * ldh + j);
       float dh;
       if (head) {
-        const float ga = g * l2v[r], gb = g * l1v[r];
+        const float ga = g * __ldg(l2v + r), gb = g * __ldg(l1v + r);
         dh = fmaf(ga, w1, fmaf(gb, w2, 2.f * g * wq * h));
-        a1 = fmaf(ga, h, a1); a2 = fmaf(gb, h, a2); aq = fmaf(g * h, h, aq);
+        a1 += (double)ga * h; a2 += (double)gb * h; aq += (double)g * h * h;
         if (j == 0) { sb1 += ga; sb2 += gb; sbq += g; }
       } else {
         dh = g * w1;
-        a1 = fmaf(g, h, a1);
+        a1 += (double)g * h;
         if (j == 0) sb1 += g;
       }
       dz = dh * tc::act_bwd_from_h(act, h);
@@ -171,41 +176,53 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(const float* __restrict__
     }
   }
   if (col) {
-    atomicAdd(ghead + j, a1);
-    if (head) { atomicAdd(ghead + H + 1 + j, a2); atomicAdd(ghead + 2 * (H + 1) + j, aq); }
+    atomicAdd(acc + j, a1);
+    if (head) { atomicAdd(acc + H + 1 + j, a2); atomicAdd(acc + 2 * (H + 1) + j, aq); }
     if (j == 0) {
-      atomicAdd(ghead + H, sb1);
-      if (head) { atomicAdd(ghead + 2 * H + 1, sb2); atomicAdd(ghead + 3 * H + 2, sbq); }
+      atomicAdd(acc + H, sb1);
+      if (head) { atomicAdd(acc + 2 * H + 1, sb2); atomicAdd(acc + 3 * H + 2, sbq); }
     }
   }
 }
 
+__global__ void __launch_bounds__(256) head_finish_kernel(const double* __restrict__ acc, int n, float* __restrict__ ghead,
+                                                          int accumulate) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) ghead[i] = accumulate ? ghead[i] + (float)acc[i] : (float)acc[i];
+}
+
 // ---- split-K reduce: partial[s][k][n] -> gW[n][k] (+)= sum_s, gb[n] (+)= sum_s partial[s][K][n] --------------
+// 8 (k) x 32 (n) elements per block, one element per thread, fp64 fixed-order sum over the splits (deterministic), then
+// a transposing store through shared memory.
 __global__ void __launch_bounds__(256) reduce_wgrad_kernel(const float* __restrict__ partial, int splits, int kpad, int npad,
                                                            int H, int K, float* __restrict__ gW, float* __restrict__ gb,
                                                            int accumulate) {
-  __shared__ float tile[32][33];
-  const int k0 = blockIdx.x * 32, n0 = blockIdx.y * 32;
+  __shared__ float tile[8][33];
+  const int k0 = blockIdx.x * 8, n0 = blockIdx.y * 32;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const long long stride = (long long)kpad * npad;
-  for (int i = ty; i < 32; i += 8) {
-    const int k = k0 + i, n = n0 + tx;
-    float acc = 0.f;
+  {
+    const int k = k0 + ty, n = n0 + tx;
+    double acc = 0.;
     if (k <= K && n < H) {
       const float* p = partial + (long long)k * npad + n;
-      for (int s = 0; s < splits; ++s) acc += p[s * stride];   // fixed order: deterministic
+#pragma unroll 8
+      for (int s = 0; s < splits; ++s) acc += (double)__ldg(p + s * stride);
     }
-    tile[i][tx] = acc;
+    tile[ty][tx] = (float)acc;
   }
   __syncthreads();
-  for (int i = ty; i < 32; i += 8) {
-    const int n = n0 + i, k = k0 + tx;
+  {
+    // 256 threads -> 32 n x 8 k, k fastest so the stores to gW[n][k] run along k
+    const int kk = threadIdx.x & 7, nn = threadIdx.x >> 3;
+    const int n = n0 + nn, k = k0 + kk;
     if (n < H) {
+      const float v = tile[kk][nn];
       if (k < K) {
         float* o = gW + (long long)n * K + k;
-        *o = accumulate ? *o + tile[tx][i] : tile[tx][i];
+        *o = accumulate ? *o + v : v;
       } else if (k == K) {
-        gb[n] = accumulate ? gb[n] + tile[tx][i] : tile[tx][i];
+        gb[n] = accumulate ? gb[n] + v : v;
       }
     }
   }
@@ -290,15 +307,15 @@ extern "C" int fdsm_mlp_backward(const fdsm_mlp_desc* desc, const float* x_hi, c
   }
   FDSM_REQUIRE(x_hi && (x_lo || y.passes == 1) && dE, "fdsm_mlp_backward: NULL pointer");
   float* ws = workspace;
-  const long long head_n = y.n_params - y.head_off;
-  if (!accumulate) {
-    rc = cuda_status(cudaMemsetAsync(grads + y.head_off, 0, head_n * sizeof(float), st), "fdsm_mlp_backward(memset)");
-    if (rc) return rc;
-  }
+  const int head_n = (int)(y.n_params - y.head_off);
+  double* hacc = reinterpret_cast<double*>(ws + y.head_acc);
+  rc = cuda_status(cudaMemsetAsync(hacc, 0, head_n * sizeof(double), st), "fdsm_mlp_backward(memset)");
+  if (rc) return rc;
   int cur = 0;
   mlp::head_bwd_kernel<<<(unsigned)((rows + mlp::HB_ROWS - 1) / mlp::HB_ROWS), 256, 0, st>>>(
       ws + y.h_last, y.npad, dE, ws + y.l1, ws + y.l2, params + y.head_off, y.H, y.npad, rows, y.act, y.head,
-      ws + y.dz_hi[cur], ws + y.dz_lo[cur], grads + y.head_off);
+      ws + y.dz_hi[cur], ws + y.dz_lo[cur], hacc);
+  mlp::head_finish_kernel<<<(head_n + 255) / 256, 256, 0, st>>>(hacc, head_n, grads + y.head_off, accumulate);
   rc = cuda_status(cudaGetLastError(), "fdsm_mlp_backward(head)");
   if (rc) return rc;
   for (int l = y.L - 1; l >= 0; --l) {
@@ -313,7 +330,7 @@ extern "C" int fdsm_mlp_backward(const fdsm_mlp_desc* desc, const float* x_hi, c
       p.out_hi = ws + y.partial; p.ldo = y.npad; p.split_stride = (long long)kp * y.npad;
       rc = tc::launch_gemm(p, In, B, K + 1, y.npad, (int)rows, y.npad, y.passes, y.splits[l], st);
       if (rc) return rc;
-      dim3 grid((K + 1 + 31) / 32, (y.H + 31) / 32);
+      dim3 grid((K + 1 + 7) / 8, (y.H + 31) / 32);
       mlp::reduce_wgrad_kernel<<<grid, 256, 0, st>>>(ws + y.partial, y.splits[l], kp, y.npad, y.H, K, grads + y.w_off[l],
                                                      grads + y.b_off[l], accumulate);
       rc = cuda_status(cudaGetLastError(), "fdsm_mlp_backward(reduce)");

@@ -1,0 +1,80 @@
+// Host-loop pieces of the training step on the flat parameter vector (DeepEBM/train_ssm.py:65-70):
+// clip_grad_norm_ (global L2 norm, coefficient clip/(norm+1e-6) clamped to 1) and the Adam update, as two
+// launches with every scalar that changes per step (step count, learning rate) read from device memory, so the
+// whole step replays from one CUDA graph.
+#include "fdsm_common.cuh"
+
+namespace fdsm {
+namespace {
+
+// single block, fixed summation order: bit-identical across ranks and runs
+__global__ void __launch_bounds__(1024) sumsq_kernel(const float* __restrict__ g, long long n, float* __restrict__ out,
+                                                     long long* __restrict__ step) {
+  __shared__ float red[32];
+  float acc = 0.f;
+  const long long n4 = n >> 2;
+  if (aligned16(g)) {
+    for (long long i = threadIdx.x; i < n4; i += blockDim.x) {
+      const float4 v = __ldg(reinterpret_cast<const float4*>(g) + i);
+      acc += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+    }
+    for (long long i = (n4 << 2) + threadIdx.x; i < n; i += blockDim.x) acc += g[i] * g[i];
+  } else {
+    for (long long i = threadIdx.x; i < n; i += blockDim.x) acc += g[i] * g[i];
+  }
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float s = 0.f;
+    for (int i = 0; i < 32; ++i) s += red[i];
+    *out = s;
+    if (step) *step += 1;
+  }
+}
+
+__global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                                                   float* __restrict__ v, long long n, float lr, const float* __restrict__ lr_dev,
+                                                   float b1, float b2, float eps, float max_norm,
+                                                   const float* __restrict__ sumsq, const long long* __restrict__ step) {
+  const float t = (float)__ldg(step);
+  const float lrv = lr_dev ? __ldg(lr_dev) : lr;
+  float coef = 1.f;
+  if (max_norm > 0.f) coef = fminf(max_norm / (sqrtf(__ldg(sumsq)) + 1e-6f), 1.f);
+  const float bc1 = 1.f - powf(b1, t), bc2s = sqrtf(1.f - powf(b2, t));
+  const float step_size = lrv / bc1;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float gi = g[i] * coef;
+    const float mi = b1 * m[i] + (1.f - b1) * gi;
+    const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    p[i] -= step_size * (mi / (sqrtf(vi) / bc2s + eps));
+  }
+}
+
+}  // namespace
+}  // namespace fdsm
+
+using namespace fdsm;
+
+extern "C" int fdsm_grad_sumsq(const float* g, int64_t n, float* sumsq, int64_t* step_counter, fdsm_stream_t stream) {
+  FDSM_REQUIRE(n >= 0 && sumsq && (g || n == 0), "fdsm_grad_sumsq: bad arguments");
+  sumsq_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(g, n, sumsq, (long long*)step_counter);
+  FDSM_LAUNCH_CHECK("fdsm_grad_sumsq");
+}
+
+extern "C" int fdsm_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
+                              const float* lr_dev, float beta1, float beta2, float eps, float max_norm, const float* sumsq,
+                              const int64_t* step_counter, fdsm_stream_t stream) {
+  FDSM_REQUIRE(n >= 0, "fdsm_adam_step: n < 0");
+  if (n == 0) return FDSM_OK;
+  FDSM_REQUIRE(params && grads && exp_avg && exp_avg_sq && step_counter, "fdsm_adam_step: NULL pointer");
+  FDSM_REQUIRE(max_norm <= 0.f || sumsq, "fdsm_adam_step: clipping needs the squared gradient norm");
+  const long long nb = (n + 255) / 256;
+  const long long cap = (long long)sm_count() * 8;
+  adam_kernel<<<(int)(nb < cap ? nb : cap), 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, n, lr, lr_dev, beta1,
+                                                                           beta2, eps, max_norm, sumsq,
+                                                                           (const long long*)step_counter);
+  FDSM_LAUNCH_CHECK("fdsm_adam_step");
+}

@@ -189,9 +189,13 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         if (++stage == STAGES) { stage = 0; phase ^= 1u; }
       }
     }
-  } else if (warp >= 4) {
-    // ===== epilogue: TMEM -> registers -> fused op -> global ======================================
+  }
+  __syncwarp();
+  {
+    // ===== epilogue (all 8 warps once their role is done): TMEM -> registers -> fused op -> global ==========
+    // warp w may read TMEM lanes 32*(w%4)..+31; warps 0-3 take the even 32-column chunks, warps 4-7 the odd ones
     const int q = warp & 3;                      // TMEM lane quarter this warp may read
+    const int half = warp >> 2;
     const int row = m0 + q * 32 + lane;
     const bool row_ok = row < p.M;
     const bool have_acc = kb1 > kb0;
@@ -203,7 +207,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
     const bool last_tile = n0 + p.BN >= p.N;   // the tile that also writes the padding columns [N, out_cols)
     const int ncols_out = (p.epi == EPI_STORE || p.epi == EPI_HEAD) ? min(p.N - n0, p.BN)
                                                                      : (last_tile ? p.out_cols - n0 : p.BN);
-    for (int c0 = 0; c0 < ncols_out; c0 += 32) {
+    for (int c0 = 32 * half; c0 < ncols_out; c0 += 64) {
       float v[32];
       if (have_acc && c0 < p.BN) {
         tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
@@ -282,7 +286,13 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         }
       }
     }
-    if (p.epi == EPI_HEAD && row_ok) {
+    if (p.epi == EPI_HEAD) {   // combine the two column halves of each row (uniform branch: whole CTA)
+      __shared__ float hsum[BM][3];
+      if (half == 1) { hsum[q * 32 + lane][0] = l1; hsum[q * 32 + lane][1] = l2; hsum[q * 32 + lane][2] = lq; }
+      __syncthreads();
+      if (half == 0) { l1 += hsum[q * 32 + lane][0]; l2 += hsum[q * 32 + lane][1]; lq += hsum[q * 32 + lane][2]; }
+    }
+    if (p.epi == EPI_HEAD && row_ok && half == 0) {
       const float b1 = __ldg(p.head_w + p.N);
       const float b2 = p.head_mode ? __ldg(p.head_w + 2 * p.N + 1) : 0.f, bq = p.head_mode ? __ldg(p.head_w + 3 * p.N + 2) : 0.f;
       l1 += b1;

@@ -158,7 +158,7 @@ class FusedEnergyMLP(nn.Module):
             self._step_state = st
         return st
 
-    def fd_ssm_loss_and_grad(self, x, eps, scale, *, u=None, v=None, draw=None, c1=2.0, mean=True):
+    def fd_ssm_loss_and_grad(self, x, eps, scale, *, u=None, v=None, draw=None, c1=2.0, mean=True, offset_dev=None):
         """loss = scale * mean_b[(E2-E3)^2/8 - E2 - E3 + c1 E1] on the stacked batch [x, x+v, x-v] and its gradient
         w.r.t. the flat parameters (SSM/losses/efficient_sm.py:47-73 with scale = D/eps^2; DeepEBM/ESM/loss_train.py:
         212-234 with scale = 1/eps^2).  Returns (loss 0-dim tensor, flat gradient); both are persistent buffers."""
@@ -171,12 +171,19 @@ class FusedEnergyMLP(nn.Module):
             ops.stack(x2, row_mask=7, scale=1.0, direction=v.reshape(B, -1), normalize=False, out=st["xh"], out_lo=st["xl"])
         else:
             ops.stack(x2, row_mask=7, scale=eps, direction=None if u is None else u.reshape(B, -1), normalize=True,
-                      out=st["xh"], out_lo=st["xl"], draw=draw)
+                      out=st["xh"], out_lo=st["xl"], draw=draw, offset_dev=offset_dev)
         s = _stream()
         flat = self.flat.data
         ops._count(self.n_hidden); check(lib.fdsm_mlp_prepare(C.byref(d), rows, _ptr(flat), _ptr(st["ws"]), s), "fdsm_mlp_prepare")
+        hook = ops.PROFILE_HOOK
+        if hook is not None:   # bench.py: CUDA events around the forward GEMM launches, on the launching stream
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
         ops._count(self.n_hidden); check(lib.fdsm_mlp_forward(C.byref(d), _ptr(st["xh"]), _ptr(st["xl"]), rows, _ptr(flat),
                                                             _ptr(st["ws"]), _ptr(st["E"]), s), "fdsm_mlp_forward")
+        if hook is not None:
+            e1.record()
+            hook.append((e0, e1))
         ops._count(2)
         check(lib.fdsm_combine_energy_fwd(_ptr(st["E"]), B, 0, float(c1), float(scale), int(mean), None, _ptr(st["loss"]), s),
               "fdsm_combine_energy_fwd")
@@ -186,3 +193,116 @@ class FusedEnergyMLP(nn.Module):
         check(lib.fdsm_mlp_backward(C.byref(d), _ptr(st["xh"]), _ptr(st["xl"]), rows, _ptr(flat), _ptr(st["ws"]), _ptr(st["dE"]),
                                     _ptr(st["grad"]), 0, s), "fdsm_mlp_backward")
         return st["loss"], st["grad"]
+
+    # ---- the training step: FD-SSM loss -> backward -> (all-reduce) -> clip -> Adam, graph-replayed ----------------
+    def flat_params(self):
+        return self
+
+    def configure_optimizer(self, lr=1e-5, betas=(0.9, 0.95), clip=0.1, adam_eps=1e-8, use_graph=True, seed=0x5EED, rank=0):
+        dev = self.flat.device
+        self._opt = dict(lr=float(lr), betas=(float(betas[0]), float(betas[1])), clip=float(clip) if clip else 0.0,
+                         eps=float(adam_eps), use_graph=bool(use_graph), seed=int(seed), rank=int(rank),
+                         m=torch.zeros_like(self.flat.data), v=torch.zeros_like(self.flat.data),
+                         sumsq=torch.zeros((), device=dev), step=torch.zeros((), device=dev, dtype=torch.int64),
+                         lr_dev=torch.full((), float(lr), device=dev))
+        self._graphs = {}
+
+    def set_lr(self, lr):
+        """Learning-rate schedules (DeepEBM/ESM/inputs.py:75-90) write the device scalar the captured step reads."""
+        self._opt["lr_dev"].fill_(float(lr))
+
+    def _loss_and_grad_captured(self, st, eps, scale):
+        o = self._opt
+        return self.fd_ssm_loss_and_grad(st["x"], eps, scale, draw=(o["seed"], 0, o["rank"] * st["B"]), offset_dev=o["step"])
+
+    def _apply_update(self, st):
+        lib, o = _lib.load(), self._opt
+        n, s = self.flat.numel(), _stream()
+        ops._count(2)
+        check(lib.fdsm_grad_sumsq(_ptr(st["grad"]), n, _ptr(o["sumsq"]), _ptr(o["step"]), s), "fdsm_grad_sumsq")
+        check(lib.fdsm_adam_step(_ptr(self.flat.data), _ptr(st["grad"]), _ptr(o["m"]), _ptr(o["v"]), n, o["lr"], _ptr(o["lr_dev"]),
+                                 o["betas"][0], o["betas"][1], o["eps"], o["clip"], _ptr(o["sumsq"]), _ptr(o["step"]), s),
+              "fdsm_adam_step")
+
+    def fd_ssm_step(self, x, eps, allreduce=None, scale=None, distributed=False):
+        """One optimisation step of DeepEBM/train_ssm.py:63-69 on a device batch x (B, ...).  Returns the loss (device
+        scalar, persistent buffer).  world == 1: the whole step is ONE CUDA-graph replay; world > 1: two replays around
+        the single gradient all-reduce."""
+        x2 = x.reshape(x.shape[0], -1)
+        B = x2.shape[0]
+        st = self._state(B, x2.device)
+        if "x" not in st:
+            st["x"] = torch.empty_like(x2)
+        scale = 1.0 / eps ** 2 if scale is None else scale
+        st["x"].copy_(x2)
+        key = (B, float(eps), float(scale), bool(distributed))
+        if not self._opt["use_graph"]:
+            self._loss_and_grad_captured(st, eps, scale)
+            if distributed and allreduce is not None:
+                allreduce(st["grad"])
+            self._apply_update(st)
+            return st["loss"]
+        if key not in self._graphs:
+            # warm-up outside capture (module-level one-time setup inside the library), then capture
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                step0 = self._opt["step"].clone()
+                self._loss_and_grad_captured(st, eps, scale)
+                self._opt["step"].copy_(step0)
+            torch.cuda.current_stream().wait_stream(side)
+            launches0 = ops.LAUNCHES
+            g1, g2 = torch.cuda.CUDAGraph(), None
+            with torch.cuda.graph(g1):
+                self._loss_and_grad_captured(st, eps, scale)
+                if not distributed:
+                    self._apply_update(st)
+            if distributed:
+                g2 = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g2):
+                    self._apply_update(st)
+            self._graphs[key] = (g1, g2, ops.LAUNCHES - launches0)
+            ops.LAUNCHES = launches0
+        g1, g2, nlaunch = self._graphs[key]
+        g1.replay()
+        if g2 is not None:
+            if allreduce is not None:
+                allreduce(st["grad"])
+            g2.replay()
+        ops._count(nlaunch)
+        return st["loss"]
+
+    def forward_flops(self, rows):
+        """Algorithmic flops of the forward GEMMs (2*M*N*K per layer; bias column, padding and head dots not credited)."""
+        return 2.0 * rows * (self.in_dim * self.hidden + (self.n_hidden - 1) * self.hidden * self.hidden)
+
+    def roofline(self, events, peaks, peaks_kind):
+        """bench.py: tensor-pipe roofline of the GEMM kernel from live CUDA-event timings of fdsm_mlp_forward
+        (n_hidden launches of gemm_kernel back to back).  Peak = measured dense bf16 / 2 (TF32 runs at half the bf16
+        rate); `achieved` counts ALGORITHMIC fp32 flops, the 3xTF32 scheme executes 3x that on the pipe."""
+        if not events:
+            return None
+        ms = sorted(a.elapsed_time(b) for a, b in events)
+        avg = sum(ms) / len(ms)
+        rows = self._step_state["rows"]
+        per_launch_flops = self.forward_flops(rows) / self.n_hidden
+        per_launch_s = avg * 1e-3 / self.n_hidden
+        ach = per_launch_flops / per_launch_s / 1e12
+        peak = peaks["bf16_tflops"] / 2.0
+        return {"kernel": f"fdsm::tc::gemm_kernel<{self.passes}> (tcgen05 kind::tf32, TMA-fed; forward launches of the energy MLP)",
+                "bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": None,
+                "peak_kind": f"{peaks_kind} dense bf16 burst / 2 (TF32 kind)", "passes": self.passes,
+                "executed_tf32_tflops": ach * self.passes, "executed_frac": ach * self.passes / peak,
+                "algorithmic_flops_per_launch": per_launch_flops, "avg_launch_us": per_launch_s * 1e6,
+                "launches_timed": len(ms) * self.n_hidden}
+
+
+def smoke(dev):
+    """__graft_entry__.smoke(): one fused FD-SSM step on a tiny batch (finite loss, non-zero update)."""
+    net = FusedEnergyMLP(64, 48, 3, act="nsoftplus", head="quadratic", device=dev, seed=7)
+    net.configure_optimizer(lr=1e-3, betas=(0.9, 0.95), clip=0.1, use_graph=False)
+    x = torch.rand(32, 64, device=dev)
+    before = net.flat.data.clone()
+    loss = net.fd_ssm_step(x, eps=0.05)
+    assert torch.isfinite(loss).item(), "fused FD-SSM smoke: non-finite loss"
+    assert float((net.flat.data - before).abs().max()) > 0, "fused FD-SSM smoke: parameters did not move"

@@ -85,7 +85,7 @@ def next_draw():
 # kernels (1)+(2)
 # --------------------------------------------------------------------------------------------
 def stack(x, *, row_mask, scale, direction=None, normalize=True, noise=None, sigma=None, labels=None,
-          perturb=True, dot_mode=0, want_v=False, want_dot=False, draw=None, out=None, out_lo=None):
+          perturb=True, dot_mode=0, want_v=False, want_dot=False, draw=None, out=None, out_lo=None, offset_dev=None):
     """Fused direction sampling + normalisation + stacked-batch build (fdsm_stack).
 
     x: (B, D) fp32 CUDA.  Returns (stacked (rows*B, D) | None, v (B, D) | None, dot (B,) | None)."""
@@ -141,6 +141,8 @@ def stack(x, *, row_mask, scale, direction=None, normalize=True, noise=None, sig
         a.dot_out = _ptr(dot)
     seed, offset, row0 = draw if draw is not None else next_draw()
     a.seed, a.offset, a.row0 = seed, offset, row0
+    if offset_dev is not None:
+        a.offset_dev = _ptr(_req(offset_dev, "offset_dev", torch.int64))
     a.B, a.D = B, D
     _count(1); check(lib.fdsm_stack(C.byref(a), _stream()), "fdsm_stack")
     return out, v, dot

@@ -12,15 +12,15 @@ class FDSSMTrainer:
         self.net = net
         self.eps, self.clip, self.loss_name = eps, clip, loss
         self.fused = hasattr(net, "fd_ssm_step")       # mlp.FusedEnergyMLP: kernels (1)-(4) + Adam in CUDA
+        rank = torch.distributed.get_rank() if ddp.is_distributed() else 0
         if self.fused:
             self.flat = net.flat_params()
-            net.configure_optimizer(lr=lr, betas=betas, clip=clip)
+            net.configure_optimizer(lr=lr, betas=betas, clip=clip, seed=seed, rank=rank)
         else:
             self.flat = ddp.FlatParams(net)
             self.opt = torch.optim.Adam([self.flat.flat], lr=lr, betas=betas, fused=self.flat.flat.is_cuda)
             self.flat.flat.grad = self.flat.grad
-        ddp.broadcast_params_(self.flat.flat)
-        rank = torch.distributed.get_rank() if ddp.is_distributed() else 0
+        ddp.broadcast_params_(self.flat.flat.data)
         ops.manual_seed(seed)
         self._rank = rank
         self._copy_stream = None
@@ -31,7 +31,7 @@ class FDSSMTrainer:
         B = x.shape[0]
         ops.set_row_offset(self._rank * B)
         if self.fused:
-            return self.net.fd_ssm_step(x, eps=self.eps, allreduce=ddp.allreduce_mean_)
+            return self.net.fd_ssm_step(x, eps=self.eps, allreduce=ddp.allreduce_mean_, distributed=ddp.is_distributed())
         self.flat.zero_grad()
         loss = losses.ssm_fd(self.net, x, eps=self.eps, batch_size=B)
         loss.backward()

@@ -83,6 +83,8 @@ typedef struct fdsm_stack_args {
   float* out_lo;         /* optional: when set, `out` receives the TF32 hi half and `out_lo` the lo half of every
                             stacked row (x = hi + lo), and columns [D, ldout) are written as the GEMM padding:
                             column D = 1 (folded bias), the rest 0 -- the operand format of fdsm_mlp_forward      */
+  const uint64_t* offset_dev; /* optional DEVICE counter added to `offset` at run time (e.g. the optimizer step
+                            counter), so a captured CUDA graph draws fresh directions on every replay             */
 } fdsm_stack_args;
 
 int fdsm_stack(const fdsm_stack_args* args, fdsm_stream_t stream);
@@ -200,6 +202,19 @@ int fdsm_mlp_forward(const fdsm_mlp_desc* desc, const float* x_hi, const float* 
 int fdsm_mlp_backward(const fdsm_mlp_desc* desc, const float* x_hi, const float* x_lo, int64_t rows,
                       const float* params, float* workspace, const float* dE, float* grads, int32_t accumulate,
                       fdsm_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Optimizer step on the flat parameter vector (the reference's host loop, DeepEBM/train_ssm.py:65-70:
+ * clip_grad_norm_(params, clip) then Adam.step()).  Per-step scalars come from device memory so the
+ * step replays from one CUDA graph.
+ * ------------------------------------------------------------------------------------------ */
+/* sumsq[0] = sum g^2 (single block, fixed order: bit-identical on every rank); *step_counter += 1 if given. */
+int fdsm_grad_sumsq(const float* g, int64_t n, float* sumsq, int64_t* step_counter, fdsm_stream_t stream);
+/* torch.optim.Adam semantics (no weight decay, no amsgrad) at t = *step_counter; gradient pre-scaled by
+ * min(1, max_norm/(sqrt(sumsq)+1e-6)) when max_norm > 0; lr_dev (device scalar) overrides lr when non-NULL. */
+int fdsm_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
+                   const float* lr_dev, float beta1, float beta2, float eps, float max_norm, const float* sumsq,
+                   const int64_t* step_counter, fdsm_stream_t stream);
 
 #ifdef __cplusplus
 }
