@@ -68,6 +68,12 @@ __device__ __forceinline__ float act_bwd_from_h(int act, float h) {
   }
 }
 
+}  // namespace tc
+}  // namespace fdsm
+#include "tc_epilogue.cuh"
+namespace fdsm {
+namespace tc {
+
 struct SmemLayout {
   // dynamic smem (1024-byte aligned): per stage [A_hi | A_lo | B_hi | B_lo]
   static __host__ __device__ constexpr int stage_bytes(int passes) {
@@ -77,9 +83,15 @@ struct SmemLayout {
   static __host__ __device__ constexpr int total(int passes) { return stages(passes) * stage_bytes(passes) + 1024 + 256; }
 };
 
-template <int PASSES>
+template <int PASSES, int EPI>
 __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant__ GemmParams p) {
   using namespace ptx;
+  // EPI_HEAD: head weights [w1 | b1], [w2 | b2], [wq | bq] staged once in shared memory (N <= 256)
+  __shared__ float head_smem[EPI == EPI_HEAD ? 3 * HW_STRIDE : 1];
+  if constexpr (EPI == EPI_HEAD) {
+    const int nh = p.head_mode ? 3 : 1;
+    for (int i = threadIdx.x; i < nh * (p.N + 1); i += kThreads) head_smem[(i / (p.N + 1)) * HW_STRIDE + i % (p.N + 1)] = __ldg(p.head_w + i);
+  }
   constexpr int STAGES = SmemLayout::stages(PASSES);
   constexpr int STAGE_BYTES = SmemLayout::stage_bytes(PASSES);
   extern __shared__ uint8_t smem_raw[];
@@ -193,8 +205,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
   __syncwarp();
   {
     // ===== epilogue (all 8 warps once their role is done): TMEM -> registers -> fused op -> global ==========
-    // warp w may read TMEM lanes 32*(w%4)..+31; warps 0-3 take the even 32-column chunks, warps 4-7 the odd ones
-    const int q = warp & 3;                      // TMEM lane quarter this warp may read
+    // warp w may read TMEM lanes 32*(w%4)..+31; warps 0-3 take the first half of the columns, warps 4-7 the second
+    const int q = warp & 3;
     const int half = warp >> 2;
     const int row = m0 + q * 32 + lane;
     const bool row_ok = row < p.M;
@@ -205,102 +217,24 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
     }
     float l1 = 0.f, l2 = 0.f, lq = 0.f;
     const bool last_tile = n0 + p.BN >= p.N;   // the tile that also writes the padding columns [N, out_cols)
-    const int ncols_out = (p.epi == EPI_STORE || p.epi == EPI_HEAD) ? min(p.N - n0, p.BN)
-                                                                     : (last_tile ? p.out_cols - n0 : p.BN);
-    for (int c0 = 32 * half; c0 < ncols_out; c0 += 64) {
-      float v[32];
-      if (have_acc && c0 < p.BN) {
-        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
-      } else {
-#pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = 0.f;
-      }
-      const int nvalid = p.N - n0 - c0;          // columns [0, nvalid) of this chunk are real outputs
-      if (p.epi == EPI_STORE) {
-        if (row_ok) {
-          float* o = p.out_hi + (long long)blockIdx.z * p.split_stride + (long long)row * p.ldo + n0 + c0;
-          if (nvalid >= 32 && ((p.ldo | (n0 + c0) | (blockIdx.z ? p.split_stride : 0)) & 3) == 0 && aligned16(p.out_hi)) {
-#pragma unroll
-            for (int i = 0; i < 32; i += 4) *reinterpret_cast<float4*>(o + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
-          } else {
-#pragma unroll
-            for (int i = 0; i < 32; ++i)
-              if (i < nvalid) o[i] = v[i];
-          }
-        }
-      } else if (p.epi == EPI_HEAD) {
-        const float* w1 = p.head_w;
-        const float* w2 = p.head_w + p.N + 1;
-        const float* wq = p.head_w + 2 * (p.N + 1);
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const int c = n0 + c0 + i;
-          float h = 0.f;
-          if (i < nvalid) {
-            h = act_fwd(p.act, v[i]);
-            l1 = fmaf(h, __ldg(w1 + c), l1);
-            if (p.head_mode) {
-              l2 = fmaf(h, __ldg(w2 + c), l2);
-              lq = fmaf(h * h, __ldg(wq + c), lq);
-            }
-          }
-          v[i] = h;
-        }
-        if (row_ok) {
-          float* o = p.out_hi + (long long)row * p.ldo + n0 + c0;
-#pragma unroll
-          for (int i = 0; i < 32; i += 4)
-            if (c0 + i < p.out_cols) *reinterpret_cast<float4*>(o + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
-        }
-      } else {
-        // EPI_ACT_SPLIT / EPI_DACT_SPLIT: hi/lo rows of the next GEMM's operand, padded to out_cols
-        float hi[32], lo[32];
-        const float* ah = p.aux_hi ? p.aux_hi + (long long)row * p.ldaux + n0 + c0 : nullptr;
-        const float* al = p.aux_lo ? p.aux_lo + (long long)row * p.ldaux + n0 + c0 : nullptr;
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float y = 0.f;
-          if (i < nvalid) {
-            if (p.epi == EPI_ACT_SPLIT) {
-              y = act_fwd(p.act, v[i]);
-            } else if (row_ok) {
-              float h = __ldg(ah + i);
-              if (al) h += __ldg(al + i);
-              y = v[i] * act_bwd_from_h(p.act, h);
-            }
-          } else if (i == nvalid && p.epi == EPI_ACT_SPLIT) {
-            y = 1.f;                              // bias column of the next layer's augmented input
-          }
-          tf32_split(y, hi[i], lo[i]);
-        }
-        if (row_ok) {
-          float* oh = p.out_hi + (long long)row * p.ldo + n0 + c0;
-          float* ol = p.out_lo + (long long)row * p.ldo + n0 + c0;
-#pragma unroll
-          for (int i = 0; i < 32; i += 4) {
-            if (c0 + i < ncols_out) {
-              *reinterpret_cast<float4*>(oh + i) = make_float4(hi[i], hi[i + 1], hi[i + 2], hi[i + 3]);
-              *reinterpret_cast<float4*>(ol + i) = make_float4(lo[i], lo[i + 1], lo[i + 2], lo[i + 3]);
-            }
-          }
-        }
-      }
-    }
-    if (p.epi == EPI_HEAD) {   // combine the two column halves of each row (uniform branch: whole CTA)
+    const int ncols_out = (EPI == EPI_STORE || EPI == EPI_HEAD) ? min(p.N - n0, p.BN) : (last_tile ? p.out_cols - n0 : p.BN);
+    const int nsteps = (ncols_out + CW - 1) / CW, s0 = (nsteps + 1) / 2;
+    const int c_begin = half ? s0 * CW : 0, c_end = half ? nsteps * CW : s0 * CW;
+    epilogue_dispatch<EPI>(p, tmem_base + ((uint32_t)(q * 32) << 16), have_acc, row, row_ok, n0, c_begin, c_end, head_smem, l1,
+                           l2, lq);
+    if constexpr (EPI == EPI_HEAD) {   // combine the two column halves of each row
       __shared__ float hsum[BM][3];
       if (half == 1) { hsum[q * 32 + lane][0] = l1; hsum[q * 32 + lane][1] = l2; hsum[q * 32 + lane][2] = lq; }
       __syncthreads();
-      if (half == 0) { l1 += hsum[q * 32 + lane][0]; l2 += hsum[q * 32 + lane][1]; lq += hsum[q * 32 + lane][2]; }
-    }
-    if (p.epi == EPI_HEAD && row_ok && half == 0) {
-      const float b1 = __ldg(p.head_w + p.N);
-      const float b2 = p.head_mode ? __ldg(p.head_w + 2 * p.N + 1) : 0.f, bq = p.head_mode ? __ldg(p.head_w + 3 * p.N + 2) : 0.f;
-      l1 += b1;
-      l2 += b2;
-      // quadratic head ln1(h)*ln2(h) + lq(h^2) (models.py:338,954) or a plain Linear(H,1) head (head_mode 0)
-      p.e_out[row] = p.head_mode ? fmaf(l1, l2, lq + bq) : l1;
-      p.l1_out[row] = l1;
-      p.l2_out[row] = l2;
+      if (half == 0 && row_ok) {
+        l1 += hsum[q * 32 + lane][0] + head_smem[p.N];
+        l2 += hsum[q * 32 + lane][1] + (p.head_mode ? head_smem[HW_STRIDE + p.N] : 0.f);
+        lq += hsum[q * 32 + lane][2] + (p.head_mode ? head_smem[2 * HW_STRIDE + p.N] : 0.f);
+        // quadratic head ln1(h)*ln2(h) + lq(h^2) (models.py:338,954) or a plain Linear(H,1) head (head_mode 0)
+        p.e_out[row] = p.head_mode ? fmaf(l1, l2, lq) : l1;
+        p.l1_out[row] = l1;
+        p.l2_out[row] = l2;
+      }
     }
     tc_fence_before();
   }

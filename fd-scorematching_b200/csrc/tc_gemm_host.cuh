@@ -81,11 +81,22 @@ inline int launch_gemm(GemmParams& p, const Operand& A, const Operand& B, int M,
   const int smem = SmemLayout::total(passes);
   static std::once_flag once;
   std::call_once(once, [] {
-    cudaFuncSetAttribute(gemm_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SmemLayout::total(1));
-    cudaFuncSetAttribute(gemm_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, SmemLayout::total(3));
+#define FDSM_SET_SMEM(P, E) cudaFuncSetAttribute(gemm_kernel<P, E>, cudaFuncAttributeMaxDynamicSharedMemorySize, SmemLayout::total(P))
+    FDSM_SET_SMEM(1, EPI_STORE); FDSM_SET_SMEM(1, EPI_ACT_SPLIT); FDSM_SET_SMEM(1, EPI_HEAD); FDSM_SET_SMEM(1, EPI_DACT_SPLIT);
+    FDSM_SET_SMEM(3, EPI_STORE); FDSM_SET_SMEM(3, EPI_ACT_SPLIT); FDSM_SET_SMEM(3, EPI_HEAD); FDSM_SET_SMEM(3, EPI_DACT_SPLIT);
+#undef FDSM_SET_SMEM
   });
-  if (passes == 3) gemm_kernel<3><<<grid, kThreads, smem, st>>>(p);
-  else gemm_kernel<1><<<grid, kThreads, smem, st>>>(p);
+#define FDSM_LAUNCH(P, E) gemm_kernel<P, E><<<grid, kThreads, smem, st>>>(p)
+#define FDSM_LAUNCH_EPI(P)                                   \
+  switch (p.epi) {                                           \
+    case EPI_STORE: FDSM_LAUNCH(P, EPI_STORE); break;        \
+    case EPI_ACT_SPLIT: FDSM_LAUNCH(P, EPI_ACT_SPLIT); break;\
+    case EPI_HEAD: FDSM_LAUNCH(P, EPI_HEAD); break;          \
+    default: FDSM_LAUNCH(P, EPI_DACT_SPLIT); break;          \
+  }
+  if (passes == 3) { FDSM_LAUNCH_EPI(3) } else { FDSM_LAUNCH_EPI(1) }
+#undef FDSM_LAUNCH_EPI
+#undef FDSM_LAUNCH
   FDSM_LAUNCH_CHECK("tc_gemm");
 }
 
