@@ -99,13 +99,22 @@ inline int make_layout(const fdsm_mlp_desc* d, long long rows, Layout& y) {
   return FDSM_OK;
 }
 
-// ---- weight preparation: flat parameters -> augmented transposed TF32 hi/lo ------------------------------
-__global__ void __launch_bounds__(256) prep_weights_kernel(const float* __restrict__ W, const float* __restrict__ b, int H, int K,
-                                                           int kpad, int npad, float* __restrict__ wt_hi,
-                                                           float* __restrict__ wt_lo) {
+// ---- weight preparation: flat parameters -> augmented transposed TF32 hi/lo (all layers in one launch) ----------
+struct PrepArgs {
+  const float* W[16]; const float* b[16];
+  float* hi[16]; float* lo[16];
+  int K[16], kpad[16];
+  int H, npad;
+};
+__global__ void __launch_bounds__(256) prep_weights_kernel(const PrepArgs a) {
   // 32x32 tile transpose through shared memory: coalesced reads of W[n][k] (k fastest) and writes of Wt[k][n]
   __shared__ float tile[32][33];
+  const int l = blockIdx.z;
+  const int K = a.K[l], kpad = a.kpad[l], H = a.H, npad = a.npad;
   const int k0 = blockIdx.x * 32, n0 = blockIdx.y * 32;
+  if (k0 >= kpad) return;   // uniform per block
+  const float* __restrict__ W = a.W[l];
+  const float* __restrict__ b = a.b[l];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8
   for (int i = ty; i < 32; i += 8) {
     const int n = n0 + i, k = k0 + tx;
@@ -122,8 +131,8 @@ __global__ void __launch_bounds__(256) prep_weights_kernel(const float* __restri
     if (k < kpad && n < npad) {
       float hi, lo;
       ptx::tf32_split(tile[tx][i], hi, lo);
-      wt_hi[(long long)k * npad + n] = hi;
-      wt_lo[(long long)k * npad + n] = lo;
+      a.hi[l][(long long)k * npad + n] = hi;
+      a.lo[l][(long long)k * npad + n] = lo;
     }
   }
 }
@@ -192,28 +201,39 @@ __global__ void __launch_bounds__(256) head_finish_kernel(const double* __restri
 }
 
 // ---- split-K reduce: partial[s][k][n] -> gW[n][k] (+)= sum_s, gb[n] (+)= sum_s partial[s][K][n] --------------
-// 8 (k) x 32 (n) elements per block, one element per thread, fp64 fixed-order sum over the splits (deterministic), then
-// a transposing store through shared memory.
-__global__ void __launch_bounds__(256) reduce_wgrad_kernel(const float* __restrict__ partial, int splits, int kpad, int npad,
-                                                           int H, int K, float* __restrict__ gW, float* __restrict__ gb,
-                                                           int accumulate) {
+// 8 (k) x 32 (n) outputs per 1024-thread block; 4 thread groups each sum a fixed quarter of the splits in fp64, the
+// quarters are combined in a fixed order (deterministic), then a transposing store through shared memory.
+constexpr int RW_GROUPS = 4;
+__global__ void __launch_bounds__(1024) reduce_wgrad_kernel(const float* __restrict__ partial, int splits, int kpad, int npad,
+                                                            int H, int K, float* __restrict__ gW, float* __restrict__ gb,
+                                                            int accumulate) {
+  __shared__ double part[RW_GROUPS][8][32];
   __shared__ float tile[8][33];
   const int k0 = blockIdx.x * 8, n0 = blockIdx.y * 32;
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int tx = threadIdx.x & 31, ty = (threadIdx.x >> 5) & 7, tz = threadIdx.x >> 8;
   const long long stride = (long long)kpad * npad;
   {
     const int k = k0 + ty, n = n0 + tx;
     double acc = 0.;
     if (k <= K && n < H) {
+      const int per = (splits + RW_GROUPS - 1) / RW_GROUPS;
+      const int s0 = tz * per, s1 = min(splits, s0 + per);
       const float* p = partial + (long long)k * npad + n;
-#pragma unroll 8
-      for (int s = 0; s < splits; ++s) acc += (double)__ldg(p + s * stride);
+#pragma unroll 4
+      for (int s = s0; s < s1; ++s) acc += (double)__ldg(p + s * stride);
     }
+    part[tz][ty][tx] = acc;
+  }
+  __syncthreads();
+  if (tz == 0) {
+    double acc = part[0][ty][tx];
+#pragma unroll
+    for (int g = 1; g < RW_GROUPS; ++g) acc += part[g][ty][tx];
     tile[ty][tx] = (float)acc;
   }
   __syncthreads();
-  {
-    // 256 threads -> 32 n x 8 k, k fastest so the stores to gW[n][k] run along k
+  if (threadIdx.x < 256) {
+    // 32 n x 8 k, k fastest so the stores to gW[n][k] run along k
     const int kk = threadIdx.x & 7, nn = threadIdx.x >> 3;
     const int n = n0 + nn, k = k0 + kk;
     if (n < H) {
@@ -252,12 +272,17 @@ extern "C" int fdsm_mlp_prepare(const fdsm_mlp_desc* desc, int64_t rows, const f
   if (rc) return rc;
   FDSM_REQUIRE(params && workspace, "fdsm_mlp_prepare: NULL pointer");
   cudaStream_t st = (cudaStream_t)stream;
+  mlp::PrepArgs a;
+  a.H = y.H; a.npad = y.npad;
+  int kmax = 0;
   for (int l = 0; l < y.L; ++l) {
-    const int K = l ? y.H : y.D, kp = l ? y.kpadh : y.kpad0;
-    dim3 grid((kp + 31) / 32, (y.npad + 31) / 32);
-    mlp::prep_weights_kernel<<<grid, 256, 0, st>>>(params + y.w_off[l], params + y.b_off[l], y.H, K, kp, y.npad,
-                                                   workspace + y.wt_hi[l], workspace + y.wt_lo[l]);
+    a.W[l] = params + y.w_off[l]; a.b[l] = params + y.b_off[l];
+    a.hi[l] = workspace + y.wt_hi[l]; a.lo[l] = workspace + y.wt_lo[l];
+    a.K[l] = l ? y.H : y.D; a.kpad[l] = l ? y.kpadh : y.kpad0;
+    if (a.kpad[l] > kmax) kmax = a.kpad[l];
   }
+  dim3 grid((kmax + 31) / 32, (y.npad + 31) / 32, y.L);
+  mlp::prep_weights_kernel<<<grid, 256, 0, st>>>(a);
   FDSM_LAUNCH_CHECK("fdsm_mlp_prepare");
 }
 
@@ -331,7 +356,7 @@ extern "C" int fdsm_mlp_backward(const fdsm_mlp_desc* desc, const float* x_hi, c
       rc = tc::launch_gemm(p, In, B, K + 1, y.npad, (int)rows, y.npad, y.passes, y.splits[l], st);
       if (rc) return rc;
       dim3 grid((K + 1 + 7) / 8, (y.H + 31) / 32);
-      mlp::reduce_wgrad_kernel<<<grid, 256, 0, st>>>(ws + y.partial, y.splits[l], kp, y.npad, y.H, K, grads + y.w_off[l],
+      mlp::reduce_wgrad_kernel<<<grid, 1024, 0, st>>>(ws + y.partial, y.splits[l], kp, y.npad, y.H, K, grads + y.w_off[l],
                                                      grads + y.b_off[l], accumulate);
       rc = cuda_status(cudaGetLastError(), "fdsm_mlp_backward(reduce)");
       if (rc) return rc;

@@ -7,29 +7,34 @@
 namespace fdsm {
 namespace {
 
-// single block, fixed summation order: bit-identical across ranks and runs
+// FDSM_SUMSQ_PARTIALS blocks, each over a fixed contiguous chunk, each with a fixed summation order: the partials (and
+// their fixed-order sum in adam_kernel) are bit-identical across ranks and runs.
+constexpr int kPartials = FDSM_SUMSQ_PARTIALS;
 __global__ void __launch_bounds__(1024) sumsq_kernel(const float* __restrict__ g, long long n, float* __restrict__ out,
                                                      long long* __restrict__ step) {
   __shared__ float red[32];
+  const long long chunk = ((n + kPartials - 1) / kPartials + 3) & ~3ll;
+  const long long lo = blockIdx.x * chunk, hi = lo + chunk < n ? lo + chunk : n;
   float acc = 0.f;
-  const long long n4 = n >> 2;
   if (aligned16(g)) {
-    for (long long i = threadIdx.x; i < n4; i += blockDim.x) {
-      const float4 v = __ldg(reinterpret_cast<const float4*>(g) + i);
+    const long long nv = hi > lo ? (hi - lo) >> 2 : 0;
+    const float4* g4 = reinterpret_cast<const float4*>(g + lo);
+    for (long long i = threadIdx.x; i < nv; i += blockDim.x) {
+      const float4 v = __ldg(g4 + i);
       acc += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
     }
-    for (long long i = (n4 << 2) + threadIdx.x; i < n; i += blockDim.x) acc += g[i] * g[i];
+    for (long long i = lo + (nv << 2) + threadIdx.x; i < hi; i += blockDim.x) acc += g[i] * g[i];
   } else {
-    for (long long i = threadIdx.x; i < n; i += blockDim.x) acc += g[i] * g[i];
+    for (long long i = lo + threadIdx.x; i < hi; i += blockDim.x) acc += g[i] * g[i];
   }
   acc = warp_sum(acc);
   if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
   __syncthreads();
   if (threadIdx.x == 0) {
     float s = 0.f;
-    for (int i = 0; i < 32; ++i) s += red[i];
-    *out = s;
-    if (step) *step += 1;
+    for (int i = 0; i < (int)(blockDim.x >> 5); ++i) s += red[i];
+    out[blockIdx.x] = s;
+    if (step && blockIdx.x == 0) *step += 1;
   }
 }
 
@@ -40,7 +45,11 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
   const float t = (float)__ldg(step);
   const float lrv = lr_dev ? __ldg(lr_dev) : lr;
   float coef = 1.f;
-  if (max_norm > 0.f) coef = fminf(max_norm / (sqrtf(__ldg(sumsq)) + 1e-6f), 1.f);
+  if (max_norm > 0.f) {
+    float ss = 0.f;
+    for (int i = 0; i < kPartials; ++i) ss += __ldg(sumsq + i);
+    coef = fminf(max_norm / (sqrtf(ss) + 1e-6f), 1.f);
+  }
   const float bc1 = 1.f - powf(b1, t), bc2s = sqrtf(1.f - powf(b2, t));
   const float step_size = lrv / bc1;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
@@ -60,7 +69,7 @@ using namespace fdsm;
 
 extern "C" int fdsm_grad_sumsq(const float* g, int64_t n, float* sumsq, int64_t* step_counter, fdsm_stream_t stream) {
   FDSM_REQUIRE(n >= 0 && sumsq && (g || n == 0), "fdsm_grad_sumsq: bad arguments");
-  sumsq_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(g, n, sumsq, (long long*)step_counter);
+  sumsq_kernel<<<kPartials, 256, 0, (cudaStream_t)stream>>>(g, n, sumsq, (long long*)step_counter);
   FDSM_LAUNCH_CHECK("fdsm_grad_sumsq");
 }
 

@@ -203,7 +203,7 @@ class FusedEnergyMLP(nn.Module):
         self._opt = dict(lr=float(lr), betas=(float(betas[0]), float(betas[1])), clip=float(clip) if clip else 0.0,
                          eps=float(adam_eps), use_graph=bool(use_graph), seed=int(seed), rank=int(rank),
                          m=torch.zeros_like(self.flat.data), v=torch.zeros_like(self.flat.data),
-                         sumsq=torch.zeros((), device=dev), step=torch.zeros((), device=dev, dtype=torch.int64),
+                         sumsq=torch.zeros(32, device=dev), step=torch.zeros((), device=dev, dtype=torch.int64),
                          lr_dev=torch.full((), float(lr), device=dev))
         self._graphs = {}
 

@@ -208,7 +208,9 @@ int fdsm_mlp_backward(const fdsm_mlp_desc* desc, const float* x_hi, const float*
  * clip_grad_norm_(params, clip) then Adam.step()).  Per-step scalars come from device memory so the
  * step replays from one CUDA graph.
  * ------------------------------------------------------------------------------------------ */
-/* sumsq[0] = sum g^2 (single block, fixed order: bit-identical on every rank); *step_counter += 1 if given. */
+/* sumsq[0..FDSM_SUMSQ_PARTIALS) = partial sums of g^2 over fixed contiguous chunks (fixed order: bit-identical on every
+ * rank); their sum is the squared norm.  *step_counter += 1 if given. */
+#define FDSM_SUMSQ_PARTIALS 32
 int fdsm_grad_sumsq(const float* g, int64_t n, float* sumsq, int64_t* step_counter, fdsm_stream_t stream);
 /* torch.optim.Adam semantics (no weight decay, no amsgrad) at t = *step_counter; gradient pre-scaled by
  * min(1, max_norm/(sqrt(sumsq)+1e-6)) when max_norm > 0; lr_dev (device scalar) overrides lr when non-NULL. */
