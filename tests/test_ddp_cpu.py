@@ -1,0 +1,103 @@
+"""World-size-2 `gloo` tests of the data-parallel host logic: batch sharding by rank, the
+positional sigma slice, the flat gradient bucket and the step's single all-reduce.  CPU only; the loss
+inside each rank is the oracle's FD-SSM restatement (checker role: the thing under test is ddp.py)."""
+import os
+import socket
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _make(seed=3, D=12, H=16):
+    torch.manual_seed(seed)
+    return torch.nn.Sequential(torch.nn.Linear(D, H), torch.nn.Softplus(), torch.nn.Linear(H, 1)).double()   # fp64: the FD loss cancels
+
+
+def _fd_loss(net, x, u, eps=0.1):
+    from oracle import fd_losses
+    v = fd_losses.sphere_direction(u, eps)
+    return fd_losses.fd_ssm(lambda z: net(z).view(-1), x, v, x.shape[1] / eps ** 2)
+
+
+def _worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import fdsm_b200  # noqa: F401
+        from fdsm_b200 import ddp
+        g = torch.Generator().manual_seed(11)
+        X, U = torch.randn(8, 12, generator=g).double(), torch.randn(8, 12, generator=g).double()
+        net = _make(seed=3 + rank)                 # ranks start different: the broadcast must fix that
+        flat = ddp.FlatParams(net)
+        ddp.broadcast_params_(flat.flat)
+        lo, hi = ddp.shard_range(8)
+        flat.zero_grad()
+        _fd_loss(net, X[lo:hi], U[lo:hi]).backward()
+        ddp.allreduce_mean_(flat.grad)
+        sig = ddp.shard_sigmas(torch.linspace(0.1, 0.8, 8))
+        q.put((rank, flat.flat.clone(), flat.grad.clone(), (lo, hi), sig.clone(), ddp.is_distributed()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(120)
+def test_two_rank_gloo_step_matches_single_process():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = sorted((q.get(timeout=100) for _ in range(2)), key=lambda t: t[0])
+    for p in procs:
+        p.join(30)
+        assert p.exitcode == 0
+    # single-process reference: full batch, rank 0's initial parameters
+    from fdsm_b200 import ddp
+    g = torch.Generator().manual_seed(11)
+    X, U = torch.randn(8, 12, generator=g).double(), torch.randn(8, 12, generator=g).double()
+    net = _make(seed=3)
+    flat = ddp.FlatParams(net)
+    flat.zero_grad()
+    _fd_loss(net, X, U).backward()
+    (r0, p0, g0, s0, sig0, d0), (r1, p1, g1, s1, sig1, d1) = got
+    assert d0 and d1
+    assert s0 == (0, 4) and s1 == (4, 8)
+    assert torch.equal(p0, p1) and torch.equal(p0, flat.flat)          # broadcast from rank 0
+    assert torch.equal(g0, g1)                                         # replicas see identical averaged grads
+    torch.testing.assert_close(g0, flat.grad, rtol=1e-9, atol=1e-11)    # mean of shard means == full-batch mean
+    assert torch.equal(sig0, torch.linspace(0.1, 0.8, 8)[:4]) and torch.equal(sig1, torch.linspace(0.1, 0.8, 8)[4:])
+
+
+def test_shard_range_rejects_ragged():
+    from fdsm_b200 import ddp
+    with pytest.raises(ValueError):
+        ddp.shard_range(10, rank=0, world=4)
+    assert ddp.shard_range(12, rank=2, world=4) == (6, 9)
+
+
+def test_flat_params_alignment_and_views():
+    from fdsm_b200 import ddp
+    net = _make(D=11, H=30)
+    before = [p.detach().clone() for p in net.parameters()]
+    flat = ddp.FlatParams(net)
+    assert all(o % 4 == 0 for o in flat.offsets)
+    for p, b in zip(net.parameters(), before):
+        assert torch.equal(p, b)
+    flat.flat.mul_(2.0)
+    for p, b in zip(net.parameters(), before):
+        assert torch.equal(p, 2 * b)          # parameters are views into the bucket
