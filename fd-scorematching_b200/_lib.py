@@ -37,6 +37,7 @@ class StackArgs(C.Structure):
         ("B", _i64), ("D", _i64),
         ("out_lo", _f32p),
         ("offset_dev", C.c_void_p),
+        ("pad_ones", _i32),
     ]
 
 
@@ -53,7 +54,8 @@ class GemmArgs(C.Structure):
 
 class MlpDesc(C.Structure):
     """Mirror of `fdsm_mlp_desc` (include/fdsm.h)."""
-    _fields_ = [("in_dim", _i32), ("hidden", _i32), ("n_hidden", _i32), ("act", _i32), ("head", _i32), ("passes", _i32)]
+    _fields_ = [("in_dim", _i32), ("hidden", _i32), ("n_hidden", _i32), ("act", _i32), ("head", _i32), ("passes", _i32),
+                ("presplit", _i32)]
 
 
 # name -> (restype, argtypes); must list every symbol include/fdsm.h declares
@@ -101,8 +103,8 @@ def load():
     for name, (res, args) in PROTOTYPES.items():
         fn = getattr(lib, name)  # AttributeError if the symbol is missing
         fn.restype, fn.argtypes = res, args
-    if lib.fdsm_version() != 2:
-        raise FdsmError(f"libfdsm ABI version {lib.fdsm_version()} != 2")
+    if lib.fdsm_version() != 3:
+        raise FdsmError(f"libfdsm ABI version {lib.fdsm_version()} != 3")
     _lib = lib
     return lib
 

@@ -25,13 +25,14 @@ inline long long round_up(long long x, long long m) { return (x + m - 1) / m * m
 
 struct Layout {
   int D, H, L, act, head, passes;
+  bool raw;            // presplit == 0 and passes == 3: plain fp32 activations, split inside the GEMMs
   long long rows;
   int npad;            // UMMA N of every hidden layer: ceil16(H)
   int kpad0, kpadh;    // padded augmented input widths: ceil32(D+1), ceil32(H+1)
   // parameter offsets
   long long w_off[16], b_off[16], head_off, n_params;
   // workspace offsets (floats)
-  long long wt_hi[16], wt_lo[16];
+  long long wt_hi[16], wt_lo[16], wt_raw[16];
   long long h_hi[16], h_lo[16];     // hidden activations 1..L-1 (hi/lo, ld kpadh)
   long long h_last;                 // H_L fp32 [rows x npad]
   long long dz_hi[2], dz_lo[2];     // ping-pong dZ hi/lo [rows x npad]
@@ -51,6 +52,8 @@ inline int make_layout(const fdsm_mlp_desc* d, long long rows, Layout& y) {
   FDSM_REQUIRE(d->passes == 1 || d->passes == 3, "fdsm_mlp: passes must be 1 or 3");
   FDSM_REQUIRE(rows >= 0 && rows < (1ll << 31), "fdsm_mlp: bad row count");
   y.D = d->in_dim; y.H = d->hidden; y.L = d->n_hidden; y.act = d->act; y.head = d->head; y.passes = d->passes;
+  y.raw = d->presplit == 0 && d->passes == 3;
+  FDSM_REQUIRE(d->presplit == 0 || d->presplit == 1, "fdsm_mlp: presplit must be 0 or 1");
   y.rows = rows;
   y.npad = (int)round_up(y.H, 16);
   y.kpad0 = (int)round_up(y.D + 1, 32);
@@ -72,6 +75,7 @@ inline int make_layout(const fdsm_mlp_desc* d, long long rows, Layout& y) {
     const int kp = l ? y.kpadh : y.kpad0;
     y.wt_hi[l] = take((long long)kp * y.npad);
     y.wt_lo[l] = take((long long)kp * y.npad);
+    y.wt_raw[l] = take((long long)kp * y.npad);
     // wgrad: M = K_l + 1 rows of dWt in tiles of 128, contraction over `rows` in k-blocks of 32
     const int mt = (int)((l ? y.H : y.D) + 1 + tc::BM - 1) / tc::BM;
     const long long kblocks = (rows + tc::BK - 1) / tc::BK;
@@ -102,7 +106,7 @@ inline int make_layout(const fdsm_mlp_desc* d, long long rows, Layout& y) {
 // ---- weight preparation: flat parameters -> augmented transposed TF32 hi/lo (all layers in one launch) ----------
 struct PrepArgs {
   const float* W[16]; const float* b[16];
-  float* hi[16]; float* lo[16];
+  float* hi[16]; float* lo[16]; float* raw[16];
   int K[16], kpad[16];
   int H, npad;
 };
@@ -133,6 +137,7 @@ __global__ void __launch_bounds__(256) prep_weights_kernel(const PrepArgs a) {
       ptx::tf32_split(tile[tx][i], hi, lo);
       a.hi[l][(long long)k * npad + n] = hi;
       a.lo[l][(long long)k * npad + n] = lo;
+      a.raw[l][(long long)k * npad + n] = tile[tx][i];
     }
   }
 }
@@ -180,8 +185,8 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(const float* __restrict__
     if (j < npad) {
       float hi, lo;
       ptx::tf32_split(dz, hi, lo);
-      dz_hi[r * npad + j] = hi;
-      dz_lo[r * npad + j] = lo;
+      dz_hi[r * npad + j] = dz_lo ? hi : dz;
+      if (dz_lo) dz_lo[r * npad + j] = lo;
     }
   }
   if (col) {
@@ -277,7 +282,7 @@ extern "C" int fdsm_mlp_prepare(const fdsm_mlp_desc* desc, int64_t rows, const f
   int kmax = 0;
   for (int l = 0; l < y.L; ++l) {
     a.W[l] = params + y.w_off[l]; a.b[l] = params + y.b_off[l];
-    a.hi[l] = workspace + y.wt_hi[l]; a.lo[l] = workspace + y.wt_lo[l];
+    a.hi[l] = workspace + y.wt_hi[l]; a.lo[l] = workspace + y.wt_lo[l]; a.raw[l] = workspace + y.wt_raw[l];
     a.K[l] = l ? y.H : y.D; a.kpad[l] = l ? y.kpadh : y.kpad0;
     if (a.kpad[l] > kmax) kmax = a.kpad[l];
   }
@@ -292,20 +297,22 @@ extern "C" int fdsm_mlp_forward(const fdsm_mlp_desc* desc, const float* x_hi, co
   int rc = mlp::make_layout(desc, rows, y);
   if (rc) return rc;
   if (rows == 0) return FDSM_OK;
-  FDSM_REQUIRE(x_hi && (x_lo || y.passes == 1) && params && workspace && energy, "fdsm_mlp_forward: NULL pointer");
+  FDSM_REQUIRE(x_hi && (x_lo || y.passes == 1 || y.raw) && params && workspace && energy, "fdsm_mlp_forward: NULL pointer");
+  auto lo = [&](float* q) -> float* { return y.raw ? nullptr : q; };
   cudaStream_t st = (cudaStream_t)stream;
   float* ws = workspace;
   for (int l = 0; l < y.L; ++l) {
     const bool last = l == y.L - 1;
     const int K = (l ? y.H : y.D) + 1;
-    tc::Operand A = l ? tc::Operand{ws + y.h_hi[l], ws + y.h_lo[l], y.kpadh, tc::MAJOR_K}
-                      : tc::Operand{x_hi, x_lo, y.kpad0, tc::MAJOR_K};
-    tc::Operand B{ws + y.wt_hi[l], ws + y.wt_lo[l], y.npad, tc::MAJOR_MN};
+    tc::Operand A = l ? tc::Operand{ws + y.h_hi[l], lo(ws + y.h_lo[l]), y.kpadh, tc::MAJOR_K}
+                      : tc::Operand{x_hi, y.raw ? nullptr : x_lo, y.kpad0, tc::MAJOR_K};
+    tc::Operand B = y.raw ? tc::Operand{ws + y.wt_raw[l], nullptr, y.npad, tc::MAJOR_MN}
+                          : tc::Operand{ws + y.wt_hi[l], ws + y.wt_lo[l], y.npad, tc::MAJOR_MN};
     tc::GemmParams p = {};
     p.act = y.act;
     if (!last) {
       p.epi = tc::EPI_ACT_SPLIT;
-      p.out_hi = ws + y.h_hi[l + 1]; p.out_lo = ws + y.h_lo[l + 1]; p.ldo = y.kpadh; p.out_cols = y.kpadh;
+      p.out_hi = ws + y.h_hi[l + 1]; p.out_lo = lo(ws + y.h_lo[l + 1]); p.ldo = y.kpadh; p.out_cols = y.kpadh;
     } else {
       p.epi = tc::EPI_HEAD;
       p.out_hi = ws + y.h_last; p.ldo = y.npad; p.out_cols = y.npad;
@@ -330,8 +337,9 @@ extern "C" int fdsm_mlp_backward(const fdsm_mlp_desc* desc, const float* x_hi, c
     if (!accumulate) return cuda_status(cudaMemsetAsync(grads, 0, y.n_params * sizeof(float), st), "fdsm_mlp_backward");
     return FDSM_OK;
   }
-  FDSM_REQUIRE(x_hi && (x_lo || y.passes == 1) && dE, "fdsm_mlp_backward: NULL pointer");
+  FDSM_REQUIRE(x_hi && (x_lo || y.passes == 1 || y.raw) && dE, "fdsm_mlp_backward: NULL pointer");
   float* ws = workspace;
+  auto lo = [&](float* q) -> float* { return y.raw ? nullptr : q; };
   const int head_n = (int)(y.n_params - y.head_off);
   double* hacc = reinterpret_cast<double*>(ws + y.head_acc);
   rc = cuda_status(cudaMemsetAsync(hacc, 0, head_n * sizeof(double), st), "fdsm_mlp_backward(memset)");
@@ -339,17 +347,17 @@ extern "C" int fdsm_mlp_backward(const fdsm_mlp_desc* desc, const float* x_hi, c
   int cur = 0;
   mlp::head_bwd_kernel<<<(unsigned)((rows + mlp::HB_ROWS - 1) / mlp::HB_ROWS), 256, 0, st>>>(
       ws + y.h_last, y.npad, dE, ws + y.l1, ws + y.l2, params + y.head_off, y.H, y.npad, rows, y.act, y.head,
-      ws + y.dz_hi[cur], ws + y.dz_lo[cur], hacc);
+      ws + y.dz_hi[cur], lo(ws + y.dz_lo[cur]), hacc);
   mlp::head_finish_kernel<<<(head_n + 255) / 256, 256, 0, st>>>(hacc, head_n, grads + y.head_off, accumulate);
   rc = cuda_status(cudaGetLastError(), "fdsm_mlp_backward(head)");
   if (rc) return rc;
   for (int l = y.L - 1; l >= 0; --l) {
     const int K = l ? y.H : y.D, kp = l ? y.kpadh : y.kpad0;
-    tc::Operand In = l ? tc::Operand{ws + y.h_hi[l], ws + y.h_lo[l], y.kpadh, tc::MAJOR_MN}
-                       : tc::Operand{x_hi, x_lo, y.kpad0, tc::MAJOR_MN};
+    tc::Operand In = l ? tc::Operand{ws + y.h_hi[l], lo(ws + y.h_lo[l]), y.kpadh, tc::MAJOR_MN}
+                       : tc::Operand{x_hi, y.raw ? nullptr : x_lo, y.kpad0, tc::MAJOR_MN};
     // ---- wgrad: dWt_l[K+1 x H] = In^T dZ_l, split-K partials then a fixed-order reduce ----------------
     {
-      tc::Operand B{ws + y.dz_hi[cur], ws + y.dz_lo[cur], y.npad, tc::MAJOR_MN};
+      tc::Operand B{ws + y.dz_hi[cur], lo(ws + y.dz_lo[cur]), y.npad, tc::MAJOR_MN};
       tc::GemmParams p = {};
       p.epi = tc::EPI_STORE;
       p.out_hi = ws + y.partial; p.ldo = y.npad; p.split_stride = (long long)kp * y.npad;
@@ -363,13 +371,14 @@ extern "C" int fdsm_mlp_backward(const fdsm_mlp_desc* desc, const float* x_hi, c
     }
     // ---- dgrad: dZ_{l-1} = (dZ_l W_l) * act'(H_{l-1})   (skipped for the input layer: x needs no gradient) ----
     if (l > 0) {
-      tc::Operand A{ws + y.dz_hi[cur], ws + y.dz_lo[cur], y.npad, tc::MAJOR_K};
-      tc::Operand B{ws + y.wt_hi[l], ws + y.wt_lo[l], y.npad, tc::MAJOR_K};    // rows k (K_l of them), contiguous n
+      tc::Operand A{ws + y.dz_hi[cur], lo(ws + y.dz_lo[cur]), y.npad, tc::MAJOR_K};
+      tc::Operand B = y.raw ? tc::Operand{ws + y.wt_raw[l], nullptr, y.npad, tc::MAJOR_K}   // rows k (K_l of them), contiguous n
+                            : tc::Operand{ws + y.wt_hi[l], ws + y.wt_lo[l], y.npad, tc::MAJOR_K};
       tc::GemmParams p = {};
       p.epi = tc::EPI_DACT_SPLIT;
       p.act = y.act;
-      p.out_hi = ws + y.dz_hi[cur ^ 1]; p.out_lo = ws + y.dz_lo[cur ^ 1]; p.ldo = y.npad; p.out_cols = y.npad;
-      p.aux_hi = ws + y.h_hi[l]; p.aux_lo = ws + y.h_lo[l]; p.ldaux = y.kpadh;
+      p.out_hi = ws + y.dz_hi[cur ^ 1]; p.out_lo = lo(ws + y.dz_lo[cur ^ 1]); p.ldo = y.npad; p.out_cols = y.npad;
+      p.aux_hi = ws + y.h_hi[l]; p.aux_lo = lo(ws + y.h_lo[l]); p.ldaux = y.kpadh;
       rc = tc::launch_gemm(p, A, B, (int)rows, K, y.npad, y.npad, y.passes, 1, st);
       if (rc) return rc;
       cur ^= 1;

@@ -175,12 +175,12 @@ __global__ void __launch_bounds__(kBlock) stack_kernel(fdsm_stack_args a) {
         for (int j = t; j < nchunk; j += G) emit(j, raw_direction<VEC>(a, b, j));
       }
     }
-    if (a.out_lo && active) {   // GEMM padding columns [D, ldout): ones column then zeros
+    if ((a.out_lo || a.pad_ones) && active) {   // GEMM padding columns [D, ldout): ones column then zeros
       for (int r = 0; r < nrows; ++r) {
         const int64_t row = (int64_t)r * a.B + b;
         for (int c = D + t; c < (int)a.ldout; c += G) {
           a.out[row * a.ldout + c] = c == D ? 1.f : 0.f;
-          a.out_lo[row * a.ldout + c] = 0.f;
+          if (a.out_lo) a.out_lo[row * a.ldout + c] = 0.f;
         }
       }
     }
@@ -236,7 +236,8 @@ extern "C" int fdsm_stack(const fdsm_stack_args* args, fdsm_stream_t stream) {
   FDSM_REQUIRE(!(a.sigma && a.noise) || a.ldnoise >= a.D, "fdsm_stack: ldnoise < D");
   FDSM_REQUIRE(!a.dot_out || a.sigma, "fdsm_stack: dot_out needs sigma (DSM noise)");
   FDSM_REQUIRE(!a.labels || a.sigma, "fdsm_stack: labels given without a sigma table");
-  FDSM_REQUIRE(!a.out_lo || (a.out && a.ldout > a.D), "fdsm_stack: out_lo needs out and ldout > D (room for the ones column)");
+  FDSM_REQUIRE(!(a.out_lo || a.pad_ones) || (a.out && a.ldout > a.D),
+               "fdsm_stack: out_lo / pad_ones need out and ldout > D (room for the ones column)");
 
   bool vec = (a.D % 4 == 0);
   auto ok = [&](const float* p, int64_t ld) { return !p || (aligned16(p) && ld % 4 == 0); };

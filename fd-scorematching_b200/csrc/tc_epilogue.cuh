@@ -106,11 +106,12 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, uint32_t tmem
         } else if (EPI == EPI_ACT_SPLIT && i == nvalid) {
           y = 1.f;   // bias column of the next layer's augmented input
         }
-        ptx::tf32_split(y, hi[i], lo[i]);
+        if (p.out_lo) ptx::tf32_split(y, hi[i], lo[i]);
+        else hi[i] = y;   // raw-operand pipeline: the consumer GEMM splits in shared memory
       }
       if (row_ok) {
         st8(p.out_hi + (long long)row * p.ldo + n0 + c, hi);
-        st8(p.out_lo + (long long)row * p.ldo + n0 + c, lo);
+        if (p.out_lo) st8(p.out_lo + (long long)row * p.ldo + n0 + c, lo);
       }
     }
   }

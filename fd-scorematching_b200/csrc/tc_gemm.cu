@@ -14,9 +14,10 @@ __global__ void __launch_bounds__(256) tf32_split_kernel(const float* __restrict
     const int c = (int)(i - r * out_cols);
     float x = 0.f;
     if (c < cols) x = __ldg(in + r * ldin + c);
-    else if (c == cols && ones_col) x = 1.f;
+    else if (c == cols && (ones_col & 1)) x = 1.f;
     float hi, lo;
     ptx::tf32_split(x, hi, lo);
+    if (ones_col & 2) hi = x;   // raw-operand format: padded fp32 copy
     out_hi[r * ldo + c] = hi;
     if (out_lo) out_lo[r * ldo + c] = lo;
   }
@@ -29,7 +30,8 @@ using namespace fdsm;
 
 extern "C" int fdsm_tf32_split(const float* in, int64_t ldin, int64_t rows, int64_t cols, float* out_hi, float* out_lo,
                                int64_t ldo, int64_t out_cols, int32_t ones_col, fdsm_stream_t stream) {
-  FDSM_REQUIRE(rows >= 0 && cols >= 0 && out_cols >= cols + (ones_col ? 1 : 0), "fdsm_tf32_split: bad shape");
+  FDSM_REQUIRE(rows >= 0 && cols >= 0 && out_cols >= cols + (ones_col & 1), "fdsm_tf32_split: bad shape");
+  FDSM_REQUIRE(!(ones_col & 2) || !out_lo, "fdsm_tf32_split: the raw (unrounded) format has no lo half");
   FDSM_REQUIRE(ldo >= out_cols && (cols == 0 || ldin >= cols), "fdsm_tf32_split: leading dimension too small");
   if (rows == 0 || out_cols == 0) return FDSM_OK;
   FDSM_REQUIRE((in || cols == 0) && out_hi, "fdsm_tf32_split: NULL pointer");

@@ -4,7 +4,7 @@
 
 #include <mutex>
 
-#include "tc_gemm.cuh"
+#include "tc_gemm_raw.cuh"
 
 namespace fdsm {
 namespace tc {
@@ -62,12 +62,14 @@ inline int launch_gemm(GemmParams& p, const Operand& A, const Operand& B, int M,
   FDSM_REQUIRE(passes == 1 || passes == 3, "tc_gemm: passes must be 1 or 3");
   FDSM_REQUIRE(M > 0 && N > 0 && K > 0, "tc_gemm: empty problem (M=%d N=%d K=%d)", M, N, K);
   FDSM_REQUIRE(BN % 16 == 0 && BN >= 16 && BN <= 256, "tc_gemm: BN=%d must be a multiple of 16 in [16, 256]", BN);
-  FDSM_REQUIRE(passes == 1 || (A.lo && B.lo), "tc_gemm: 3-pass mode needs the lo halves");
+  const bool raw = passes == 3 && !A.lo && !B.lo;   // plain fp32 operands: hi/lo split inside the kernel
+  FDSM_REQUIRE(passes == 1 || raw || (A.lo && B.lo),
+               "tc_gemm: 3-pass mode needs the lo halves of both operands, or of neither (in-kernel split)");
   const int kblocks = (K + BK - 1) / BK;
   FDSM_REQUIRE(splits >= 1 && splits <= kblocks, "tc_gemm: splits=%d must be in [1, %d]", splits, kblocks);
   p.M = M; p.N = N; p.K = K; p.BN = BN; p.a_major = A.major; p.b_major = B.major; p.passes = passes;
   int rc;
-  for (int h = 0; h < (passes == 3 ? 2 : 1); ++h) {
+  for (int h = 0; h < (passes == 3 && !raw ? 2 : 1); ++h) {
     CUtensorMap* ta = h ? &p.ta_lo : &p.ta_hi;
     CUtensorMap* tb = h ? &p.tb_lo : &p.tb_hi;
     if (A.major == MAJOR_K) rc = make_tmap(ta, h ? A.lo : A.hi, M, K, A.ld, BM, false, "tc_gemm A");
@@ -78,6 +80,25 @@ inline int launch_gemm(GemmParams& p, const Operand& A, const Operand& B, int M,
     if (rc) return rc;
   }
   dim3 grid((M + BM - 1) / BM, (N + BN - 1) / BN, splits);
+  if (raw) {
+    static std::once_flag once_raw;
+    std::call_once(once_raw, [] {
+#define FDSM_SET_SMEM_RAW(E) cudaFuncSetAttribute(gemm_raw_kernel<E>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 5 * 1024)
+      FDSM_SET_SMEM_RAW(EPI_STORE); FDSM_SET_SMEM_RAW(EPI_ACT_SPLIT); FDSM_SET_SMEM_RAW(EPI_HEAD); FDSM_SET_SMEM_RAW(EPI_DACT_SPLIT);
+#undef FDSM_SET_SMEM_RAW
+    });
+    p.slot_bytes = raw_slot_bytes(BN, B.major);
+    p.raw_slots = MAX_RAW_SLOTS;
+    while (p.raw_slots > 1 && raw_smem_total(p.raw_slots, p.slot_bytes) > 227 * 1024 - 5 * 1024) --p.raw_slots;
+    const int smem_raw = raw_smem_total(p.raw_slots, p.slot_bytes);
+    switch (p.epi) {
+      case EPI_STORE: gemm_raw_kernel<EPI_STORE><<<grid, kThreads, smem_raw, st>>>(p); break;
+      case EPI_ACT_SPLIT: gemm_raw_kernel<EPI_ACT_SPLIT><<<grid, kThreads, smem_raw, st>>>(p); break;
+      case EPI_HEAD: gemm_raw_kernel<EPI_HEAD><<<grid, kThreads, smem_raw, st>>>(p); break;
+      default: gemm_raw_kernel<EPI_DACT_SPLIT><<<grid, kThreads, smem_raw, st>>>(p); break;
+    }
+    FDSM_LAUNCH_CHECK("tc_gemm(raw)");
+  }
   const int smem = SmemLayout::total(passes);
   static std::once_flag once;
   std::call_once(once, [] {

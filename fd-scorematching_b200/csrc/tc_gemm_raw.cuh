@@ -1,0 +1,235 @@
+// Kernel (3), raw-operand flavour: the same 3xTF32 tcgen05 GEMM as tc_gemm.cuh, but the operands arrive as
+// PLAIN fp32 and the TF32 hi/lo split happens inside the kernel, in shared memory.
+//
+// Why: an SM ingests ~43-46 B/clk from L2 (B300_MICROARCH.md, "LTS throughput cap" / 148), and the pre-split
+// kernel moves hi AND lo of both operands through that port: 84 KB per k-block against 1248 clk of MMA work
+// (12 x 128x208x8 kind::tf32) -> load-bound at ~65 GB/s per SM (measured, profiles/r01_gemm_sweep.txt).  Loading
+// the fp32 value once halves the ingest (42 KB per k-block < the MMA time) and halves the HBM traffic of every
+// producer (stack kernel, activation epilogues).
+//
+// Pipeline (per k-block i; r = i % R raw slots, l = i % 2 lo slots):
+//   warp 0   TMA: waits raw_empty[r], loads raw A|B tiles into raw slot r (raw_full[r], expect-tx)
+//   warps 2-7 converters: wait raw_full[r] and lo_empty[l]; x -> hi = rna_tf32(x) rewritten IN PLACE, lo =
+//            rna_tf32(x - hi) into lo slot l (elementwise, so the TMA swizzle is irrelevant); fence.proxy.async;
+//            arrive conv[l]
+//   warp 1   MMA: waits conv[l]; hi*hi + hi*lo + lo*hi per UMMA_K; tcgen05.commit -> raw_empty[r], lo_empty[l]
+// Results are bit-identical to the pre-split kernel fed by ptx::tf32_split (same rounding, same MMA order).
+#pragma once
+#include "tc_gemm.cuh"
+
+namespace fdsm {
+namespace tc {
+
+constexpr int LO_SLOTS = 2;
+#ifndef FDSM_RAW_REWRITE_HI
+#define FDSM_RAW_REWRITE_HI 1
+#endif
+constexpr int CONV_WARP0 = 2;                       // warps [2, 8) convert
+constexpr int CONV_WARPS = kThreads / 32 - CONV_WARP0;
+constexpr int MAX_RAW_SLOTS = 4;
+
+__host__ __device__ inline int raw_b_tile_bytes(int BN, int b_major) {
+  return b_major == MAJOR_K ? BN * BK * 4 : ((BN + 31) / 32) * 32 * BK * 4;
+}
+__host__ __device__ inline int raw_slot_bytes(int BN, int b_major) {
+  return A_TILE_BYTES + ((raw_b_tile_bytes(BN, b_major) + 1023) & ~1023);
+}
+__host__ inline int raw_smem_total(int raw_slots, int slot_bytes) { return (raw_slots + LO_SLOTS) * slot_bytes + 1024 + 256; }
+
+template <int EPI>
+__global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_constant__ GemmParams p) {
+  using namespace ptx;
+  __shared__ float head_smem[EPI == EPI_HEAD ? 3 * HW_STRIDE : 1];
+  if constexpr (EPI == EPI_HEAD) {
+    const int nh = p.head_mode ? 3 : 1;
+    for (int i = threadIdx.x; i < nh * (p.N + 1); i += kThreads) head_smem[(i / (p.N + 1)) * HW_STRIDE + i % (p.N + 1)] = __ldg(p.head_w + i);
+  }
+  const int R = p.raw_slots;
+  const int SLOT = p.slot_bytes;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  uint8_t* gen = smem_raw + (base - raw);
+  const uint32_t lo_base = base + R * SLOT;
+  const uint32_t bars = base + (R + LO_SLOTS) * SLOT;
+  // barriers: raw_full[4] raw_empty[4] conv[2] lo_empty[2] tmem_full ; then the TMEM base pointer
+  auto raw_full = [&](int s) { return bars + 8u * s; };
+  auto raw_empty = [&](int s) { return bars + 8u * (MAX_RAW_SLOTS + s); };
+  auto conv_bar = [&](int s) { return bars + 8u * (2 * MAX_RAW_SLOTS + s); };
+  auto lo_empty = [&](int s) { return bars + 8u * (2 * MAX_RAW_SLOTS + LO_SLOTS + s); };
+  const uint32_t tmem_full_bar = bars + 8u * (2 * MAX_RAW_SLOTS + 2 * LO_SLOTS);
+  volatile uint32_t* tmem_ptr_smem =
+      reinterpret_cast<volatile uint32_t*>(gen + (R + LO_SLOTS) * SLOT + 8 * (2 * MAX_RAW_SLOTS + 2 * LO_SLOTS + 1));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * BM, n0 = blockIdx.y * p.BN;
+  const int kblocks = (p.K + BK - 1) / BK;
+  const int kb0 = (int)((long long)kblocks * blockIdx.z / gridDim.z);
+  const int kb1 = (int)((long long)kblocks * (blockIdx.z + 1) / gridDim.z);
+  const int b_bytes = raw_b_tile_bytes(p.BN, p.b_major);
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&p.ta_hi);
+    prefetch_tensormap(&p.tb_hi);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < MAX_RAW_SLOTS; ++s) {
+      mbar_init(raw_full(s), 1);
+      mbar_init(raw_empty(s), 1);
+    }
+    for (int s = 0; s < LO_SLOTS; ++s) {
+      mbar_init(conv_bar(s), CONV_WARPS);
+      mbar_init(lo_empty(s), 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc(smem_u32((const void*)tmem_ptr_smem), TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    // ===== TMA producer ===========================================================================
+    if (lane == 0) {
+      const int b_boxes_mn = (p.BN + 31) / 32;
+      const uint32_t tx = (uint32_t)(A_TILE_BYTES + b_bytes);
+      int r = 0;
+      uint32_t phase = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(raw_empty(r), phase ^ 1u);
+        const uint32_t a_dst = base + r * SLOT, b_dst = a_dst + A_TILE_BYTES;
+        const uint32_t fb = raw_full(r);
+        mbar_arrive_expect_tx(fb, tx);
+        const int k0 = kb * BK;
+        if (p.a_major == MAJOR_K) {
+          tma_load_2d(a_dst, &p.ta_hi, fb, k0, m0);
+        } else {
+          for (int i = 0; i < BM / 32; ++i) tma_load_2d(a_dst + i * 4096, &p.ta_hi, fb, m0 + 32 * i, k0);
+        }
+        if (p.b_major == MAJOR_K) {
+          tma_load_2d(b_dst, &p.tb_hi, fb, k0, n0);
+        } else {
+          for (int i = 0; i < b_boxes_mn; ++i) tma_load_2d(b_dst + i * 4096, &p.tb_hi, fb, n0 + 32 * i, k0);
+        }
+        if (++r == R) { r = 0; phase ^= 1u; }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (one thread) ================================================================
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_tf32(BM, p.BN, p.a_major, p.b_major);
+      const uint32_t a_lbo = p.a_major == MAJOR_K ? 16u : 4096u, b_lbo = p.b_major == MAJOR_K ? 16u : 4096u;
+      const uint32_t a_step = p.a_major == MAJOR_K ? 32u : 1024u, b_step = p.b_major == MAJOR_K ? 32u : 1024u;
+      const uint32_t a_sbo = p.a_major == MAJOR_K ? 1024u : 512u, b_sbo = p.b_major == MAJOR_K ? 1024u : 512u;
+      const uint32_t a_lay = p.a_major == MAJOR_K ? 2u : 1u, b_lay = p.b_major == MAJOR_K ? 2u : 1u;
+      int r = 0, l = 0;
+      uint32_t lphase = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(conv_bar(l), lphase);
+        tc_fence_after();
+        const uint32_t a_hi = base + r * SLOT, b_hi = a_hi + A_TILE_BYTES;
+        const uint32_t a_lo = lo_base + l * SLOT, b_lo = a_lo + A_TILE_BYTES;
+#pragma unroll
+        for (int k8 = 0; k8 < BK / UMMA_K; ++k8) {
+          const uint64_t dah = make_smem_desc(a_hi + k8 * a_step, a_lbo, a_sbo, a_lay);
+          const uint64_t dbh = make_smem_desc(b_hi + k8 * b_step, b_lbo, b_sbo, b_lay);
+          const uint64_t dal = make_smem_desc(a_lo + k8 * a_step, a_lbo, a_sbo, a_lay);
+          const uint64_t dbl = make_smem_desc(b_lo + k8 * b_step, b_lbo, b_sbo, b_lay);
+          mma_tf32_ss(tmem_base, dah, dbh, idesc, (kb > kb0 || k8 > 0) ? 1u : 0u);
+          mma_tf32_ss(tmem_base, dah, dbl, idesc, 1u);
+          mma_tf32_ss(tmem_base, dal, dbh, idesc, 1u);
+        }
+        tc_commit(raw_empty(r));
+        tc_commit(lo_empty(l));
+        if (kb == kb1 - 1) tc_commit(tmem_full_bar);
+        if (++r == R) r = 0;
+        if (++l == LO_SLOTS) { l = 0; lphase ^= 1u; }
+      }
+    }
+  } else {
+    // ===== converters (warps 2..7): raw fp32 -> TF32 hi (in place) + lo ==================================
+    const int ct = threadIdx.x - CONV_WARP0 * 32;
+    const int nvec = (A_TILE_BYTES + b_bytes) >> 4;   // A and B tiles are adjacent inside a slot
+    int r = 0, l = 0;
+    uint32_t rphase = 0, lphase = 0;
+    for (int kb = kb0; kb < kb1; ++kb) {
+      mbar_wait(raw_full(r), rphase);
+      mbar_wait(lo_empty(l), lphase ^ 1u);
+      float4* src = reinterpret_cast<float4*>(gen + r * SLOT);
+      float4* dst = reinterpret_cast<float4*>(gen + (R + l) * SLOT);
+      constexpr int CT = CONV_WARPS * 32, UNR = 4;
+      for (int i0 = ct; i0 < nvec; i0 += CT * UNR) {
+        float4 x[UNR];
+#pragma unroll
+        for (int u = 0; u < UNR; ++u)
+          if (i0 + u * CT < nvec) x[u] = src[i0 + u * CT];
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) {
+          if (i0 + u * CT < nvec) {
+            float4 hi, lo;
+#if FDSM_RAW_REWRITE_HI
+            tf32_split_alu(x[u].x, hi.x, lo.x); tf32_split_alu(x[u].y, hi.y, lo.y);
+            tf32_split_alu(x[u].z, hi.z, lo.z); tf32_split_alu(x[u].w, hi.w, lo.w);
+            src[i0 + u * CT] = hi;
+#else
+            // the tensor core ignores the 13 low mantissa bits of a kind::tf32 operand (truncation): the raw value
+            // already IS the hi half; lo = rna_tf32(x - trunc(x)), no write-back
+            tf32_split_trunc(x[u].x, hi.x, lo.x); tf32_split_trunc(x[u].y, hi.y, lo.y);
+            tf32_split_trunc(x[u].z, hi.z, lo.z); tf32_split_trunc(x[u].w, hi.w, lo.w);
+#endif
+            dst[i0 + u * CT] = lo;
+          }
+        }
+      }
+      fence_proxy_async();   // generic-proxy stores -> visible to the tensor core's async-proxy reads
+      __syncwarp();
+      if (lane == 0) mbar_arrive(conv_bar(l));
+      if (++r == R) { r = 0; rphase ^= 1u; }
+      if (++l == LO_SLOTS) { l = 0; lphase ^= 1u; }
+    }
+  }
+  __syncwarp();
+  {
+    // ===== epilogue: identical to gemm_kernel's ==========================================================
+    const int q = warp & 3;
+    const int half = warp >> 2;
+    const int row = m0 + q * 32 + lane;
+    const bool row_ok = row < p.M;
+    const bool have_acc = kb1 > kb0;
+    if (have_acc) {
+      mbar_wait(tmem_full_bar, 0);
+      tc_fence_after();
+    }
+    float l1 = 0.f, l2 = 0.f, lq = 0.f;
+    const bool last_tile = n0 + p.BN >= p.N;
+    const int ncols_out = (EPI == EPI_STORE || EPI == EPI_HEAD) ? min(p.N - n0, p.BN) : (last_tile ? p.out_cols - n0 : p.BN);
+    const int nsteps = (ncols_out + CW - 1) / CW, s0 = (nsteps + 1) / 2;
+    const int c_begin = half ? s0 * CW : 0, c_end = half ? nsteps * CW : s0 * CW;
+    epilogue_dispatch<EPI>(p, tmem_base + ((uint32_t)(q * 32) << 16), have_acc, row, row_ok, n0, c_begin, c_end, head_smem, l1,
+                           l2, lq);
+    if constexpr (EPI == EPI_HEAD) {
+      __shared__ float hsum[BM][3];
+      if (half == 1) { hsum[q * 32 + lane][0] = l1; hsum[q * 32 + lane][1] = l2; hsum[q * 32 + lane][2] = lq; }
+      __syncthreads();
+      if (half == 0 && row_ok) {
+        l1 += hsum[q * 32 + lane][0] + head_smem[p.N];
+        l2 += hsum[q * 32 + lane][1] + (p.head_mode ? head_smem[HW_STRIDE + p.N] : 0.f);
+        lq += hsum[q * 32 + lane][2] + (p.head_mode ? head_smem[2 * HW_STRIDE + p.N] : 0.f);
+        p.e_out[row] = p.head_mode ? fmaf(l1, l2, lq) : l1;
+        p.l1_out[row] = l1;
+        p.l2_out[row] = l2;
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+}  // namespace tc
+}  // namespace fdsm

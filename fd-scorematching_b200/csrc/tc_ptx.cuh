@@ -133,6 +133,18 @@ __device__ __forceinline__ float tf32_rn(float x) {
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
   return __uint_as_float(r);
 }
+// The same split on the integer pipe (cvt.rna.tf32 issues at a fraction of the ALU rate): round-to-nearest, ties
+// away from zero, on the 13 dropped mantissa bits == add half an ulp to the magnitude bits and mask.  Bit-identical
+// to tf32_split for finite inputs.
+__device__ __forceinline__ float tf32_rn_alu(float x) { return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u); }
+__device__ __forceinline__ void tf32_split_alu(float x, float& hi, float& lo) {
+  hi = tf32_rn_alu(x);
+  lo = tf32_rn_alu(x - hi);
+}
+__device__ __forceinline__ void tf32_split_trunc(float x, float& hi, float& lo) {
+  hi = __uint_as_float(__float_as_uint(x) & 0xFFFFE000u);
+  lo = tf32_rn_alu(x - hi);
+}
 __device__ __forceinline__ void tf32_split(float x, float& hi, float& lo) {
   hi = tf32_rn(x);
   lo = tf32_rn(x - hi);

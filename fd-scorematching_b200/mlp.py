@@ -45,14 +45,14 @@ class _MlpFunction(torch.autograd.Function):
         lib = _lib.load()
         rows = x2.shape[0]
         sz = net.sizes(rows)
-        xh, xl = ops.tf32_split(x2, out_cols=sz.in_ld, ones_col=True)
+        xh, xl = ops.tf32_split(x2, out_cols=sz.in_ld, ones_col=True, raw=not net.presplit)
         ws = torch.empty(sz.workspace, device=x2.device, dtype=torch.float32)
         E = torch.empty(rows, device=x2.device, dtype=torch.float32)
         d = net.desc
         ops._count(net.n_hidden); check(lib.fdsm_mlp_prepare(C.byref(d), rows, _ptr(flat), _ptr(ws), _stream()), "fdsm_mlp_prepare")
         ops._count(net.n_hidden); check(lib.fdsm_mlp_forward(C.byref(d), _ptr(xh), _ptr(xl), rows, _ptr(flat), _ptr(ws), _ptr(E),
                                                            _stream()), "fdsm_mlp_forward")
-        ctx.save_for_backward(flat, xh, xl, ws)
+        ctx.save_for_backward(flat, xh, xl if xl is not None else xh.new_empty(0), ws)
         ctx.net, ctx.rows = net, rows
         return E
 
@@ -60,6 +60,7 @@ class _MlpFunction(torch.autograd.Function):
     def backward(ctx, dE):
         lib = _lib.load()
         flat, xh, xl, ws = ctx.saved_tensors
+        xl = xl if xl.numel() else None
         net, rows = ctx.net, ctx.rows
         dE = dE.contiguous().float()
         g = torch.empty_like(flat)
@@ -70,14 +71,18 @@ class _MlpFunction(torch.autograd.Function):
 
 
 class FusedEnergyMLP(nn.Module):
-    def __init__(self, in_dim, hidden, n_hidden=3, act="nsoftplus", head="quadratic", device="cuda", seed=None, passes=3):
+    def __init__(self, in_dim, hidden, n_hidden=3, act="nsoftplus", head="quadratic", device="cuda", seed=None, passes=3,
+                 presplit=False):
         super().__init__()
         if act not in ACTS:
             raise ValueError(f"act must be one of {sorted(ACTS)}")
         if head not in ("quadratic", "linear"):
             raise ValueError("head must be 'quadratic' or 'linear'")
         self.in_dim, self.hidden, self.n_hidden, self.act, self.head, self.passes = in_dim, hidden, n_hidden, act, head, passes
-        self.desc = MlpDesc(in_dim, hidden, n_hidden, ACTS[act], 1 if head == "quadratic" else 0, passes)
+        # presplit=False: activations stay plain fp32 in HBM, the GEMMs split into TF32 hi/lo in shared memory;
+        # presplit=True: hi/lo halves are materialised in HBM by the producing kernels (twice the traffic)
+        self.presplit = bool(presplit) or passes != 3
+        self.desc = MlpDesc(in_dim, hidden, n_hidden, ACTS[act], 1 if head == "quadratic" else 0, passes, int(self.presplit))
         self._sizes = {}
         n = self.sizes(0).n_params
         self.flat = nn.Parameter(torch.zeros(n, device=device, dtype=torch.float32))
@@ -152,7 +157,7 @@ class FusedEnergyMLP(nn.Module):
             sz = self.sizes(rows)
             f = dict(device=device, dtype=torch.float32)
             st = dict(B=B, rows=rows, sz=sz,
-                      xh=torch.empty(rows, sz.in_ld, **f), xl=torch.empty(rows, sz.in_ld, **f),
+                      xh=torch.empty(rows, sz.in_ld, **f), xl=torch.empty(rows, sz.in_ld, **f) if self.presplit else None,
                       ws=torch.empty(sz.workspace, **f), E=torch.empty(rows, **f), dE=torch.empty(rows, **f),
                       loss=torch.zeros((), **f), grad=torch.zeros(sz.n_params, **f))
             self._step_state = st
@@ -168,10 +173,11 @@ class FusedEnergyMLP(nn.Module):
         st = self._state(B, x2.device)
         rows, d = st["rows"], self.desc
         if v is not None:
-            ops.stack(x2, row_mask=7, scale=1.0, direction=v.reshape(B, -1), normalize=False, out=st["xh"], out_lo=st["xl"])
+            ops.stack(x2, row_mask=7, scale=1.0, direction=v.reshape(B, -1), normalize=False, out=st["xh"], out_lo=st["xl"],
+                      pad_ones=not self.presplit)
         else:
             ops.stack(x2, row_mask=7, scale=eps, direction=None if u is None else u.reshape(B, -1), normalize=True,
-                      out=st["xh"], out_lo=st["xl"], draw=draw, offset_dev=offset_dev)
+                      out=st["xh"], out_lo=st["xl"], draw=draw, offset_dev=offset_dev, pad_ones=not self.presplit)
         s = _stream()
         flat = self.flat.data
         ops._count(self.n_hidden); check(lib.fdsm_mlp_prepare(C.byref(d), rows, _ptr(flat), _ptr(st["ws"]), s), "fdsm_mlp_prepare")

@@ -85,7 +85,8 @@ def next_draw():
 # kernels (1)+(2)
 # --------------------------------------------------------------------------------------------
 def stack(x, *, row_mask, scale, direction=None, normalize=True, noise=None, sigma=None, labels=None,
-          perturb=True, dot_mode=0, want_v=False, want_dot=False, draw=None, out=None, out_lo=None, offset_dev=None):
+          perturb=True, dot_mode=0, want_v=False, want_dot=False, draw=None, out=None, out_lo=None, offset_dev=None,
+          pad_ones=False):
     """Fused direction sampling + normalisation + stacked-batch build (fdsm_stack).
 
     x: (B, D) fp32 CUDA.  Returns (stacked (rows*B, D) | None, v (B, D) | None, dot (B,) | None)."""
@@ -131,6 +132,7 @@ def stack(x, *, row_mask, scale, direction=None, normalize=True, noise=None, sig
             if out_lo.shape != out.shape or out_lo.stride() != out.stride():
                 raise ValueError("out_lo must have the shape and strides of out")
             a.out_lo = _ptr(out_lo)
+        a.pad_ones = int(bool(pad_ones))
     a.row_mask = row_mask
     v = dot = None
     if want_v:
@@ -283,16 +285,17 @@ def combine_score_fused(s2d, v, *, k, sigma=None, labels=None, power=2.0, projec
 # --------------------------------------------------------------------------------------------
 # kernel (3) building blocks: TF32 hi/lo split and the tcgen05 GEMM
 # --------------------------------------------------------------------------------------------
-def tf32_split(x, out_cols=None, ones_col=False, want_lo=True):
+def tf32_split(x, out_cols=None, ones_col=False, want_lo=True, raw=False):
     """(hi, lo) with x = hi + lo, both TF32-representable; rows padded to `out_cols` columns (multiple of 4),
-    column x.shape[1] set to 1 when `ones_col` (bias column of an augmented operand)."""
+    column x.shape[1] set to 1 when `ones_col` (bias column of an augmented operand).  raw=True: (padded fp32 copy, None) --
+    the operand format of the in-kernel-split GEMMs."""
     lib = _lib.load()
     x, ldx = _rows(_req(x, "x"), "x")
     R, Cc = x.shape
     oc = out_cols if out_cols is not None else (Cc + int(ones_col) + 3) // 4 * 4
     hi = torch.empty((R, oc), device=x.device, dtype=torch.float32)
-    lo = torch.empty((R, oc), device=x.device, dtype=torch.float32) if want_lo else None
-    _count(1); check(lib.fdsm_tf32_split(_ptr(x), ldx, R, Cc, _ptr(hi), _ptr(lo), oc, oc, int(ones_col), _stream()),
+    lo = torch.empty((R, oc), device=x.device, dtype=torch.float32) if (want_lo and not raw) else None
+    _count(1); check(lib.fdsm_tf32_split(_ptr(x), ldx, R, Cc, _ptr(hi), _ptr(lo), oc, oc, int(ones_col) | (2 if raw else 0), _stream()),
                      "fdsm_tf32_split")
     return hi, lo
 

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define FDSM_ABI_VERSION 2
+#define FDSM_ABI_VERSION 3
 
 #define FDSM_OK 0
 #define FDSM_ERR_INVALID_ARGUMENT (-1)
@@ -85,6 +85,8 @@ typedef struct fdsm_stack_args {
                             column D = 1 (folded bias), the rest 0 -- the operand format of fdsm_mlp_forward      */
   const uint64_t* offset_dev; /* optional DEVICE counter added to `offset` at run time (e.g. the optimizer step
                             counter), so a captured CUDA graph draws fresh directions on every replay             */
+  int32_t pad_ones;      /* 1 (with out_lo == NULL): `out` rows are plain fp32 but columns [D, ldout) still get the GEMM
+                            padding (column D = 1, rest 0): the operand format of fdsm_mlp_forward with presplit = 0 */
 } fdsm_stack_args;
 
 int fdsm_stack(const fdsm_stack_args* args, fdsm_stream_t stream);
@@ -144,8 +146,10 @@ int fdsm_combine_score(const float* s, int64_t lds, const float* v, int64_t ldv,
  * kind: operands are pre-split x = hi + lo (both TF32-representable) and passes=3 issues
  * hi*hi + hi*lo + lo*hi per k-step (fp32-grade products, fp32 accumulation in TMEM).
  * ------------------------------------------------------------------------------------------ */
-/* out_hi/out_lo[r,c] = split(in[r,c]) (c < cols); column `cols` := 1 if ones_col (bias column of an
- * augmented operand) ; remaining columns up to out_cols := 0.  out_lo may be NULL (hi only). */
+/* out_hi/out_lo[r,c] = split(in[r,c]) (c < cols); column `cols` := 1 if (ones_col & 1) (bias column of an
+ * augmented operand) ; remaining columns up to out_cols := 0.  out_lo may be NULL (hi only).
+ * ones_col & 2: no rounding -- out_hi receives the fp32 value itself (padded copy; out_lo must be NULL): the
+ * raw-operand format of the in-kernel-split GEMM. */
 int fdsm_tf32_split(const float* in, int64_t ldin, int64_t rows, int64_t cols, float* out_hi, float* out_lo,
                     int64_t ldo, int64_t out_cols, int32_t ones_col, fdsm_stream_t stream);
 
@@ -156,7 +160,8 @@ typedef struct fdsm_gemm_args {
   const float* a_hi; const float* a_lo; int64_t lda; int32_t a_major;
   const float* b_hi; const float* b_lo; int64_t ldb; int32_t b_major;
   int64_t M, N, K;
-  int32_t passes;        /* 1: hi*hi (plain TF32) ; 3: 3xTF32                                      */
+  int32_t passes;        /* 1: hi*hi (plain TF32) ; 3: 3xTF32.  passes = 3 with a_lo == b_lo == NULL: the operands
+                            are plain fp32 and the hi/lo split happens inside the kernel (shared memory)            */
   int32_t splits;        /* split-K: partial s is written at out + s*split_stride (caller reduces) */
   int32_t tile_n;        /* UMMA N (multiple of 16, <= 256); 0 = auto                              */
   float* out; int64_t ldo; int64_t split_stride;
@@ -177,7 +182,7 @@ int fdsm_tc_gemm(const fdsm_gemm_args* args, fdsm_stream_t stream);
  * ln2.weight[H], ln2.bias, lq.weight[H], lq.bias -- or out.weight[H], out.bias for head = 0).
  * The input rows arrive as the TF32 hi/lo halves of the augmented batch [rows x in_ld]
  * (column in_dim = 1, the folded bias; remaining padding 0): exactly what fdsm_stack writes when
- * `out_lo` is set.  All scratch lives in the caller's workspace.
+ * `out_lo` is set -- or, with presplit = 0, as the plain fp32 rows fdsm_stack writes with `pad_ones`.  All scratch lives in the caller's workspace.
  * ------------------------------------------------------------------------------------------ */
 typedef struct fdsm_mlp_desc {
   int32_t in_dim;    /* D                                                         */
@@ -186,6 +191,9 @@ typedef struct fdsm_mlp_desc {
   int32_t act;       /* 1 softplus, 2 softplus - ln2 (NormalizedSoftplus), 3 ELU  */
   int32_t head;      /* 1 quadratic head, 0 Linear(H,1)                           */
   int32_t passes;    /* 3 = 3xTF32 (fp32-grade), 1 = plain TF32                   */
+  int32_t presplit;  /* 0 (default): activations travel through HBM as plain fp32 and every GEMM splits its operands
+                        into TF32 hi/lo in shared memory (x_lo ignored, may be NULL; x_hi = the fp32 rows);
+                        1: activations are stored pre-split (x_hi/x_lo both required), twice the HBM traffic  */
 } fdsm_mlp_desc;
 
 /* Sizes for `rows` stacked input rows: parameter count, workspace floats, padded input leading dim. */

@@ -16,10 +16,10 @@ def _relv(a, b):
     return float((a - b).norm() / b.norm().clamp_min(1e-300))
 
 
-def _pair(fdsm, D, H, L, act, head, seed=0):
+def _pair(fdsm, D, H, L, act, head, seed=0, presplit=False):
     ref = nets.QuadraticMLP(D, H, L, act) if head == "quadratic" else nets.SoftplusMLP(D, H)
     nets.init_from_numpy(ref, seed)
-    net = fdsm.mlp.FusedEnergyMLP(D, H, L, act=act, head=head, device=DEV)
+    net = fdsm.mlp.FusedEnergyMLP(D, H, L, act=act, head=head, device=DEV, presplit=presplit)
     net.load_reference_state_dict([p.detach().float() for p in ref.parameters()])
     return net, ref.double()
 
@@ -28,9 +28,11 @@ def _pair(fdsm, D, H, L, act, head, seed=0):
     (64, 48, 3, "nsoftplus", "quadratic", 96), (11, 128, 2, "softplus", "linear", 192), (11, 30, 2, "softplus", "linear", 7),
     (100, 40, 3, "elu", "quadratic", 48), (784, 200, 3, "nsoftplus", "quadratic", 3 * 256), (784, 200, 3, "elu", "quadratic", 130),
     (20, 256, 1, "softplus", "quadratic", 33)])
-def test_forward_backward_match_fp64(fdsm, D, H, L, act, head, rows):
-    """3xTF32 GEMMs + fused epilogues vs fp64 autograd: energies 5e-6, flat parameter gradient 1e-5 (fp32 SGEMM grade)."""
-    net, ref = _pair(fdsm, D, H, L, act, head)
+@pytest.mark.parametrize("presplit", [False, True])
+def test_forward_backward_match_fp64(fdsm, D, H, L, act, head, rows, presplit):
+    """3xTF32 GEMMs + fused epilogues vs fp64 autograd: energies 5e-6, flat parameter gradient 1e-5 (fp32 SGEMM grade).
+    presplit=False: fp32 activations in HBM, hi/lo split inside the GEMMs; True: hi/lo halves materialised in HBM."""
+    net, ref = _pair(fdsm, D, H, L, act, head, presplit=presplit)
     x = nets.np_rand(1, rows, D)
     g = nets.np_randn(2, rows)
     E = net(x.float().to(DEV))

@@ -9,14 +9,17 @@ pytestmark = pytest.mark.gpu
 TOL = {1: 2e-3, 3: 3e-6}   # max |D - ref| / (|a_m| |b_n|): TF32 (10-bit mantissa) vs 3xTF32 (~fp32)
 
 
-def _run(fdsm, M, N, K, am, bm, passes, splits=1, tile_n=0, seed=0):
+def _run(fdsm, M, N, K, am, bm, passes, splits=1, tile_n=0, seed=0, raw=False, want_out=False):
     dev = torch.device("cuda:0")
     g = torch.Generator(device=dev).manual_seed(seed)
     A = torch.randn(M, K, device=dev, generator=g)
     B = torch.randn(N, K, device=dev, generator=g)
-    ah, al = fdsm.ops.tf32_split(A if am == 0 else A.t().contiguous())
-    bh, bl = fdsm.ops.tf32_split(B if bm == 0 else B.t().contiguous())
+    # raw=True: plain fp32 operands (padded copy), hi/lo split inside the kernel
+    ah, al = fdsm.ops.tf32_split(A if am == 0 else A.t().contiguous(), raw=raw)
+    bh, bl = fdsm.ops.tf32_split(B if bm == 0 else B.t().contiguous(), raw=raw)
     out = fdsm.ops.tc_gemm(ah, al, bh, bl, M, N, K, a_major=am, b_major=bm, passes=passes, splits=splits, tile_n=tile_n)
+    if want_out:
+        return out
     D = out.double().sum(0)
     ref = A.double() @ B.double().t()
     scale = A.double().norm(dim=1)[:, None] * B.double().norm(dim=1)[None, :]
@@ -28,6 +31,24 @@ def _run(fdsm, M, N, K, am, bm, passes, splits=1, tile_n=0, seed=0):
 @pytest.mark.parametrize("M,N,K", [(128, 16, 32), (128, 208, 64), (300, 200, 224), (77, 100, 45 * 4)])
 def test_gemm_matches_fp64(fdsm, am, bm, passes, M, N, K):
     assert _run(fdsm, M, N, K, am, bm, passes) < TOL[passes]
+
+
+@pytest.mark.parametrize("am,bm", [(0, 0), (0, 1), (1, 1), (1, 0)])
+@pytest.mark.parametrize("M,N,K", [(128, 16, 32), (128, 208, 64), (300, 200, 224), (77, 100, 45 * 4), (256, 256, 32 * 9)])
+def test_raw_operand_gemm_matches_fp64_and_presplit(fdsm, am, bm, M, N, K):
+    """In-kernel hi/lo split (shared-memory converter warps): fp32-grade vs fp64, and the same bits as the pre-split
+    kernel (same rounding, same MMA order)."""
+    assert _run(fdsm, M, N, K, am, bm, 3, raw=True) < TOL[3]
+    a = _run(fdsm, M, N, K, am, bm, 3, raw=True, want_out=True)
+    b = _run(fdsm, M, N, K, am, bm, 3, raw=False, want_out=True)
+    assert torch.equal(a, b)
+
+
+def test_raw_operand_gemm_config_shapes(fdsm):
+    assert _run(fdsm, 12288, 200, 800, 0, 1, 3, raw=True) < TOL[3]
+    assert _run(fdsm, 12288, 200, 208, 0, 0, 3, raw=True) < TOL[3]
+    assert _run(fdsm, 800, 200, 12288, 1, 1, 3, splits=21, raw=True) < TOL[3]
+    assert _run(fdsm, 201, 200, 12288, 1, 1, 3, splits=74, raw=True) < TOL[3]
 
 
 def test_gemm_split_k_and_config_shapes(fdsm):
@@ -53,6 +74,6 @@ def test_gemm_argument_errors(fdsm):
     dev = torch.device("cuda:0")
     a = torch.zeros(128, 32, device=dev)
     with pytest.raises(fdsm._lib.FdsmError):
-        fdsm.ops.tc_gemm(a, None, a, None, 128, 128, 32, passes=3)          # 3-pass needs lo halves
+        fdsm.ops.tc_gemm(a, a, a, None, 128, 128, 32, passes=3)             # lo halves: both operands or neither
     with pytest.raises(fdsm._lib.FdsmError):
         fdsm.ops.tc_gemm(a, a, a, a, 128, 128, 32, passes=3, splits=5)     # more splits than k-blocks
