@@ -35,10 +35,11 @@ struct Layout {
   long long wt_hi[16], wt_lo[16], wt_raw[16];
   long long h_hi[16], h_lo[16];     // hidden activations 1..L-1 (hi/lo, ld kpadh)
   long long h_last;                 // H_L fp32 [rows x npad]
-  long long dz_hi[2], dz_lo[2];     // ping-pong dZ hi/lo [rows x npad]
+  long long dz_hi[16], dz_lo[16];   // dZ_l per layer [rows x npad] (lo only in presplit mode): wgrad_l runs on a side
+                                    // stream while dgrad_l..1 continue, so the buffers are not recycled
   long long l1, l2;                 // per-row head dot products
   long long head_acc;               // fp64 accumulators of the head-parameter gradients (3(H+1) doubles)
-  long long partial;                // split-K partials
+  long long partial[2];             // split-K partials: [0] input layer (main stream), [1] hidden layers (side stream)
   long long total;
   int splits[16];
 };
@@ -70,7 +71,7 @@ inline int make_layout(const fdsm_mlp_desc* d, long long rows, Layout& y) {
   // workspace
   long long w = 0;
   auto take = [&](long long n) { long long r = w; w += round_up(n, 64); return r; };   // 256-byte aligned sections
-  long long max_partial = 0;
+  long long max_partial[2] = {0, 0};
   for (int l = 0; l < y.L; ++l) {
     const int kp = l ? y.kpadh : y.kpad0;
     y.wt_hi[l] = take((long long)kp * y.npad);
@@ -84,21 +85,22 @@ inline int make_layout(const fdsm_mlp_desc* d, long long rows, Layout& y) {
     if (s < 1) s = 1;
     y.splits[l] = (int)s;
     const long long ps = s * (long long)kp * y.npad;
-    if (ps > max_partial) max_partial = ps;
+    if (ps > max_partial[l ? 1 : 0]) max_partial[l ? 1 : 0] = ps;
   }
   for (int l = 1; l < y.L; ++l) {
     y.h_hi[l] = take(rows * y.kpadh);
     y.h_lo[l] = take(rows * y.kpadh);
   }
   y.h_last = take(rows * y.npad);
-  for (int i = 0; i < 2; ++i) {
-    y.dz_hi[i] = take(rows * y.npad);
-    y.dz_lo[i] = take(rows * y.npad);
+  for (int l = 0; l < y.L; ++l) {   // dZ_l = dL/d(pre-activation of layer l)
+    y.dz_hi[l] = take(rows * y.npad);
+    y.dz_lo[l] = y.raw ? y.dz_hi[l] : take(rows * y.npad);
   }
   y.l1 = take(rows);
   y.l2 = take(rows);
   y.head_acc = take(2ll * 3 * (y.H + 1));
-  y.partial = take(max_partial);
+  y.partial[0] = take(max_partial[0]);
+  y.partial[1] = take(max_partial[1]);
   y.total = w;
   return FDSM_OK;
 }
@@ -253,6 +255,25 @@ __global__ void __launch_bounds__(1024) reduce_wgrad_kernel(const float* __restr
   }
 }
 
+// Per-host-thread side stream + fork/join events (created once, never destroyed; no device memory involved).
+struct SideStream {
+  cudaStream_t stream = nullptr;
+  cudaEvent_t fork[2] = {nullptr, nullptr}, join = nullptr;
+  bool ok() const { return stream && fork[0] && fork[1] && join; }
+};
+inline SideStream& side_stream() {
+  static thread_local SideStream s;
+  static thread_local bool tried = false;
+  if (!tried) {
+    tried = true;
+    if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess) s.stream = nullptr;
+    for (auto* e : {&s.fork[0], &s.fork[1], &s.join})
+      if (cudaEventCreateWithFlags(e, cudaEventDisableTiming) != cudaSuccess) *e = nullptr;
+    (void)cudaGetLastError();
+  }
+  return s;
+}
+
 }  // namespace mlp
 }  // namespace fdsm
 
@@ -344,45 +365,62 @@ extern "C" int fdsm_mlp_backward(const fdsm_mlp_desc* desc, const float* x_hi, c
   double* hacc = reinterpret_cast<double*>(ws + y.head_acc);
   rc = cuda_status(cudaMemsetAsync(hacc, 0, head_n * sizeof(double), st), "fdsm_mlp_backward(memset)");
   if (rc) return rc;
-  int cur = 0;
+  // Two streams: the critical chain head_bwd -> dgrad_{L-1} -> ... -> dgrad_1 -> wgrad_0 stays on `stream`; the hidden
+  // layers' weight gradients (wgrad_l + reduce_l, l >= 1) only need dZ_l and run on a side stream, filling the SMs the
+  // 96-CTA dgrad launches leave idle and hiding their launch/fill/drain latencies.  Fork/join by events: capturable.
+  mlp::SideStream& side = mlp::side_stream();
+  const bool forked = y.L > 1 && side.ok();
+  cudaStream_t sd = forked ? side.stream : st;
+  const int L1 = y.L - 1;
   mlp::head_bwd_kernel<<<(unsigned)((rows + mlp::HB_ROWS - 1) / mlp::HB_ROWS), 256, 0, st>>>(
       ws + y.h_last, y.npad, dE, ws + y.l1, ws + y.l2, params + y.head_off, y.H, y.npad, rows, y.act, y.head,
-      ws + y.dz_hi[cur], lo(ws + y.dz_lo[cur]), hacc);
+      ws + y.dz_hi[L1], lo(ws + y.dz_lo[L1]), hacc);
   mlp::head_finish_kernel<<<(head_n + 255) / 256, 256, 0, st>>>(hacc, head_n, grads + y.head_off, accumulate);
   rc = cuda_status(cudaGetLastError(), "fdsm_mlp_backward(head)");
   if (rc) return rc;
-  for (int l = y.L - 1; l >= 0; --l) {
+  auto wgrad = [&](int l, cudaStream_t s) -> int {
+    // dWt_l[K+1 x H] = In_l^T dZ_l: split-K partials, then a fixed-order reduce + transpose into the flat gradient
     const int K = l ? y.H : y.D, kp = l ? y.kpadh : y.kpad0;
     tc::Operand In = l ? tc::Operand{ws + y.h_hi[l], lo(ws + y.h_lo[l]), y.kpadh, tc::MAJOR_MN}
                        : tc::Operand{x_hi, y.raw ? nullptr : x_lo, y.kpad0, tc::MAJOR_MN};
-    // ---- wgrad: dWt_l[K+1 x H] = In^T dZ_l, split-K partials then a fixed-order reduce ----------------
-    {
-      tc::Operand B{ws + y.dz_hi[cur], lo(ws + y.dz_lo[cur]), y.npad, tc::MAJOR_MN};
-      tc::GemmParams p = {};
-      p.epi = tc::EPI_STORE;
-      p.out_hi = ws + y.partial; p.ldo = y.npad; p.split_stride = (long long)kp * y.npad;
-      rc = tc::launch_gemm(p, In, B, K + 1, y.npad, (int)rows, y.npad, y.passes, y.splits[l], st);
-      if (rc) return rc;
-      dim3 grid((K + 1 + 7) / 8, (y.H + 31) / 32);
-      mlp::reduce_wgrad_kernel<<<grid, 1024, 0, st>>>(ws + y.partial, y.splits[l], kp, y.npad, y.H, K, grads + y.w_off[l],
-                                                     grads + y.b_off[l], accumulate);
-      rc = cuda_status(cudaGetLastError(), "fdsm_mlp_backward(reduce)");
+    tc::Operand B{ws + y.dz_hi[l], lo(ws + y.dz_lo[l]), y.npad, tc::MAJOR_MN};
+    float* partial = ws + y.partial[l ? 1 : 0];
+    tc::GemmParams p = {};
+    p.epi = tc::EPI_STORE;
+    p.out_hi = partial; p.ldo = y.npad; p.split_stride = (long long)kp * y.npad;
+    int r = tc::launch_gemm(p, In, B, K + 1, y.npad, (int)rows, y.npad, y.passes, y.splits[l], s);
+    if (r) return r;
+    dim3 grid((K + 1 + 7) / 8, (y.H + 31) / 32);
+    mlp::reduce_wgrad_kernel<<<grid, 1024, 0, s>>>(partial, y.splits[l], kp, y.npad, y.H, K, grads + y.w_off[l],
+                                                  grads + y.b_off[l], accumulate);
+    return cuda_status(cudaGetLastError(), "fdsm_mlp_backward(reduce)");
+  };
+  for (int l = L1; l >= 1; --l) {
+    if (forked) {   // side stream: wait until dZ_l is complete, then wgrad_l
+      rc = cuda_status(cudaEventRecord(side.fork[l & 1], st), "fdsm_mlp_backward(fork)");
+      if (!rc) rc = cuda_status(cudaStreamWaitEvent(sd, side.fork[l & 1], 0), "fdsm_mlp_backward(fork)");
       if (rc) return rc;
     }
-    // ---- dgrad: dZ_{l-1} = (dZ_l W_l) * act'(H_{l-1})   (skipped for the input layer: x needs no gradient) ----
-    if (l > 0) {
-      tc::Operand A{ws + y.dz_hi[cur], lo(ws + y.dz_lo[cur]), y.npad, tc::MAJOR_K};
-      tc::Operand B = y.raw ? tc::Operand{ws + y.wt_raw[l], nullptr, y.npad, tc::MAJOR_K}   // rows k (K_l of them), contiguous n
-                            : tc::Operand{ws + y.wt_hi[l], ws + y.wt_lo[l], y.npad, tc::MAJOR_K};
-      tc::GemmParams p = {};
-      p.epi = tc::EPI_DACT_SPLIT;
-      p.act = y.act;
-      p.out_hi = ws + y.dz_hi[cur ^ 1]; p.out_lo = lo(ws + y.dz_lo[cur ^ 1]); p.ldo = y.npad; p.out_cols = y.npad;
-      p.aux_hi = ws + y.h_hi[l]; p.aux_lo = lo(ws + y.h_lo[l]); p.ldaux = y.kpadh;
-      rc = tc::launch_gemm(p, A, B, (int)rows, K, y.npad, y.npad, y.passes, 1, st);
-      if (rc) return rc;
-      cur ^= 1;
-    }
+    rc = wgrad(l, sd);
+    if (rc) return rc;
+    // dgrad: dZ_{l-1} = (dZ_l W_l) * act'(H_{l-1})
+    tc::Operand A{ws + y.dz_hi[l], lo(ws + y.dz_lo[l]), y.npad, tc::MAJOR_K};
+    tc::Operand B = y.raw ? tc::Operand{ws + y.wt_raw[l], nullptr, y.npad, tc::MAJOR_K}   // rows k (K_l of them), contiguous n
+                          : tc::Operand{ws + y.wt_hi[l], ws + y.wt_lo[l], y.npad, tc::MAJOR_K};
+    tc::GemmParams p = {};
+    p.epi = tc::EPI_DACT_SPLIT;
+    p.act = y.act;
+    p.out_hi = ws + y.dz_hi[l - 1]; p.out_lo = lo(ws + y.dz_lo[l - 1]); p.ldo = y.npad; p.out_cols = y.npad;
+    p.aux_hi = ws + y.h_hi[l]; p.aux_lo = lo(ws + y.h_lo[l]); p.ldaux = y.kpadh;
+    rc = tc::launch_gemm(p, A, B, (int)rows, y.H, y.npad, y.npad, y.passes, 1, st);
+    if (rc) return rc;
+  }
+  rc = wgrad(0, st);
+  if (rc) return rc;
+  if (forked) {
+    rc = cuda_status(cudaEventRecord(side.join, sd), "fdsm_mlp_backward(join)");
+    if (!rc) rc = cuda_status(cudaStreamWaitEvent(st, side.join, 0), "fdsm_mlp_backward(join)");
+    if (rc) return rc;
   }
   return FDSM_OK;
 }

@@ -104,9 +104,20 @@ __global__ void __launch_bounds__(kBlock) stack_kernel(fdsm_stack_args a) {
 
     // ---- pass 1: direction chunks -> registers, sum of squares -> group reduction -------------
     float4 d[MAXC];
+    float4 xb[MAXC];   // CACHE: the sample row is requested BEFORE the Philox/Box-Muller arithmetic so that the HBM
+                       // latency hides under it (the kernel was alternating compute-only and memory-only phases)
     float ss = 0.f;
     if (active) {
       if constexpr (CACHE) {
+        if (a.x) {
+          const float* xrow0 = a.x + b * a.ldx;
+#pragma unroll
+          for (int c = 0; c < MAXC; ++c) {
+            const int j = t + c * G;
+            xb[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (j < nchunk) xb[c] = load4<VEC>(xrow0, j, D);
+          }
+        }
 #pragma unroll
         for (int c = 0; c < MAXC; ++c) {
           const int j = t + c * G;
@@ -129,10 +140,8 @@ __global__ void __launch_bounds__(kBlock) stack_kernel(fdsm_stack_args a) {
       float sig = 0.f;
       if (a.sigma) sig = a.labels ? __ldg(a.sigma + __ldg(a.labels + b)) : __ldg(a.sigma + b);
       const float* xrow = a.x ? a.x + b * a.ldx : nullptr;
-      auto emit = [&](int j, float4 dc) {
+      auto emit = [&](int j, float4 dc, float4 base) {
         const float4 v = need_norm ? normalise(dc, nrm, a.dir_scale) : dc;
-        float4 base = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (xrow) base = load4<VEC>(xrow, j, D);
         if (a.sigma) {
           const float4 n = raw_noise<VEC>(a, b, j);
           const float4 sn = make_float4(__fmul_rn(sig, n.x), __fmul_rn(sig, n.y), __fmul_rn(sig, n.z),
@@ -169,10 +178,11 @@ __global__ void __launch_bounds__(kBlock) stack_kernel(fdsm_stack_args a) {
 #pragma unroll
         for (int c = 0; c < MAXC; ++c) {
           const int j = t + c * G;
-          if (j < nchunk) emit(j, d[c]);
+          if (j < nchunk) emit(j, d[c], xrow ? xb[c] : make_float4(0.f, 0.f, 0.f, 0.f));
         }
       } else {
-        for (int j = t; j < nchunk; j += G) emit(j, raw_direction<VEC>(a, b, j));
+        for (int j = t; j < nchunk; j += G)
+          emit(j, raw_direction<VEC>(a, b, j), xrow ? load4<VEC>(xrow, j, D) : make_float4(0.f, 0.f, 0.f, 0.f));
       }
     }
     if ((a.out_lo || a.pad_ones) && active) {   // GEMM padding columns [D, ldout): ones column then zeros

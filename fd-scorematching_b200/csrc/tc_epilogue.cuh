@@ -7,6 +7,9 @@
 namespace fdsm {
 namespace tc {
 
+#ifndef FDSM_FAST_ACT
+#define FDSM_FAST_ACT 0
+#endif
 constexpr int CW = 8;   // columns per epilogue step
 constexpr int HW_STRIDE = 260;   // shared-memory row stride of the staged head weights [w(N) | b]
 
@@ -15,8 +18,16 @@ __device__ __forceinline__ float act_fwd_t(float z) {
   if constexpr (ACT == ACT_SOFTPLUS || ACT == ACT_NSOFTPLUS) {
     // nn.Softplus(beta=1, threshold=20): z > 20 ? z : log1p(exp(z)); evaluated branch-free (exp overflow -> inf is
     // discarded by the select)
+#if FDSM_FAST_ACT
+    // softplus(z) = max(z, 0) + log1p(exp(-|z|)) on the MUFU pipe (ex2.approx / lg2.approx): absolute error ~2e-7 at
+    // O(1) values (3 fp32 ulp) for ~10 instructions instead of ~45 -- the precise form made the epilogue, not the MMA,
+    // the critical path of the K=200 layers.  z > 20 falls out naturally (log1p(e^-20) < 2^-24 z).
+    const float t = __expf(-fabsf(z));
+    const float r = fmaxf(z, 0.f) + __logf(1.f + t);
+#else
     const float sp = log1pf(expf(z));
     const float r = z > 20.f ? z : sp;
+#endif
     return ACT == ACT_NSOFTPLUS ? r - 0.69314718055994531f : r;   // models.py:19-28
   } else if constexpr (ACT == ACT_ELU) {
     return z > 0.f ? z : expm1f(z);
@@ -26,8 +37,13 @@ __device__ __forceinline__ float act_fwd_t(float z) {
 }
 template <int ACT>
 __device__ __forceinline__ float act_bwd_t(float h) {   // derivative through the stored activation h = act(z)
+#if FDSM_FAST_ACT
+  if constexpr (ACT == ACT_SOFTPLUS) return 1.f - __expf(-h);
+  else if constexpr (ACT == ACT_NSOFTPLUS) return 1.f - 0.5f * __expf(-h);
+#else
   if constexpr (ACT == ACT_SOFTPLUS) return 1.f - expf(-h);
   else if constexpr (ACT == ACT_NSOFTPLUS) return 1.f - 0.5f * expf(-h);
+#endif
   else if constexpr (ACT == ACT_ELU) return h > 0.f ? 1.f : h + 1.f;
   else return 1.f;
 }

@@ -64,3 +64,6 @@ extern "C" int fdsm_tc_gemm(const fdsm_gemm_args* g, fdsm_stream_t stream) {
   return tc::launch_gemm(p, A, B, (int)g->M, (int)g->N, (int)g->K, BN, g->passes, g->splits > 0 ? g->splits : 1,
                          (cudaStream_t)stream);
 }
+
+/* Debug only (not in include/fdsm.h): per-CTA phase timestamps of the raw-operand GEMM, see scripts/gemm_trace.py. */
+extern "C" void fdsm_debug_set_gemm_trace(unsigned long long* device_buffer) { tc::trace_buffer() = device_buffer; }

@@ -43,6 +43,7 @@ struct alignas(64) GemmParams {
   int a_major, b_major;
   int passes;               // 1 or 3
   int raw_slots, slot_bytes;  // gemm_raw_kernel only: raw ring depth and bytes per slot
+  unsigned long long* trace;  // debug: per-CTA phase timestamps (8 per CTA), NULL in production
   int epi, act;
   float* out_hi; float* out_lo; long long ldo; long long split_stride; int out_cols;
   const float* aux_hi; const float* aux_lo; long long ldaux;     // EPI_DACT_SPLIT: H of the previous layer

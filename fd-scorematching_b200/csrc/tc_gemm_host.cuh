@@ -52,6 +52,12 @@ inline int make_tmap(CUtensorMap* m, const float* ptr, long long rows, long long
   return FDSM_OK;
 }
 
+// debug hook (scripts/gemm_trace.py): when set, every raw-operand launch writes 8 %globaltimer stamps per CTA
+inline unsigned long long*& trace_buffer() {
+  static unsigned long long* buf = nullptr;
+  return buf;
+}
+
 struct Operand {
   const float* hi; const float* lo; long long ld; int major;   // MAJOR_K: [R x K] row-major; MAJOR_MN: [K x R] row-major
 };
@@ -87,6 +93,7 @@ inline int launch_gemm(GemmParams& p, const Operand& A, const Operand& B, int M,
       FDSM_SET_SMEM_RAW(EPI_STORE); FDSM_SET_SMEM_RAW(EPI_ACT_SPLIT); FDSM_SET_SMEM_RAW(EPI_HEAD); FDSM_SET_SMEM_RAW(EPI_DACT_SPLIT);
 #undef FDSM_SET_SMEM_RAW
     });
+    p.trace = trace_buffer();
     p.slot_bytes = raw_slot_bytes(BN, B.major);
     p.raw_slots = MAX_RAW_SLOTS;
     while (p.raw_slots > 1 && raw_smem_total(p.raw_slots, p.slot_bytes) > 227 * 1024 - 5 * 1024) --p.raw_slots;

@@ -36,6 +36,14 @@ __host__ __device__ inline int raw_slot_bytes(int BN, int b_major) {
 }
 __host__ inline int raw_smem_total(int raw_slots, int slot_bytes) { return (raw_slots + LO_SLOTS) * slot_bytes + 1024 + 256; }
 
+__device__ __forceinline__ void trace_stamp(const GemmParams& p, int slot) {
+  if (p.trace) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    p.trace[((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 8 + slot] = t;
+  }
+}
+
 template <int EPI>
 __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_constant__ GemmParams p) {
   using namespace ptx;
@@ -44,6 +52,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
     const int nh = p.head_mode ? 3 : 1;
     for (int i = threadIdx.x; i < nh * (p.N + 1); i += kThreads) head_smem[(i / (p.N + 1)) * HW_STRIDE + i % (p.N + 1)] = __ldg(p.head_w + i);
   }
+  if (threadIdx.x == 0) trace_stamp(p, 0);   // CTA start
   const int R = p.raw_slots;
   const int SLOT = p.slot_bytes;
   extern __shared__ uint8_t smem_raw[];
@@ -89,6 +98,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  if (threadIdx.x == 0) trace_stamp(p, 1);   // setup done
 
   if (warp == 0) {
     // ===== TMA producer ===========================================================================
@@ -129,6 +139,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
       for (int kb = kb0; kb < kb1; ++kb) {
         mbar_wait(conv_bar(l), lphase);
         tc_fence_after();
+        if (kb == kb0) trace_stamp(p, 2);      // first k-block converted: MMA starts
+        if (kb == kb1 - 1) trace_stamp(p, 3);  // last k-block converted
         const uint32_t a_hi = base + r * SLOT, b_hi = a_hi + A_TILE_BYTES;
         const uint32_t a_lo = lo_base + l * SLOT, b_lo = a_lo + A_TILE_BYTES;
 #pragma unroll
@@ -202,6 +214,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
       mbar_wait(tmem_full_bar, 0);
       tc_fence_after();
     }
+    if (threadIdx.x == 128) trace_stamp(p, 4);   // accumulator complete
     float l1 = 0.f, l2 = 0.f, lq = 0.f;
     const bool last_tile = n0 + p.BN >= p.N;
     const int ncols_out = (EPI == EPI_STORE || EPI == EPI_HEAD) ? min(p.N - n0, p.BN) : (last_tile ? p.out_cols - n0 : p.BN);
@@ -209,6 +222,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
     const int c_begin = half ? s0 * CW : 0, c_end = half ? nsteps * CW : s0 * CW;
     epilogue_dispatch<EPI>(p, tmem_base + ((uint32_t)(q * 32) << 16), have_acc, row, row_ok, n0, c_begin, c_end, head_smem, l1,
                            l2, lq);
+    if (threadIdx.x == 128) trace_stamp(p, 5);   // epilogue of warp 4 done
     if constexpr (EPI == EPI_HEAD) {
       __shared__ float hsum[BM][3];
       if (half == 1) { hsum[q * 32 + lane][0] = l1; hsum[q * 32 + lane][1] = l2; hsum[q * 32 + lane][2] = lq; }
@@ -225,6 +239,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
     tc_fence_before();
   }
   __syncthreads();
+  if (threadIdx.x == 0) trace_stamp(p, 6);   // all warps done
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc(tmem_base, TMEM_COLS);

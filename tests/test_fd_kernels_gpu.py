@@ -21,8 +21,9 @@ def _dev():
 def test_philox_normals_match_numpy_oracle(fdsm, B, D):
     got = fdsm.ops.philox_normal(B, D, 0, seed=0x1234ABCD5678, offset=5, row0=3).cpu().numpy()
     want = philox.normals(B, D, 0, 0x1234ABCD5678, 5, 3)
-    # uniforms are bit-exact (integer Philox); logf/sincospif differ from numpy by a few ulp
-    np.testing.assert_allclose(got, want, rtol=0, atol=2e-6)
+    # uniforms are bit-exact (integer Philox); the Box-Muller transform runs on the MUFU pipe (lg2/sin/cos.approx,
+    # log1p series near u = 1): within 1e-5 absolute of the float64 transform for |n| up to 5.8
+    np.testing.assert_allclose(got, want, rtol=0, atol=1e-5)
 
 
 def test_philox_statistics(fdsm):
