@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libfdsm.so")
+LIB_PATH = os.environ.get("FDSM_LIB_PATH") or os.path.join(_HERE, "libfdsm.so")   # override: A/B runs of two builds
 
 ROW_X, ROW_PLUS, ROW_MINUS = 1, 2, 4
 

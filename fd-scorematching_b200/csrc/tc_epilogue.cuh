@@ -30,7 +30,11 @@ __device__ __forceinline__ float act_fwd_t(float z) {
 #endif
     return ACT == ACT_NSOFTPLUS ? r - 0.69314718055994531f : r;   // models.py:19-28
   } else if constexpr (ACT == ACT_ELU) {
+#if FDSM_FAST_ACT
+    return z > 0.f ? z : __expf(z) - 1.f;   // absolute error ~1e-7, branch-free
+#else
     return z > 0.f ? z : expm1f(z);
+#endif
   } else {
     return z;
   }
@@ -54,10 +58,14 @@ __device__ __forceinline__ void st8(float* o, const float (&v)[CW]) {
 }
 
 // One thread = one output row; columns [c_begin, c_end) of this CTA's tile in steps of CW.
-template <int EPI, int ACT>
+// STAGED: results go to this thread's row of a shared-memory tile (`srow`, columns relative to n0) and are written to
+// global memory afterwards by coalesced row copies (stage_store_tile); EPI_DACT_SPLIT then also finds its aux operand in
+// the same tile (stage_load_tile), which it overwrites in place.  Un-staged, every warp-wide 16-byte store touches 32
+// different rows = 32 L1 wavefronts, and the epilogue of a 128x208 tile took 4.7 us (profiles/r01_gemm_trace.txt).
+template <int EPI, int ACT, bool STAGED = false>
 __device__ __forceinline__ void epilogue_loop(const GemmParams& p, uint32_t tmem_row, bool have_acc, int row, bool row_ok,
                                               int n0, int c_begin, int c_end, const float* __restrict__ hw, float& l1,
-                                              float& l2, float& lq) {
+                                              float& l2, float& lq, float* srow = nullptr) {
   const bool vec_ok = ((p.ldo | n0) & 3) == 0 && aligned16(p.out_hi) && ((blockIdx.z ? p.split_stride : 0) & 3) == 0;
 #pragma unroll 1
   for (int c = c_begin; c < c_end; c += CW) {
@@ -69,7 +77,9 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, uint32_t tmem
       for (int i = 0; i < CW; ++i) v[i] = 0.f;
     }
     const int nvalid = p.N - n0 - c;   // columns [0, nvalid) of this step are real outputs
-    if constexpr (EPI == EPI_STORE) {
+    if constexpr (STAGED && EPI == EPI_STORE) {
+      st8(srow + c, v);
+    } else if constexpr (EPI == EPI_STORE) {
       if (row_ok) {
         float* o = p.out_hi + (long long)blockIdx.z * p.split_stride + (long long)row * p.ldo + n0 + c;
         if (nvalid >= CW && vec_ok) {
@@ -83,26 +93,30 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, uint32_t tmem
     } else if constexpr (EPI == EPI_HEAD) {
 #pragma unroll
       for (int i = 0; i < CW; ++i) {
-        float h = 0.f;
-        if (i < nvalid) {
-          h = act_fwd_t<ACT>(v[i]);
-          const int cc = n0 + c + i;
-          l1 = fmaf(h, hw[cc], l1);
-          if (p.head_mode) {
-            l2 = fmaf(h, hw[HW_STRIDE + cc], l2);
-            lq = fmaf(h * h, hw[2 * HW_STRIDE + cc], lq);
-          }
+        // branch-free (selects, not predicated blocks): the 8 columns of a step must overlap in the pipes; with
+        // per-element branches each activation ran alone, ~100 clk per element (profiles/r01_step_trace.txt)
+        const bool ok = i < nvalid;
+        const float h = ok ? act_fwd_t<ACT>(v[i]) : 0.f;
+        const int cc = n0 + c + i;   // < HW_STRIDE: the staged head weights are readable (finite or not) beyond N
+        l1 = fmaf(h, ok ? hw[cc] : 0.f, l1);
+        if (p.head_mode) {
+          l2 = fmaf(h, ok ? hw[HW_STRIDE + cc] : 0.f, l2);
+          lq = fmaf(h * h, ok ? hw[2 * HW_STRIDE + cc] : 0.f, lq);
         }
         v[i] = h;
       }
-      if (row_ok && c < p.out_cols) st8(p.out_hi + (long long)row * p.ldo + n0 + c, v);
+      if constexpr (STAGED) st8(srow + c, v);
+      else if (row_ok && c < p.out_cols) st8(p.out_hi + (long long)row * p.ldo + n0 + c, v);
     } else {
       // EPI_ACT_SPLIT / EPI_DACT_SPLIT: TF32 hi/lo rows of the next GEMM's operand, padded to out_cols
       float hi[CW], lo[CW], a[CW];
       if constexpr (EPI == EPI_DACT_SPLIT) {
 #pragma unroll
         for (int i = 0; i < CW; ++i) a[i] = 0.f;
-        if (row_ok && nvalid > 0) {
+        if constexpr (STAGED) {
+          const float4 x0 = *reinterpret_cast<const float4*>(srow + c), x1 = *reinterpret_cast<const float4*>(srow + c + 4);
+          a[0] = x0.x; a[1] = x0.y; a[2] = x0.z; a[3] = x0.w; a[4] = x1.x; a[5] = x1.y; a[6] = x1.z; a[7] = x1.w;
+        } else if (row_ok && nvalid > 0) {
           const float* ah = p.aux_hi + (long long)row * p.ldaux + n0 + c;   // ldaux % 4 == 0, 16-byte aligned base
           const float4 x0 = ldg4(ah), x1 = ldg4(ah + 4);
           a[0] = x0.x; a[1] = x0.y; a[2] = x0.z; a[3] = x0.w; a[4] = x1.x; a[5] = x1.y; a[6] = x1.z; a[7] = x1.w;
@@ -115,17 +129,20 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, uint32_t tmem
       }
 #pragma unroll
       for (int i = 0; i < CW; ++i) {
-        float y = 0.f;
-        if (i < nvalid) {
-          if constexpr (EPI == EPI_ACT_SPLIT) y = act_fwd_t<ACT>(v[i]);
-          else y = v[i] * act_bwd_t<ACT>(a[i]);
-        } else if (EPI == EPI_ACT_SPLIT && i == nvalid) {
-          y = 1.f;   // bias column of the next layer's augmented input
+        float y;   // branch-free, see EPI_HEAD
+        if constexpr (EPI == EPI_ACT_SPLIT) {
+          const float h = act_fwd_t<ACT>(v[i]);
+          y = i < nvalid ? h : (i == nvalid ? 1.f : 0.f);   // column N: bias column of the next layer's augmented input
+        } else {
+          const float g = v[i] * act_bwd_t<ACT>(a[i]);
+          y = i < nvalid ? g : 0.f;
         }
         if (p.out_lo) ptx::tf32_split(y, hi[i], lo[i]);
         else hi[i] = y;   // raw-operand pipeline: the consumer GEMM splits in shared memory
       }
-      if (row_ok) {
+      if constexpr (STAGED) {
+        st8(srow + c, hi);   // raw-operand pipeline only: out_lo == NULL
+      } else if (row_ok) {
         st8(p.out_hi + (long long)row * p.ldo + n0 + c, hi);
         if (p.out_lo) st8(p.out_lo + (long long)row * p.ldo + n0 + c, lo);
       }
@@ -133,19 +150,64 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, uint32_t tmem
   }
 }
 
-template <int EPI>
+template <int EPI, bool STAGED = false>
 __device__ __forceinline__ void epilogue_dispatch(const GemmParams& p, uint32_t tmem_row, bool have_acc, int row, bool row_ok,
                                                   int n0, int c_begin, int c_end, const float* hw, float& l1, float& l2,
-                                                  float& lq) {
+                                                  float& lq, float* srow = nullptr) {
   if constexpr (EPI == EPI_STORE) {
-    epilogue_loop<EPI, ACT_NONE>(p, tmem_row, have_acc, row, row_ok, n0, c_begin, c_end, hw, l1, l2, lq);
+    epilogue_loop<EPI, ACT_NONE, STAGED>(p, tmem_row, have_acc, row, row_ok, n0, c_begin, c_end, hw, l1, l2, lq, srow);
   } else {
     switch (p.act) {   // warp-uniform, outside the column loop
-      case ACT_SOFTPLUS: epilogue_loop<EPI, ACT_SOFTPLUS>(p, tmem_row, have_acc, row, row_ok, n0, c_begin, c_end, hw, l1, l2, lq); break;
-      case ACT_NSOFTPLUS: epilogue_loop<EPI, ACT_NSOFTPLUS>(p, tmem_row, have_acc, row, row_ok, n0, c_begin, c_end, hw, l1, l2, lq); break;
-      case ACT_ELU: epilogue_loop<EPI, ACT_ELU>(p, tmem_row, have_acc, row, row_ok, n0, c_begin, c_end, hw, l1, l2, lq); break;
-      default: epilogue_loop<EPI, ACT_NONE>(p, tmem_row, have_acc, row, row_ok, n0, c_begin, c_end, hw, l1, l2, lq); break;
+      case ACT_SOFTPLUS: epilogue_loop<EPI, ACT_SOFTPLUS, STAGED>(p, tmem_row, have_acc, row, row_ok, n0, c_begin, c_end, hw, l1, l2, lq, srow); break;
+      case ACT_NSOFTPLUS: epilogue_loop<EPI, ACT_NSOFTPLUS, STAGED>(p, tmem_row, have_acc, row, row_ok, n0, c_begin, c_end, hw, l1, l2, lq, srow); break;
+      case ACT_ELU: epilogue_loop<EPI, ACT_ELU, STAGED>(p, tmem_row, have_acc, row, row_ok, n0, c_begin, c_end, hw, l1, l2, lq, srow); break;
+      default: epilogue_loop<EPI, ACT_NONE, STAGED>(p, tmem_row, have_acc, row, row_ok, n0, c_begin, c_end, hw, l1, l2, lq, srow); break;
     }
+  }
+}
+
+// Coalesced copies between a [rows x ld] global tile and the [BM x ldt] shared staging tile: warp w takes rows w, w+8, ...;
+// the lanes sweep a row in 16-byte pieces (scalar when the global side is not 16-byte aligned).
+__device__ __forceinline__ void stage_store_tile(const float* __restrict__ stage, int ldt, float* __restrict__ g, long long ld,
+                                                 int rows, int cols, bool vec) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int c4 = vec ? (cols & ~3) : 0;
+  for (int r = warp; r < rows; r += kThreads / 32) {
+    const float* s = stage + r * ldt;
+    float* o = g + (long long)r * ld;
+    for (int c = 4 * lane; c < c4; c += 128) *reinterpret_cast<float4*>(o + c) = *reinterpret_cast<const float4*>(s + c);
+    for (int c = c4 + lane; c < cols; c += 32) o[c] = s[c];
+  }
+}
+__device__ __forceinline__ void stage_load_tile(float* __restrict__ stage, int ldt, const float* __restrict__ g, long long ld,
+                                                int rows, int cols, bool vec) {
+  // the tile as a flat list of 16-byte pieces, 8 independent loads in flight per thread (a row-by-row loop exposed one
+  // global-memory latency per row: 14 us for a 128x200 tile, profiles/r01_step_trace.txt)
+  if (vec) {
+    const int c4n = cols >> 2, total = rows * c4n;
+    constexpr int UNR = 8;
+    for (int i0 = threadIdx.x; i0 < total; i0 += kThreads * UNR) {
+      float4 x[UNR];
+      int off[UNR];
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        const int i = i0 + u * kThreads;
+        if (i < total) {
+          const int r = i / c4n, c = (i - r * c4n) << 2;
+          off[u] = r * ldt + c;
+          x[u] = ldg4(g + (long long)r * ld + c);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < UNR; ++u)
+        if (i0 + u * kThreads < total) *reinterpret_cast<float4*>(stage + off[u]) = x[u];
+    }
+  }
+  const int c4 = vec ? (cols & ~3) : 0;
+  if (c4 < cols) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int r = warp; r < rows; r += kThreads / 32)
+      for (int c = c4 + lane; c < cols; c += 32) stage[r * ldt + c] = __ldg(g + (long long)r * ld + c);
   }
 }
 

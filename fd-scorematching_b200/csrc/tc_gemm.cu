@@ -66,4 +66,7 @@ extern "C" int fdsm_tc_gemm(const fdsm_gemm_args* g, fdsm_stream_t stream) {
 }
 
 /* Debug only (not in include/fdsm.h): per-CTA phase timestamps of the raw-operand GEMM, see scripts/gemm_trace.py. */
-extern "C" void fdsm_debug_set_gemm_trace(unsigned long long* device_buffer) { tc::trace_buffer() = device_buffer; }
+extern "C" void fdsm_debug_set_gemm_trace(unsigned long long* device_buffer) {
+  tc::trace_buffer() = device_buffer;   // launch i (since this call) writes at device_buffer + i * 8 * 160
+  tc::trace_launch_index() = 0;
+}

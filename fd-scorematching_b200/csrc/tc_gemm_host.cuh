@@ -57,6 +57,11 @@ inline unsigned long long*& trace_buffer() {
   static unsigned long long* buf = nullptr;
   return buf;
 }
+constexpr int TRACE_STRIDE = 8 * 160;   // stamps per launch slot (<= 160 CTAs traced)
+inline int& trace_launch_index() {
+  static int idx = 0;
+  return idx;
+}
 
 struct Operand {
   const float* hi; const float* lo; long long ld; int major;   // MAJOR_K: [R x K] row-major; MAJOR_MN: [K x R] row-major
@@ -93,7 +98,7 @@ inline int launch_gemm(GemmParams& p, const Operand& A, const Operand& B, int M,
       FDSM_SET_SMEM_RAW(EPI_STORE); FDSM_SET_SMEM_RAW(EPI_ACT_SPLIT); FDSM_SET_SMEM_RAW(EPI_HEAD); FDSM_SET_SMEM_RAW(EPI_DACT_SPLIT);
 #undef FDSM_SET_SMEM_RAW
     });
-    p.trace = trace_buffer();
+    p.trace = trace_buffer() ? trace_buffer() + (size_t)TRACE_STRIDE * trace_launch_index()++ : nullptr;
     p.slot_bytes = raw_slot_bytes(BN, B.major);
     p.raw_slots = MAX_RAW_SLOTS;
     while (p.raw_slots > 1 && raw_smem_total(p.raw_slots, p.slot_bytes) > 227 * 1024 - 5 * 1024) --p.raw_slots;

@@ -40,7 +40,8 @@ __device__ __forceinline__ void trace_stamp(const GemmParams& p, int slot) {
   if (p.trace) {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    p.trace[((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 8 + slot] = t;
+    const unsigned cta = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+    if (cta < 160) p.trace[cta * 8 + slot] = t;
   }
 }
 
@@ -77,11 +78,27 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
   const int kb1 = (int)((long long)kblocks * (blockIdx.z + 1) / gridDim.z);
   const int b_bytes = raw_b_tile_bytes(p.BN, p.b_major);
 
+  // TMA producer state; the first R k-blocks are requested BEFORE the CTA-wide setup barrier (TMEM allocation takes
+  // ~0.5 us and the first load ~2 us: they overlap instead of adding up).
+  const int b_boxes_mn = (p.BN + 31) / 32;
+  auto issue_loads = [&](int kb, int r) {
+    const uint32_t a_dst = base + r * SLOT, b_dst = a_dst + A_TILE_BYTES;
+    const uint32_t fb = raw_full(r);
+    mbar_arrive_expect_tx(fb, (uint32_t)(A_TILE_BYTES + b_bytes));
+    const int k0 = kb * BK;
+    if (p.a_major == MAJOR_K) {
+      tma_load_2d(a_dst, &p.ta_hi, fb, k0, m0);
+    } else {
+      for (int i = 0; i < BM / 32; ++i) tma_load_2d(a_dst + i * 4096, &p.ta_hi, fb, m0 + 32 * i, k0);
+    }
+    if (p.b_major == MAJOR_K) {
+      tma_load_2d(b_dst, &p.tb_hi, fb, k0, n0);
+    } else {
+      for (int i = 0; i < b_boxes_mn; ++i) tma_load_2d(b_dst + i * 4096, &p.tb_hi, fb, n0 + 32 * i, k0);
+    }
+  };
+  const int pre = min(R, kb1 - kb0);
   if (warp == 0 && lane == 0) {
-    prefetch_tensormap(&p.ta_hi);
-    prefetch_tensormap(&p.tb_hi);
-  }
-  if (warp == 1 && lane == 0) {
     for (int s = 0; s < MAX_RAW_SLOTS; ++s) {
       mbar_init(raw_full(s), 1);
       mbar_init(raw_empty(s), 1);
@@ -92,6 +109,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
     }
     mbar_init(tmem_full_bar, 1);
     fence_barrier_init();
+    for (int i = 0; i < pre; ++i) issue_loads(kb0 + i, i);
   }
   if (warp == 2) tmem_alloc(smem_u32((const void*)tmem_ptr_smem), TMEM_COLS);
   tc_fence_before();
@@ -103,26 +121,11 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
   if (warp == 0) {
     // ===== TMA producer ===========================================================================
     if (lane == 0) {
-      const int b_boxes_mn = (p.BN + 31) / 32;
-      const uint32_t tx = (uint32_t)(A_TILE_BYTES + b_bytes);
-      int r = 0;
-      uint32_t phase = 0;
-      for (int kb = kb0; kb < kb1; ++kb) {
+      int r = pre % R;
+      uint32_t phase = pre == R ? 1u : 0u;
+      for (int kb = kb0 + pre; kb < kb1; ++kb) {
         mbar_wait(raw_empty(r), phase ^ 1u);
-        const uint32_t a_dst = base + r * SLOT, b_dst = a_dst + A_TILE_BYTES;
-        const uint32_t fb = raw_full(r);
-        mbar_arrive_expect_tx(fb, tx);
-        const int k0 = kb * BK;
-        if (p.a_major == MAJOR_K) {
-          tma_load_2d(a_dst, &p.ta_hi, fb, k0, m0);
-        } else {
-          for (int i = 0; i < BM / 32; ++i) tma_load_2d(a_dst + i * 4096, &p.ta_hi, fb, m0 + 32 * i, k0);
-        }
-        if (p.b_major == MAJOR_K) {
-          tma_load_2d(b_dst, &p.tb_hi, fb, k0, n0);
-        } else {
-          for (int i = 0; i < b_boxes_mn; ++i) tma_load_2d(b_dst + i * 4096, &p.tb_hi, fb, n0 + 32 * i, k0);
-        }
+        issue_loads(kb, r);
         if (++r == R) { r = 0; phase ^= 1u; }
       }
     }
@@ -204,14 +207,16 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
   }
   __syncwarp();
   {
-    // ===== epilogue: identical to gemm_kernel's ==========================================================
+    // ===== epilogue: TMEM -> registers -> fused op -> shared staging tile -> coalesced global stores ==========
+    // warp w may read TMEM lanes 32*(w%4)..+31; warps 0-3 take the first half of the columns, warps 4-7 the second.
     const int q = warp & 3;
     const int half = warp >> 2;
-    const int row = m0 + q * 32 + lane;
+    const int rloc = q * 32 + lane;
+    const int row = m0 + rloc;
     const bool row_ok = row < p.M;
     const bool have_acc = kb1 > kb0;
     if (have_acc) {
-      mbar_wait(tmem_full_bar, 0);
+      mbar_wait(tmem_full_bar, 0);   // every MMA has completed: the pipeline's shared memory is free from here on
       tc_fence_after();
     }
     if (threadIdx.x == 128) trace_stamp(p, 4);   // accumulator complete
@@ -220,9 +225,18 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
     const int ncols_out = (EPI == EPI_STORE || EPI == EPI_HEAD) ? min(p.N - n0, p.BN) : (last_tile ? p.out_cols - n0 : p.BN);
     const int nsteps = (ncols_out + CW - 1) / CW, s0 = (nsteps + 1) / 2;
     const int c_begin = half ? s0 * CW : 0, c_end = half ? nsteps * CW : s0 * CW;
-    epilogue_dispatch<EPI>(p, tmem_base + ((uint32_t)(q * 32) << 16), have_acc, row, row_ok, n0, c_begin, c_end, head_smem, l1,
-                           l2, lq);
-    if (threadIdx.x == 128) trace_stamp(p, 5);   // epilogue of warp 4 done
+    float* stage = reinterpret_cast<float*>(gen);
+    const int ldt = nsteps * CW + 4;   // +4 floats: 16-byte row stores of 8 consecutive rows fall into distinct banks
+    const int rows_valid = min(BM, p.M - m0);
+    if constexpr (EPI == EPI_DACT_SPLIT) {
+      __syncthreads();   // all warps are past the pipeline before the tile is overwritten
+      const bool avec = ((p.ldaux | n0) & 3) == 0 && aligned16(p.aux_hi);
+      stage_load_tile(stage, ldt, p.aux_hi + (long long)m0 * p.ldaux + n0, p.ldaux, rows_valid, min(p.N - n0, p.BN), avec);
+    }
+    __syncthreads();
+    epilogue_dispatch<EPI, true>(p, tmem_base + ((uint32_t)(q * 32) << 16), have_acc, row, row_ok, n0, c_begin, c_end, head_smem,
+                                 l1, l2, lq, stage + rloc * ldt);
+    if (threadIdx.x == 128) trace_stamp(p, 5);   // epilogue math of warp 4 done
     if constexpr (EPI == EPI_HEAD) {
       __shared__ float hsum[BM][3];
       if (half == 1) { hsum[q * 32 + lane][0] = l1; hsum[q * 32 + lane][1] = l2; hsum[q * 32 + lane][2] = lq; }
@@ -235,6 +249,14 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
         p.l1_out[row] = l1;
         p.l2_out[row] = l2;
       }
+    } else {
+      __syncthreads();
+    }
+    {
+      float* gout = p.out_hi + (long long)blockIdx.z * p.split_stride + (long long)m0 * p.ldo + n0;
+      const bool ovec = ((p.ldo | n0) & 3) == 0 && aligned16(p.out_hi) && ((blockIdx.z ? p.split_stride : 0) & 3) == 0;
+      const int cols_store = EPI == EPI_HEAD ? min(nsteps * CW, p.out_cols - n0) : ncols_out;
+      stage_store_tile(stage, ldt, gout, p.ldo, rows_valid, cols_store, ovec);
     }
     tc_fence_before();
   }
