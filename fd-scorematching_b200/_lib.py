@@ -81,6 +81,8 @@ PROTOTYPES = {
     "fdsm_mlp_prepare": (C.c_int, [C.POINTER(MlpDesc), _i64, _f32p, _f32p, _stream]),
     "fdsm_mlp_forward": (C.c_int, [C.POINTER(MlpDesc), _f32p, _f32p, _i64, _f32p, _f32p, _f32p, _stream]),
     "fdsm_mlp_backward": (C.c_int, [C.POINTER(MlpDesc), _f32p, _f32p, _i64, _f32p, _f32p, _f32p, _f32p, _i32, _stream]),
+    "fdsm_mlp_backward_fd_ssm": (C.c_int, [C.POINTER(MlpDesc), _f32p, _f32p, _i64, _f32p, _f32p, _f32p, _f32, _f32, _i32,
+                                           _f32p, _f32p, _i32, _stream]),
 }
 
 _lib = None
@@ -103,8 +105,8 @@ def load():
     for name, (res, args) in PROTOTYPES.items():
         fn = getattr(lib, name)  # AttributeError if the symbol is missing
         fn.restype, fn.argtypes = res, args
-    if lib.fdsm_version() != 3:
-        raise FdsmError(f"libfdsm ABI version {lib.fdsm_version()} != 3")
+    if lib.fdsm_version() != 4:
+        raise FdsmError(f"libfdsm ABI version {lib.fdsm_version()} != 4")
     _lib = lib
     return lib
 

@@ -3,50 +3,20 @@
 //   score-net form: O(B*D) streaming, HBM-bound; fused fwd+bwd pass = 20*D bytes per sample
 //   (R s1,s2,v ; W ds1,ds2).  Row sums by warp shuffles + shared-memory staging, then a tiny
 //   fixed-order mean kernel.
-#include "fdsm_common.cuh"
+#include "fd_combine.cuh"
 
 namespace fdsm {
 namespace {
 
 constexpr int kBlock = 256;
 
-__device__ __forceinline__ float block_sum_1024(float v, float* red) {
-  v = warp_sum(v);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  __syncthreads();
-  if (lane == 0) red[warp] = v;
-  __syncthreads();
-  float s = 0.f;
-  const int nw = blockDim.x >> 5;
-  for (int i = 0; i < nw; ++i) s += red[i];
-  return s;
-}
-
-// ---- energy form ------------------------------------------------------------------------------
-__device__ __forceinline__ float energy_per(const float* E, int64_t B, int64_t b, int mode, float c1) {
-  if (mode == 0) {
-    const float e1 = E[b], e2 = E[B + b], e3 = E[2 * B + b];
-    const float d = e2 - e3;
-    // (d*d)/8 - e2 - e3 + c1*e1 in the reference's left-to-right order (efficient_sm.py:65-67)
-    return __fadd_rn(__fmul_rn(__fmul_rn(d, d), 0.125f), __fadd_rn(__fsub_rn(-e2, e3), __fmul_rn(c1, e1)));
-  }
-  const float d = E[b] - E[B + b];
-  return __fadd_rn(__fmul_rn(d, d), __fmul_rn(4.f, d));
-}
-
+// ---- energy form (device helpers in fd_combine.cuh) ----------------------------------------------
 __global__ void __launch_bounds__(1024) combine_energy_fwd_kernel(const float* __restrict__ E, int64_t B, int mode,
                                                                   float c1, float scale, int mean,
                                                                   float* __restrict__ per_sample,
                                                                   float* __restrict__ loss) {
   __shared__ float red[32];
-  float acc = 0.f;
-  for (int64_t b = threadIdx.x; b < B; b += blockDim.x) {
-    const float p = energy_per(E, B, b, mode, c1);
-    if (per_sample) per_sample[b] = p * scale;
-    acc += p;
-  }
-  acc = block_sum_1024(acc, red);
-  if (threadIdx.x == 0 && loss) *loss = (mean ? acc / (float)B : acc) * scale;
+  combine_energy_fwd_block(E, B, mode, c1, scale, mean, per_sample, loss, red);
 }
 
 __global__ void __launch_bounds__(256) combine_energy_bwd_kernel(const float* __restrict__ E, int64_t B, int mode,

@@ -16,12 +16,20 @@
 // Backward dgrad l: A = dZ_l (K-major over n), B = Wt_l (K-major: rows k, contiguous n) -> * act'(H_{l-1}) -> dZ_{l-1}
 //          wgrad l: A = input_l (MN-major, M = K_l+1), B = dZ_l (MN-major), contraction over the rows, split-K
 //                   partials -> deterministic fixed-order reduce + transpose into the flat gradient.
+#include <type_traits>
+
 #include "tc_gemm_host.cuh"
+#include "fd_combine.cuh"
 
 namespace fdsm {
 namespace mlp {
 
 inline long long round_up(long long x, long long m) { return (x + m - 1) / m * m; }
+constexpr int HB_WARPS = 8;   // head_bwd_kernel: warps (= rows in flight) per block
+inline int head_blocks(long long rows) {
+  long long b = (rows + HB_WARPS - 1) / HB_WARPS, cap = 2ll * sm_count();
+  return (int)(b < cap ? (b < 1 ? 1 : b) : cap);
+}
 
 struct Layout {
   int D, H, L, act, head, passes;
@@ -38,7 +46,7 @@ struct Layout {
   long long dz_hi[16], dz_lo[16];   // dZ_l per layer [rows x npad] (lo only in presplit mode): wgrad_l runs on a side
                                     // stream while dgrad_l..1 continue, so the buffers are not recycled
   long long l1, l2;                 // per-row head dot products
-  long long head_acc;               // fp64 accumulators of the head-parameter gradients (3(H+1) doubles)
+  long long head_acc;               // per-block fp64 partial sums of the head-parameter gradients
   long long partial[2];             // split-K partials: [0] input layer (main stream), [1] hidden layers (side stream)
   long long total;
   int splits[16];
@@ -98,7 +106,7 @@ inline int make_layout(const fdsm_mlp_desc* d, long long rows, Layout& y) {
   }
   y.l1 = take(rows);
   y.l2 = take(rows);
-  y.head_acc = take(2ll * 3 * (y.H + 1));
+  y.head_acc = take(2ll * head_blocks(rows) * (y.head ? 3 : 1) * (y.H + 1));   // per-block fp64 partials
   y.partial[0] = take(max_partial[0]);
   y.partial[1] = take(max_partial[1]);
   y.total = w;
@@ -144,67 +152,135 @@ __global__ void __launch_bounds__(256) prep_weights_kernel(const PrepArgs a) {
   }
 }
 
-// ---- head backward: dE -> dZ_L (hi/lo) and the head parameter gradients -----------------------------------
+// ---- head backward: dE -> dZ_L and the head parameter gradients --------------------------------------------
 // dH[r,j] = g (l2 w1[j] + l1 w2[j] + 2 wq[j] h)   (quadratic)   |   g w[j]   (linear);   dZ = dH * act'(h)
+// g = dL/dE_r comes either from an explicit dE vector (generic autograd path) or -- FD-SSM energy form -- straight from
+// the stacked energies (the combine backward folded in: no dE round trip, no extra launch).
 // The head-parameter sums cancel heavily across the x / x+v / x-v rows of a sample (dE = 2c, c(q-1), c(-q-1)), so they
-// are accumulated in fp64 (registers, then fp64 atomics into `acc`) and rounded to fp32 once by head_finish_kernel.
-constexpr int HB_ROWS = 32;
-__global__ void __launch_bounds__(256) head_bwd_kernel(const float* __restrict__ hlast, int ldh, const float* __restrict__ dE,
-                                                       const float* __restrict__ l1v, const float* __restrict__ l2v,
-                                                       const float* __restrict__ head_w, int H, int npad, long long rows,
-                                                       int act, int head, float* __restrict__ dz_hi, float* __restrict__ dz_lo,
-                                                       double* __restrict__ acc) {
-  const int j = threadIdx.x;
-  const long long r0 = (long long)blockIdx.x * HB_ROWS;
-  const bool col = j < H;
-  float w1 = 0.f, w2 = 0.f, wq = 0.f;
-  if (col) {
-    w1 = head_w[j];
-    if (head) { w2 = head_w[H + 1 + j]; wq = head_w[2 * (H + 1) + j]; }
+// are accumulated in fp64: registers -> fixed-order block reduce -> per-block partials -> fixed-order sum in
+// head_finish_kernel (bit-reproducible, no atomics).
+// One warp per row, lanes across the columns (coalesced 128-byte row segments), grid ~ 2 blocks per SM.
+struct HeadGrad {
+  const float* dE;                                    // explicit dL/dE, or NULL:
+  const float* E; long long B; float c1, coef;        // energy-form combine, rows = 3B
+};
+__device__ __forceinline__ float head_g(const HeadGrad& s, long long r) {
+  return s.dE ? __ldg(s.dE + r) : combine_energy_grad_row(s.E, s.B, s.c1, s.coef, r);
+}
+template <int NI>
+__global__ void __launch_bounds__(HB_WARPS * 32) head_bwd_kernel(const float* __restrict__ hlast, int ldh, const HeadGrad src,
+                                                                 const float* __restrict__ l1v, const float* __restrict__ l2v,
+                                                                 const float* __restrict__ head_w, int H, int npad,
+                                                                 long long rows, int act, int head, float* __restrict__ dz_hi,
+                                                                 float* __restrict__ dz_lo, double* __restrict__ partial) {
+  __shared__ double red[HB_WARPS][NI * 32];
+  __shared__ double redb[HB_WARPS][3];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const long long W = (long long)gridDim.x * HB_WARPS;
+  float w1[NI], w2[NI], wq[NI];
+  double a1[NI], a2[NI], aq[NI];
+#pragma unroll
+  for (int i = 0; i < NI; ++i) {
+    const int j = lane + 32 * i;
+    w1[i] = w2[i] = wq[i] = 0.f;
+    a1[i] = a2[i] = aq[i] = 0.;
+    if (j < H) {
+      w1[i] = __ldg(head_w + j);
+      if (head) { w2[i] = __ldg(head_w + H + 1 + j); wq[i] = __ldg(head_w + 2 * (H + 1) + j); }
+    }
   }
-  double a1 = 0., a2 = 0., aq = 0., sb1 = 0., sb2 = 0., sbq = 0.;
-#pragma unroll 4
-  for (int i = 0; i < HB_ROWS; ++i) {
-    const long long r = r0 + i;
-    if (r >= rows) break;
-    const float g = __ldg(dE + r);
-    float dz = 0.f;
-    if (col) {
-      const float h = __ldg(hlast + r * ldh + j);
-      float dh;
-      if (head) {
-        const float ga = g * __ldg(l2v + r), gb = g * __ldg(l1v + r);
-        dh = fmaf(ga, w1, fmaf(gb, w2, 2.f * g * wq * h));
-        a1 += (double)ga * h; a2 += (double)gb * h; aq += (double)g * h * h;
-        if (j == 0) { sb1 += ga; sb2 += gb; sbq += g; }
-      } else {
-        dh = g * w1;
-        a1 += (double)g * h;
-        if (j == 0) sb1 += g;
+  double sb1 = 0., sb2 = 0., sbq = 0.;
+  for (long long r = (long long)blockIdx.x * HB_WARPS + warp; r < rows; r += W) {
+    const float g = head_g(src, r);
+    float ga = g, gb = 0.f;
+    if (head) { ga = g * __ldg(l2v + r); gb = g * __ldg(l1v + r); }
+    float h[NI];
+#pragma unroll
+    for (int i = 0; i < NI; ++i) {
+      const int j = lane + 32 * i;
+      h[i] = j < H ? __ldg(hlast + r * ldh + j) : 0.f;
+    }
+    const double dga = (double)ga, dgb = (double)gb, dg = (double)g;
+#pragma unroll
+    for (int i = 0; i < NI; ++i) {
+      const int j = lane + 32 * i;
+      float dz = 0.f;
+      if (j < H) {
+        float dh;
+        const double hd = (double)h[i];
+        if (head) {
+          dh = fmaf(ga, w1[i], fmaf(gb, w2[i], 2.f * g * wq[i] * h[i]));
+          a1[i] += dga * hd; a2[i] += dgb * hd; aq[i] += dg * hd * hd;
+        } else {
+          dh = g * w1[i];
+          a1[i] += dg * hd;
+        }
+        dz = dh * tc::act_bwd_from_h(act, h[i]);
       }
-      dz = dh * tc::act_bwd_from_h(act, h);
+      if (j < npad) {
+        if (dz_lo) {
+          float hi, lo;
+          ptx::tf32_split(dz, hi, lo);
+          dz_hi[r * npad + j] = hi;
+          dz_lo[r * npad + j] = lo;
+        } else {
+          dz_hi[r * npad + j] = dz;
+        }
+      }
     }
-    if (j < npad) {
-      float hi, lo;
-      ptx::tf32_split(dz, hi, lo);
-      dz_hi[r * npad + j] = dz_lo ? hi : dz;
-      if (dz_lo) dz_lo[r * npad + j] = lo;
-    }
+    sb1 += dga; sb2 += dgb; sbq += dg;
   }
-  if (col) {
-    atomicAdd(acc + j, a1);
-    if (head) { atomicAdd(acc + H + 1 + j, a2); atomicAdd(acc + 2 * (H + 1) + j, aq); }
-    if (j == 0) {
-      atomicAdd(acc + H, sb1);
-      if (head) { atomicAdd(acc + 2 * H + 1, sb2); atomicAdd(acc + 3 * H + 2, sbq); }
+  // fixed-order block reduction of the per-warp sums, one accumulator family at a time
+  const int head_n = head ? 3 * (H + 1) : (H + 1);
+  double* out = partial + (long long)blockIdx.x * head_n;
+  const int nacc = head ? 3 : 1;
+  for (int q = 0; q < nacc; ++q) {
+#pragma unroll
+    for (int i = 0; i < NI; ++i) red[warp][lane + 32 * i] = q == 0 ? a1[i] : (q == 1 ? a2[i] : aq[i]);
+    if (lane == 0) redb[warp][q] = q == 0 ? sb1 : (q == 1 ? sb2 : sbq);
+    __syncthreads();
+    for (int j = threadIdx.x; j <= H; j += HB_WARPS * 32) {
+      double s = 0.;
+      if (j < H) {
+#pragma unroll
+        for (int w = 0; w < HB_WARPS; ++w) s += red[w][j];
+      } else {
+#pragma unroll
+        for (int w = 0; w < HB_WARPS; ++w) s += redb[w][q];
+      }
+      out[q * (H + 1) + j] = s;
     }
+    __syncthreads();
   }
 }
 
-__global__ void __launch_bounds__(256) head_finish_kernel(const double* __restrict__ acc, int n, float* __restrict__ ghead,
-                                                          int accumulate) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) ghead[i] = accumulate ? ghead[i] + (float)acc[i] : (float)acc[i];
+// ghead[j] (+)= sum over the head_bwd blocks of partial[b][j] in a fixed order; when `loss` is set, one extra block
+// evaluates the energy-form combine forward (the step's loss) -- same code as fdsm_combine_energy_fwd.
+struct HeadLoss {
+  const float* E; long long B; float c1, scale; int mean; float* loss;
+};
+__global__ void __launch_bounds__(1024) head_finish_kernel(const double* __restrict__ partial, int nblk, int n,
+                                                           float* __restrict__ ghead, int accumulate, const HeadLoss hl) {
+  __shared__ double part[32][33];
+  __shared__ float red[32];
+  const int nb = (n + 31) / 32;
+  if ((int)blockIdx.x >= nb) {
+    combine_energy_fwd_block(hl.E, hl.B, 0, hl.c1, hl.scale, hl.mean, nullptr, hl.loss, red);
+    return;
+  }
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int j = blockIdx.x * 32 + tx;
+  double s = 0.;
+  if (j < n)
+    for (int b = ty; b < nblk; b += 32) s += partial[(long long)b * n + j];
+  part[ty][tx] = s;
+  __syncthreads();
+  if (ty == 0 && j < n) {
+    double t = 0.;
+#pragma unroll
+    for (int g = 0; g < 32; ++g) t += part[g][tx];
+    ghead[j] = accumulate ? ghead[j] + (float)t : (float)t;
+  }
 }
 
 // ---- split-K reduce: partial[s][k][n] -> gW[n][k] (+)= sum_s, gb[n] (+)= sum_s partial[s][K][n] --------------
@@ -346,9 +422,11 @@ extern "C" int fdsm_mlp_forward(const fdsm_mlp_desc* desc, const float* x_hi, co
   return FDSM_OK;
 }
 
-extern "C" int fdsm_mlp_backward(const fdsm_mlp_desc* desc, const float* x_hi, const float* x_lo, int64_t rows,
-                                 const float* params, float* workspace, const float* dE, float* grads, int32_t accumulate,
-                                 fdsm_stream_t stream) {
+namespace fdsm {
+namespace mlp {
+static int backward_impl(const fdsm_mlp_desc* desc, const float* x_hi, const float* x_lo, int64_t rows, const float* params,
+                         float* workspace, const HeadGrad& hg, const HeadLoss& hl, float* grads, int32_t accumulate,
+                         fdsm_stream_t stream) {
   Layout y;
   int rc = mlp::make_layout(desc, rows, y);
   if (rc) return rc;
@@ -358,13 +436,11 @@ extern "C" int fdsm_mlp_backward(const fdsm_mlp_desc* desc, const float* x_hi, c
     if (!accumulate) return cuda_status(cudaMemsetAsync(grads, 0, y.n_params * sizeof(float), st), "fdsm_mlp_backward");
     return FDSM_OK;
   }
-  FDSM_REQUIRE(x_hi && (x_lo || y.passes == 1 || y.raw) && dE, "fdsm_mlp_backward: NULL pointer");
+  FDSM_REQUIRE(x_hi && (x_lo || y.passes == 1 || y.raw) && (hg.dE || hg.E), "fdsm_mlp_backward: NULL pointer");
   float* ws = workspace;
   auto lo = [&](float* q) -> float* { return y.raw ? nullptr : q; };
   const int head_n = (int)(y.n_params - y.head_off);
   double* hacc = reinterpret_cast<double*>(ws + y.head_acc);
-  rc = cuda_status(cudaMemsetAsync(hacc, 0, head_n * sizeof(double), st), "fdsm_mlp_backward(memset)");
-  if (rc) return rc;
   // Two streams: the critical chain head_bwd -> dgrad_{L-1} -> ... -> dgrad_1 -> wgrad_0 stays on `stream`; the hidden
   // layers' weight gradients (wgrad_l + reduce_l, l >= 1) only need dZ_l and run on a side stream, filling the SMs the
   // 96-CTA dgrad launches leave idle and hiding their launch/fill/drain latencies.  Fork/join by events: capturable.
@@ -372,12 +448,39 @@ extern "C" int fdsm_mlp_backward(const fdsm_mlp_desc* desc, const float* x_hi, c
   const bool forked = y.L > 1 && side.ok();
   cudaStream_t sd = forked ? side.stream : st;
   const int L1 = y.L - 1;
-  mlp::head_bwd_kernel<<<(unsigned)((rows + mlp::HB_ROWS - 1) / mlp::HB_ROWS), 256, 0, st>>>(
-      ws + y.h_last, y.npad, dE, ws + y.l1, ws + y.l2, params + y.head_off, y.H, y.npad, rows, y.act, y.head,
-      ws + y.dz_hi[L1], lo(ws + y.dz_lo[L1]), hacc);
-  mlp::head_finish_kernel<<<(head_n + 255) / 256, 256, 0, st>>>(hacc, head_n, grads + y.head_off, accumulate);
-  rc = cuda_status(cudaGetLastError(), "fdsm_mlp_backward(head)");
-  if (rc) return rc;
+  {
+    const int nblk = mlp::head_blocks(rows), ni = (y.npad + 31) / 32;
+    auto launch_head = [&](auto tag) {
+      constexpr int NI = decltype(tag)::value;
+      mlp::head_bwd_kernel<NI><<<nblk, mlp::HB_WARPS * 32, 0, st>>>(
+          ws + y.h_last, y.npad, hg, ws + y.l1, ws + y.l2, params + y.head_off, y.H, y.npad, rows, y.act, y.head,
+          ws + y.dz_hi[L1], lo(ws + y.dz_lo[L1]), hacc);
+    };
+    switch (ni) {
+      case 1: launch_head(std::integral_constant<int, 1>{}); break;
+      case 2: launch_head(std::integral_constant<int, 2>{}); break;
+      case 3: launch_head(std::integral_constant<int, 3>{}); break;
+      case 4: launch_head(std::integral_constant<int, 4>{}); break;
+      case 5: launch_head(std::integral_constant<int, 5>{}); break;
+      case 6: launch_head(std::integral_constant<int, 6>{}); break;
+      case 7: launch_head(std::integral_constant<int, 7>{}); break;
+      default: launch_head(std::integral_constant<int, 8>{}); break;
+    }
+    rc = cuda_status(cudaGetLastError(), "fdsm_mlp_backward(head)");
+    if (rc) return rc;
+    // the head-gradient sums (and the loss) are off the critical chain: side stream
+    cudaStream_t sf = st;
+    if (forked) {
+      rc = cuda_status(cudaEventRecord(side.fork[(L1 + 1) & 1], st), "fdsm_mlp_backward(fork)");
+      if (!rc) rc = cuda_status(cudaStreamWaitEvent(sd, side.fork[(L1 + 1) & 1], 0), "fdsm_mlp_backward(fork)");
+      if (rc) return rc;
+      sf = sd;
+    }
+    mlp::head_finish_kernel<<<(head_n + 31) / 32 + (hl.loss ? 1 : 0), 1024, 0, sf>>>(hacc, nblk, head_n, grads + y.head_off,
+                                                                                      accumulate, hl);
+    rc = cuda_status(cudaGetLastError(), "fdsm_mlp_backward(head_finish)");
+    if (rc) return rc;
+  }
   auto wgrad = [&](int l, cudaStream_t s) -> int {
     // dWt_l[K+1 x H] = In_l^T dZ_l: split-K partials, then a fixed-order reduce + transpose into the flat gradient
     const int K = l ? y.H : y.D, kp = l ? y.kpadh : y.kpad0;
@@ -423,4 +526,30 @@ extern "C" int fdsm_mlp_backward(const fdsm_mlp_desc* desc, const float* x_hi, c
     if (rc) return rc;
   }
   return FDSM_OK;
+}
+}  // namespace mlp
+}  // namespace fdsm
+
+extern "C" int fdsm_mlp_backward(const fdsm_mlp_desc* desc, const float* x_hi, const float* x_lo, int64_t rows,
+                                 const float* params, float* workspace, const float* dE, float* grads, int32_t accumulate,
+                                 fdsm_stream_t stream) {
+  FDSM_REQUIRE(rows == 0 || dE, "fdsm_mlp_backward: dE is NULL");
+  mlp::HeadGrad hg = {dE, nullptr, 0, 0.f, 0.f};
+  mlp::HeadLoss hl = {nullptr, 0, 0.f, 0.f, 0, nullptr};
+  return mlp::backward_impl(desc, x_hi, x_lo, rows, params, workspace, hg, hl, grads, accumulate, stream);
+}
+
+extern "C" int fdsm_mlp_backward_fd_ssm(const fdsm_mlp_desc* desc, const float* x_hi, const float* x_lo, int64_t B,
+                                        const float* params, float* workspace, const float* energy, float c1, float scale,
+                                        int32_t mean, float* loss, float* grads, int32_t accumulate, fdsm_stream_t stream) {
+  FDSM_REQUIRE(B >= 0 && B < (1ll << 29), "fdsm_mlp_backward_fd_ssm: bad batch size");
+  FDSM_REQUIRE(B == 0 || energy, "fdsm_mlp_backward_fd_ssm: energy is NULL");
+  const float coef = mean && B ? scale / (float)B : scale;
+  mlp::HeadGrad hg = {nullptr, energy, B, c1, coef};
+  mlp::HeadLoss hl = {energy, B, c1, scale, mean, B ? loss : nullptr};
+  if (B == 0 && loss) {
+    int rc = cuda_status(cudaMemsetAsync(loss, 0, sizeof(float), (cudaStream_t)stream), "fdsm_mlp_backward_fd_ssm");
+    if (rc) return rc;
+  }
+  return mlp::backward_impl(desc, x_hi, x_lo, 3 * B, params, workspace, hg, hl, grads, accumulate, stream);
 }

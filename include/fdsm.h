@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define FDSM_ABI_VERSION 3
+#define FDSM_ABI_VERSION 4
 
 #define FDSM_OK 0
 #define FDSM_ERR_INVALID_ARGUMENT (-1)
@@ -206,10 +206,18 @@ int fdsm_mlp_prepare(const fdsm_mlp_desc* desc, int64_t rows, const float* param
 int fdsm_mlp_forward(const fdsm_mlp_desc* desc, const float* x_hi, const float* x_lo, int64_t rows,
                      const float* params, float* workspace, float* energy, fdsm_stream_t stream);
 /* grads (flat, same layout as params) (+)= dL/dparams given dE[rows] = dL/dE; needs the workspace of the
- * matching forward.  Deterministic (fixed-order split-K reduction) except the 3(H+1) head sums (atomics). */
+ * matching forward.  Deterministic: fixed-order split-K reduction, fixed-order fp64 head sums (no atomics). */
 int fdsm_mlp_backward(const fdsm_mlp_desc* desc, const float* x_hi, const float* x_lo, int64_t rows,
                       const float* params, float* workspace, const float* dE, float* grads, int32_t accumulate,
                       fdsm_stream_t stream);
+/* FD-SSM energy form (a1/a7: SSM/losses/efficient_sm.py:65-71, DeepEBM/ESM/loss_train.py:227-233) with the combine
+ * folded into the backward: `energy` = the forward's output on the stacked batch [x | x+v | x-v] (3B rows).
+ *   *loss = scale * mean_b|sum_b [ (E2-E3)^2/8 - E2 - E3 + c1 E1 ]   (same arithmetic as fdsm_combine_energy_fwd)
+ *   grads (+)= dloss/dparams, dE taken analytically inside the head-backward kernel (as fdsm_combine_energy_bwd).
+ * Replaces the launches combine_fwd + combine_bwd + backward(dE) of the un-fused sequence.  loss may be NULL. */
+int fdsm_mlp_backward_fd_ssm(const fdsm_mlp_desc* desc, const float* x_hi, const float* x_lo, int64_t B,
+                             const float* params, float* workspace, const float* energy, float c1, float scale,
+                             int32_t mean, float* loss, float* grads, int32_t accumulate, fdsm_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------
  * Optimizer step on the flat parameter vector (the reference's host loop, DeepEBM/train_ssm.py:65-70:

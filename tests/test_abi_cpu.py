@@ -27,7 +27,7 @@ def test_library_exports_every_declared_symbol(fdsm):
     for s in syms:
         assert hasattr(lib, s), f"libfdsm.so does not export {s}"
     assert syms == set(fdsm._lib.PROTOTYPES), "ctypes prototype table out of sync with include/*.h"
-    assert lib.fdsm_version() == 3
+    assert lib.fdsm_version() == 4
 
 
 def test_stack_args_struct_matches_header(fdsm):

@@ -149,3 +149,36 @@ def test_graph_replay_equals_eager(fdsm):
         assert float(la) == float(lb)            # same Philox draws (device step counter), same kernels
     assert torch.equal(a.flat.data, b.flat.data)
     assert int(a._opt["step"]) == 4
+
+
+@pytest.mark.parametrize("D,H,L,act,head,B", [(64, 48, 3, "nsoftplus", "quadratic", 100), (11, 30, 2, "softplus", "linear", 37),
+                                              (784, 200, 3, "nsoftplus", "quadratic", 4096)])
+def test_fused_combine_backward_equals_explicit_sequence(fdsm, D, H, L, act, head, B):
+    """fdsm_mlp_backward_fd_ssm (combine forward + analytic dE + MLP backward in one entry point) against the explicit
+    sequence combine_energy_fwd -> combine_energy_bwd -> fdsm_mlp_backward(dE): the loss is bit-identical (same block
+    reduction), the gradient is bit-identical too (same dE arithmetic, fixed-order sums) -- and twice in a row."""
+    import ctypes as C
+    from fdsm_b200 import _lib, ops
+    from fdsm_b200.mlp import _ptr, _stream
+    lib = _lib.load()
+    net = fdsm.mlp.FusedEnergyMLP(D, H, L, act=act, head=head, device=DEV, seed=5)
+    x = torch.rand(B, D, device=DEV)
+    u = torch.randn(B, D, device=DEV)
+    eps, scale = 0.05, 1.0 / 0.05 ** 2
+    loss, grad = net.fd_ssm_loss_and_grad(x, eps, scale, u=u)
+    loss1, grad1 = loss.clone(), grad.clone()
+    st = net._step_state
+    # explicit sequence on the same workspace / energies
+    l2 = torch.zeros((), device=DEV)
+    dE = torch.empty(3 * B, device=DEV)
+    g2 = torch.empty_like(grad)
+    s = _stream()
+    _lib.check(lib.fdsm_combine_energy_fwd(_ptr(st["E"]), B, 0, 2.0, scale, 1, None, _ptr(l2), s), "fwd")
+    _lib.check(lib.fdsm_combine_energy_bwd(_ptr(st["E"]), B, 0, 2.0, scale, 1, None, _ptr(dE), s), "bwd")
+    _lib.check(lib.fdsm_mlp_backward(C.byref(net.desc), _ptr(st["xh"]), _ptr(st["xl"]), 3 * B, _ptr(net.flat.data), _ptr(st["ws"]),
+                                     _ptr(dE), _ptr(g2), 0, s), "mlp_bwd")
+    torch.cuda.synchronize()
+    assert float(loss1) == float(l2)
+    assert torch.equal(grad1, g2)
+    loss3, grad3 = net.fd_ssm_loss_and_grad(x, eps, scale, u=u)
+    assert float(loss3) == float(loss1) and torch.equal(grad3, grad1)      # deterministic: no atomics anywhere
