@@ -81,6 +81,9 @@ PROTOTYPES = {
     "fdsm_mlp_prepare": (C.c_int, [C.POINTER(MlpDesc), _i64, _f32p, _f32p, _stream]),
     "fdsm_mlp_forward": (C.c_int, [C.POINTER(MlpDesc), _f32p, _f32p, _i64, _f32p, _f32p, _f32p, _stream]),
     "fdsm_mlp_backward": (C.c_int, [C.POINTER(MlpDesc), _f32p, _f32p, _i64, _f32p, _f32p, _f32p, _f32p, _i32, _stream]),
+    "fdsm_peer_buffer_bytes": (C.c_int64, [_i64, _i32]),
+    "fdsm_peer_allreduce": (C.c_int, [_f32p, _f32p, _i64, C.POINTER(C.c_void_p), _i32, _i32, _f32, _f32p, C.c_void_p,
+                                      C.c_void_p, _stream]),
     "fdsm_mlp_backward_fd_ssm": (C.c_int, [C.POINTER(MlpDesc), _f32p, _f32p, _i64, _f32p, _f32p, _f32p, _f32, _f32, _i32,
                                            _f32p, _f32p, _i32, _stream]),
 }
@@ -97,11 +100,12 @@ def load():
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(LIB_PATH):
+    path = os.environ.get("FDSM_LIB", LIB_PATH)     # A/B builds of the same ABI (profiling); default: the in-tree library
+    if not os.path.exists(path):
         raise FdsmError(
             f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
             "(or `make -C fd-scorematching_b200/csrc`).  There is no CPU/PyTorch fallback.")
-    lib = C.CDLL(LIB_PATH)
+    lib = C.CDLL(path)
     for name, (res, args) in PROTOTYPES.items():
         fn = getattr(lib, name)  # AttributeError if the symbol is missing
         fn.restype, fn.argtypes = res, args

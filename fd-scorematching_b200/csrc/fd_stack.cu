@@ -133,6 +133,14 @@ __global__ void __launch_bounds__(kBlock) stack_kernel(fdsm_stack_args a) {
     }
     float nrm = 1.f;
     if (need_norm) nrm = sqrtf(group_sum<G>(ss, red));  // uniform branch: all threads take it
+    // Injected directions (parity with the reference's torch ops) keep its rounding sequence u / ||u|| * eps with IEEE
+    // division per element; for in-kernel Philox draws there is no reference bit pattern to match, so the row uses one
+    // division (eps / ||u||) and a multiply per element: ~40 fewer instructions per float4 (the kernel is issue-bound).
+#ifndef FDSM_FAST_NORMALISE
+#define FDSM_FAST_NORMALISE 1
+#endif
+    const bool exact_div = !FDSM_FAST_NORMALISE || a.dir != nullptr;
+    const float inv = need_norm && !exact_div ? __fdiv_rn(a.dir_scale, nrm) : 0.f;
 
     // ---- pass 2: build rows -----------------------------------------------------------------
     float dot = 0.f;
@@ -141,7 +149,9 @@ __global__ void __launch_bounds__(kBlock) stack_kernel(fdsm_stack_args a) {
       if (a.sigma) sig = a.labels ? __ldg(a.sigma + __ldg(a.labels + b)) : __ldg(a.sigma + b);
       const float* xrow = a.x ? a.x + b * a.ldx : nullptr;
       auto emit = [&](int j, float4 dc, float4 base) {
-        const float4 v = need_norm ? normalise(dc, nrm, a.dir_scale) : dc;
+        const float4 v = !need_norm ? dc
+                         : exact_div ? normalise(dc, nrm, a.dir_scale)
+                                     : make_float4(dc.x * inv, dc.y * inv, dc.z * inv, dc.w * inv);
         if (a.sigma) {
           const float4 n = raw_noise<VEC>(a, b, j);
           const float4 sn = make_float4(__fmul_rn(sig, n.x), __fmul_rn(sig, n.y), __fmul_rn(sig, n.z),

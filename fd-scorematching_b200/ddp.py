@@ -71,3 +71,64 @@ def broadcast_params_(flat):
     """Once, at step 0.  Replicas then stay bit-identical because they apply identical averaged grads."""
     if is_distributed():
         dist.broadcast(flat, src=0)
+
+
+class PeerAllReduce:
+    """The gradient exchange as ONE kernel over NVLink peer memory (`fdsm_peer_allreduce`, csrc/fd_peer.cu): every rank
+    pushes its flat gradient into the peers' receive slots, then sums the slots in rank order -- fused with the
+    squared-norm partials of the clip and the optimizer's step counter.  Graph-capturable, so a distributed training step
+    is a single CUDA-graph replay.  The receive buffers are torch symmetric memory (peer-mapped over NVLink)."""
+
+    fused_sumsq = True
+
+    def __init__(self, n, device, group=None):
+        import ctypes as C
+        import torch.distributed._symmetric_memory as symm
+        from . import _lib
+        self._C, self._lib = C, _lib.load()
+        group = dist.group.WORLD if group is None else group
+        self.world, self.rank, self.n = dist.get_world_size(group), dist.get_rank(group), int(n)
+        nbytes = self._lib.fdsm_peer_buffer_bytes(self.n, self.world)
+        if nbytes < 0:
+            raise ValueError(f"world size {self.world} not supported by fdsm_peer_allreduce")
+        self.buf = symm.empty(nbytes // 4, dtype=torch.float32, device=device)
+        self.hdl = symm.rendezvous(self.buf, group)
+        self.buf.zero_()
+        self.scratch = torch.zeros(4 + 128, dtype=torch.int32, device=device)
+        torch.cuda.synchronize(device)
+        dist.barrier(group)                       # nobody pushes before every receive buffer is zeroed
+        ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        self._ptrs = (C.c_void_p * self.world)(*ptrs)
+
+    def __call__(self, grad, sumsq=None, step=None, out=None):
+        C = self._C
+        out = grad if out is None else out
+        if grad.numel() != self.n or grad.dtype != torch.float32 or not grad.is_contiguous():
+            raise ValueError("PeerAllReduce: gradient must be the contiguous fp32 vector it was sized for")
+        p = lambda t: C.c_void_p(t.data_ptr()) if t is not None else None
+        rc = self._lib.fdsm_peer_allreduce(p(grad), p(out), self.n, self._ptrs, self.rank, self.world, 1.0 / self.world,
+                                           p(sumsq), p(step), p(self.scratch),
+                                           C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        if rc:
+            from ._lib import check
+            check(rc, "fdsm_peer_allreduce")
+        return out
+
+    def timed_out(self):
+        """True if any launch gave up waiting for a peer (host sync)."""
+        return bool(int(self.scratch[2]))
+
+
+def make_allreduce(n, device):
+    """The exchange step for a flat fp32 gradient of n elements: the peer-memory kernel when the ranks share an NVLink
+    domain (FDSM_ALLREDUCE=nccl forces the NCCL library collective), else NCCL."""
+    import os
+    import sys
+    if not is_distributed():
+        return allreduce_mean_
+    if os.environ.get("FDSM_ALLREDUCE", "peer") != "nccl" and torch.device(device).type == "cuda":
+        try:
+            return PeerAllReduce(n, device)
+        except Exception as e:   # no P2P / symmetric memory on this box: library collective
+            print(f"[fdsm] peer all-reduce unavailable ({type(e).__name__}: {e}); using NCCL", file=sys.stderr)
+    return allreduce_mean_

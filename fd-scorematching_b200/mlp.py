@@ -226,19 +226,20 @@ class FusedEnergyMLP(nn.Module):
         o = self._opt
         return self.fd_ssm_loss_and_grad(st["x"], eps, scale, draw=(o["seed"], 0, o["rank"] * st["B"]), offset_dev=o["step"])
 
-    def _apply_update(self, st):
+    def _apply_update(self, st, have_sumsq=False):
         lib, o = _lib.load(), self._opt
         n, s = self.flat.numel(), _stream()
-        ops._count(2)
-        check(lib.fdsm_grad_sumsq(_ptr(st["grad"]), n, _ptr(o["sumsq"]), _ptr(o["step"]), s), "fdsm_grad_sumsq")
+        ops._count(1 if have_sumsq else 2)
+        if not have_sumsq:
+            check(lib.fdsm_grad_sumsq(_ptr(st["grad"]), n, _ptr(o["sumsq"]), _ptr(o["step"]), s), "fdsm_grad_sumsq")
         check(lib.fdsm_adam_step(_ptr(self.flat.data), _ptr(st["grad"]), _ptr(o["m"]), _ptr(o["v"]), n, o["lr"], _ptr(o["lr_dev"]),
                                  o["betas"][0], o["betas"][1], o["eps"], o["clip"], _ptr(o["sumsq"]), _ptr(o["step"]), s),
               "fdsm_adam_step")
 
     def fd_ssm_step(self, x, eps, allreduce=None, scale=None, distributed=False):
         """One optimisation step of DeepEBM/train_ssm.py:63-69 on a device batch x (B, ...).  Returns the loss (device
-        scalar, persistent buffer).  world == 1: the whole step is ONE CUDA-graph replay; world > 1: two replays around
-        the single gradient all-reduce."""
+        scalar, persistent buffer).  The whole step is ONE CUDA-graph replay -- also for world > 1 when `allreduce` is the
+        peer-memory kernel (ddp.PeerAllReduce); with the NCCL library collective it is two replays around the all-reduce."""
         x2 = x.reshape(x.shape[0], -1)
         B = x2.shape[0]
         st = self._state(B, x2.device)
@@ -246,12 +247,22 @@ class FusedEnergyMLP(nn.Module):
             st["x"] = torch.empty_like(x2)
         scale = 1.0 / eps ** 2 if scale is None else scale
         st["x"].copy_(x2)
-        key = (B, float(eps), float(scale), bool(distributed))
+        peer = distributed and getattr(allreduce, "fused_sumsq", False)    # ddp.PeerAllReduce: capturable, emits the sumsq
+        key = (B, float(eps), float(scale), bool(distributed), bool(peer))
+
+        def exchange_and_update():
+            if peer:
+                allreduce(st["grad"], sumsq=self._opt["sumsq"], step=self._opt["step"])
+                ops._count(1)
+                self._apply_update(st, have_sumsq=True)
+            else:
+                self._apply_update(st)
+
         if not self._opt["use_graph"]:
             self._loss_and_grad_captured(st, eps, scale)
-            if distributed and allreduce is not None:
+            if distributed and allreduce is not None and not peer:
                 allreduce(st["grad"])
-            self._apply_update(st)
+            exchange_and_update()
             return st["loss"]
         if key not in self._graphs:
             # warm-up outside capture (module-level one-time setup inside the library), then capture
@@ -264,11 +275,12 @@ class FusedEnergyMLP(nn.Module):
             torch.cuda.current_stream().wait_stream(side)
             launches0 = ops.LAUNCHES
             g1, g2 = torch.cuda.CUDAGraph(), None
+            one_graph = not distributed or peer
             with torch.cuda.graph(g1):
                 self._loss_and_grad_captured(st, eps, scale)
-                if not distributed:
-                    self._apply_update(st)
-            if distributed:
+                if one_graph:
+                    exchange_and_update()
+            if not one_graph:
                 g2 = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(g2):
                     self._apply_update(st)

@@ -21,6 +21,7 @@ class FDSSMTrainer:
             self.opt = torch.optim.Adam([self.flat.flat], lr=lr, betas=betas, fused=self.flat.flat.is_cuda)
             self.flat.flat.grad = self.flat.grad
         ddp.broadcast_params_(self.flat.flat.data)
+        self._allreduce = ddp.make_allreduce(self.flat.flat.numel(), self.flat.flat.device) if self.fused else ddp.allreduce_mean_
         ops.manual_seed(seed)
         self._rank = rank
         self._copy_stream = None
@@ -31,7 +32,7 @@ class FDSSMTrainer:
         B = x.shape[0]
         ops.set_row_offset(self._rank * B)
         if self.fused:
-            return self.net.fd_ssm_step(x, eps=self.eps, allreduce=ddp.allreduce_mean_, distributed=ddp.is_distributed())
+            return self.net.fd_ssm_step(x, eps=self.eps, allreduce=self._allreduce, distributed=ddp.is_distributed())
         self.flat.zero_grad()
         loss = losses.ssm_fd(self.net, x, eps=self.eps, batch_size=B)
         loss.backward()

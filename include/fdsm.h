@@ -234,6 +234,25 @@ int fdsm_adam_step(float* params, const float* grads, float* exp_avg, float* exp
                    const float* lr_dev, float beta1, float beta2, float eps, float max_norm, const float* sumsq,
                    const int64_t* step_counter, fdsm_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------
+ * The step's single exchange over NVLink peer memory: all-reduce of the flat fp32 gradient
+ * (sum over ranks in rank order, times `scale`), fused with the squared-norm partials fdsm_adam_step reads and the
+ * step-counter increment.  Replaces the reference's nn.DataParallel gradient reduction
+ * (DeepEBM/train_ssm.py:33-34) and, in this package, grad.mul_(1/W) + ncclAllReduce + fdsm_grad_sumsq.
+ *
+ * peer_buffers[r] = address, valid on THIS device, of rank r's receive buffer (fdsm_peer_buffer_bytes(n, world)
+ * bytes, zero-filled once before the first call on any rank; e.g. torch symmetric memory or cudaIpc mappings).
+ * scratch: >= 4*(4 + FDSM_PEER_MAX_BLOCKS) bytes of LOCAL device memory, zero-filled once; scratch[2] != 0 after a
+ * launch means a peer did not arrive within 20 s (the kernel gives up instead of hanging the GPU).
+ * out may alias grad.  Every rank must call it the same number of times with the same n.  Graph-capturable.
+ * Results are bit-identical on every rank. */
+#define FDSM_PEER_MAX_WORLD 8
+#define FDSM_PEER_MAX_BLOCKS 128
+int64_t fdsm_peer_buffer_bytes(int64_t n, int32_t world);
+int fdsm_peer_allreduce(const float* grad, float* out, int64_t n, void* const* peer_buffers, int32_t rank,
+                        int32_t world, float scale, float* sumsq, int64_t* step_counter, uint32_t* scratch,
+                        fdsm_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

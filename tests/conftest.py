@@ -22,3 +22,11 @@ def golden():
 def fdsm():
     import fdsm_b200
     return fdsm_b200
+
+
+@pytest.fixture(autouse=True)
+def _seed_everything():
+    """Every test starts from the same torch RNG state (CPU and CUDA): no test outcome depends on test order."""
+    import torch
+    torch.manual_seed(20260101)
+    yield

@@ -116,7 +116,9 @@ def test_stack_noised_matches_torch(fdsm, B, D, dot_mode):
 
 
 def test_stack_philox_fused_equals_two_step(fdsm):
-    """Philox-mode fused build == standalone Philox draws fed through the injected path."""
+    """Philox-mode fused build == standalone Philox draws fed through the injected path, up to the normalisation's last
+    bit: injected directions divide per element (the reference's rounding sequence), in-kernel draws multiply by one
+    per-row reciprocal (no reference bit pattern exists for them)."""
     B, D = 32, 784
     x = torch.rand(B, D, device=_dev())
     draw = (99, 4, 100)
@@ -125,7 +127,9 @@ def test_stack_philox_fused_equals_two_step(fdsm):
     u = fdsm.ops.philox_normal(B, D, 0, *draw)
     n = fdsm.ops.philox_normal(B, D, 1, *draw)
     out2, v2, dot2 = fdsm.ops.stack(x, row_mask=6, scale=0.1, direction=u, noise=n, sigma=sig, want_v=True, want_dot=True)
-    assert torch.equal(out, out2) and torch.equal(v, v2) and torch.equal(dot, dot2)
+    torch.testing.assert_close(v, v2, rtol=3e-7, atol=0)
+    torch.testing.assert_close(out, out2, rtol=0, atol=1.2e-7)        # rows in [0, 1.1]: at most one ulp
+    torch.testing.assert_close(dot, dot2, rtol=1e-5, atol=1e-7)
 
 
 @pytest.mark.parametrize("B", [1, 5, 1024, 4099])

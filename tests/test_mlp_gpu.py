@@ -106,7 +106,7 @@ def test_fused_step_on_exact_quadratic_energy(fdsm):
     B, D, H = 4096, 784, 64
     net = fdsm.mlp.FusedEnergyMLP(D, H, 1, act="elu", head="quadratic", device=DEV, seed=3)
     v = net.named_views()
-    v["fc1.weight"].mul_(0.02); v["fc1.bias"].fill_(2.0)          # pre-activations stay > 0: ELU is the identity
+    v["fc1.weight"].mul_(0.5); v["fc1.bias"].fill_(2.0)           # pre-activations stay in 2 +- 0.8 > 0: ELU is the identity
     x = torch.rand(B, D, device=DEV)
     u = torch.randn(B, D, device=DEV)
     losses = [float(net.fd_ssm_loss_and_grad(x, eps, D / eps ** 2, u=u)[0]) for eps in (0.2, 0.1)]
