@@ -9,11 +9,15 @@
 //
 // Pipeline (per k-block i; r = i % R raw slots, l = i % 2 lo slots):
 //   warp 0   TMA: waits raw_empty[r], loads raw A|B tiles into raw slot r (raw_full[r], expect-tx)
-//   warps 2-7 converters: wait raw_full[r] and lo_empty[l]; x -> hi = rna_tf32(x) rewritten IN PLACE, lo =
-//            rna_tf32(x - hi) into lo slot l (elementwise, so the TMA swizzle is irrelevant); fence.proxy.async;
-//            arrive conv[l]
+//   warps 2-7 converters: wait raw_full[r] and lo_empty[l]; the raw fp32 tile IS the hi operand (kind::tf32 ignores the
+//            13 low mantissa bits: hi = trunc_tf32(x), nothing to write back); lo = rna_tf32(x - trunc_tf32(x)) into lo
+//            slot l (elementwise, so the TMA swizzle is irrelevant); fence.proxy.async; arrive conv[l]
+//            (-DFDSM_RAW_REWRITE_HI=1: hi = rna_tf32(x) rewritten in place -- bit-identical to the pre-split kernel but
+//            42 KB more shared-memory traffic per k-block; the main loop is shared-memory-port bound: 297 -> 255 KB
+//            per k-block, measured 28.6 -> 24.1 us on the layer-1 forward GEMM)
 //   warp 1   MMA: waits conv[l]; hi*hi + hi*lo + lo*hi per UMMA_K; tcgen05.commit -> raw_empty[r], lo_empty[l]
-// Results are bit-identical to the pre-split kernel fed by ptx::tf32_split (same rounding, same MMA order).
+// Same MMA order as the pre-split kernel; the split differs in the last bit of hi (truncation instead of round-to-
+// nearest), so results agree with it to fp32 rounding, not bit for bit (tests/test_tc_gemm_gpu.py).
 #pragma once
 #include "tc_gemm.cuh"
 
@@ -22,7 +26,7 @@ namespace tc {
 
 constexpr int LO_SLOTS = 2;
 #ifndef FDSM_RAW_REWRITE_HI
-#define FDSM_RAW_REWRITE_HI 1
+#define FDSM_RAW_REWRITE_HI 0
 #endif
 constexpr int CONV_WARP0 = 2;                       // warps [2, 8) convert
 constexpr int CONV_WARPS = kThreads / 32 - CONV_WARP0;
