@@ -86,7 +86,8 @@ inline int make_layout(const fdsm_mlp_desc* d, long long rows, Layout& y) {
     y.wt_lo[l] = take((long long)kp * y.npad);
     y.wt_raw[l] = take((long long)kp * y.npad);
     // wgrad: M = K_l + 1 rows of dWt in tiles of 128, contraction over `rows` in k-blocks of 32
-    const int mt = (int)((l ? y.H : y.D) + 1 + tc::BM - 1) / tc::BM;
+    int mt = (int)((l ? y.H : y.D) + 1 + tc::BM - 1) / tc::BM;
+    if (y.raw && tc::pair_mode() && mt >= 2) mt = (mt + 1) & ~1;   // CTA pairs: the grid's x extent is padded to even
     const long long kblocks = (rows + tc::BK - 1) / tc::BK;
     long long s = (2ll * sm_count() / 2) / mt;   // ~one CTA per SM
     if (s > kblocks) s = kblocks;

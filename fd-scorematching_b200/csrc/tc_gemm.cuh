@@ -42,7 +42,7 @@ struct alignas(64) GemmParams {
   int BN;                   // UMMA N (multiple of 16, <= 256, >= N - n0 for the last tile)
   int a_major, b_major;
   int passes;               // 1 or 3
-  int raw_slots, slot_bytes;  // gemm_raw_kernel only: raw ring depth and bytes per slot
+  int raw_slots, lo_slots, slot_bytes;  // gemm_raw_kernel only: raw / lo ring depths and bytes per slot
   unsigned long long* trace;  // debug: per-CTA phase timestamps (8 per CTA), NULL in production
   int epi, act;
   float* out_hi; float* out_lo; long long ldo; long long split_stride; int out_cols;

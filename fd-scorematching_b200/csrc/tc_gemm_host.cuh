@@ -2,6 +2,7 @@
 #pragma once
 #include <cudaTypedefs.h>
 
+#include <cstdlib>
 #include <mutex>
 
 #include "tc_gemm_raw.cuh"
@@ -63,6 +64,27 @@ inline int& trace_launch_index() {
   return idx;
 }
 
+// CTA pairs (cta_group::2) are OPT-IN (FDSM_GEMM_PAIR=1 in the environment, read once).  Measured on B200
+// (profiles/r01_gemm_pair_vs_single.txt): correct, and 7% faster on a deep-K 4096^3 problem, but every kind::tf32 MMA is
+// only K=8 deep and the paired instruction carries a fixed cross-SM cost: the config-2 shapes (25 / 7 k-blocks per CTA)
+// run at ~1.3 us per k-block against 0.96 us for the single-CTA kernel, so the single-CTA kernel stays the default.
+inline bool pair_mode() {
+  static const bool on = [] {
+    const char* e = getenv("FDSM_GEMM_PAIR");
+    return e && e[0] == '1';
+  }();
+  return on;
+}
+
+inline int lo_slots_override() {
+  static const int v = [] {
+    const char* e = getenv("FDSM_GEMM_LO_SLOTS");
+    const int x = e ? atoi(e) : 0;
+    return x >= 1 && x <= MAX_LO_SLOTS ? x : 0;
+  }();
+  return v;
+}
+
 struct Operand {
   const float* hi; const float* lo; long long ld; int major;   // MAJOR_K: [R x K] row-major; MAJOR_MN: [K x R] row-major
 };
@@ -94,22 +116,56 @@ inline int launch_gemm(GemmParams& p, const Operand& A, const Operand& B, int M,
   if (raw) {
     static std::once_flag once_raw;
     std::call_once(once_raw, [] {
-#define FDSM_SET_SMEM_RAW(E) cudaFuncSetAttribute(gemm_raw_kernel<E>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 5 * 1024)
+#define FDSM_SET_SMEM_RAW(E)                                                                                                 \
+  cudaFuncSetAttribute(gemm_raw_kernel<E, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 5 * 1024);       \
+  cudaFuncSetAttribute(gemm_raw_kernel<E, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 5 * 1024)
       FDSM_SET_SMEM_RAW(EPI_STORE); FDSM_SET_SMEM_RAW(EPI_ACT_SPLIT); FDSM_SET_SMEM_RAW(EPI_HEAD); FDSM_SET_SMEM_RAW(EPI_DACT_SPLIT);
 #undef FDSM_SET_SMEM_RAW
     });
-    p.trace = trace_buffer() ? trace_buffer() + (size_t)TRACE_STRIDE * trace_launch_index()++ : nullptr;
-    p.slot_bytes = raw_slot_bytes(BN, B.major);
-    p.raw_slots = MAX_RAW_SLOTS;
-    while (p.raw_slots > 1 && raw_smem_total(p.raw_slots, p.slot_bytes) > 227 * 1024 - 5 * 1024) --p.raw_slots;
-    const int smem_raw = raw_smem_total(p.raw_slots, p.slot_bytes);
-    switch (p.epi) {
-      case EPI_STORE: gemm_raw_kernel<EPI_STORE><<<grid, kThreads, smem_raw, st>>>(p); break;
-      case EPI_ACT_SPLIT: gemm_raw_kernel<EPI_ACT_SPLIT><<<grid, kThreads, smem_raw, st>>>(p); break;
-      case EPI_HEAD: gemm_raw_kernel<EPI_HEAD><<<grid, kThreads, smem_raw, st>>>(p); break;
-      default: gemm_raw_kernel<EPI_DACT_SPLIT><<<grid, kThreads, smem_raw, st>>>(p); break;
+    // CTA pairs (cta_group::2) whenever there are at least two M tiles; an odd tile count is padded by one CTA whose rows
+    // are all out of range (TMA zero fill, nothing stored)
+    const bool pair = pair_mode() && grid.x >= 2;
+    if (pair) {
+      grid.x = (grid.x + 1) & ~1u;
+      if (B.major == MAJOR_K) {   // this CTA stages BN/2 rows of B: rebuild the map with the half-height box
+        rc = make_tmap(&p.tb_hi, B.hi, N, K, B.ld, BN / 2, false, "tc_gemm B");
+        if (rc) return rc;
+      }
     }
-    FDSM_LAUNCH_CHECK("tc_gemm(raw)");
+    p.trace = trace_buffer() ? trace_buffer() + (size_t)TRACE_STRIDE * trace_launch_index()++ : nullptr;
+    p.slot_bytes = raw_slot_bytes(pair ? BN / 2 : BN, B.major);
+    // ring depths: a CTA pair hands every k-block across two SMs (remote arrive -> MMA -> multicast commit), so it wants
+    // a deeper lo ring (3) than the single CTA (2); the raw ring takes what is left (>= 2: TMA latency)
+    const int budget = 227 * 1024 - 5 * 1024;
+    p.lo_slots = lo_slots_override() > 0 ? lo_slots_override() : (pair ? 3 : 2);
+    p.raw_slots = MAX_RAW_SLOTS;
+    while (p.raw_slots > 1 && raw_smem_total(p.raw_slots, p.lo_slots, p.slot_bytes) > budget) --p.raw_slots;
+    while (p.raw_slots < 2 && p.lo_slots > 2) {
+      --p.lo_slots;
+      p.raw_slots = MAX_RAW_SLOTS;
+      while (p.raw_slots > 1 && raw_smem_total(p.raw_slots, p.lo_slots, p.slot_bytes) > budget) --p.raw_slots;
+    }
+    const int smem_raw = raw_smem_total(p.raw_slots, p.lo_slots, p.slot_bytes);
+    // the epilogue stages the 128 x BN output tile in the pipeline's shared memory
+    FDSM_REQUIRE(BM * (((BN + CW - 1) / CW) * CW + 4) * 4 <= (p.raw_slots + p.lo_slots) * p.slot_bytes,
+                 "tc_gemm: output staging tile does not fit the pipeline's shared memory (BN=%d)", BN);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = smem_raw; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = pair ? 2 : 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    cudaError_t e;
+#define FDSM_LAUNCH_RAW(E) \
+  e = pair ? cudaLaunchKernelEx(&cfg, gemm_raw_kernel<E, true>, p) : cudaLaunchKernelEx(&cfg, gemm_raw_kernel<E, false>, p)
+    switch (p.epi) {
+      case EPI_STORE: FDSM_LAUNCH_RAW(EPI_STORE); break;
+      case EPI_ACT_SPLIT: FDSM_LAUNCH_RAW(EPI_ACT_SPLIT); break;
+      case EPI_HEAD: FDSM_LAUNCH_RAW(EPI_HEAD); break;
+      default: FDSM_LAUNCH_RAW(EPI_DACT_SPLIT); break;
+    }
+#undef FDSM_LAUNCH_RAW
+    return cuda_status(e, "tc_gemm(raw)");
   }
   const int smem = SmemLayout::total(passes);
   static std::once_flag once;

@@ -24,7 +24,7 @@
 namespace fdsm {
 namespace tc {
 
-constexpr int LO_SLOTS = 2;
+constexpr int MAX_LO_SLOTS = 4;   // lo ring depth is a launch parameter (GemmParams::lo_slots), barriers are laid out for the maximum
 #ifndef FDSM_RAW_REWRITE_HI
 #define FDSM_RAW_REWRITE_HI 0
 #endif
@@ -38,7 +38,7 @@ __host__ __device__ inline int raw_b_tile_bytes(int BN, int b_major) {
 __host__ __device__ inline int raw_slot_bytes(int BN, int b_major) {
   return A_TILE_BYTES + ((raw_b_tile_bytes(BN, b_major) + 1023) & ~1023);
 }
-__host__ inline int raw_smem_total(int raw_slots, int slot_bytes) { return (raw_slots + LO_SLOTS) * slot_bytes + 1024 + 256; }
+__host__ inline int raw_smem_total(int raw_slots, int lo_slots, int slot_bytes) { return (raw_slots + lo_slots) * slot_bytes + 1024 + 256; }
 
 __device__ __forceinline__ void trace_stamp(const GemmParams& p, int slot) {
   if (p.trace) {
@@ -49,9 +49,16 @@ __device__ __forceinline__ void trace_stamp(const GemmParams& p, int slot) {
   }
 }
 
-template <int EPI>
+// PAIR = true: launched as clusters of 2 CTAs along x (cta_group::2).  The pair computes a 256 x BN tile with ONE MMA stream
+// issued by the leader (cluster rank 0): each CTA stages its own 128 rows of A and HALF of the B tile (BN/2 columns) and
+// converts them locally; the tensor cores of both SMs read both halves of B.  Per SM and k-block the shared-memory port
+// moves 16+13 KB (TMA) + 29 (converter reads) + 29 (lo writes) + 12 x 7.3 KB (MMA operand reads) = 175 KB instead of
+// 255 KB: the main loop is bound by that port.
+template <int EPI, bool PAIR>
 __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_constant__ GemmParams p) {
   using namespace ptx;
+  const uint32_t crank = PAIR ? cluster_ctarank() : 0u;     // 0 = leader
+  const int BNL = PAIR ? p.BN / 2 : p.BN;                   // B-tile columns staged by THIS CTA
   __shared__ float head_smem[EPI == EPI_HEAD ? 3 * HW_STRIDE : 1];
   if constexpr (EPI == EPI_HEAD) {
     const int nh = p.head_mode ? 3 : 1;
@@ -65,26 +72,28 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
   const uint32_t base = (raw + 1023u) & ~1023u;
   uint8_t* gen = smem_raw + (base - raw);
   const uint32_t lo_base = base + R * SLOT;
+  const int LO_SLOTS = p.lo_slots;
   const uint32_t bars = base + (R + LO_SLOTS) * SLOT;
   // barriers: raw_full[4] raw_empty[4] conv[2] lo_empty[2] tmem_full ; then the TMEM base pointer
   auto raw_full = [&](int s) { return bars + 8u * s; };
   auto raw_empty = [&](int s) { return bars + 8u * (MAX_RAW_SLOTS + s); };
   auto conv_bar = [&](int s) { return bars + 8u * (2 * MAX_RAW_SLOTS + s); };
-  auto lo_empty = [&](int s) { return bars + 8u * (2 * MAX_RAW_SLOTS + LO_SLOTS + s); };
-  const uint32_t tmem_full_bar = bars + 8u * (2 * MAX_RAW_SLOTS + 2 * LO_SLOTS);
+  auto lo_empty = [&](int s) { return bars + 8u * (2 * MAX_RAW_SLOTS + MAX_LO_SLOTS + s); };
+  const uint32_t tmem_full_bar = bars + 8u * (2 * MAX_RAW_SLOTS + 2 * MAX_LO_SLOTS);
   volatile uint32_t* tmem_ptr_smem =
-      reinterpret_cast<volatile uint32_t*>(gen + (R + LO_SLOTS) * SLOT + 8 * (2 * MAX_RAW_SLOTS + 2 * LO_SLOTS + 1));
+      reinterpret_cast<volatile uint32_t*>(gen + (R + LO_SLOTS) * SLOT + 8 * (2 * MAX_RAW_SLOTS + 2 * MAX_LO_SLOTS + 1));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m0 = blockIdx.x * BM, n0 = blockIdx.y * p.BN;
   const int kblocks = (p.K + BK - 1) / BK;
   const int kb0 = (int)((long long)kblocks * blockIdx.z / gridDim.z);
   const int kb1 = (int)((long long)kblocks * (blockIdx.z + 1) / gridDim.z);
-  const int b_bytes = raw_b_tile_bytes(p.BN, p.b_major);
+  const int b_bytes = raw_b_tile_bytes(BNL, p.b_major);
+  const int nb0 = n0 + (int)crank * BNL;                    // first B column staged by this CTA
 
   // TMA producer state; the first R k-blocks are requested BEFORE the CTA-wide setup barrier (TMEM allocation takes
   // ~0.5 us and the first load ~2 us: they overlap instead of adding up).
-  const int b_boxes_mn = (p.BN + 31) / 32;
+  const int b_boxes_mn = (BNL + 31) / 32;
   auto issue_loads = [&](int kb, int r) {
     const uint32_t a_dst = base + r * SLOT, b_dst = a_dst + A_TILE_BYTES;
     const uint32_t fb = raw_full(r);
@@ -96,9 +105,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
       for (int i = 0; i < BM / 32; ++i) tma_load_2d(a_dst + i * 4096, &p.ta_hi, fb, m0 + 32 * i, k0);
     }
     if (p.b_major == MAJOR_K) {
-      tma_load_2d(b_dst, &p.tb_hi, fb, k0, n0);
+      tma_load_2d(b_dst, &p.tb_hi, fb, k0, nb0);
     } else {
-      for (int i = 0; i < b_boxes_mn; ++i) tma_load_2d(b_dst + i * 4096, &p.tb_hi, fb, n0 + 32 * i, k0);
+      for (int i = 0; i < b_boxes_mn; ++i) tma_load_2d(b_dst + i * 4096, &p.tb_hi, fb, nb0 + 32 * i, k0);
     }
   };
   const int pre = min(R, kb1 - kb0);
@@ -108,16 +117,20 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
       mbar_init(raw_empty(s), 1);
     }
     for (int s = 0; s < LO_SLOTS; ++s) {
-      mbar_init(conv_bar(s), CONV_WARPS);
+      mbar_init(conv_bar(s), PAIR ? 2 * CONV_WARPS : CONV_WARPS);   // pair: the peer's converters arrive on the leader's
       mbar_init(lo_empty(s), 1);
     }
     mbar_init(tmem_full_bar, 1);
     fence_barrier_init();
     for (int i = 0; i < pre; ++i) issue_loads(kb0 + i, i);
   }
-  if (warp == 2) tmem_alloc(smem_u32((const void*)tmem_ptr_smem), TMEM_COLS);
+  if (warp == 2) {
+    if constexpr (PAIR) tmem_alloc_pair(smem_u32((const void*)tmem_ptr_smem), TMEM_COLS);
+    else tmem_alloc(smem_u32((const void*)tmem_ptr_smem), TMEM_COLS);
+  }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (PAIR) cluster_sync_all();   // both CTAs' barriers are initialised before any remote arrive / multicast commit
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
   if (threadIdx.x == 0) trace_stamp(p, 1);   // setup done
@@ -134,9 +147,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (one thread) ================================================================
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc_tf32(BM, p.BN, p.a_major, p.b_major);
+    // ===== MMA issuer (one thread; pair: of the leader CTA only) ===================================
+    if (lane == 0 && crank == 0) {
+      const uint32_t idesc = make_idesc_tf32(PAIR ? 2 * BM : BM, p.BN, p.a_major, p.b_major);
       const uint32_t a_lbo = p.a_major == MAJOR_K ? 16u : 4096u, b_lbo = p.b_major == MAJOR_K ? 16u : 4096u;
       const uint32_t a_step = p.a_major == MAJOR_K ? 32u : 1024u, b_step = p.b_major == MAJOR_K ? 32u : 1024u;
       const uint32_t a_sbo = p.a_major == MAJOR_K ? 1024u : 512u, b_sbo = p.b_major == MAJOR_K ? 1024u : 512u;
@@ -144,7 +157,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
       int r = 0, l = 0;
       uint32_t lphase = 0;
       for (int kb = kb0; kb < kb1; ++kb) {
-        mbar_wait(conv_bar(l), lphase);
+        if constexpr (PAIR) mbar_wait_cluster(conv_bar(l), lphase);
+        else mbar_wait(conv_bar(l), lphase);
         tc_fence_after();
         if (kb == kb0) trace_stamp(p, 2);      // first k-block converted: MMA starts
         if (kb == kb1 - 1) trace_stamp(p, 3);  // last k-block converted
@@ -156,13 +170,25 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
           const uint64_t dbh = make_smem_desc(b_hi + k8 * b_step, b_lbo, b_sbo, b_lay);
           const uint64_t dal = make_smem_desc(a_lo + k8 * a_step, a_lbo, a_sbo, a_lay);
           const uint64_t dbl = make_smem_desc(b_lo + k8 * b_step, b_lbo, b_sbo, b_lay);
-          mma_tf32_ss(tmem_base, dah, dbh, idesc, (kb > kb0 || k8 > 0) ? 1u : 0u);
-          mma_tf32_ss(tmem_base, dah, dbl, idesc, 1u);
-          mma_tf32_ss(tmem_base, dal, dbh, idesc, 1u);
+          if constexpr (PAIR) {
+            mma_tf32_ss_pair(tmem_base, dah, dbh, idesc, (kb > kb0 || k8 > 0) ? 1u : 0u);
+            mma_tf32_ss_pair(tmem_base, dah, dbl, idesc, 1u);
+            mma_tf32_ss_pair(tmem_base, dal, dbh, idesc, 1u);
+          } else {
+            mma_tf32_ss(tmem_base, dah, dbh, idesc, (kb > kb0 || k8 > 0) ? 1u : 0u);
+            mma_tf32_ss(tmem_base, dah, dbl, idesc, 1u);
+            mma_tf32_ss(tmem_base, dal, dbh, idesc, 1u);
+          }
         }
-        tc_commit(raw_empty(r));
-        tc_commit(lo_empty(l));
-        if (kb == kb1 - 1) tc_commit(tmem_full_bar);
+        if constexpr (PAIR) {   // free the stage / publish the accumulator in BOTH CTAs
+          tc_commit_pair(raw_empty(r));
+          tc_commit_pair(lo_empty(l));
+          if (kb == kb1 - 1) tc_commit_pair(tmem_full_bar);
+        } else {
+          tc_commit(raw_empty(r));
+          tc_commit(lo_empty(l));
+          if (kb == kb1 - 1) tc_commit(tmem_full_bar);
+        }
         if (++r == R) r = 0;
         if (++l == LO_SLOTS) { l = 0; lphase ^= 1u; }
       }
@@ -204,7 +230,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
       }
       fence_proxy_async();   // generic-proxy stores -> visible to the tensor core's async-proxy reads
       __syncwarp();
-      if (lane == 0) mbar_arrive(conv_bar(l));
+      if (lane == 0) {
+        if constexpr (PAIR) mbar_arrive_remote(conv_bar(l), 0u);   // the leader's barrier (also from the leader itself)
+        else mbar_arrive(conv_bar(l));
+      }
       if (++r == R) { r = 0; rphase ^= 1u; }
       if (++l == LO_SLOTS) { l = 0; lphase ^= 1u; }
     }
@@ -264,11 +293,13 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
     }
     tc_fence_before();
   }
-  __syncthreads();
+  if constexpr (PAIR) cluster_sync_all();    // both CTAs are done with their accumulators before the paired dealloc
+  else __syncthreads();
   if (threadIdx.x == 0) trace_stamp(p, 6);   // all warps done
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, TMEM_COLS);
+    if constexpr (PAIR) tmem_dealloc_pair(tmem_base, TMEM_COLS);
+    else tmem_dealloc(tmem_base, TMEM_COLS);
   }
 }
 

@@ -45,8 +45,9 @@ for i in range(NL):
     m = t[i][:, 0] > 0
     if not m.any():
         continue
+    ld = m & (t[i][:, 2] > 0)      # CTA pairs: only the leader's MMA thread stamps slots 2 and 3
     rows.append((float(t[i][m][:, 0].min()), float(t[i][m][:, 6].max()), int(m.sum()),
-                 float((t[i][m][:, 2] - t[i][m][:, 0]).mean()), float((t[i][m][:, 4] - t[i][m][:, 2]).mean()),
+                 float((t[i][ld][:, 2] - t[i][ld][:, 0]).mean()), float((t[i][ld][:, 4] - t[i][ld][:, 2]).mean()),
                  float((t[i][m][:, 5] - t[i][m][:, 4]).mean()), float((t[i][m][:, 6] - t[i][m][:, 5]).mean())))
 rows.sort()
 T0 = rows[0][0]

@@ -77,3 +77,15 @@ def test_gemm_argument_errors(fdsm):
         fdsm.ops.tc_gemm(a, a, a, None, 128, 128, 32, passes=3)             # lo halves: both operands or neither
     with pytest.raises(fdsm._lib.FdsmError):
         fdsm.ops.tc_gemm(a, a, a, a, 128, 128, 32, passes=3, splits=5)     # more splits than k-blocks
+
+
+def test_cta_pair_kernel_in_a_subprocess():
+    """The opt-in cta_group::2 flavour of the raw-operand GEMM (FDSM_GEMM_PAIR=1 is read once per process): same parity
+    bars on the config shapes and the ragged ones, odd tile counts included (padded pair)."""
+    import os
+    import subprocess
+    import sys
+    env = dict(os.environ, FDSM_GEMM_PAIR="1")
+    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-m", "gpu", __file__, "-k", "raw_operand"], env=env,
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
