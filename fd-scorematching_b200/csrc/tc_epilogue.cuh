@@ -7,9 +7,44 @@
 namespace fdsm {
 namespace tc {
 
+// Activation arithmetic of the epilogues.  The 128 x 208 tile of one CTA is 26 624 activations on 256 threads, so the
+// epilogue is ALU-issue bound: libdevice's log1pf(expf(z)) costs ~45 instructions per element = 4.8 us per tile, more
+// than a K=200 main loop (profiles/r01_step_trace_gemm_timeline.txt: epi-math 7.3 us).
+//   0: libdevice (log1pf(expf(z)), expm1f, expf)
+//   1: MUFU only (ex2.approx / lg2.approx): ~10 instructions, absolute error ~2e-7 (3 ulp at O(1))
+//   2 (default): ex2.approx for e^-|z| and log1p(t) = 2 atanh(t / (2 + t)) as an odd polynomial in s = t/(2+t) <= 1/3
+//      (Newton-refined reciprocal, 6 FMAs): ~19 instructions, |error| <= 5 ulp, the same grade as 0 (3 ulp; simulated
+//      against float64 in fp32 arithmetic over [-25, 25]); derivative 1 - c e^-h with ex2.approx (|error| < 1 ulp)
 #ifndef FDSM_FAST_ACT
-#define FDSM_FAST_ACT 0
+#define FDSM_FAST_ACT 2
 #endif
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// softplus(z) = max(z, 0) + log1p(e^-|z|)
+__device__ __forceinline__ float softplus_poly(float z) {
+  const float t = ex2_approx(fabsf(z) * -1.4426950408889634f);   // e^-|z| in (0, 1]
+  const float d = 2.f + t;
+  const float r0 = rcp_approx(d);
+  const float s0 = t * r0;
+  const float s = fmaf(fmaf(-d, s0, t), r0, s0);                  // t / (2 + t), one Newton step on the quotient
+  const float u = s * s;                                         // <= 1/9
+  float q = 0.076923077f;                                        // 1/13
+  q = fmaf(q, u, 0.090909091f);
+  q = fmaf(q, u, 0.11111111f);
+  q = fmaf(q, u, 0.14285715f);
+  q = fmaf(q, u, 0.2f);
+  q = fmaf(q, u, 0.33333334f);
+  const float s2 = s + s;
+  return fmaxf(z, 0.f) + fmaf(s2 * u, q, s2);                    // 2 atanh(s) = 2s (1 + u/3 + u^2/5 + ...)
+}
 constexpr int CW = 8;   // columns per epilogue step
 constexpr int HW_STRIDE = 260;   // shared-memory row stride of the staged head weights [w(N) | b]
 
@@ -18,7 +53,9 @@ __device__ __forceinline__ float act_fwd_t(float z) {
   if constexpr (ACT == ACT_SOFTPLUS || ACT == ACT_NSOFTPLUS) {
     // nn.Softplus(beta=1, threshold=20): z > 20 ? z : log1p(exp(z)); evaluated branch-free (exp overflow -> inf is
     // discarded by the select)
-#if FDSM_FAST_ACT
+#if FDSM_FAST_ACT == 2
+    const float r = softplus_poly(z);
+#elif FDSM_FAST_ACT == 1
     // softplus(z) = max(z, 0) + log1p(exp(-|z|)) on the MUFU pipe (ex2.approx / lg2.approx): absolute error ~2e-7 at
     // O(1) values (3 fp32 ulp) for ~10 instructions instead of ~45 -- the precise form made the epilogue, not the MMA,
     // the critical path of the K=200 layers.  z > 20 falls out naturally (log1p(e^-20) < 2^-24 z).
@@ -30,7 +67,7 @@ __device__ __forceinline__ float act_fwd_t(float z) {
 #endif
     return ACT == ACT_NSOFTPLUS ? r - 0.69314718055994531f : r;   // models.py:19-28
   } else if constexpr (ACT == ACT_ELU) {
-#if FDSM_FAST_ACT
+#if FDSM_FAST_ACT == 1
     return z > 0.f ? z : __expf(z) - 1.f;   // absolute error ~1e-7, branch-free
 #else
     return z > 0.f ? z : expm1f(z);
@@ -42,8 +79,8 @@ __device__ __forceinline__ float act_fwd_t(float z) {
 template <int ACT>
 __device__ __forceinline__ float act_bwd_t(float h) {   // derivative through the stored activation h = act(z)
 #if FDSM_FAST_ACT
-  if constexpr (ACT == ACT_SOFTPLUS) return 1.f - __expf(-h);
-  else if constexpr (ACT == ACT_NSOFTPLUS) return 1.f - 0.5f * __expf(-h);
+  if constexpr (ACT == ACT_SOFTPLUS) return 1.f - ex2_approx(h * -1.4426950408889634f);
+  else if constexpr (ACT == ACT_NSOFTPLUS) return fmaf(-0.5f, ex2_approx(h * -1.4426950408889634f), 1.f);
 #else
   if constexpr (ACT == ACT_SOFTPLUS) return 1.f - expf(-h);
   else if constexpr (ACT == ACT_NSOFTPLUS) return 1.f - 0.5f * expf(-h);
