@@ -46,7 +46,8 @@ __device__ __forceinline__ float softplus_poly(float z) {
   return fmaxf(z, 0.f) + fmaf(s2 * u, q, s2);                    // 2 atanh(s) = 2s (1 + u/3 + u^2/5 + ...)
 }
 constexpr int CW = 8;   // columns per epilogue step
-constexpr int HW_STRIDE = 260;   // shared-memory row stride of the staged head weights [w(N) | b]
+constexpr int HW_STRIDE = 260;   // shared-memory row stride of the staged head weights: w[0, N), zeros, bias at HW_BIAS
+constexpr int HW_BIAS = HW_STRIDE - 1;
 
 template <int ACT>
 __device__ __forceinline__ float act_fwd_t(float z) {
@@ -128,19 +129,30 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, uint32_t tmem
         }
       }
     } else if constexpr (EPI == EPI_HEAD) {
+      // head weights of these 8 columns: 128-bit broadcast loads (zero beyond N, so no per-element select on them)
+      const float* hwc = hw + n0 + c;
+      float wa[CW], wb[CW], wq[CW];
+      {
+        const float4 a0 = *reinterpret_cast<const float4*>(hwc), a1 = *reinterpret_cast<const float4*>(hwc + 4);
+        wa[0] = a0.x; wa[1] = a0.y; wa[2] = a0.z; wa[3] = a0.w; wa[4] = a1.x; wa[5] = a1.y; wa[6] = a1.z; wa[7] = a1.w;
+        if (p.head_mode) {
+          const float4 b0 = *reinterpret_cast<const float4*>(hwc + HW_STRIDE), b1 = *reinterpret_cast<const float4*>(hwc + HW_STRIDE + 4);
+          const float4 q0 = *reinterpret_cast<const float4*>(hwc + 2 * HW_STRIDE), q1 = *reinterpret_cast<const float4*>(hwc + 2 * HW_STRIDE + 4);
+          wb[0] = b0.x; wb[1] = b0.y; wb[2] = b0.z; wb[3] = b0.w; wb[4] = b1.x; wb[5] = b1.y; wb[6] = b1.z; wb[7] = b1.w;
+          wq[0] = q0.x; wq[1] = q0.y; wq[2] = q0.z; wq[3] = q0.w; wq[4] = q1.x; wq[5] = q1.y; wq[6] = q1.z; wq[7] = q1.w;
+        }
+      }
 #pragma unroll
       for (int i = 0; i < CW; ++i) {
-        // branch-free (selects, not predicated blocks): the 8 columns of a step must overlap in the pipes; with
-        // per-element branches each activation ran alone, ~100 clk per element (profiles/r01_step_trace.txt)
-        const bool ok = i < nvalid;
-        const float h = ok ? act_fwd_t<ACT>(v[i]) : 0.f;
-        const int cc = n0 + c + i;   // < HW_STRIDE: the staged head weights are readable (finite or not) beyond N
-        l1 = fmaf(h, ok ? hw[cc] : 0.f, l1);
+        // branch-free: the 8 columns of a step must overlap in the pipes; with per-element branches each activation
+        // ran alone, ~100 clk per element (profiles/r01_step_trace.txt)
+        const float h = act_fwd_t<ACT>(v[i]);     // finite for padding columns too (accumulator 0)
+        l1 = fmaf(h, wa[i], l1);
         if (p.head_mode) {
-          l2 = fmaf(h, ok ? hw[HW_STRIDE + cc] : 0.f, l2);
-          lq = fmaf(h * h, ok ? hw[2 * HW_STRIDE + cc] : 0.f, lq);
+          l2 = fmaf(h, wb[i], l2);
+          lq = fmaf(h * h, wq[i], lq);
         }
-        v[i] = h;
+        v[i] = i < nvalid ? h : 0.f;
       }
       if constexpr (STAGED) st8(srow + c, v);
       else if (row_ok && c < p.out_cols) st8(p.out_hi + (long long)row * p.ldo + n0 + c, v);

@@ -89,10 +89,14 @@ template <int PASSES, int EPI>
 __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant__ GemmParams p) {
   using namespace ptx;
   // EPI_HEAD: head weights [w1 | b1], [w2 | b2], [wq | bq] staged once in shared memory (N <= 256)
-  __shared__ float head_smem[EPI == EPI_HEAD ? 3 * HW_STRIDE : 1];
+  __shared__ __align__(16) float head_smem[EPI == EPI_HEAD ? 3 * HW_STRIDE : 4];
   if constexpr (EPI == EPI_HEAD) {
     const int nh = p.head_mode ? 3 : 1;
-    for (int i = threadIdx.x; i < nh * (p.N + 1); i += kThreads) head_smem[(i / (p.N + 1)) * HW_STRIDE + i % (p.N + 1)] = __ldg(p.head_w + i);
+    // weights [0, N), zeros up to HW_BIAS, the bias at HW_BIAS: columns beyond N then contribute nothing without a select
+    for (int i = threadIdx.x; i < nh * HW_STRIDE; i += kThreads) {
+      const int h = i / HW_STRIDE, j = i % HW_STRIDE;
+      head_smem[i] = j < p.N ? __ldg(p.head_w + h * (p.N + 1) + j) : (j == HW_BIAS ? __ldg(p.head_w + h * (p.N + 1) + p.N) : 0.f);
+    }
   }
   constexpr int STAGES = SmemLayout::stages(PASSES);
   constexpr int STAGE_BYTES = SmemLayout::stage_bytes(PASSES);
@@ -229,9 +233,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       if (half == 1) { hsum[q * 32 + lane][0] = l1; hsum[q * 32 + lane][1] = l2; hsum[q * 32 + lane][2] = lq; }
       __syncthreads();
       if (half == 0 && row_ok) {
-        l1 += hsum[q * 32 + lane][0] + head_smem[p.N];
-        l2 += hsum[q * 32 + lane][1] + (p.head_mode ? head_smem[HW_STRIDE + p.N] : 0.f);
-        lq += hsum[q * 32 + lane][2] + (p.head_mode ? head_smem[2 * HW_STRIDE + p.N] : 0.f);
+        l1 += hsum[q * 32 + lane][0] + head_smem[HW_BIAS];
+        l2 += hsum[q * 32 + lane][1] + (p.head_mode ? head_smem[HW_STRIDE + HW_BIAS] : 0.f);
+        lq += hsum[q * 32 + lane][2] + (p.head_mode ? head_smem[2 * HW_STRIDE + HW_BIAS] : 0.f);
         // quadratic head ln1(h)*ln2(h) + lq(h^2) (models.py:338,954) or a plain Linear(H,1) head (head_mode 0)
         p.e_out[row] = p.head_mode ? fmaf(l1, l2, lq) : l1;
         p.l1_out[row] = l1;

@@ -59,11 +59,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
   using namespace ptx;
   const uint32_t crank = PAIR ? cluster_ctarank() : 0u;     // 0 = leader
   const int BNL = PAIR ? p.BN / 2 : p.BN;                   // B-tile columns staged by THIS CTA
-  __shared__ float head_smem[EPI == EPI_HEAD ? 3 * HW_STRIDE : 1];
-  if constexpr (EPI == EPI_HEAD) {
-    const int nh = p.head_mode ? 3 : 1;
-    for (int i = threadIdx.x; i < nh * (p.N + 1); i += kThreads) head_smem[(i / (p.N + 1)) * HW_STRIDE + i % (p.N + 1)] = __ldg(p.head_w + i);
-  }
+  __shared__ __align__(16) float head_smem[EPI == EPI_HEAD ? 3 * HW_STRIDE : 4];
   if (threadIdx.x == 0) trace_stamp(p, 0);   // CTA start
   const int R = p.raw_slots;
   const int SLOT = p.slot_bytes;
@@ -116,17 +112,29 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
       mbar_init(raw_full(s), 1);
       mbar_init(raw_empty(s), 1);
     }
-    for (int s = 0; s < LO_SLOTS; ++s) {
+    for (int s = 0; s < MAX_LO_SLOTS; ++s) {
       mbar_init(conv_bar(s), PAIR ? 2 * CONV_WARPS : CONV_WARPS);   // pair: the peer's converters arrive on the leader's
       mbar_init(lo_empty(s), 1);
     }
     mbar_init(tmem_full_bar, 1);
     fence_barrier_init();
-    for (int i = 0; i < pre; ++i) issue_loads(kb0 + i, i);
   }
   if (warp == 2) {
     if constexpr (PAIR) tmem_alloc_pair(smem_u32((const void*)tmem_ptr_smem), TMEM_COLS);
     else tmem_alloc(smem_u32((const void*)tmem_ptr_smem), TMEM_COLS);
+  }
+  // Everything above is independent of the previous kernel's output and overlaps its tail when this grid was launched
+  // with programmatic stream serialization; from here on its global-memory writes are visible.
+  griddep_wait();
+  if (warp == 0 && lane == 0)
+    for (int i = 0; i < pre; ++i) issue_loads(kb0 + i, i);   // first loads in flight before the CTA-wide barrier
+  if constexpr (EPI == EPI_HEAD) {
+    const int nh = p.head_mode ? 3 : 1;
+    // weights [0, N), zeros up to HW_BIAS, the bias at HW_BIAS: columns beyond N then contribute nothing without a select
+    for (int i = threadIdx.x; i < nh * HW_STRIDE; i += kThreads) {
+      const int h = i / HW_STRIDE, j = i % HW_STRIDE;
+      head_smem[i] = j < p.N ? __ldg(p.head_w + h * (p.N + 1) + j) : (j == HW_BIAS ? __ldg(p.head_w + h * (p.N + 1) + p.N) : 0.f);
+    }
   }
   tc_fence_before();
   if constexpr (PAIR) cluster_sync_all();   // both CTAs' barriers are initialised before any remote arrive / multicast commit
@@ -253,6 +261,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
       tc_fence_after();
     }
     if (threadIdx.x == 128) trace_stamp(p, 4);   // accumulator complete
+    griddep_launch_dependents();   // main loop done: let the next kernel's CTAs take the idle SMs and set up
     float l1 = 0.f, l2 = 0.f, lq = 0.f;
     const bool last_tile = n0 + p.BN >= p.N;
     const int ncols_out = (EPI == EPI_STORE || EPI == EPI_HEAD) ? min(p.N - n0, p.BN) : (last_tile ? p.out_cols - n0 : p.BN);
@@ -275,9 +284,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
       if (half == 1) { hsum[q * 32 + lane][0] = l1; hsum[q * 32 + lane][1] = l2; hsum[q * 32 + lane][2] = lq; }
       __syncthreads();
       if (half == 0 && row_ok) {
-        l1 += hsum[q * 32 + lane][0] + head_smem[p.N];
-        l2 += hsum[q * 32 + lane][1] + (p.head_mode ? head_smem[HW_STRIDE + p.N] : 0.f);
-        lq += hsum[q * 32 + lane][2] + (p.head_mode ? head_smem[2 * HW_STRIDE + p.N] : 0.f);
+        l1 += hsum[q * 32 + lane][0] + head_smem[HW_BIAS];
+        l2 += hsum[q * 32 + lane][1] + (p.head_mode ? head_smem[HW_STRIDE + HW_BIAS] : 0.f);
+        lq += hsum[q * 32 + lane][2] + (p.head_mode ? head_smem[2 * HW_STRIDE + HW_BIAS] : 0.f);
         p.e_out[row] = p.head_mode ? fmaf(l1, l2, lq) : l1;
         p.l1_out[row] = l1;
         p.l2_out[row] = l2;

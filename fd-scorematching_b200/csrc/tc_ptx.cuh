@@ -74,6 +74,11 @@ __device__ __forceinline__ void mma_tf32_ss(uint32_t tmem_d, uint64_t adesc, uin
       : "memory");
 }
 
+// ---- programmatic dependent launch: the next kernel's CTAs may be scheduled (and run their prologue) while this grid
+// ---- drains; nothing that depends on the predecessor's global-memory writes may be touched before griddep_wait ----
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ---- CTA pair (cta_group::2): two CTAs of one cluster drive ONE 256-row MMA, each holding its 128 rows of A and
 // ---- half of the B tile in its own shared memory; only the leader (cluster rank 0) issues ------------------------
 __device__ __forceinline__ uint32_t cluster_ctarank() {
