@@ -220,6 +220,20 @@ __device__ __forceinline__ void epilogue_dispatch(const GemmParams& p, uint32_t 
 __device__ __forceinline__ void stage_store_tile(const float* __restrict__ stage, int ldt, float* __restrict__ g, long long ld,
                                                  int rows, int cols, bool vec) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (vec && (cols & 3) == 0 && (ldt & 3) == 0 && cols > 0) {
+    // one asynchronous bulk copy per row (shared -> global through the TMA unit): the threads only wait until the
+    // shared-memory reads are done, the global writes drain behind the CTA
+    ptx::fence_proxy_async();   // this thread's generic-proxy tile writes -> visible to the async proxy
+    __syncthreads();
+    for (int r = threadIdx.x; r < rows; r += kThreads) {
+      asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                   ::"l"(g + (long long)r * ld), "r"(ptx::smem_u32(stage + r * ldt)), "r"(cols * 4)
+                   : "memory");
+    }
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    return;
+  }
   const int c4 = vec ? (cols & ~3) : 0;
   for (int r = warp; r < rows; r += kThreads / 32) {
     const float* s = stage + r * ldt;

@@ -76,6 +76,15 @@ inline bool pair_mode() {
   return on;
 }
 
+// FDSM_GEMM_PDL=0 in the environment launches the GEMMs without programmatic stream serialization (A/B measurements)
+inline bool pdl_mode() {
+  static const bool on = [] {
+    const char* e = getenv("FDSM_GEMM_PDL");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
+
 inline int lo_slots_override() {
   static const int v = [] {
     const char* e = getenv("FDSM_GEMM_LO_SLOTS");
@@ -151,10 +160,14 @@ inline int launch_gemm(GemmParams& p, const Operand& A, const Operand& B, int M,
                  "tc_gemm: output staging tile does not fit the pipeline's shared memory (BN=%d)", BN);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid; cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = smem_raw; cfg.stream = st;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = pair ? 2 : 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
+    // programmatic dependent launch: this grid's CTAs may start (barrier init, TMEM allocation) while the previous kernel
+    // of the stream drains; the kernel executes griddepcontrol.wait before it touches global memory
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = pdl_mode() ? 2 : 1;
     cudaError_t e;
 #define FDSM_LAUNCH_RAW(E) \
   e = pair ? cudaLaunchKernelEx(&cfg, gemm_raw_kernel<E, true>, p) : cudaLaunchKernelEx(&cfg, gemm_raw_kernel<E, false>, p)
