@@ -2,17 +2,20 @@
 // gradient fused with the global-norm partial sums of clip_grad_norm_ and the optimizer's step-counter increment.
 // Replaces  grad.mul_(1/W) -> ncclAllReduce -> sumsq  (3 launches, the NCCL one with ~20-30 us of latency at 1 MB).
 //
-// Push design, no grid-wide or end-of-kernel barrier:
-//   every rank owns a peer-mapped receive buffer   slot[parity][src rank][n_pad]   +   flag[parity][block][src rank]
-//   block i:  (1) stores chunk i of the local gradient into slot[parity][me] of EVERY peer (posted NVLink writes),
-//             (2) fence.sys, then sets flag[parity][i][me] = epoch on every peer (st.release.sys),
-//             (3) spins (ld.acquire.sys) until its own flag[parity][i][r] reached epoch for every r,
-//             (4) sums chunk i over the ranks in rank order 0..W-1 (own chunk from the local gradient) -> every rank
-//                 computes bit-identical sums; scales by 1/W; accumulates the squared norm of its chunk.
-//   Block i only ever depends on block i of the peers, so the kernel cannot deadlock on residency.
-//   parity = epoch & 1 double-buffers the receive slots: a peer can run at most one step ahead (its step t+1 push needs
-//   nothing from me, its step t+2 push needs my step t+1 flags, which I set after finishing step t), so a slot is never
-//   overwritten while it is being read.  The epoch lives in device memory -> the kernel replays from a CUDA graph.
+// One-shot push with the flag INSIDE the data ("LL16"): the gradient travels as 16-byte words {g[3w], g[3w+1], g[3w+2],
+// epoch}.  A 16-byte aligned vector store is one memory transaction, so a receiver that sees the epoch sees the three
+// floats: no membar.sys, no separate flag round trip (the first version -- plain stores, __threadfence_system, flag
+// store, flag poll -- spent 7.5 us in the fence and 5 us waiting for the peer's fence; profiles/r01_peer_allreduce.txt).
+//   every rank owns a peer-mapped receive buffer   slot[parity][src rank][n3]   of 16-byte words, n3 = ceil(n / 3)
+//   thread t, word w:  (1) stores word w of the local gradient into slot[parity][me][w] of EVERY peer (posted NVLink writes),
+//                      (2) polls its own slot[parity][r][w] (volatile 16-byte loads, L1 bypassed) until the epoch shows up,
+//                      (3) sums the ranks in rank order 0..W-1 (own value from registers) -> bit-identical on every rank;
+//                          scales by 1/W; writes out[3w..3w+2]; accumulates the squared norm.
+//   A thread only ever depends on the same word of the peers, so the kernel cannot deadlock on residency.
+//   parity = epoch & 1 double-buffers the receive slots: a peer can run at most one step ahead (its epoch t+2 push comes
+//   after its epoch t+1 wait, which needs my epoch t+1 push, which I issue after finishing epoch t), so a word is never
+//   overwritten before it is read, and a stale word (epoch t-2) never passes for a fresh one.  The epoch lives in device
+//   memory -> the kernel replays from a CUDA graph.
 //   The last block to finish (ticket counter) folds the per-block squared norms into the FDSM_SUMSQ_PARTIALS slots the
 //   Adam kernel reads (fixed order -> deterministic) and advances epoch and step counter.
 #include "fdsm_common.cuh"
@@ -25,9 +28,8 @@ constexpr int kMaxWorld = FDSM_PEER_MAX_WORLD;
 constexpr int kMaxBlocks = FDSM_PEER_MAX_BLOCKS;
 
 struct PeerArgs {
-  const float* grad; float* out; long long n, n_pad;
-  float* slot[kMaxWorld];        // receive-slot base of every rank (peer-mapped addresses valid on THIS device)
-  unsigned* flag[kMaxWorld];     // flag base of every rank
+  const float* grad; float* out; long long n, n3;
+  uint4* slot[kMaxWorld];        // receive-slot base of every rank (peer-mapped addresses valid on THIS device)
   int rank, world;
   float scale;
   float* sumsq; long long* step;
@@ -35,18 +37,18 @@ struct PeerArgs {
   unsigned long long timeout_ns;
 };
 
-__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
-  unsigned v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
 __device__ __forceinline__ unsigned long long globaltimer() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
+}
+__device__ __forceinline__ uint4 ld_volatile_16(const uint4* p) {
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_16(uint4* p, uint4 v) {
+  asm volatile("st.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
 __global__ void __launch_bounds__(kPeerThreads) peer_allreduce_kernel(const PeerArgs a) {
@@ -54,71 +56,59 @@ __global__ void __launch_bounds__(kPeerThreads) peer_allreduce_kernel(const Peer
   __shared__ int is_last;
   const int tid = threadIdx.x, blk = blockIdx.x, nblk = gridDim.x, W = a.world, me = a.rank;
   const unsigned epoch = *reinterpret_cast<volatile unsigned*>(a.scratch) + 1u;
-  const int parity = (int)(epoch & 1u);
-  // chunk i of the vector, in units of 4 floats
-  const long long nv = a.n_pad >> 2, per = (nv + nblk - 1) / nblk;
-  const long long v0 = blk * per, v1 = v0 + per < nv ? v0 + per : nv;
-  const bool vec = aligned16(a.grad) && aligned16(a.out);
-  auto load4 = [&](const float* base, long long v) -> float4 {
-    const long long e = v << 2;
-    if (vec && e + 3 < a.n) return *reinterpret_cast<const float4*>(base + e);
-    return make_float4(e < a.n ? base[e] : 0.f, e + 1 < a.n ? base[e + 1] : 0.f, e + 2 < a.n ? base[e + 2] : 0.f,
-                       e + 3 < a.n ? base[e + 3] : 0.f);
-  };
-  // (1) push my chunk into every peer's slot[parity][me]
-  const long long my_slot = ((long long)(parity * W + me)) * a.n_pad;
-  for (long long v = v0 + tid; v < v1; v += kPeerThreads) {
-    const float4 x = load4(a.grad, v);
+  // phase stamps of block 0 (debug, u64 at scratch[192..]): start, pushed, reduced, done
+  unsigned long long* stamps = reinterpret_cast<unsigned long long*>(a.scratch + 192);
+  const bool stamp = blk == 0 && tid == 0;
+  if (stamp) stamps[0] = globaltimer();
+  const long long parity_off = (long long)(epoch & 1u) * W * a.n3;
+  const long long per = (a.n3 + nblk - 1) / nblk;
+  const long long w0 = blk * per, w1 = w0 + per < a.n3 ? w0 + per : a.n3;
+  // (1) push: word w of my gradient, tagged with the epoch, into slot[parity][me][w] of every peer
+  for (long long w = w0 + tid; w < w1; w += kPeerThreads) {
+    const long long e = 3 * w;
+    uint4 x;
+    x.x = __float_as_uint(a.grad[e]);
+    x.y = e + 1 < a.n ? __float_as_uint(a.grad[e + 1]) : 0u;
+    x.z = e + 2 < a.n ? __float_as_uint(a.grad[e + 2]) : 0u;
+    x.w = epoch;
     for (int p = 0; p < W; ++p)
-      if (p != me) *reinterpret_cast<float4*>(a.slot[p] + my_slot + (v << 2)) = x;
+      if (p != me) st_16(a.slot[p] + parity_off + (long long)me * a.n3 + w, x);
   }
-  // (2) publish: every thread's stores are ordered before the flag by fence + barrier + release store
-  __threadfence_system();
-  __syncthreads();
-  const long long fidx = ((long long)(parity * kMaxBlocks + blk)) * kMaxWorld;
-  if (tid < W && tid != me) st_release_sys(a.flag[tid] + fidx + me, epoch);
-  // (3) wait for chunk i of every peer
-  if (tid < W && tid != me) {
-    const unsigned* f = a.flag[me] + fidx + tid;
-    // tight volatile poll; the timeout clock is read once per 4096 polls only (%globaltimer is slow to read)
-    const volatile unsigned* fv = f;
-    unsigned long long t0 = 0;
-    bool arrived = false;
-    while (!arrived) {
-      for (int i = 0; i < 4096 && !arrived; ++i) arrived = (int)(*fv - epoch) >= 0;
-      if (arrived) break;
-      const unsigned long long t = globaltimer();
-      if (t0 == 0) t0 = t;
-      if (t - t0 > a.timeout_ns) {   // a peer died: do not hang the GPU, flag the error and go on
-        atomicExch(a.scratch + 2, 1u);
-        break;
-      }
-    }
-    (void)ld_acquire_sys(f);         // acquire: the peer's slot stores happen-before the reads below
-  }
-  __syncthreads();
-  // (4) reduce in rank order (bit-identical on every rank), scale, squared norm
+  if (stamp) stamps[1] = globaltimer();
+  // (2)+(3) wait per word, reduce in rank order (bit-identical on every rank), scale, squared norm
   float acc2 = 0.f;
-  for (long long v = v0 + tid; v < v1; v += kPeerThreads) {
-    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+  unsigned long long t0 = 0;
+  for (long long w = w0 + tid; w < w1; w += kPeerThreads) {
+    const long long e = 3 * w;
+    const float g0 = a.grad[e], g1 = e + 1 < a.n ? a.grad[e + 1] : 0.f, g2 = e + 2 < a.n ? a.grad[e + 2] : 0.f;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f;
     for (int p = 0; p < W; ++p) {
-      float4 x;
-      if (p == me) x = load4(a.grad, v);
-      else x = __ldcg(reinterpret_cast<const float4*>(a.slot[me] + ((long long)(parity * W + p)) * a.n_pad + (v << 2)));
-      s.x += x.x; s.y += x.y; s.z += x.z; s.w += x.w;
+      if (p == me) {
+        s0 += g0; s1 += g1; s2 += g2;
+        continue;
+      }
+      const uint4* src = a.slot[me] + parity_off + (long long)p * a.n3 + w;
+      uint4 x = ld_volatile_16(src);
+      for (unsigned spin = 1; x.w != epoch; ++spin) {
+        if ((spin & 1023u) == 0) {   // the timeout clock is read once per 1024 polls (%globaltimer is slow to read)
+          const unsigned long long t = globaltimer();
+          if (t0 == 0) t0 = t;
+          if (t - t0 > a.timeout_ns) {   // a peer died: do not hang the GPU, flag the error and go on
+            atomicExch(a.scratch + 2, 1u);
+            break;
+          }
+        }
+        x = ld_volatile_16(src);
+      }
+      s0 += __uint_as_float(x.x); s1 += __uint_as_float(x.y); s2 += __uint_as_float(x.z);
     }
-    s.x *= a.scale; s.y *= a.scale; s.z *= a.scale; s.w *= a.scale;
-    const long long e = v << 2;
-    if (vec && e + 3 < a.n) {
-      *reinterpret_cast<float4*>(a.out + e) = s;
-    } else {
-      if (e < a.n) a.out[e] = s.x; else s.x = 0.f;
-      if (e + 1 < a.n) a.out[e + 1] = s.y; else s.y = 0.f;
-      if (e + 2 < a.n) a.out[e + 2] = s.z; else s.z = 0.f;
-      if (e + 3 < a.n) a.out[e + 3] = s.w; else s.w = 0.f;
-    }
-    acc2 += s.x * s.x + s.y * s.y + s.z * s.z + s.w * s.w;
+    s0 *= a.scale; s1 *= a.scale; s2 *= a.scale;
+    a.out[e] = s0;
+    if (e + 1 < a.n) a.out[e + 1] = s1; else s1 = 0.f;
+    if (e + 2 < a.n) a.out[e + 2] = s2; else s2 = 0.f;
+    acc2 += s0 * s0 + s1 * s1 + s2 * s2;
   }
+  if (stamp) stamps[2] = globaltimer();
   acc2 = warp_sum(acc2);
   if ((tid & 31) == 0) red[tid >> 5] = acc2;
   __syncthreads();
@@ -130,6 +120,7 @@ __global__ void __launch_bounds__(kPeerThreads) peer_allreduce_kernel(const Peer
     is_last = atomicAdd(a.scratch + 1, 1u) == (unsigned)(nblk - 1);
   }
   __syncthreads();
+  if (stamp) stamps[3] = globaltimer();
   if (is_last) {
     __threadfence();
     const volatile float* part = reinterpret_cast<const volatile float*>(a.scratch + 4);
@@ -153,8 +144,8 @@ using namespace fdsm;
 
 extern "C" int64_t fdsm_peer_buffer_bytes(int64_t n, int32_t world) {
   if (n < 0 || world < 1 || world > kMaxWorld) return -1;
-  const int64_t n_pad = (n + 3) / 4 * 4;
-  return 2 * (int64_t)world * n_pad * 4 + 2ll * kMaxBlocks * kMaxWorld * 4;
+  const int64_t n3 = (n + 2) / 3;
+  return 2 * (int64_t)world * (n3 > 0 ? n3 : 1) * 16;
 }
 
 extern "C" int fdsm_peer_allreduce(const float* grad, float* out, int64_t n, void* const* peer_buffers, int32_t rank,
@@ -163,16 +154,15 @@ extern "C" int fdsm_peer_allreduce(const float* grad, float* out, int64_t n, voi
   FDSM_REQUIRE(world >= 1 && world <= kMaxWorld && rank >= 0 && rank < world, "fdsm_peer_allreduce: bad rank/world");
   FDSM_REQUIRE(n >= 0 && (n == 0 || (grad && out)) && peer_buffers && scratch, "fdsm_peer_allreduce: bad arguments");
   PeerArgs a = {};
-  a.grad = grad; a.out = out; a.n = n; a.n_pad = (n + 3) / 4 * 4;
+  a.grad = grad; a.out = out; a.n = n; a.n3 = (n + 2) / 3;
   for (int p = 0; p < world; ++p) {
     FDSM_REQUIRE(peer_buffers[p] && aligned16(peer_buffers[p]), "fdsm_peer_allreduce: peer buffer %d NULL or misaligned", p);
-    a.slot[p] = static_cast<float*>(peer_buffers[p]);
-    a.flag[p] = reinterpret_cast<unsigned*>(a.slot[p] + 2ll * world * a.n_pad);
+    a.slot[p] = static_cast<uint4*>(peer_buffers[p]);
   }
   a.rank = rank; a.world = world; a.scale = scale; a.sumsq = sumsq; a.step = (long long*)step_counter; a.scratch = scratch;
   a.timeout_ns = 20ull * 1000000000ull;
-  // the grid is a function of n only: it must be identical on every rank (flags are per block)
-  long long nblk = (a.n_pad / 4 + 511) / 512;
+  // the grid is a function of n only (one 16-byte word per thread where possible)
+  long long nblk = (a.n3 + kPeerThreads - 1) / kPeerThreads;
   if (nblk < 1) nblk = 1;
   if (nblk > kMaxBlocks) nblk = kMaxBlocks;
   peer_allreduce_kernel<<<(int)nblk, kPeerThreads, 0, (cudaStream_t)stream>>>(a);

@@ -94,7 +94,7 @@ class PeerAllReduce:
         self.buf = symm.empty(nbytes // 4, dtype=torch.float32, device=device)
         self.hdl = symm.rendezvous(self.buf, group)
         self.buf.zero_()
-        self.scratch = torch.zeros(4 + 128, dtype=torch.int32, device=device)
+        self.scratch = torch.zeros(256, dtype=torch.int32, device=device)
         torch.cuda.synchronize(device)
         dist.barrier(group)                       # nobody pushes before every receive buffer is zeroed
         ptrs = [int(p) for p in self.hdl.buffer_ptrs]
@@ -113,6 +113,11 @@ class PeerAllReduce:
             from ._lib import check
             check(rc, "fdsm_peer_allreduce")
         return out
+
+    def phase_stamps_us(self):
+        """Debug: block 0's phase durations of the LAST launch (us): push, wait + reduce, tail."""
+        t = self.scratch[192:200].view(torch.int64).cpu().tolist()
+        return [(t[i + 1] - t[i]) / 1e3 for i in range(3)]
 
     def timed_out(self):
         """True if any launch gave up waiting for a peer (host sync)."""

@@ -242,12 +242,12 @@ int fdsm_adam_step(float* params, const float* grads, float* exp_avg, float* exp
  *
  * peer_buffers[r] = address, valid on THIS device, of rank r's receive buffer (fdsm_peer_buffer_bytes(n, world)
  * bytes, zero-filled once before the first call on any rank; e.g. torch symmetric memory or cudaIpc mappings).
- * scratch: >= 4*(4 + FDSM_PEER_MAX_BLOCKS) bytes of LOCAL device memory, zero-filled once; scratch[2] != 0 after a
+ * scratch: >= 1024 bytes of LOCAL device memory, zero-filled once (words [192, 204): debug phase timestamps of block 0); scratch[2] != 0 after a
  * launch means a peer did not arrive within 20 s (the kernel gives up instead of hanging the GPU).
  * out may alias grad.  Every rank must call it the same number of times with the same n.  Graph-capturable.
  * Results are bit-identical on every rank. */
 #define FDSM_PEER_MAX_WORLD 8
-#define FDSM_PEER_MAX_BLOCKS 128
+#define FDSM_PEER_MAX_BLOCKS 160
 int64_t fdsm_peer_buffer_bytes(int64_t n, int32_t world);
 int fdsm_peer_allreduce(const float* grad, float* out, int64_t n, void* const* peer_buffers, int32_t rank,
                         int32_t world, float scale, float* sumsq, int64_t* step_counter, uint32_t* scratch,

@@ -87,7 +87,9 @@ def main():
                 dist.all_reduce(buf)
             e1.record(); torch.cuda.synchronize()
             t_nccl = e0.elapsed_time(e1) / 200 * 1e3
+            ph = ar.phase_stamps_us()
             if rank == 0:
+                print("block-0 phases of the last launch (us): push %.1f  wait+reduce %.1f  tail %.1f" % tuple(ph))
                 print(f"n={n} ({4 * n / 1e6:.2f} MB) world={world}: peer kernel {t_peer:.1f} us/launch (incl. sumsq + step), "
                       f"NCCL mul_+all_reduce {t_nccl:.1f} us/iter (eager launches)")
         if rank == 0:
