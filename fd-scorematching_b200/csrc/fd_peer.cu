@@ -18,6 +18,8 @@
 //   memory -> the kernel replays from a CUDA graph.
 //   The last block to finish (ticket counter) folds the per-block squared norms into the FDSM_SUMSQ_PARTIALS slots the
 //   Adam kernel reads (fixed order -> deterministic) and advances epoch and step counter.
+#include <cstdlib>
+
 #include "fdsm_common.cuh"
 
 namespace fdsm {
@@ -29,6 +31,7 @@ constexpr int kMaxBlocks = FDSM_PEER_MAX_BLOCKS;
 
 struct PeerArgs {
   const float* grad; float* out; long long n, n3;
+  long long nown;                // two-shot: words owned per rank = ceil(n3 / world)
   uint4* slot[kMaxWorld];        // receive-slot base of every rank (peer-mapped addresses valid on THIS device)
   int rank, world;
   float scale;
@@ -137,6 +140,125 @@ __global__ void __launch_bounds__(kPeerThreads) peer_allreduce_kernel(const Peer
   }
 }
 
+
+// Two-shot flavour for large worlds (the one-shot push moves (W-1) x n words in and out of every GPU: 12 us of NVLink
+// time at W = 8).  Rank o owns the words [o*nown, (o+1)*nown):
+//   (1) every rank sends each word to its OWNER only            -> slotA[parity][src][w - o*nown]   (reduce-scatter)
+//   (2) the owner polls the W-1 contributions, sums in rank order, scales, and sends the RESULT word to every peer
+//                                                               -> slotB[parity][w]                 (all-gather)
+//   (3) every rank polls the result words it does not own.
+// Traffic per GPU: 2 x (W-1)/W x n words instead of (W-1) x n; one more NVLink hop of latency.  Same flag-in-data words,
+// same parity double buffering; every element is summed by exactly one rank, so all ranks hold identical bits.
+// Receive buffer layout (16-byte words): A = [2][W][nown], then B = [2][W * nown].
+__device__ __forceinline__ uint4 poll_word(const uint4* src, unsigned epoch, unsigned long long& t0, const PeerArgs& a) {
+  uint4 x = ld_volatile_16(src);
+  for (unsigned spin = 1; x.w != epoch; ++spin) {
+    if ((spin & 1023u) == 0) {
+      const unsigned long long t = globaltimer();
+      if (t0 == 0) t0 = t;
+      if (t - t0 > a.timeout_ns) {
+        atomicExch(a.scratch + 2, 1u);
+        break;
+      }
+    }
+    x = ld_volatile_16(src);
+  }
+  return x;
+}
+
+__global__ void __launch_bounds__(kPeerThreads) peer_allreduce2_kernel(const PeerArgs a) {
+  __shared__ float red[kPeerThreads / 32];
+  __shared__ int is_last;
+  const int tid = threadIdx.x, blk = blockIdx.x, nblk = gridDim.x, W = a.world, me = a.rank;
+  const unsigned epoch = *reinterpret_cast<volatile unsigned*>(a.scratch) + 1u;
+  unsigned long long* stamps = reinterpret_cast<unsigned long long*>(a.scratch + 192);
+  const bool stamp = blk == 0 && tid == 0;
+  if (stamp) stamps[0] = globaltimer();
+  const long long nown = a.nown, gsz = (long long)nblk * kPeerThreads, gtid = (long long)blk * kPeerThreads + tid;
+  const long long offA = (long long)(epoch & 1u) * W * nown;                    // slotA[parity]
+  const long long offB = 2ll * W * nown + (long long)(epoch & 1u) * W * nown;   // slotB[parity]
+  auto load_word = [&](long long w) -> uint4 {
+    const long long e = 3 * w;
+    uint4 x;
+    x.x = e < a.n ? __float_as_uint(a.grad[e]) : 0u;
+    x.y = e + 1 < a.n ? __float_as_uint(a.grad[e + 1]) : 0u;
+    x.z = e + 2 < a.n ? __float_as_uint(a.grad[e + 2]) : 0u;
+    x.w = epoch;
+    return x;
+  };
+  // (1) reduce-scatter sends: the ranges of the other owners, the nearest owner first
+  for (int d = 1; d < W; ++d) {
+    const int o = (me + d) % W;
+    for (long long i = gtid; i < nown; i += gsz) {
+      const long long w = (long long)o * nown + i;
+      if (w < a.n3) st_16(a.slot[o] + offA + (long long)me * nown + i, load_word(w));
+    }
+  }
+  if (stamp) stamps[1] = globaltimer();
+  float acc2 = 0.f;
+  unsigned long long t0 = 0;
+  auto emit = [&](long long w, float s0, float s1, float s2) {
+    const long long e = 3 * w;
+    if (e < a.n) a.out[e] = s0; else s0 = 0.f;
+    if (e + 1 < a.n) a.out[e + 1] = s1; else s1 = 0.f;
+    if (e + 2 < a.n) a.out[e + 2] = s2; else s2 = 0.f;
+    acc2 += s0 * s0 + s1 * s1 + s2 * s2;
+  };
+  // (2) my range: gather, reduce in rank order, broadcast the result
+  for (long long i = gtid; i < nown; i += gsz) {
+    const long long w = (long long)me * nown + i;
+    if (w >= a.n3) break;
+    const uint4 mine = load_word(w);
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f;
+    for (int p = 0; p < W; ++p) {
+      const uint4 x = p == me ? mine : poll_word(a.slot[me] + offA + (long long)p * nown + i, epoch, t0, a);
+      s0 += __uint_as_float(x.x); s1 += __uint_as_float(x.y); s2 += __uint_as_float(x.z);
+    }
+    s0 *= a.scale; s1 *= a.scale; s2 *= a.scale;
+    uint4 r;
+    r.x = __float_as_uint(s0); r.y = __float_as_uint(s1); r.z = __float_as_uint(s2); r.w = epoch;
+    for (int d = 1; d < W; ++d) st_16(a.slot[(me + d) % W] + offB + w, r);
+    emit(w, s0, s1, s2);
+  }
+  // (3) the other ranges: wait for the owners' results
+  for (int d = 1; d < W; ++d) {
+    const int o = (me + d) % W;
+    for (long long i = gtid; i < nown; i += gsz) {
+      const long long w = (long long)o * nown + i;
+      if (w >= a.n3) break;
+      const uint4 x = poll_word(a.slot[me] + offB + w, epoch, t0, a);
+      emit(w, __uint_as_float(x.x), __uint_as_float(x.y), __uint_as_float(x.z));
+    }
+  }
+  if (stamp) stamps[2] = globaltimer();
+  acc2 = warp_sum(acc2);
+  if ((tid & 31) == 0) red[tid >> 5] = acc2;
+  __syncthreads();
+  if (tid == 0) {
+    float s = 0.f;
+    for (int i = 0; i < kPeerThreads / 32; ++i) s += red[i];
+    reinterpret_cast<float*>(a.scratch + 4)[blk] = s;
+    __threadfence();
+    is_last = atomicAdd(a.scratch + 1, 1u) == (unsigned)(nblk - 1);
+  }
+  __syncthreads();
+  if (stamp) stamps[3] = globaltimer();
+  if (is_last) {
+    __threadfence();
+    const volatile float* part = reinterpret_cast<const volatile float*>(a.scratch + 4);
+    if (tid < FDSM_SUMSQ_PARTIALS) {
+      float s = 0.f;
+      for (int j = tid; j < nblk; j += FDSM_SUMSQ_PARTIALS) s += part[j];
+      if (a.sumsq) a.sumsq[tid] = s;
+    }
+    if (tid == 0) {
+      a.scratch[1] = 0u;
+      a.scratch[0] = epoch;
+      if (a.step) *a.step += 1;
+    }
+  }
+}
+
 }  // namespace
 }  // namespace fdsm
 
@@ -145,7 +267,10 @@ using namespace fdsm;
 extern "C" int64_t fdsm_peer_buffer_bytes(int64_t n, int32_t world) {
   if (n < 0 || world < 1 || world > kMaxWorld) return -1;
   const int64_t n3 = (n + 2) / 3;
-  return 2 * (int64_t)world * (n3 > 0 ? n3 : 1) * 16;
+  const int64_t nown = (n3 + world - 1) / world;
+  const int64_t one_shot = 2 * (int64_t)world * (n3 > 0 ? n3 : 1);           // [2][W][n3]
+  const int64_t two_shot = 4 * (int64_t)world * (nown > 0 ? nown : 1);       // A [2][W][nown] + B [2][W * nown]
+  return (one_shot > two_shot ? one_shot : two_shot) * 16;                   // either protocol fits
 }
 
 extern "C" int fdsm_peer_allreduce(const float* grad, float* out, int64_t n, void* const* peer_buffers, int32_t rank,
@@ -159,12 +284,21 @@ extern "C" int fdsm_peer_allreduce(const float* grad, float* out, int64_t n, voi
     FDSM_REQUIRE(peer_buffers[p] && aligned16(peer_buffers[p]), "fdsm_peer_allreduce: peer buffer %d NULL or misaligned", p);
     a.slot[p] = static_cast<uint4*>(peer_buffers[p]);
   }
+  a.nown = (a.n3 + world - 1) / world;
   a.rank = rank; a.world = world; a.scale = scale; a.sumsq = sumsq; a.step = (long long*)step_counter; a.scratch = scratch;
   a.timeout_ns = 20ull * 1000000000ull;
   // the grid is a function of n only (one 16-byte word per thread where possible)
   long long nblk = (a.n3 + kPeerThreads - 1) / kPeerThreads;
   if (nblk < 1) nblk = 1;
   if (nblk > kMaxBlocks) nblk = kMaxBlocks;
-  peer_allreduce_kernel<<<(int)nblk, kPeerThreads, 0, (cudaStream_t)stream>>>(a);
+  // one-shot up to 4 ranks (one NVLink hop); two-shot beyond (the one-shot push is NVLink-bandwidth bound at 8);
+  // FDSM_PEER_TWO_SHOT=0/1 overrides -- it must be set identically on every rank
+  static const int two_shot_env = [] {
+    const char* e = getenv("FDSM_PEER_TWO_SHOT");
+    return e ? (e[0] == '1' ? 1 : 0) : -1;
+  }();
+  const bool two_shot = world > 1 && (two_shot_env >= 0 ? two_shot_env == 1 : world > 4);
+  if (two_shot) peer_allreduce2_kernel<<<(int)nblk, kPeerThreads, 0, (cudaStream_t)stream>>>(a);
+  else peer_allreduce_kernel<<<(int)nblk, kPeerThreads, 0, (cudaStream_t)stream>>>(a);
   FDSM_LAUNCH_CHECK("fdsm_peer_allreduce");
 }
