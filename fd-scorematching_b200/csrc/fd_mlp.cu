@@ -191,45 +191,56 @@ __global__ void __launch_bounds__(HB_WARPS * 32) head_bwd_kernel(const float* __
     }
   }
   double sb1 = 0., sb2 = 0., sbq = 0.;
-  for (long long r = (long long)blockIdx.x * HB_WARPS + warp; r < rows; r += W) {
-    const float g = head_g(src, r);
-    float ga = g, gb = 0.f;
-    if (head) { ga = g * __ldg(l2v + r); gb = g * __ldg(l1v + r); }
-    float h[NI];
+  // two rows per iteration, every load of both rows issued before the arithmetic: the kernel is latency-bound (each warp
+  // walks ~5 rows; one row at a time exposed two dependent L2 round trips per row)
+  for (long long r = (long long)blockIdx.x * HB_WARPS + warp; r < rows; r += 2 * W) {
+    const long long rr[2] = {r, r + W};
+    const bool okr[2] = {true, r + W < rows};
+    float g[2], ga[2], gb[2], h[2][NI];
 #pragma unroll
-    for (int i = 0; i < NI; ++i) {
-      const int j = lane + 32 * i;
-      h[i] = j < H ? __ldg(hlast + r * ldh + j) : 0.f;
-    }
-    const double dga = (double)ga, dgb = (double)gb, dg = (double)g;
+    for (int u = 0; u < 2; ++u) {
+      g[u] = okr[u] ? head_g(src, rr[u]) : 0.f;
+      ga[u] = g[u]; gb[u] = 0.f;
+      if (head && okr[u]) { ga[u] = g[u] * __ldg(l2v + rr[u]); gb[u] = g[u] * __ldg(l1v + rr[u]); }
 #pragma unroll
-    for (int i = 0; i < NI; ++i) {
-      const int j = lane + 32 * i;
-      float dz = 0.f;
-      if (j < H) {
-        float dh;
-        const double hd = (double)h[i];
-        if (head) {
-          dh = fmaf(ga, w1[i], fmaf(gb, w2[i], 2.f * g * wq[i] * h[i]));
-          a1[i] += dga * hd; a2[i] += dgb * hd; aq[i] += dg * hd * hd;
-        } else {
-          dh = g * w1[i];
-          a1[i] += dg * hd;
-        }
-        dz = dh * tc::act_bwd_from_h(act, h[i]);
-      }
-      if (j < npad) {
-        if (dz_lo) {
-          float hi, lo;
-          ptx::tf32_split(dz, hi, lo);
-          dz_hi[r * npad + j] = hi;
-          dz_lo[r * npad + j] = lo;
-        } else {
-          dz_hi[r * npad + j] = dz;
-        }
+      for (int i = 0; i < NI; ++i) {
+        const int j = lane + 32 * i;
+        h[u][i] = (okr[u] && j < H) ? __ldg(hlast + rr[u] * ldh + j) : 0.f;
       }
     }
-    sb1 += dga; sb2 += dgb; sbq += dg;
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (!okr[u]) continue;
+      const double dga = (double)ga[u], dgb = (double)gb[u], dg = (double)g[u];
+#pragma unroll
+      for (int i = 0; i < NI; ++i) {
+        const int j = lane + 32 * i;
+        float dz = 0.f;
+        if (j < H) {
+          float dh;
+          const double hd = (double)h[u][i];
+          if (head) {
+            dh = fmaf(ga[u], w1[i], fmaf(gb[u], w2[i], 2.f * g[u] * wq[i] * h[u][i]));
+            a1[i] += dga * hd; a2[i] += dgb * hd; aq[i] += dg * hd * hd;
+          } else {
+            dh = g[u] * w1[i];
+            a1[i] += dg * hd;
+          }
+          dz = dh * tc::act_bwd_from_h(act, h[u][i]);
+        }
+        if (j < npad) {
+          if (dz_lo) {
+            float hi, lo;
+            ptx::tf32_split(dz, hi, lo);
+            dz_hi[rr[u] * npad + j] = hi;
+            dz_lo[rr[u] * npad + j] = lo;
+          } else {
+            dz_hi[rr[u] * npad + j] = dz;
+          }
+        }
+      }
+      sb1 += dga; sb2 += dgb; sbq += dg;
+    }
   }
   // fixed-order block reduction of the per-warp sums, one accumulator family at a time
   const int head_n = head ? 3 * (H + 1) : (H + 1);
@@ -287,11 +298,14 @@ __global__ void __launch_bounds__(1024) head_finish_kernel(const double* __restr
 // ---- split-K reduce: partial[s][k][n] -> gW[n][k] (+)= sum_s, gb[n] (+)= sum_s partial[s][K][n] --------------
 // 8 (k) x 32 (n) outputs per 1024-thread block; 4 thread groups each sum a fixed quarter of the splits in fp64, the
 // quarters are combined in a fixed order (deterministic), then a transposing store through shared memory.
-constexpr int RW_GROUPS = 4;
-__global__ void __launch_bounds__(1024) reduce_wgrad_kernel(const float* __restrict__ partial, int splits, int kpad, int npad,
-                                                            int H, int K, float* __restrict__ gW, float* __restrict__ gb,
-                                                            int accumulate) {
-  __shared__ double part[RW_GROUPS][8][32];
+// GROUPS = 4 (many splits: the hidden layers' 74): four thread groups each sum a fixed quarter of the splits, combined in
+// a fixed order.  GROUPS = 1 (<= 24 splits: the input layer's 21): 256-thread blocks, every load of a thread in flight at
+// once, the whole grid in one wave -- this launch sits on the step's critical path.
+template <int GROUPS>
+__global__ void __launch_bounds__(256 * GROUPS) reduce_wgrad_kernel(const float* __restrict__ partial, int splits, int kpad,
+                                                                    int npad, int H, int K, float* __restrict__ gW,
+                                                                    float* __restrict__ gb, int accumulate) {
+  __shared__ double part[GROUPS][8][32];
   __shared__ float tile[8][33];
   const int k0 = blockIdx.x * 8, n0 = blockIdx.y * 32;
   const int tx = threadIdx.x & 31, ty = (threadIdx.x >> 5) & 7, tz = threadIdx.x >> 8;
@@ -300,11 +314,18 @@ __global__ void __launch_bounds__(1024) reduce_wgrad_kernel(const float* __restr
     const int k = k0 + ty, n = n0 + tx;
     double acc = 0.;
     if (k <= K && n < H) {
-      const int per = (splits + RW_GROUPS - 1) / RW_GROUPS;
+      const int per = (splits + GROUPS - 1) / GROUPS;
       const int s0 = tz * per, s1 = min(splits, s0 + per);
       const float* p = partial + (long long)k * npad + n;
-#pragma unroll 4
-      for (int s = s0; s < s1; ++s) acc += (double)__ldg(p + s * stride);
+      int s = s0;
+      for (; s + 8 <= s1; s += 8) {
+        float v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) v[u] = __ldg(p + (s + u) * stride);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) acc += (double)v[u];
+      }
+      for (; s < s1; ++s) acc += (double)__ldg(p + s * stride);
     }
     part[tz][ty][tx] = acc;
   }
@@ -312,7 +333,7 @@ __global__ void __launch_bounds__(1024) reduce_wgrad_kernel(const float* __restr
   if (tz == 0) {
     double acc = part[0][ty][tx];
 #pragma unroll
-    for (int g = 1; g < RW_GROUPS; ++g) acc += part[g][ty][tx];
+    for (int g = 1; g < GROUPS; ++g) acc += part[g][ty][tx];
     tile[ty][tx] = (float)acc;
   }
   __syncthreads();
@@ -495,8 +516,12 @@ static int backward_impl(const fdsm_mlp_desc* desc, const float* x_hi, const flo
     int r = tc::launch_gemm(p, In, B, K + 1, y.npad, (int)rows, y.npad, y.passes, y.splits[l], s);
     if (r) return r;
     dim3 grid((K + 1 + 7) / 8, (y.H + 31) / 32);
-    mlp::reduce_wgrad_kernel<<<grid, 1024, 0, s>>>(partial, y.splits[l], kp, y.npad, y.H, K, grads + y.w_off[l],
-                                                  grads + y.b_off[l], accumulate);
+    if (y.splits[l] <= 24)
+      mlp::reduce_wgrad_kernel<1><<<grid, 256, 0, s>>>(partial, y.splits[l], kp, y.npad, y.H, K, grads + y.w_off[l],
+                                                      grads + y.b_off[l], accumulate);
+    else
+      mlp::reduce_wgrad_kernel<4><<<grid, 1024, 0, s>>>(partial, y.splits[l], kp, y.npad, y.H, K, grads + y.w_off[l],
+                                                       grads + y.b_off[l], accumulate);
     return cuda_status(cudaGetLastError(), "fdsm_mlp_backward(reduce)");
   };
   for (int l = L1; l >= 1; --l) {

@@ -52,13 +52,24 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
   }
   const float bc1 = 1.f - powf(b1, t), bc2s = sqrtf(1.f - powf(b2, t));
   const float step_size = lrv / bc1;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-    const float gi = g[i] * coef;
-    const float mi = b1 * m[i] + (1.f - b1) * gi;
-    const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
-    m[i] = mi;
-    v[i] = vi;
-    p[i] -= step_size * (mi / (sqrtf(vi) / bc2s + eps));
+  auto upd = [&](float& pi, float gi, float& mi, float& vi) {
+    gi *= coef;
+    mi = b1 * mi + (1.f - b1) * gi;
+    vi = b2 * vi + (1.f - b2) * gi * gi;
+    pi -= step_size * (mi / (sqrtf(vi) / bc2s + eps));
+  };
+  const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x, nth = (long long)gridDim.x * blockDim.x;
+  if (aligned16(p) && aligned16(g) && aligned16(m) && aligned16(v)) {   // 128-bit path + scalar tail
+    const long long nv = n >> 2;
+    for (long long i = tid; i < nv; i += nth) {
+      float4 p4 = reinterpret_cast<float4*>(p)[i], m4 = reinterpret_cast<float4*>(m)[i], v4 = reinterpret_cast<float4*>(v)[i];
+      const float4 g4 = reinterpret_cast<const float4*>(g)[i];
+      upd(p4.x, g4.x, m4.x, v4.x); upd(p4.y, g4.y, m4.y, v4.y); upd(p4.z, g4.z, m4.z, v4.z); upd(p4.w, g4.w, m4.w, v4.w);
+      reinterpret_cast<float4*>(p)[i] = p4; reinterpret_cast<float4*>(m)[i] = m4; reinterpret_cast<float4*>(v)[i] = v4;
+    }
+    for (long long i = (nv << 2) + tid; i < n; i += nth) upd(p[i], g[i], m[i], v[i]);
+  } else {
+    for (long long i = tid; i < n; i += nth) upd(p[i], g[i], m[i], v[i]);
   }
 }
 
@@ -80,7 +91,7 @@ extern "C" int fdsm_adam_step(float* params, const float* grads, float* exp_avg,
   if (n == 0) return FDSM_OK;
   FDSM_REQUIRE(params && grads && exp_avg && exp_avg_sq && step_counter, "fdsm_adam_step: NULL pointer");
   FDSM_REQUIRE(max_norm <= 0.f || sumsq, "fdsm_adam_step: clipping needs the squared gradient norm");
-  const long long nb = (n + 255) / 256;
+  const long long nb = (n / 4 + 255) / 256 + 1;
   const long long cap = (long long)sm_count() * 8;
   adam_kernel<<<(int)(nb < cap ? nb : cap), 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, n, lr, lr_dev, beta1,
                                                                            beta2, eps, max_norm, sumsq,

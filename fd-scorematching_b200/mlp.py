@@ -182,12 +182,19 @@ class FusedEnergyMLP(nn.Module):
         self._prep_stream.wait_stream(cur)
         with torch.cuda.stream(self._prep_stream):
             ops._count(1); check(lib.fdsm_mlp_prepare(C.byref(d), rows, _ptr(flat), _ptr(st["ws"]), _stream()), "fdsm_mlp_prepare")
+        shook = ops.PROFILE_HOOK_STACK      # bench.py: CUDA events around the stack-build launch
+        if shook is not None:
+            s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s0.record()
         if v is not None:
             ops.stack(x2, row_mask=7, scale=1.0, direction=v.reshape(B, -1), normalize=False, out=st["xh"], out_lo=st["xl"],
                       pad_ones=not self.presplit)
         else:
             ops.stack(x2, row_mask=7, scale=eps, direction=None if u is None else u.reshape(B, -1), normalize=True,
                       out=st["xh"], out_lo=st["xl"], draw=draw, offset_dev=offset_dev, pad_ones=not self.presplit)
+        if shook is not None:
+            s1.record()
+            shook.append((s0, s1))
         cur.wait_stream(self._prep_stream)
         hook = ops.PROFILE_HOOK
         if hook is not None:   # bench.py: CUDA events around the forward GEMM launches, on the launching stream
