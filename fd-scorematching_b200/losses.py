@@ -225,6 +225,73 @@ def anneal_ESM_scorenet_VR(scorenet, samples, sigmas, labels=None, anneal_power=
 
 
 # ------------------------------------------------------------------------------------------------
+# a17: the exact (Hessian-vector-product) sliced score matching losses the FD objectives are compared against
+# (BASELINE.json config 2 "FD-SSM vs exact SSM").  Generic mode only: the two autograd.grad(create_graph=True) passes
+# run through the caller's torch network (a fused forward-mode kernel for our MLP energies is SURVEY.md §8f row N2);
+# the projection vectors come from kernel (1) (Philox normals; sign / sphere variants derived from the same draw).
+# ------------------------------------------------------------------------------------------------
+def _projection_vectors(x2, noise_type, u):
+    B, D = x2.shape
+    if u is None:
+        seed, offset, row0 = ops.next_draw()
+        u = ops.philox_normal(B, D, 0, seed, offset, row0, device=x2.device)
+    if noise_type == "radermacher":      # the reference's spelling (SSM/losses/sliced_sm.py:12)
+        return u.sign()
+    if noise_type == "sphere":
+        return ops.direction(B, D, math.sqrt(D), u=u)
+    if noise_type == "gaussian":
+        return u
+    raise ValueError("Noise type not implemented")
+
+
+def _ssm_hvp(energy_net, x, vectors, vr, detach=False):
+    x = x.requires_grad_(True)
+    logp = -energy_net(x).sum()
+    grad1 = torch.autograd.grad(logp, x, create_graph=True)[0]
+    gradv = torch.sum(grad1 * vectors)
+    loss1 = (torch.norm(grad1, dim=-1) ** 2 if vr else torch.sum(grad1 * vectors, dim=-1) ** 2) * 0.5
+    grad2 = torch.autograd.grad(gradv, x, create_graph=True)[0]
+    loss2 = torch.sum(vectors * grad2, dim=-1)
+    if detach:
+        loss1, loss2 = loss1.detach(), loss2.detach()
+    return loss1 + loss2, grad1, grad2
+
+
+def single_sliced_score_matching(energy_net, samples, noise=None, detach=False, noise_type="radermacher", *, u=None):
+    """SSM/losses/sliced_sm.py:7-34: 0.5 (v.grad logp)^2 + v.grad(v.grad logp), one projection; returns
+    (loss, grad1, grad2) like the reference."""
+    vectors = noise if noise is not None else _projection_vectors(samples.reshape(samples.shape[0], -1), noise_type, u).view_as(samples)
+    per, g1, g2 = _ssm_hvp(energy_net, samples, vectors, vr=False, detach=detach)
+    return per.mean(), g1, g2
+
+
+def sliced_VR_score_matching(energy_net, samples, noise=None, detach=False, noise_type="radermacher", *, u=None):
+    """SSM/losses/sliced_sm.py:37-62 (variance-reduced: 0.5 ||grad logp||^2 replaces the squared projection); the reference
+    accepts 'radermacher' and 'gaussian' here."""
+    if noise is None and noise_type not in ("radermacher", "gaussian"):
+        raise ValueError("Noise type not implemented")
+    vectors = noise if noise is not None else _projection_vectors(samples.reshape(samples.shape[0], -1), noise_type, u).view_as(samples)
+    per, g1, g2 = _ssm_hvp(energy_net, samples, vectors, vr=True, detach=detach)
+    return per.mean(), g1, g2
+
+
+def ssm(energy, x, *, batch_size=None, u=None):
+    """DeepEBM/ESM/loss_train.py:173-189 (Gaussian projections, x viewed as (FLAGS.batch_size, dim))."""
+    bs = batch_size if batch_size is not None else (FLAGS.batch_size or x.shape[0])
+    x2 = x.reshape(bs, -1)
+    per, _, _ = _ssm_hvp(energy, x2, _projection_vectors(x2, "gaussian", u), vr=False)
+    return per.mean()
+
+
+def ssm_vr(energy, x, mean=True, *, batch_size=None, u=None):
+    """DeepEBM/ESM/loss_train.py:192-209."""
+    bs = batch_size if batch_size is not None else (FLAGS.batch_size or x.shape[0])
+    x2 = x.reshape(bs, -1)
+    per, _, _ = _ssm_hvp(energy, x2, _projection_vectors(x2, "gaussian", u), vr=True)
+    return per.mean() if mean is True else per
+
+
+# ------------------------------------------------------------------------------------------------
 # unified entry point (BASELINE.json: "(model, samples, n_particles, eps, sigma)")
 # ------------------------------------------------------------------------------------------------
 def fd_loss(model, samples, n_particles=1, eps=0.1, sigma=None, *, mode="ssm", labels=None, sigmas=None, noise=None,

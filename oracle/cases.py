@@ -42,6 +42,12 @@ CASES = {
                     eps=0.1, data="unit"),
     "a13_img": dict(fn="a13", net=("score", (3, 8, 8), 40, 12, True), B=12, D=192, eps=0.1, L=12, smax=50.0,
                     smin=0.01, anneal_power=2.0, data="unit"),
+    # a17 exact (Hessian-vector-product) SSM comparison losses: DeepEBM ssm / ssm_vr (Gaussian projections), SSM-repo
+    # single_sliced_score_matching (sign projections) and sliced_VR_score_matching
+    "a17_ssm_d64": dict(fn="a17_ssm", net=("quadratic_mlp", 64, 48, 3, "nsoftplus"), B=32, D=64, eps=0.0, data="unit"),
+    "a17_ssmvr_d64": dict(fn="a17_ssm_vr", net=("quadratic_mlp", 64, 48, 3, "nsoftplus"), B=32, D=64, eps=0.0, data="unit"),
+    "a17_sliced_gmm11": dict(fn="a17_sliced", net=("softplus_mlp", 11, 30), B=48, D=11, eps=0.0, data="gmm"),
+    "a17_slicedvr_gmm11": dict(fn="a17_sliced_vr", net=("softplus_mlp", 11, 30), B=48, D=11, eps=0.0, data="gmm"),
     "a13_img_p1": dict(fn="a13", net=("score", (3, 8, 8), 40, 12, True), B=10, D=192, eps=0.1, L=12, smax=50.0,
                        smin=0.01, anneal_power=1.0, data="unit"),
 }

@@ -61,6 +61,7 @@ def load_reference():
     ref = types.SimpleNamespace()
     ref.FLAGS = flags_mod.FLAGS
     ref.esm = _load(f"{REF}/SSM/losses/efficient_sm.py", "ref_ssm_efficient_sm")
+    ref.sliced = _load(f"{REF}/SSM/losses/sliced_sm.py", "ref_ssm_sliced_sm")
     ref.ssm_dsm = _load(f"{REF}/SSM/losses/dsm.py", "ref_ssm_dsm", extra_path=f"{REF}/SSM")
     ref.deepebm = _load(f"{REF}/DeepEBM/ESM/loss_train.py", "ref_deepebm_loss_train", stubs=stubs)
     ref.deepebm_models = _load(f"{REF}/DeepEBM/ESM/models.py", "ref_deepebm_models", stubs=stubs)
@@ -136,6 +137,18 @@ def reference_loss(ref, c):
     if fn == "a13":   # labels=None -> drawn inside with torch.randint (ncsnv2/losses/dsm.py:88-91)
         with Replay([n, u], [c["labels"]]):
             return ref.ncsnv2.anneal_ESM_scorenet_VR(net, x, c["sigmas"], None, c["anneal_power"], None, 1, eps)
+    if fn == "a17_ssm":
+        with Replay([u.reshape(c["B"], -1)]):
+            return ref.deepebm.ssm(net, x)
+    if fn == "a17_ssm_vr":
+        with Replay([u.reshape(c["B"], -1)]):
+            return ref.deepebm.ssm_vr(net, x)
+    if fn == "a17_sliced":      # default noise_type='radermacher': sign of the replayed normal draw
+        with Replay([u]):
+            return ref.sliced.single_sliced_score_matching(net, x)[0]
+    if fn == "a17_sliced_vr":
+        with Replay([u]):
+            return ref.sliced.sliced_VR_score_matching(net, x)[0]
     raise KeyError(fn)
 
 

@@ -20,6 +20,11 @@ def directions(c):
 def oracle_loss(c, net=None):
     net = net or c["net"]
     fn, x, eps, D, B = c["fn"], c["x"], c["eps"], c["D"], c["B"]
+    if fn.startswith("a17"):   # exact SSM (HVP) comparison losses: Gaussian (DeepEBM) or sign (SSM repo) projections
+        xf, uf = x.reshape(B, -1), c["u"].reshape(B, -1)
+        if fn in ("a17_sliced", "a17_sliced_vr"):
+            uf = uf.sign()
+        return F.ssm_hvp(net, xf, uf, vr=fn in ("a17_ssm_vr", "a17_sliced_vr"))
     v = directions(c)
     if fn == "a1":
         return F.fd_ssm(net, x, v, D / eps ** 2)

@@ -13,7 +13,7 @@ from oracle import cases, run_case
 
 pytestmark = pytest.mark.gpu
 
-WELL_CONDITIONED = {"a4", "a5", "a6", "a9", "a10", "a11", "a12", "a13"}
+WELL_CONDITIONED = {"a4", "a5", "a6", "a9", "a10", "a11", "a12", "a13", "a17_ssm", "a17_ssm_vr", "a17_sliced", "a17_sliced_vr"}
 
 
 def _rel(a, b):
@@ -29,6 +29,14 @@ def run_adapter(fdsm, c, dev):
     fn, net, eps = c["fn"], c["net"].to(dev), c["eps"]
     x, u, n = c["x"].to(dev), c["u"].to(dev), c["n"].to(dev)
     L = fdsm.losses
+    if fn == "a17_ssm":
+        return L.ssm(net, x, u=u.reshape(c["B"], -1))
+    if fn == "a17_ssm_vr":
+        return L.ssm_vr(net, x, u=u.reshape(c["B"], -1))
+    if fn == "a17_sliced":
+        return L.single_sliced_score_matching(net, x, u=u)[0]
+    if fn == "a17_sliced_vr":
+        return L.sliced_VR_score_matching(net, x, u=u)[0]
     if fn == "a1":
         return L.efficient_score_matching_conjugate(net, x, eps=eps, u=u)
     if fn == "a7":
