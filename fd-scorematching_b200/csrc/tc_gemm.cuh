@@ -24,7 +24,11 @@ constexpr int BK = 32;             // fp32 elements per k-block (128 B)
 constexpr int UMMA_K = 8;          // tf32: 32 B per instruction
 constexpr int A_TILE_BYTES = BM * BK * 4;    // 16 KB
 constexpr int B_TILE_BYTES = 256 * BK * 4;   // 32 KB (max BN)
-constexpr int kThreads = 256;
+// 16 warps: warp 0 TMA, warp 1 MMA issue, warp 2 TMEM allocation (raw kernel: warps 2-15 convert), ALL warps run the
+// epilogue.  The epilogue is ALU-issue bound with dependent chains (activation polynomials): 8 warps left each scheduler
+// with 2 warps and half its issue slots empty (4.7 us per 128x208 activation tile); 16 warps = 4 per scheduler.
+constexpr int kThreads = 512;
+constexpr int EPI_PARTS = kThreads / 128;   // warps per 32-lane TMEM quarter
 constexpr int TMEM_COLS = 256;
 
 enum Major : int { MAJOR_K = 0, MAJOR_MN = 1 };
@@ -211,9 +215,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
   __syncwarp();
   {
     // ===== epilogue (all 8 warps once their role is done): TMEM -> registers -> fused op -> global ==========
-    // warp w may read TMEM lanes 32*(w%4)..+31; warps 0-3 take the first half of the columns, warps 4-7 the second
+    // warp w may read TMEM lanes 32*(w%4)..+31; the EPI_PARTS warps of a quarter split the columns
     const int q = warp & 3;
-    const int half = warp >> 2;
+    const int part = warp >> 2;   // EPI_PARTS warps share each 32-lane quarter: each takes a contiguous range of column steps
     const int row = m0 + q * 32 + lane;
     const bool row_ok = row < p.M;
     const bool have_acc = kb1 > kb0;
@@ -224,18 +228,22 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
     float l1 = 0.f, l2 = 0.f, lq = 0.f;
     const bool last_tile = n0 + p.BN >= p.N;   // the tile that also writes the padding columns [N, out_cols)
     const int ncols_out = (EPI == EPI_STORE || EPI == EPI_HEAD) ? min(p.N - n0, p.BN) : (last_tile ? p.out_cols - n0 : p.BN);
-    const int nsteps = (ncols_out + CW - 1) / CW, s0 = (nsteps + 1) / 2;
-    const int c_begin = half ? s0 * CW : 0, c_end = half ? nsteps * CW : s0 * CW;
+    const int nsteps = (ncols_out + CW - 1) / CW, sper = (nsteps + EPI_PARTS - 1) / EPI_PARTS;
+    const int c_begin = min(part * sper, nsteps) * CW, c_end = min((part + 1) * sper, nsteps) * CW;
     epilogue_dispatch<EPI>(p, tmem_base + ((uint32_t)(q * 32) << 16), have_acc, row, row_ok, n0, c_begin, c_end, head_smem, l1,
                            l2, lq);
     if constexpr (EPI == EPI_HEAD) {   // combine the two column halves of each row
-      __shared__ float hsum[BM][3];
-      if (half == 1) { hsum[q * 32 + lane][0] = l1; hsum[q * 32 + lane][1] = l2; hsum[q * 32 + lane][2] = lq; }
+      __shared__ float hsum[EPI_PARTS - 1][BM][3];
+      if (part > 0) { hsum[part - 1][q * 32 + lane][0] = l1; hsum[part - 1][q * 32 + lane][1] = l2; hsum[part - 1][q * 32 + lane][2] = lq; }
       __syncthreads();
-      if (half == 0 && row_ok) {
-        l1 += hsum[q * 32 + lane][0] + head_smem[HW_BIAS];
-        l2 += hsum[q * 32 + lane][1] + (p.head_mode ? head_smem[HW_STRIDE + HW_BIAS] : 0.f);
-        lq += hsum[q * 32 + lane][2] + (p.head_mode ? head_smem[2 * HW_STRIDE + HW_BIAS] : 0.f);
+      if (part == 0 && row_ok) {
+#pragma unroll
+        for (int h = 0; h < EPI_PARTS - 1; ++h) {   // fixed order: deterministic
+          l1 += hsum[h][q * 32 + lane][0]; l2 += hsum[h][q * 32 + lane][1]; lq += hsum[h][q * 32 + lane][2];
+        }
+        l1 += head_smem[HW_BIAS];
+        l2 += p.head_mode ? head_smem[HW_STRIDE + HW_BIAS] : 0.f;
+        lq += p.head_mode ? head_smem[2 * HW_STRIDE + HW_BIAS] : 0.f;
         // quadratic head ln1(h)*ln2(h) + lq(h^2) (models.py:338,954) or a plain Linear(H,1) head (head_mode 0)
         p.e_out[row] = p.head_mode ? fmaf(l1, l2, lq) : l1;
         p.l1_out[row] = l1;

@@ -156,7 +156,7 @@ inline int launch_gemm(GemmParams& p, const Operand& A, const Operand& B, int M,
     }
     const int smem_raw = raw_smem_total(p.raw_slots, p.lo_slots, p.slot_bytes);
     // the epilogue stages the 128 x BN output tile in the pipeline's shared memory
-    FDSM_REQUIRE(BM * (((BN + CW - 1) / CW) * CW + 4) * 4 <= (p.raw_slots + p.lo_slots) * p.slot_bytes,
+    FDSM_REQUIRE(BM * (((BN + CW - 1) / CW) * CW + 4) * 4 + (EPI_PARTS - 1) * BM * 3 * 4 <= (p.raw_slots + p.lo_slots) * p.slot_bytes,
                  "tc_gemm: output staging tile does not fit the pipeline's shared memory (BN=%d)", BN);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid; cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = smem_raw; cfg.stream = st;

@@ -249,9 +249,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
   __syncwarp();
   {
     // ===== epilogue: TMEM -> registers -> fused op -> shared staging tile -> coalesced global stores ==========
-    // warp w may read TMEM lanes 32*(w%4)..+31; warps 0-3 take the first half of the columns, warps 4-7 the second.
+    // warp w may read TMEM lanes 32*(w%4)..+31; the EPI_PARTS warps of a quarter split the columns.
     const int q = warp & 3;
-    const int half = warp >> 2;
+    const int part = warp >> 2;   // EPI_PARTS warps share each 32-lane quarter: each takes a contiguous range of column steps
     const int rloc = q * 32 + lane;
     const int row = m0 + rloc;
     const bool row_ok = row < p.M;
@@ -265,8 +265,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
     float l1 = 0.f, l2 = 0.f, lq = 0.f;
     const bool last_tile = n0 + p.BN >= p.N;
     const int ncols_out = (EPI == EPI_STORE || EPI == EPI_HEAD) ? min(p.N - n0, p.BN) : (last_tile ? p.out_cols - n0 : p.BN);
-    const int nsteps = (ncols_out + CW - 1) / CW, s0 = (nsteps + 1) / 2;
-    const int c_begin = half ? s0 * CW : 0, c_end = half ? nsteps * CW : s0 * CW;
+    const int nsteps = (ncols_out + CW - 1) / CW, sper = (nsteps + EPI_PARTS - 1) / EPI_PARTS;
+    const int c_begin = min(part * sper, nsteps) * CW, c_end = min((part + 1) * sper, nsteps) * CW;
     float* stage = reinterpret_cast<float*>(gen);
     const int ldt = nsteps * CW + 4;   // +4 floats: 16-byte row stores of 8 consecutive rows fall into distinct banks
     const int rows_valid = min(BM, p.M - m0);
@@ -280,13 +280,18 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
                                  l1, l2, lq, stage + rloc * ldt);
     if (threadIdx.x == 128) trace_stamp(p, 5);   // epilogue math of warp 4 done
     if constexpr (EPI == EPI_HEAD) {
-      __shared__ float hsum[BM][3];
-      if (half == 1) { hsum[q * 32 + lane][0] = l1; hsum[q * 32 + lane][1] = l2; hsum[q * 32 + lane][2] = lq; }
+      // partial head sums of parts 1..: in the (free) pipeline memory behind the staging tile, not in static shared memory
+      float (*hsum)[BM][3] = reinterpret_cast<float (*)[BM][3]>(stage + BM * ldt);
+      if (part > 0) { hsum[part - 1][q * 32 + lane][0] = l1; hsum[part - 1][q * 32 + lane][1] = l2; hsum[part - 1][q * 32 + lane][2] = lq; }
       __syncthreads();
-      if (half == 0 && row_ok) {
-        l1 += hsum[q * 32 + lane][0] + head_smem[HW_BIAS];
-        l2 += hsum[q * 32 + lane][1] + (p.head_mode ? head_smem[HW_STRIDE + HW_BIAS] : 0.f);
-        lq += hsum[q * 32 + lane][2] + (p.head_mode ? head_smem[2 * HW_STRIDE + HW_BIAS] : 0.f);
+      if (part == 0 && row_ok) {
+#pragma unroll
+        for (int h = 0; h < EPI_PARTS - 1; ++h) {   // fixed order: deterministic
+          l1 += hsum[h][q * 32 + lane][0]; l2 += hsum[h][q * 32 + lane][1]; lq += hsum[h][q * 32 + lane][2];
+        }
+        l1 += head_smem[HW_BIAS];
+        l2 += p.head_mode ? head_smem[HW_STRIDE + HW_BIAS] : 0.f;
+        lq += p.head_mode ? head_smem[2 * HW_STRIDE + HW_BIAS] : 0.f;
         p.e_out[row] = p.head_mode ? fmaf(l1, l2, lq) : l1;
         p.l1_out[row] = l1;
         p.l2_out[row] = l2;
