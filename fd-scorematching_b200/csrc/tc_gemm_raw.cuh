@@ -25,6 +25,9 @@ namespace fdsm {
 namespace tc {
 
 constexpr int MAX_LO_SLOTS = 4;   // lo ring depth is a launch parameter (GemmParams::lo_slots), barriers are laid out for the maximum
+#ifndef FDSM_A_COLLECTOR
+#define FDSM_A_COLLECTOR 1
+#endif
 #ifndef FDSM_RAW_REWRITE_HI
 #define FDSM_RAW_REWRITE_HI 0
 #endif
@@ -183,8 +186,13 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
             mma_tf32_ss_pair(tmem_base, dah, dbl, idesc, 1u);
             mma_tf32_ss_pair(tmem_base, dal, dbh, idesc, 1u);
           } else {
+#if FDSM_A_COLLECTOR
+            mma_tf32_ss_afill(tmem_base, dah, dbh, idesc, (kb > kb0 || k8 > 0) ? 1u : 0u);
+            mma_tf32_ss_alastuse(tmem_base, dah, dbl, idesc, 1u);
+#else
             mma_tf32_ss(tmem_base, dah, dbh, idesc, (kb > kb0 || k8 > 0) ? 1u : 0u);
             mma_tf32_ss(tmem_base, dah, dbl, idesc, 1u);
+#endif
             mma_tf32_ss(tmem_base, dal, dbh, idesc, 1u);
           }
         }
