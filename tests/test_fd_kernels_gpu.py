@@ -208,3 +208,20 @@ def test_combine_rejects_bad_arguments(fdsm):
     lib = fdsm._lib.load()
     rc = lib.fdsm_combine_energy_fwd(None, 4, 5, 2.0, 1.0, 1, None, None, None)
     assert rc == -1 and b"mode" in lib.fdsm_last_error_string()
+
+
+def test_peer_allreduce_across_gpus():
+    """fdsm_peer_allreduce (NVLink peer-memory all-reduce + squared norm + step counter) against NCCL, across ranks and
+    under graph replay -- scripts/peer_allreduce_check.py under torchrun on every visible GPU (needs >= 2)."""
+    import os
+    import subprocess
+    import sys
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs at least 2 GPUs")
+    n = 8 if n >= 8 else (4 if n >= 4 else 2)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr",
+                        "127.0.0.1", "--master-port", "29533", os.path.join(root, "scripts", "peer_allreduce_check.py")],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
