@@ -4,7 +4,7 @@ Import as ``fdsm_b200`` (see the ``fdsm_b200.py`` shim at the repo root; the dir
 contains a hyphen).  Public surface = the reference's loss-function signatures (``losses``), the
 kernel-level ops (``ops``) and the fused energy MLPs (``mlp``).
 """
-from . import _lib, losses, mlp, ops  # noqa: F401
+from . import _lib, losses, mlp, ops, sampling  # noqa: F401
 from .losses import (FLAGS, MLE_efficient_score_matching_conjugate, anneal_ESM_scorenet_VR, dsm_fd,  # noqa: F401
                      dsm_tracetrick_FD, efficient_score_matching_conjugate, esm_scorenet_VR, fd_loss, mdsm_fd,
                      mdsm_fd_nop, ncsn_anneal_ESM_scorenet, ncsn_anneal_ESM_scorenet_VR,

@@ -81,6 +81,9 @@ PROTOTYPES = {
     "fdsm_mlp_prepare": (C.c_int, [C.POINTER(MlpDesc), _i64, _f32p, _f32p, _stream]),
     "fdsm_mlp_forward": (C.c_int, [C.POINTER(MlpDesc), _f32p, _f32p, _i64, _f32p, _f32p, _f32p, _stream]),
     "fdsm_mlp_backward": (C.c_int, [C.POINTER(MlpDesc), _f32p, _f32p, _i64, _f32p, _f32p, _f32p, _f32p, _i32, _stream]),
+    "fdsm_langevin_step": (C.c_int, [_f32p, _i64, _f32p, _i64, _f32p, _i64, _f32p, _i64, _i64, _i64, _f32, _f32, _u64, _u64, _u64,
+                                     _stream]),
+    "fdsm_ema_update": (C.c_int, [_f32p, _f32p, _i64, _f32, _f32, _stream]),
     "fdsm_peer_buffer_bytes": (C.c_int64, [_i64, _i32]),
     "fdsm_peer_allreduce": (C.c_int, [_f32p, _f32p, _i64, C.POINTER(C.c_void_p), _i32, _i32, _f32, _f32p, C.c_void_p,
                                       C.c_void_p, _stream]),

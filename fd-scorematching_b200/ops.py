@@ -4,6 +4,7 @@ PyTorch is plumbing here: it owns device memory and streams; every computation b
 through the C ABI (``_lib``).  No fallback path exists.
 """
 import ctypes as C
+import math
 import threading
 
 import torch
@@ -314,3 +315,45 @@ def tc_gemm(a_hi, a_lo, b_hi, b_lo, M, N, K, *, a_major=0, b_major=0, passes=3, 
     g.out, g.ldo, g.split_stride = _ptr(out), N, M * N
     _count(1); check(lib.fdsm_tc_gemm(C.byref(g), _stream()), "fdsm_tc_gemm")
     return out
+
+
+# --------------------------------------------------------------------------------------------
+# Langevin update and EMA (callers either side of the hot path)
+# --------------------------------------------------------------------------------------------
+def langevin_step(x, score, step_size, *, noise=None, noise_scale=None, draw=None, out=None):
+    """x + step_size*score + noise*sqrt(2*step_size) in one pass (fdsm_langevin_step); `noise` injected (parity) or drawn
+    in-kernel from the Philox noise stream.  `out` may be `x` (in place)."""
+    lib = _lib.load()
+    shape = x.shape
+    if x.dim() < 2:
+        raise ValueError("x must have a batch dimension and at least one data dimension")
+    Dflat = 1
+    for d in shape[1:]:
+        Dflat *= d
+    x2, ldx = _rows(_req(x, "x").reshape(shape[0], Dflat), "x")
+    s2, lds = _rows(_req(score, "score").reshape(shape[0], Dflat), "score")
+    B, D = x2.shape
+    n2, ldn = (None, 0)
+    if noise is not None:
+        n2, ldn = _rows(_req(noise, "noise").reshape(shape[0], Dflat), "noise")
+    o = torch.empty_like(x2) if out is None else _req(out, "out").reshape(shape[0], Dflat)
+    if o.dim() != 2 or o.shape != x2.shape or (o.numel() and o.stride(1) != 1):
+        raise ValueError("out must be a row-major tensor of the shape of x")
+    ldo = o.stride(0) if B > 1 else max(D, 1)
+    seed, offset, row0 = draw if draw is not None else (next_draw() if noise is None else (0, 0, 0))
+    scale = math.sqrt(2.0 * float(step_size)) if noise_scale is None else float(noise_scale)
+    _count(1)
+    check(lib.fdsm_langevin_step(_ptr(x2), ldx, _ptr(s2), lds, _ptr(n2), ldn, _ptr(o), ldo, B, D, float(step_size), scale, seed,
+                                 offset, row0, _stream()), "fdsm_langevin_step")
+    return o.view(shape)
+
+
+def ema_update(shadow, params, mu):
+    """shadow <- (1 - mu) * params + mu * shadow, in place (fdsm_ema_update)."""
+    lib = _lib.load()
+    _req(shadow, "shadow"); _req(params, "params")
+    if shadow.numel() != params.numel() or not shadow.is_contiguous() or not params.is_contiguous():
+        raise ValueError("shadow and params must be contiguous tensors of the same size")
+    _count(1)
+    check(lib.fdsm_ema_update(_ptr(shadow), _ptr(params), shadow.numel(), 1.0 - float(mu), float(mu), _stream()), "fdsm_ema_update")
+    return shadow

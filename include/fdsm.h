@@ -253,6 +253,19 @@ int fdsm_peer_allreduce(const float* grad, float* out, int64_t n, void* const* p
                         int32_t world, float scale, float* sumsq, int64_t* step_counter, uint32_t* scratch,
                         fdsm_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------
+ * SURVEY.md §8f rows N3 / N4 (the callers either side of the hot path).
+ * fdsm_langevin_step: out = (x + step_size * score) + noise * noise_scale, the reference's rounding order
+ * (ncsnv2/models/__init__.py:34-39 with noise_scale = sqrt(2 step_size); DeepEBM/ESM/sampling_mdsm.py:63-96).
+ * noise == NULL draws N(0,1) in-kernel from the Philox noise stream keyed by (seed, offset, row0 + row).  out may alias x.
+ * fdsm_ema_update: shadow = one_minus_mu * params + mu * shadow (ncsnv2/models/ema.py:16-21; the caller rounds 1 - mu
+ * from double, as Python does in the reference).
+ * ------------------------------------------------------------------------------------------ */
+int fdsm_langevin_step(const float* x, int64_t ldx, const float* score, int64_t lds, const float* noise, int64_t ldnoise,
+                       float* out, int64_t ldo, int64_t B, int64_t D, float step_size, float noise_scale, uint64_t seed,
+                       uint64_t offset, uint64_t row0, fdsm_stream_t stream);
+int fdsm_ema_update(float* shadow, const float* params, int64_t n, float one_minus_mu, float mu, fdsm_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -195,6 +195,36 @@ def main():
             out[f"net_mlpq_mnist_{act}/ssm_fd_loss_{tag}"] = l.detach().double().numpy()
             out[f"net_mlpq_mnist_{act}/ssm_fd_gradnorm_{tag}"] = g.norm().numpy()
             out[f"net_mlpq_mnist_{act}/ssm_fd_grad_head_{tag}"] = g[-603:].numpy()  # ln1, ln2, lq
+    # N3 / N4: the reference's annealed Langevin sampler and EMA helper on a tiny conditional score net
+    sys.path.insert(0, f"{REF}/ncsnv2")
+    for k in [k for k in sys.modules if k == "models" or k.startswith("models.") or k == "losses" or k.startswith("losses.")]:
+        del sys.modules[k]
+    import models as ref_models          # ncsnv2/models/__init__.py
+    from models.ema import EMAHelper as RefEMA
+    from . import sampling as osamp
+    sig = cases.geometric_sigmas(1.0, 0.1, 3)
+    for tag, dt in (("f32", torch.float32), ("f64", torch.float64)):
+        net = nets.TinyCondScore((3, 8, 8), 40, 3, sigmas=sig)
+        nets.init_from_numpy(net, 4242)
+        net = net.to(dt)
+        x0 = nets.np_rand(4243, 6, 3, 8, 8).to(dt)
+        zs = [nets.np_randn(4300 + i, 6, 3, 8, 8).to(dt) for i in range(6)]
+        with Replay([z.clone() for z in zs]):
+            xs = ref_models.anneal_Langevin_dynamics(x0.clone(), net, sig.numpy(), n_steps_each=2, step_lr=2e-3, final_only=True)
+        out[f"n3_langevin/x_final_{tag}"] = xs[0].double().numpy()
+        mine = osamp.anneal_langevin(x0, net, sig.numpy(), 2, 2e-3, zs)
+        print(f"n3_langevin        {tag} |ref - oracle| max = {float((xs[0] - mine).abs().max()):.2e}")
+        # EMA: three updates with drifting parameters
+        lin = torch.nn.Linear(7, 5).to(dt)
+        nets.init_from_numpy(lin, 4400)
+        h = RefEMA(mu=0.9)
+        h.register(lin)
+        for i in range(3):
+            with torch.no_grad():
+                for j, p in enumerate(lin.parameters()):
+                    p.add_(nets.np_randn(4410 + 10 * i + j, *p.shape).to(dt) * 0.1)
+            h.update(lin)
+        out[f"n4_ema/shadow_{tag}"] = torch.cat([h.shadow[n].reshape(-1) for n, _ in lin.named_parameters()]).double().numpy()
     np.savez_compressed(os.path.join(OUT, "reference_outputs.npz"), **out)
     print("wrote", os.path.join(OUT, "reference_outputs.npz"), os.path.getsize(os.path.join(OUT, "reference_outputs.npz")))
 
