@@ -26,16 +26,26 @@ namespace mlp {
 
 inline long long round_up(long long x, long long m) { return (x + m - 1) / m * m; }
 constexpr int HB_WARPS = 8;   // head_bwd_kernel: warps (= rows in flight) per block
-inline int head_blocks(long long rows) {
-  long long b = (rows + HB_WARPS - 1) / HB_WARPS, cap = 2ll * sm_count();
-  return (int)(b < cap ? (b < 1 ? 1 : b) : cap);
+// number of per-block partial-sum records of the head backward: H <= 256: one warp per row, ~2 blocks per SM;
+// H > 256 (head_bwd_wide_kernel): row groups, so that column tiles x row groups ~ 2 blocks per SM
+inline int head_blocks(long long rows, int H) {
+  if (H <= 256) {
+    long long b = (rows + HB_WARPS - 1) / HB_WARPS, cap = 2ll * sm_count();
+    return (int)(b < cap ? (b < 1 ? 1 : b) : cap);
+  }
+  const long long ct = (H + 255) / 256;
+  long long g = 2ll * sm_count() / ct;
+  if (g < 1) g = 1;
+  if (g > rows) g = rows < 1 ? 1 : rows;
+  return (int)g;
 }
 
 struct Layout {
   int D, H, L, act, head, passes;
   bool raw;            // presplit == 0 and passes == 3: plain fp32 activations, split inside the GEMMs
   long long rows;
-  int npad;            // UMMA N of every hidden layer: ceil16(H)
+  int npad;            // padded hidden width: ceil16(H)
+  int bn, nt;          // UMMA N per CTA (min(npad, 256)) and number of N tiles (> 1 when H > 256)
   int kpad0, kpadh;    // padded augmented input widths: ceil32(D+1), ceil32(H+1)
   // parameter offsets
   long long w_off[16], b_off[16], head_off, n_params;
@@ -46,6 +56,7 @@ struct Layout {
   long long dz_hi[16], dz_lo[16];   // dZ_l per layer [rows x npad] (lo only in presplit mode): wgrad_l runs on a side
                                     // stream while dgrad_l..1 continue, so the buffers are not recycled
   long long l1, l2;                 // per-row head dot products
+  long long head_part;              // nt > 1: per-tile partial head dots [nt][rows][3]
   long long head_acc;               // per-block fp64 partial sums of the head-parameter gradients
   long long partial[2];             // split-K partials: [0] input layer (main stream), [1] hidden layers (side stream)
   long long total;
@@ -55,7 +66,6 @@ struct Layout {
 inline int make_layout(const fdsm_mlp_desc* d, long long rows, Layout& y) {
   FDSM_REQUIRE(d != nullptr, "fdsm_mlp: desc is NULL");
   FDSM_REQUIRE(d->in_dim >= 1 && d->hidden >= 1 && d->n_hidden >= 1 && d->n_hidden <= 15, "fdsm_mlp: bad sizes");
-  FDSM_REQUIRE(d->hidden <= 256, "fdsm_mlp: hidden=%d > 256 is not supported by the fused head epilogue yet", d->hidden);
   FDSM_REQUIRE(d->act >= 1 && d->act <= 3, "fdsm_mlp: act must be 1 (softplus), 2 (nsoftplus) or 3 (elu)");
   FDSM_REQUIRE(d->head == 0 || d->head == 1, "fdsm_mlp: head must be 0 (linear) or 1 (quadratic)");
   FDSM_REQUIRE(d->passes == 1 || d->passes == 3, "fdsm_mlp: passes must be 1 or 3");
@@ -65,6 +75,8 @@ inline int make_layout(const fdsm_mlp_desc* d, long long rows, Layout& y) {
   FDSM_REQUIRE(d->presplit == 0 || d->presplit == 1, "fdsm_mlp: presplit must be 0 or 1");
   y.rows = rows;
   y.npad = (int)round_up(y.H, 16);
+  y.bn = y.npad < 256 ? y.npad : 256;
+  y.nt = (y.npad + y.bn - 1) / y.bn;
   y.kpad0 = (int)round_up(y.D + 1, 32);
   y.kpadh = (int)round_up(y.H + 1, 32);
   long long o = 0;
@@ -82,14 +94,15 @@ inline int make_layout(const fdsm_mlp_desc* d, long long rows, Layout& y) {
   long long max_partial[2] = {0, 0};
   for (int l = 0; l < y.L; ++l) {
     const int kp = l ? y.kpadh : y.kpad0;
-    y.wt_hi[l] = take((long long)kp * y.npad);
-    y.wt_lo[l] = take((long long)kp * y.npad);
-    y.wt_raw[l] = take((long long)kp * y.npad);
+    // raw-operand pipeline: only the fp32 transposed weight; pre-split pipeline: its TF32 hi/lo halves
+    y.wt_hi[l] = y.raw ? 0 : take((long long)kp * y.npad);
+    y.wt_lo[l] = y.raw ? 0 : take((long long)kp * y.npad);
+    y.wt_raw[l] = y.raw ? take((long long)kp * y.npad) : 0;
     // wgrad: M = K_l + 1 rows of dWt in tiles of 128, contraction over `rows` in k-blocks of 32
     int mt = (int)((l ? y.H : y.D) + 1 + tc::BM - 1) / tc::BM;
     if (y.raw && tc::pair_mode() && mt >= 2) mt = (mt + 1) & ~1;   // CTA pairs: the grid's x extent is padded to even
     const long long kblocks = (rows + tc::BK - 1) / tc::BK;
-    long long s = (2ll * sm_count() / 2) / mt;   // ~one CTA per SM
+    long long s = (2ll * sm_count() / 2) / ((long long)mt * y.nt);   // ~one CTA per SM
     if (s > kblocks) s = kblocks;
     if (s < 1) s = 1;
     y.splits[l] = (int)s;
@@ -107,7 +120,8 @@ inline int make_layout(const fdsm_mlp_desc* d, long long rows, Layout& y) {
   }
   y.l1 = take(rows);
   y.l2 = take(rows);
-  y.head_acc = take(2ll * head_blocks(rows) * (y.head ? 3 : 1) * (y.H + 1));   // per-block fp64 partials
+  y.head_part = y.nt > 1 ? take(3ll * y.nt * rows) : 0;
+  y.head_acc = take(2ll * head_blocks(rows, y.H) * (y.head ? 3 : 1) * (y.H + 1));   // per-block fp64 partials
   y.partial[0] = take(max_partial[0]);
   y.partial[1] = take(max_partial[1]);
   y.total = w;
@@ -144,11 +158,14 @@ __global__ void __launch_bounds__(256) prep_weights_kernel(const PrepArgs a) {
   for (int i = ty; i < 32; i += 8) {
     const int k = k0 + i, n = n0 + tx;
     if (k < kpad && n < npad) {
-      float hi, lo;
-      ptx::tf32_split(tile[tx][i], hi, lo);
-      a.hi[l][(long long)k * npad + n] = hi;
-      a.lo[l][(long long)k * npad + n] = lo;
-      a.raw[l][(long long)k * npad + n] = tile[tx][i];
+      if (a.raw[l]) {
+        a.raw[l][(long long)k * npad + n] = tile[tx][i];
+      } else {
+        float hi, lo;
+        ptx::tf32_split(tile[tx][i], hi, lo);
+        a.hi[l][(long long)k * npad + n] = hi;
+        a.lo[l][(long long)k * npad + n] = lo;
+      }
     }
   }
 }
@@ -264,6 +281,84 @@ __global__ void __launch_bounds__(HB_WARPS * 32) head_bwd_kernel(const float* __
     }
     __syncthreads();
   }
+}
+
+// H > 256: one thread per column, a block = 256 columns x one row group (blockIdx.y); the three fp64 sums live in
+// registers, the per-block record goes to partial[blockIdx.y][...] (the same format head_finish_kernel reduces).
+__global__ void __launch_bounds__(256) head_bwd_wide_kernel(const float* __restrict__ hlast, int ldh, const HeadGrad src,
+                                                            const float* __restrict__ l1v, const float* __restrict__ l2v,
+                                                            const float* __restrict__ head_w, int H, int npad, long long rows,
+                                                            int act, int head, float* __restrict__ dz_hi,
+                                                            float* __restrict__ dz_lo, double* __restrict__ partial) {
+  const int j = blockIdx.x * 256 + threadIdx.x;
+  const long long per = (rows + gridDim.y - 1) / gridDim.y;
+  const long long r0 = blockIdx.y * per, r1 = r0 + per < rows ? r0 + per : rows;
+  const bool col = j < H;
+  float w1 = 0.f, w2 = 0.f, wq = 0.f;
+  if (col) {
+    w1 = __ldg(head_w + j);
+    if (head) { w2 = __ldg(head_w + H + 1 + j); wq = __ldg(head_w + 2 * (H + 1) + j); }
+  }
+  double a1 = 0., a2 = 0., aq = 0., sb1 = 0., sb2 = 0., sbq = 0.;
+#pragma unroll 4
+  for (long long r = r0; r < r1; ++r) {
+    const float g = head_g(src, r);
+    float ga = g, gb = 0.f;
+    if (head) { ga = g * __ldg(l2v + r); gb = g * __ldg(l1v + r); }
+    float dz = 0.f;
+    if (col) {
+      const float h = __ldg(hlast + r * ldh + j);
+      float dh;
+      if (head) {
+        dh = fmaf(ga, w1, fmaf(gb, w2, 2.f * g * wq * h));
+        a1 += (double)ga * h; a2 += (double)gb * h; aq += (double)g * h * h;
+      } else {
+        dh = g * w1;
+        a1 += (double)g * h;
+      }
+      dz = dh * tc::act_bwd_from_h(act, h);
+    }
+    if (j < npad) {
+      if (dz_lo) {
+        float hi, lo;
+        ptx::tf32_split(dz, hi, lo);
+        dz_hi[r * npad + j] = hi;
+        dz_lo[r * npad + j] = lo;
+      } else {
+        dz_hi[r * npad + j] = dz;
+      }
+    }
+    if (j == 0) { sb1 += (double)ga; sb2 += (double)gb; sbq += (double)g; }
+  }
+  const int head_n = head ? 3 * (H + 1) : (H + 1);
+  double* out = partial + (long long)blockIdx.y * head_n;
+  if (col) {
+    out[j] = a1;
+    if (head) { out[H + 1 + j] = a2; out[2 * (H + 1) + j] = aq; }
+  }
+  if (j == 0) {
+    out[H] = sb1;
+    if (head) { out[2 * H + 1] = sb2; out[3 * H + 2] = sbq; }
+  }
+}
+
+// H > 256 forward: E, l1, l2 from the per-tile partial dots of EPI_HEAD (fixed tile order), biases added here
+__global__ void __launch_bounds__(256) head_energy_kernel(const float* __restrict__ part, int nt, long long rows,
+                                                          const float* __restrict__ head_w, int H, int head,
+                                                          float* __restrict__ e_out, float* __restrict__ l1_out,
+                                                          float* __restrict__ l2_out) {
+  const long long r = blockIdx.x * 256ll + threadIdx.x;
+  if (r >= rows) return;
+  float l1 = 0.f, l2 = 0.f, lq = 0.f;
+  for (int t = 0; t < nt; ++t) {
+    const float* p = part + ((long long)t * rows + r) * 3;
+    l1 += p[0]; l2 += p[1]; lq += p[2];
+  }
+  l1 += __ldg(head_w + H);
+  if (head) { l2 += __ldg(head_w + 2 * H + 1); lq += __ldg(head_w + 3 * H + 2); }
+  e_out[r] = head ? fmaf(l1, l2, lq) : l1;
+  l1_out[r] = l1;
+  l2_out[r] = l2;
 }
 
 // ghead[j] (+)= sum over the head_bwd blocks of partial[b][j] in a fixed order; when `loss` is set, one extra block
@@ -401,7 +496,8 @@ extern "C" int fdsm_mlp_prepare(const fdsm_mlp_desc* desc, int64_t rows, const f
   int kmax = 0;
   for (int l = 0; l < y.L; ++l) {
     a.W[l] = params + y.w_off[l]; a.b[l] = params + y.b_off[l];
-    a.hi[l] = workspace + y.wt_hi[l]; a.lo[l] = workspace + y.wt_lo[l]; a.raw[l] = workspace + y.wt_raw[l];
+    a.hi[l] = y.raw ? nullptr : workspace + y.wt_hi[l]; a.lo[l] = y.raw ? nullptr : workspace + y.wt_lo[l];
+    a.raw[l] = y.raw ? workspace + y.wt_raw[l] : nullptr;
     a.K[l] = l ? y.H : y.D; a.kpad[l] = l ? y.kpadh : y.kpad0;
     if (a.kpad[l] > kmax) kmax = a.kpad[l];
   }
@@ -437,9 +533,15 @@ extern "C" int fdsm_mlp_forward(const fdsm_mlp_desc* desc, const float* x_hi, co
       p.out_hi = ws + y.h_last; p.ldo = y.npad; p.out_cols = y.npad;
       p.head_w = params + y.head_off; p.head_mode = y.head;
       p.e_out = energy; p.l1_out = ws + y.l1; p.l2_out = ws + y.l2;
+      p.head_part = y.nt > 1 ? ws + y.head_part : nullptr;
     }
-    rc = tc::launch_gemm(p, A, B, (int)rows, y.H, K, y.npad, y.passes, 1, st);
+    rc = tc::launch_gemm(p, A, B, (int)rows, y.H, K, y.bn, y.passes, 1, st);
     if (rc) return rc;
+  }
+  if (y.nt > 1) {   // several N tiles: combine the per-tile head dots (fixed order), add the biases, form the energy
+    mlp::head_energy_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, st>>>(ws + y.head_part, y.nt, rows, params + y.head_off,
+                                                                             y.H, y.head, energy, ws + y.l1, ws + y.l2);
+    return cuda_status(cudaGetLastError(), "fdsm_mlp_forward(head_energy)");
   }
   return FDSM_OK;
 }
@@ -471,7 +573,12 @@ static int backward_impl(const fdsm_mlp_desc* desc, const float* x_hi, const flo
   cudaStream_t sd = forked ? side.stream : st;
   const int L1 = y.L - 1;
   {
-    const int nblk = mlp::head_blocks(rows), ni = (y.npad + 31) / 32;
+    const int nblk = mlp::head_blocks(rows, y.H), ni = (y.npad + 31) / 32;
+    if (y.H > 256) {
+      dim3 grid((y.npad + 255) / 256, nblk);
+      mlp::head_bwd_wide_kernel<<<grid, 256, 0, st>>>(ws + y.h_last, y.npad, hg, ws + y.l1, ws + y.l2, params + y.head_off, y.H,
+                                                      y.npad, rows, y.act, y.head, ws + y.dz_hi[L1], lo(ws + y.dz_lo[L1]), hacc);
+    } else {
     auto launch_head = [&](auto tag) {
       constexpr int NI = decltype(tag)::value;
       mlp::head_bwd_kernel<NI><<<nblk, mlp::HB_WARPS * 32, 0, st>>>(
@@ -487,6 +594,7 @@ static int backward_impl(const fdsm_mlp_desc* desc, const float* x_hi, const flo
       case 6: launch_head(std::integral_constant<int, 6>{}); break;
       case 7: launch_head(std::integral_constant<int, 7>{}); break;
       default: launch_head(std::integral_constant<int, 8>{}); break;
+    }
     }
     rc = cuda_status(cudaGetLastError(), "fdsm_mlp_backward(head)");
     if (rc) return rc;
@@ -513,7 +621,7 @@ static int backward_impl(const fdsm_mlp_desc* desc, const float* x_hi, const flo
     tc::GemmParams p = {};
     p.epi = tc::EPI_STORE;
     p.out_hi = partial; p.ldo = y.npad; p.split_stride = (long long)kp * y.npad;
-    int r = tc::launch_gemm(p, In, B, K + 1, y.npad, (int)rows, y.npad, y.passes, y.splits[l], s);
+    int r = tc::launch_gemm(p, In, B, K + 1, y.npad, (int)rows, y.bn, y.passes, y.splits[l], s);
     if (r) return r;
     dim3 grid((K + 1 + 7) / 8, (y.H + 31) / 32);
     if (y.splits[l] <= 24)
@@ -541,7 +649,7 @@ static int backward_impl(const fdsm_mlp_desc* desc, const float* x_hi, const flo
     p.act = y.act;
     p.out_hi = ws + y.dz_hi[l - 1]; p.out_lo = lo(ws + y.dz_lo[l - 1]); p.ldo = y.npad; p.out_cols = y.npad;
     p.aux_hi = ws + y.h_hi[l]; p.aux_lo = lo(ws + y.h_lo[l]); p.ldaux = y.kpadh;
-    rc = tc::launch_gemm(p, A, B, (int)rows, y.H, y.npad, y.npad, y.passes, 1, st);
+    rc = tc::launch_gemm(p, A, B, (int)rows, y.H, y.npad, y.bn, y.passes, 1, st);
     if (rc) return rc;
   }
   rc = wgrad(0, st);

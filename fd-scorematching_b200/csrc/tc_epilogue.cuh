@@ -130,7 +130,7 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, uint32_t tmem
       }
     } else if constexpr (EPI == EPI_HEAD) {
       // head weights of these 8 columns: 128-bit broadcast loads (zero beyond N, so no per-element select on them)
-      const float* hwc = hw + n0 + c;
+      const float* hwc = hw + c;   // staged per tile: index = column within the tile
       float wa[CW], wb[CW], wq[CW];
       {
         const float4 a0 = *reinterpret_cast<const float4*>(hwc), a1 = *reinterpret_cast<const float4*>(hwc + 4);

@@ -54,6 +54,8 @@ struct alignas(64) GemmParams {
   const float* head_w;      // EPI_HEAD: [w1(N) | b1 | w2(N) | b2 | wq(N) | bq] = the reference's ln1, ln2, lq parameters
   int head_mode;            // 1: quadratic head ; 0: linear head [w(N) | b]
   float* e_out; float* l1_out; float* l2_out;
+  float* head_part;         // EPI_HEAD with more than one N tile (H > 256): partial dots [tile][M][3] (no biases), summed by
+                            // mlp::head_energy_kernel; NULL = single tile, the epilogue finishes the energy itself
 };
 
 __device__ __forceinline__ float act_fwd(int act, float z) {
@@ -99,7 +101,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
     // weights [0, N), zeros up to HW_BIAS, the bias at HW_BIAS: columns beyond N then contribute nothing without a select
     for (int i = threadIdx.x; i < nh * HW_STRIDE; i += kThreads) {
       const int h = i / HW_STRIDE, j = i % HW_STRIDE;
-      head_smem[i] = j < p.N ? __ldg(p.head_w + h * (p.N + 1) + j) : (j == HW_BIAS ? __ldg(p.head_w + h * (p.N + 1) + p.N) : 0.f);
+      const int col = blockIdx.y * p.BN + j;   // this tile's columns [n0, n0 + BN)
+      head_smem[i] = (j < p.BN && col < p.N) ? __ldg(p.head_w + h * (p.N + 1) + col)
+                                             : (j == HW_BIAS ? __ldg(p.head_w + h * (p.N + 1) + p.N) : 0.f);
     }
   }
   constexpr int STAGES = SmemLayout::stages(PASSES);
@@ -240,6 +244,11 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
 #pragma unroll
         for (int h = 0; h < EPI_PARTS - 1; ++h) {   // fixed order: deterministic
           l1 += hsum[h][q * 32 + lane][0]; l2 += hsum[h][q * 32 + lane][1]; lq += hsum[h][q * 32 + lane][2];
+        }
+        if (p.head_part) {   // several N tiles: leave the partial dots, mlp::head_energy_kernel adds biases and combines
+          float* hp = p.head_part + ((long long)blockIdx.y * p.M + row) * 3;
+          hp[0] = l1; hp[1] = l2; hp[2] = lq;
+          l1 = l2 = lq = 0.f;
         }
         l1 += head_smem[HW_BIAS];
         l2 += p.head_mode ? head_smem[HW_STRIDE + HW_BIAS] : 0.f;

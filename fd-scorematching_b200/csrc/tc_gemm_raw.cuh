@@ -136,7 +136,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
     // weights [0, N), zeros up to HW_BIAS, the bias at HW_BIAS: columns beyond N then contribute nothing without a select
     for (int i = threadIdx.x; i < nh * HW_STRIDE; i += kThreads) {
       const int h = i / HW_STRIDE, j = i % HW_STRIDE;
-      head_smem[i] = j < p.N ? __ldg(p.head_w + h * (p.N + 1) + j) : (j == HW_BIAS ? __ldg(p.head_w + h * (p.N + 1) + p.N) : 0.f);
+      const int col = blockIdx.y * p.BN + j;   // this tile's columns [n0, n0 + BN)
+      head_smem[i] = (j < p.BN && col < p.N) ? __ldg(p.head_w + h * (p.N + 1) + col)
+                                             : (j == HW_BIAS ? __ldg(p.head_w + h * (p.N + 1) + p.N) : 0.f);
     }
   }
   tc_fence_before();
@@ -296,6 +298,11 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_raw_kernel(const __grid_cons
 #pragma unroll
         for (int h = 0; h < EPI_PARTS - 1; ++h) {   // fixed order: deterministic
           l1 += hsum[h][q * 32 + lane][0]; l2 += hsum[h][q * 32 + lane][1]; lq += hsum[h][q * 32 + lane][2];
+        }
+        if (p.head_part) {   // several N tiles: leave the partial dots, mlp::head_energy_kernel adds biases and combines
+          float* hp = p.head_part + ((long long)blockIdx.y * p.M + row) * 3;
+          hp[0] = l1; hp[1] = l2; hp[2] = lq;
+          l1 = l2 = lq = 0.f;
         }
         l1 += head_smem[HW_BIAS];
         l2 += p.head_mode ? head_smem[HW_STRIDE + HW_BIAS] : 0.f;

@@ -186,7 +186,7 @@ int fdsm_tc_gemm(const fdsm_gemm_args* args, fdsm_stream_t stream);
  * ------------------------------------------------------------------------------------------ */
 typedef struct fdsm_mlp_desc {
   int32_t in_dim;    /* D                                                         */
-  int32_t hidden;    /* H (<= 256)                                                */
+  int32_t hidden;    /* H; H > 256 (MLP_Quadratic: 5000) runs with several 256-wide N tiles per GEMM */
   int32_t n_hidden;  /* number of fc layers (3 for MLP_Quadratic_MNIST)           */
   int32_t act;       /* 1 softplus, 2 softplus - ln2 (NormalizedSoftplus), 3 ELU  */
   int32_t head;      /* 1 quadratic head, 0 Linear(H,1)                           */

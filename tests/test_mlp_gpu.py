@@ -27,7 +27,9 @@ def _pair(fdsm, D, H, L, act, head, seed=0, presplit=False):
 @pytest.mark.parametrize("D,H,L,act,head,rows", [
     (64, 48, 3, "nsoftplus", "quadratic", 96), (11, 128, 2, "softplus", "linear", 192), (11, 30, 2, "softplus", "linear", 7),
     (100, 40, 3, "elu", "quadratic", 48), (784, 200, 3, "nsoftplus", "quadratic", 3 * 256), (784, 200, 3, "elu", "quadratic", 130),
-    (20, 256, 1, "softplus", "quadratic", 33)])
+    (20, 256, 1, "softplus", "quadratic", 33),
+    # H > 256: several N tiles per GEMM, per-tile head partials, column-per-thread head backward (MLP_Quadratic is 5000 wide)
+    (64, 300, 2, "nsoftplus", "quadratic", 200), (20, 520, 2, "softplus", "linear", 130), (48, 272, 2, "softplus", "quadratic", 7)])
 @pytest.mark.parametrize("presplit", [False, True])
 def test_forward_backward_match_fp64(fdsm, D, H, L, act, head, rows, presplit):
     """3xTF32 GEMMs + fused epilogues vs fp64 autograd: energies 5e-6, flat parameter gradient 1e-5 (fp32 SGEMM grade).
