@@ -45,7 +45,8 @@ __device__ __forceinline__ void combine_energy_fwd_block(const float* __restrict
 
 // dL/dE of row r of the stacked energies (mode 0: [E1 | E2 | E3], coef = scale/B or scale)
 __device__ __forceinline__ float combine_energy_grad_row(const float* __restrict__ E, int64_t B, float c1, float coef, int64_t r) {
-  const int64_t which = r / B, b = r - which * B;
+  const int which = (r >= B) + (r >= 2 * B);   // rows = 3B: no 64-bit division (it cost ~80 instructions per row)
+  const int64_t b = r - which * B;
   if (which == 0) return coef * c1;
   const float q = (__ldg(E + B + b) - __ldg(E + 2 * B + b)) * 0.25f;
   return which == 1 ? coef * (q - 1.f) : coef * (-q - 1.f);
