@@ -319,7 +319,8 @@ class FusedEnergyMLP(nn.Module):
         per_launch_s = avg * 1e-3 / self.n_hidden
         ach = per_launch_flops / per_launch_s / 1e12
         peak = peaks["bf16_tflops"] / 2.0
-        return {"kernel": f"fdsm::tc::gemm_kernel<{self.passes}> (tcgen05 kind::tf32, TMA-fed; forward launches of the energy MLP)",
+        kname = "gemm_kernel" if self.presplit else "gemm_raw_kernel"
+        return {"kernel": f"fdsm::tc::{kname} ({self.passes}-pass tcgen05 kind::tf32, TMA-fed; forward launches of the energy MLP)",
                 "bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": None,
                 "peak_kind": f"{peaks_kind} dense bf16 burst / 2 (TF32 kind)", "passes": self.passes,
                 "executed_tf32_tflops": ach * self.passes, "executed_frac": ach * self.passes / peak,
