@@ -292,6 +292,23 @@ def ssm_vr(energy, x, mean=True, *, batch_size=None, u=None):
 
 
 # ------------------------------------------------------------------------------------------------
+# N4: GAN_FD's one-sided finite-difference gradient penalty (GAN_FD/library/trainer_fd.py:57-73 real data, :82-100 fake)
+# ------------------------------------------------------------------------------------------------
+def fd_gradient_penalty(discriminator, x, y, fd_eps, reg_param=1.0, *, u=None):
+    """d = D(cat[x, x - noise], cat[y, y]) with noise = fd_eps * sqrt(D) * u/||u|| (one launch of kernels (1)+(2), rows
+    X | MINUS); returns (d_real = d[:B], reg = reg_param * mean(((d[:B] - d[B:]) / fd_eps)**2)) as the reference computes
+    them; the caller adds its own GAN loss on d_real and calls backward()."""
+    x2, B, D = _flat(x)
+    stacked, _, _ = ops.stack(x2, row_mask=ROW_X | ROW_MINUS, scale=float(fd_eps) * math.sqrt(D),
+                              direction=None if u is None else u.reshape(B, -1), normalize=True)
+    cat_y = torch.cat([y, y], 0) if y is not None else None
+    d = discriminator(stacked.view(2 * B, *x.shape[1:]), cat_y) if cat_y is not None else discriminator(stacked.view(2 * B, *x.shape[1:]))
+    d1, d2 = d[:B], d[B:]
+    reg = reg_param * (((d1 - d2) / fd_eps) ** 2).mean()
+    return d1, reg
+
+
+# ------------------------------------------------------------------------------------------------
 # unified entry point (BASELINE.json: "(model, samples, n_particles, eps, sigma)")
 # ------------------------------------------------------------------------------------------------
 def fd_loss(model, samples, n_particles=1, eps=0.1, sigma=None, *, mode="ssm", labels=None, sigmas=None, noise=None,

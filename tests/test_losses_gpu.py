@@ -136,3 +136,25 @@ def test_philox_mode_is_a_valid_estimator(fdsm):
     # and it is deterministic under the same seed, different under another
     fdsm.manual_seed(123)
     assert float(fdsm.efficient_score_matching_conjugate(energy, x, eps=eps)) == float(loss)
+
+
+def test_gan_fd_gradient_penalty_matches_reference_expression(fdsm):
+    """N4: GAN_FD/library/trainer_fd.py:57-73 restated inline (randn_like -> l2norm over dims [1,2,3] -> noise = u/||u|| *
+    fd_eps * sqrt(D); cat[x, x - noise]; reg = mean(((d1 - d2)/fd_eps)^2)) on injected draws."""
+    dev = torch.device("cuda:0")
+    B, shape, fd_eps, reg_param = 16, (3, 8, 8), 0.1, 10.0
+    x = torch.rand(B, *shape, device=dev)
+    y = torch.randint(0, 10, (B,), device=dev)
+    u = torch.randn(B, *shape, device=dev)
+    emb = torch.nn.Embedding(10, 8).to(dev)
+    body = torch.nn.Sequential(torch.nn.Linear(3 * 8 * 8 + 8, 32), torch.nn.ELU(), torch.nn.Linear(32, 1)).to(dev)
+    disc = lambda inp, lab: body(torch.cat([inp.reshape(inp.shape[0], -1), emb(lab)], 1)).view(-1)
+    d_real, reg = fdsm.fd_gradient_penalty(disc, x, y, fd_eps, reg_param, u=u)
+    l2norm = torch.pow(torch.sum(u ** 2, dim=[1, 2, 3]), 0.5).view(B, 1, 1, 1)
+    noise = u / l2norm * fd_eps * np.sqrt(3 * 8 * 8)
+    cat_d = disc(torch.cat([x, x - noise], 0), torch.cat([y, y], 0))
+    want_reg = reg_param * (((cat_d[:B] - cat_d[B:]) / fd_eps) ** 2).mean()
+    assert torch.allclose(d_real, cat_d[:B], rtol=0, atol=0)
+    assert _rel(reg, want_reg) < 2e-4          # (u/||u||)*c vs u/||u||*eps*sqrt(D): one rounding apart, amplified by 1/eps
+    (d_real.mean() + reg).backward()
+    assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in body.parameters())
