@@ -208,6 +208,8 @@ __global__ void __launch_bounds__(HB_WARPS * 32) head_bwd_kernel(const float* __
     }
   }
   double sb1 = 0., sb2 = 0., sbq = 0.;
+  pdl_launch_dependents();   // the dgrad GEMM sets up behind this grid
+  pdl_wait();                // launched programmatically behind the last forward GEMM: head weights above, E / H_L below
   // two rows per iteration, every load of both rows issued before the arithmetic: the kernel is latency-bound (each warp
   // walks ~5 rows; one row at a time exposed two dependent L2 round trips per row)
   for (long long r = (long long)blockIdx.x * HB_WARPS + warp; r < rows; r += 2 * W) {
@@ -402,6 +404,8 @@ __global__ void __launch_bounds__(256 * GROUPS) reduce_wgrad_kernel(const float*
                                                                     float* __restrict__ gb, int accumulate) {
   __shared__ double part[GROUPS][8][32];
   __shared__ float tile[8][33];
+  pdl_launch_dependents();
+  pdl_wait();   // no-ops unless launched programmatically (main-stream instance only: fd_mlp.cu wgrad())
   const int k0 = blockIdx.x * 8, n0 = blockIdx.y * 32;
   const int tx = threadIdx.x & 31, ty = (threadIdx.x >> 5) & 7, tz = threadIdx.x >> 8;
   const long long stride = (long long)kpad * npad;
@@ -581,9 +585,9 @@ static int backward_impl(const fdsm_mlp_desc* desc, const float* x_hi, const flo
     } else {
     auto launch_head = [&](auto tag) {
       constexpr int NI = decltype(tag)::value;
-      mlp::head_bwd_kernel<NI><<<nblk, mlp::HB_WARPS * 32, 0, st>>>(
-          ws + y.h_last, y.npad, hg, ws + y.l1, ws + y.l2, params + y.head_off, y.H, y.npad, rows, y.act, y.head,
-          ws + y.dz_hi[L1], lo(ws + y.dz_lo[L1]), hacc);
+      launch_pdl(mlp::head_bwd_kernel<NI>, dim3(nblk), dim3(mlp::HB_WARPS * 32), 0, st, (const float*)(ws + y.h_last), y.npad, hg,
+                 (const float*)(ws + y.l1), (const float*)(ws + y.l2), params + y.head_off, y.H, y.npad, (long long)rows, y.act,
+                 y.head, ws + y.dz_hi[L1], lo(ws + y.dz_lo[L1]), hacc);
     };
     switch (ni) {
       case 1: launch_head(std::integral_constant<int, 1>{}); break;
@@ -624,13 +628,22 @@ static int backward_impl(const fdsm_mlp_desc* desc, const float* x_hi, const flo
     int r = tc::launch_gemm(p, In, B, K + 1, y.npad, (int)rows, y.bn, y.passes, y.splits[l], s);
     if (r) return r;
     dim3 grid((K + 1 + 7) / 8, (y.H + 31) / 32);
+    // the main-stream instance (layer 0, the last kernel of the backward) is launched programmatically: its blocks are
+    // resident when the wgrad GEMM drains; side-stream instances are not (idle blocks would take the SM slots the
+    // main stream's dgrad CTAs want)
+    const bool pdl = s == st && forked;
+    cudaError_t e;
     if (y.splits[l] <= 24)
-      mlp::reduce_wgrad_kernel<1><<<grid, 256, 0, s>>>(partial, y.splits[l], kp, y.npad, y.H, K, grads + y.w_off[l],
-                                                      grads + y.b_off[l], accumulate);
+      e = pdl ? launch_pdl(mlp::reduce_wgrad_kernel<1>, grid, dim3(256), 0, s, (const float*)partial, y.splits[l], kp, y.npad, y.H,
+                           K, grads + y.w_off[l], grads + y.b_off[l], (int)accumulate)
+              : (mlp::reduce_wgrad_kernel<1><<<grid, 256, 0, s>>>(partial, y.splits[l], kp, y.npad, y.H, K, grads + y.w_off[l],
+                                                                 grads + y.b_off[l], accumulate), cudaGetLastError());
     else
-      mlp::reduce_wgrad_kernel<4><<<grid, 1024, 0, s>>>(partial, y.splits[l], kp, y.npad, y.H, K, grads + y.w_off[l],
-                                                       grads + y.b_off[l], accumulate);
-    return cuda_status(cudaGetLastError(), "fdsm_mlp_backward(reduce)");
+      e = pdl ? launch_pdl(mlp::reduce_wgrad_kernel<4>, grid, dim3(1024), 0, s, (const float*)partial, y.splits[l], kp, y.npad, y.H,
+                           K, grads + y.w_off[l], grads + y.b_off[l], (int)accumulate)
+              : (mlp::reduce_wgrad_kernel<4><<<grid, 1024, 0, s>>>(partial, y.splits[l], kp, y.npad, y.H, K, grads + y.w_off[l],
+                                                                  grads + y.b_off[l], accumulate), cudaGetLastError());
+    return cuda_status(e, "fdsm_mlp_backward(reduce)");
   };
   for (int l = L1; l >= 1; --l) {
     if (forked) {   // side stream: wait until dZ_l is complete, then wgrad_l

@@ -13,6 +13,8 @@ constexpr int kPartials = FDSM_SUMSQ_PARTIALS;
 __global__ void __launch_bounds__(1024) sumsq_kernel(const float* __restrict__ g, long long n, float* __restrict__ out,
                                                      long long* __restrict__ step) {
   __shared__ float red[32];
+  pdl_launch_dependents();
+  pdl_wait();
   const long long chunk = ((n + kPartials - 1) / kPartials + 3) & ~3ll;
   const long long lo = blockIdx.x * chunk, hi = lo + chunk < n ? lo + chunk : n;
   float acc = 0.f;
@@ -42,6 +44,7 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
                                                    float* __restrict__ v, long long n, float lr, const float* __restrict__ lr_dev,
                                                    float b1, float b2, float eps, float max_norm,
                                                    const float* __restrict__ sumsq, const long long* __restrict__ step) {
+  pdl_wait();
   const float t = (float)__ldg(step);
   const float lrv = lr_dev ? __ldg(lr_dev) : lr;
   float coef = 1.f;
@@ -80,8 +83,8 @@ using namespace fdsm;
 
 extern "C" int fdsm_grad_sumsq(const float* g, int64_t n, float* sumsq, int64_t* step_counter, fdsm_stream_t stream) {
   FDSM_REQUIRE(n >= 0 && sumsq && (g || n == 0), "fdsm_grad_sumsq: bad arguments");
-  sumsq_kernel<<<kPartials, 256, 0, (cudaStream_t)stream>>>(g, n, sumsq, (long long*)step_counter);
-  FDSM_LAUNCH_CHECK("fdsm_grad_sumsq");
+  return cuda_status(launch_pdl(sumsq_kernel, dim3(kPartials), dim3(256), 0, (cudaStream_t)stream, g, (long long)n, sumsq,
+                                (long long*)step_counter), "fdsm_grad_sumsq");
 }
 
 extern "C" int fdsm_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
@@ -93,8 +96,7 @@ extern "C" int fdsm_adam_step(float* params, const float* grads, float* exp_avg,
   FDSM_REQUIRE(max_norm <= 0.f || sumsq, "fdsm_adam_step: clipping needs the squared gradient norm");
   const long long nb = (n / 4 + 255) / 256 + 1;
   const long long cap = (long long)sm_count() * 8;
-  adam_kernel<<<(int)(nb < cap ? nb : cap), 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, n, lr, lr_dev, beta1,
-                                                                           beta2, eps, max_norm, sumsq,
-                                                                           (const long long*)step_counter);
-  FDSM_LAUNCH_CHECK("fdsm_adam_step");
+  return cuda_status(launch_pdl(adam_kernel, dim3((unsigned)(nb < cap ? nb : cap)), dim3(256), 0, (cudaStream_t)stream, params, grads,
+                                exp_avg, exp_avg_sq, (long long)n, lr, lr_dev, beta1, beta2, eps, max_norm, sumsq,
+                                (const long long*)step_counter), "fdsm_adam_step");
 }

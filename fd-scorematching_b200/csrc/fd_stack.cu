@@ -88,6 +88,7 @@ __device__ __forceinline__ float4 normalise(float4 d, float nrm, float scale) {
 
 template <int G, bool VEC, bool CACHE>
 __global__ void __launch_bounds__(kBlock) stack_kernel(fdsm_stack_args a) {
+  pdl_launch_dependents();   // the GEMM that consumes the stacked rows sets up (barriers, TMEM) while this grid runs
   if (a.offset_dev) a.offset += __ldg(reinterpret_cast<const unsigned long long*>(a.offset_dev));
   constexpr int RPB = kBlock / G;
   __shared__ float red[kBlock / 32];

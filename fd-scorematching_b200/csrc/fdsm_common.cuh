@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "../../include/fdsm.h"
 
@@ -24,6 +25,30 @@ int cuda_status(cudaError_t e, const char* what);
 
 __host__ __device__ static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 int sm_count();
+
+// ---- programmatic dependent launch (PDL) for the small kernels of the step's critical chain: a kernel launched through
+// launch_pdl may become resident while its stream predecessor drains and must execute pdl_wait() before it touches
+// anything the predecessor wrote; pdl_launch_dependents() lets the NEXT kernel of the stream (if it was launched with
+// the attribute) do the same.  Both instructions are no-ops in a grid launched without the attribute.
+// FDSM_GEMM_PDL=0 switches every programmatic launch of the library off. ----
+inline bool pdl_enabled() {
+  static const bool on = [] { const char* e = getenv("FDSM_GEMM_PDL"); return !(e && e[0] == '0'); }();
+  return on;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#endif
 
 // ---- Philox4x32-10 (Salmon et al. 2011), counter-based --------------------------------------
 // counter = (chunk index within the row, global row lo, global row hi | stream<<28, draw offset)
