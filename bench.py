@@ -28,7 +28,8 @@ import torch  # noqa: E402
 B_PER_GPU, D, HID, NHID, EPS = 4096, 784, 200, 3, 0.05
 LR, BETAS, CLIP = 1e-5, (0.9, 0.95), 0.1
 POOL = 16  # rotating device batches: 16 x 12.85 MB = 205 MB > 126 MB L2
-WORKLOAD = "cfg2: DeepEBM ssm_fd, MLP_Quadratic_MNIST(nsoftplus) 784-200-200-200, B=4096/GPU, D=784, Adam+clip"
+ACT = os.environ.get("FDSM_BENCH_ACT", "nsoftplus")   # authors' command.sh:5; "elu" = default.yaml:12 (second cfg2 variant)
+WORKLOAD = f"cfg2: DeepEBM ssm_fd, MLP_Quadratic_MNIST({ACT}) 784-200-200-200, B=4096/GPU, D=784, Adam+clip"
 
 
 def peaks():
@@ -106,7 +107,7 @@ def synth_batch(gen, n, device):
 def cpu_step_fn(batch):
     from oracle import fd_losses, nets
     torch.manual_seed(1234)
-    net = nets.init_from_numpy(nets.QuadraticMLP(D, HID, NHID, "nsoftplus"), 1234)
+    net = nets.init_from_numpy(nets.QuadraticMLP(D, HID, NHID, ACT), 1234)
     opt = torch.optim.Adam(net.parameters(), lr=LR, betas=BETAS)
     g = torch.Generator().manual_seed(1234)
     xs = [synth_batch(g, batch, "cpu") for _ in range(2)]
@@ -178,7 +179,7 @@ class TorchQuadraticMLP(torch.nn.Module):
 
     def forward(self, x):
         for fc in self.fcs:
-            x = torch.nn.functional.softplus(fc(x)) - 0.6931471805599453
+            x = torch.nn.functional.elu(fc(x)) if ACT == "elu" else torch.nn.functional.softplus(fc(x)) - 0.6931471805599453
         return (self.ln1(x) * self.ln2(x) + self.lq(x * x)).view(-1)
 
 
@@ -213,7 +214,7 @@ def main():
 
     use_fused = args.network in ("auto", "fused")
     if use_fused:
-        net = fdsm.mlp.FusedEnergyMLP(D, HID, NHID, act="nsoftplus", head="quadratic", device=dev, seed=1234)
+        net = fdsm.mlp.FusedEnergyMLP(D, HID, NHID, act=ACT, head="quadratic", device=dev, seed=1234)
         network = "fused tcgen05 3xTF32 MLP (ours): kernels (1)-(4) + clip + Adam, one CUDA-graph replay per step"
     else:
         net = TorchQuadraticMLP(D, HID, NHID).to(dev)

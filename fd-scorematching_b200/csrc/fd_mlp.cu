@@ -102,7 +102,25 @@ inline int make_layout(const fdsm_mlp_desc* d, long long rows, Layout& y) {
     int mt = (int)((l ? y.H : y.D) + 1 + tc::BM - 1) / tc::BM;
     if (y.raw && tc::pair_mode() && mt >= 2) mt = (mt + 1) & ~1;   // CTA pairs: the grid's x extent is padded to even
     const long long kblocks = (rows + tc::BK - 1) / tc::BK;
-    long long s = (2ll * sm_count() / 2) / ((long long)mt * y.nt);   // ~one CTA per SM
+    // ~one CTA per SM.  Hidden layers (l >= 1) run on the side stream next to a dgrad launch of ceil(rows/128)*nt CTAs
+    // (one CTA per SM: ~200 KB of shared memory each): sized to the SMs that launch leaves free, so that neither grid
+    // queues behind the other (FDSM_WGRAD_SIDE_CTAS / FDSM_WGRAD_MAIN_CTAS override the CTA budgets)
+    long long budget = sm_count();
+    if (y.L > 1) {
+      static const int forced_side = [] { const char* e = getenv("FDSM_WGRAD_SIDE_CTAS"); return e ? atoi(e) : 0; }();
+      static const int forced_main = [] { const char* e = getenv("FDSM_WGRAD_MAIN_CTAS"); return e ? atoi(e) : 0; }();
+      const long long dgrad_ctas = ((rows + tc::BM - 1) / tc::BM) * y.nt, free_sms = sm_count() - dgrad_ctas;
+      const bool share = free_sms >= sm_count() / 4 && dgrad_ctas >= sm_count() / 4;
+      const long long unit_h = (long long)((y.H + 1 + tc::BM - 1) / tc::BM) * y.nt;   // CTAs per split of a hidden layer
+      long long side = forced_side > 0 ? forced_side : (share ? 3 * free_sms / 4 : sm_count());
+      if (side < unit_h) side = unit_h;
+      // layer 0 (main stream, after the last dgrad) runs next to the side stream's wgrad_1 and is the longer of the two
+      // (K_0 >> H): it gets every SM the side grid does not take (measured optimum at config 2: 36-44 side / 104-112 main)
+      const long long side_ctas = side / unit_h * unit_h;
+      if (l >= 1) budget = side;
+      else budget = forced_main > 0 ? forced_main : (share && side_ctas < sm_count() ? sm_count() - side_ctas : budget);
+    }
+    long long s = budget / ((long long)mt * y.nt);
     if (s > kblocks) s = kblocks;
     if (s < 1) s = 1;
     y.splits[l] = (int)s;
