@@ -203,27 +203,34 @@ struct HeadGrad {
 __device__ __forceinline__ float head_g(const HeadGrad& s, long long r) {
   return s.dE ? __ldg(s.dE + r) : combine_energy_grad_row(s.E, s.B, s.c1, s.coef, r);
 }
-template <int NI>
+template <int NI, bool HEAD>
 __global__ void __launch_bounds__(HB_WARPS * 32) head_bwd_kernel(const float* __restrict__ hlast, int ldh, const HeadGrad src,
                                                                  const float* __restrict__ l1v, const float* __restrict__ l2v,
                                                                  const float* __restrict__ head_w, int H, int npad,
-                                                                 long long rows, int act, int head, float* __restrict__ dz_hi,
+                                                                 long long rows, int act, float* __restrict__ dz_hi,
                                                                  float* __restrict__ dz_lo, double* __restrict__ partial) {
+  constexpr int head = HEAD ? 1 : 0;
   __shared__ double red[HB_WARPS][NI * 32];
   __shared__ double redb[HB_WARPS][3];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const long long W = (long long)gridDim.x * HB_WARPS;
+  // columns beyond H carry zero weights and zero activations: every sum below gets exact zeros from them and dZ = 0 is
+  // what the padded columns must hold, so the inner loops need no column branches (bit i of the masks = column
+  // lane + 32 i is a real / a stored one)
   float w1[NI], w2[NI], wq[NI];
   double a1[NI], a2[NI], aq[NI];
+  unsigned hmask = 0, nmask = 0;
 #pragma unroll
   for (int i = 0; i < NI; ++i) {
     const int j = lane + 32 * i;
     w1[i] = w2[i] = wq[i] = 0.f;
     a1[i] = a2[i] = aq[i] = 0.;
     if (j < H) {
+      hmask |= 1u << i;
       w1[i] = __ldg(head_w + j);
-      if (head) { w2[i] = __ldg(head_w + H + 1 + j); wq[i] = __ldg(head_w + 2 * (H + 1) + j); }
+      if (HEAD) { w2[i] = __ldg(head_w + H + 1 + j); wq[i] = __ldg(head_w + 2 * (H + 1) + j); }
     }
+    if (j < npad) nmask |= 1u << i;
   }
   double sb1 = 0., sb2 = 0., sbq = 0.;
   pdl_launch_dependents();   // the dgrad GEMM sets up behind this grid
@@ -238,41 +245,38 @@ __global__ void __launch_bounds__(HB_WARPS * 32) head_bwd_kernel(const float* __
     for (int u = 0; u < 2; ++u) {
       g[u] = okr[u] ? head_g(src, rr[u]) : 0.f;
       ga[u] = g[u]; gb[u] = 0.f;
-      if (head && okr[u]) { ga[u] = g[u] * __ldg(l2v + rr[u]); gb[u] = g[u] * __ldg(l1v + rr[u]); }
+      if (HEAD && okr[u]) { ga[u] = g[u] * __ldg(l2v + rr[u]); gb[u] = g[u] * __ldg(l1v + rr[u]); }
+      const float* hrow = hlast + rr[u] * ldh + lane;
 #pragma unroll
-      for (int i = 0; i < NI; ++i) {
-        const int j = lane + 32 * i;
-        h[u][i] = (okr[u] && j < H) ? __ldg(hlast + rr[u] * ldh + j) : 0.f;
-      }
+      for (int i = 0; i < NI; ++i) h[u][i] = (okr[u] && (hmask >> i & 1)) ? __ldg(hrow + 32 * i) : 0.f;
     }
 #pragma unroll
     for (int u = 0; u < 2; ++u) {
       if (!okr[u]) continue;
       const double dga = (double)ga[u], dgb = (double)gb[u], dg = (double)g[u];
+      const float g2 = 2.f * g[u];
+      float* drow = dz_hi + rr[u] * npad + lane;
+      float* lrow = dz_lo ? dz_lo + rr[u] * npad + lane : nullptr;
 #pragma unroll
       for (int i = 0; i < NI; ++i) {
-        const int j = lane + 32 * i;
-        float dz = 0.f;
-        if (j < H) {
-          float dh;
-          const double hd = (double)h[u][i];
-          if (head) {
-            dh = fmaf(ga[u], w1[i], fmaf(gb[u], w2[i], 2.f * g[u] * wq[i] * h[u][i]));
-            a1[i] += dga * hd; a2[i] += dgb * hd; aq[i] += dg * hd * hd;
-          } else {
-            dh = g[u] * w1[i];
-            a1[i] += dg * hd;
-          }
-          dz = dh * tc::act_bwd_from_h(act, h[u][i]);
+        const double hd = (double)h[u][i];
+        float dh;
+        if (HEAD) {
+          dh = fmaf(ga[u], w1[i], fmaf(gb[u], w2[i], g2 * wq[i] * h[u][i]));
+          a1[i] += dga * hd; a2[i] += dgb * hd; aq[i] += dg * hd * hd;
+        } else {
+          dh = g[u] * w1[i];
+          a1[i] += dg * hd;
         }
-        if (j < npad) {
-          if (dz_lo) {
+        const float dz = dh * tc::act_bwd_from_h(act, h[u][i]);
+        if (nmask >> i & 1) {
+          if (lrow) {
             float hi, lo;
             ptx::tf32_split(dz, hi, lo);
-            dz_hi[rr[u] * npad + j] = hi;
-            dz_lo[rr[u] * npad + j] = lo;
+            drow[32 * i] = hi;
+            lrow[32 * i] = lo;
           } else {
-            dz_hi[rr[u] * npad + j] = dz;
+            drow[32 * i] = dz;
           }
         }
       }
@@ -603,9 +607,12 @@ static int backward_impl(const fdsm_mlp_desc* desc, const float* x_hi, const flo
     } else {
     auto launch_head = [&](auto tag) {
       constexpr int NI = decltype(tag)::value;
-      launch_pdl(mlp::head_bwd_kernel<NI>, dim3(nblk), dim3(mlp::HB_WARPS * 32), 0, st, (const float*)(ws + y.h_last), y.npad, hg,
-                 (const float*)(ws + y.l1), (const float*)(ws + y.l2), params + y.head_off, y.H, y.npad, (long long)rows, y.act,
-                 y.head, ws + y.dz_hi[L1], lo(ws + y.dz_lo[L1]), hacc);
+      auto go = [&](auto kernel) {
+        launch_pdl(kernel, dim3(nblk), dim3(mlp::HB_WARPS * 32), 0, st, (const float*)(ws + y.h_last), y.npad, hg,
+                   (const float*)(ws + y.l1), (const float*)(ws + y.l2), params + y.head_off, y.H, y.npad, (long long)rows, y.act,
+                   ws + y.dz_hi[L1], lo(ws + y.dz_lo[L1]), hacc);
+      };
+      if (y.head) go(mlp::head_bwd_kernel<NI, true>); else go(mlp::head_bwd_kernel<NI, false>);
     };
     switch (ni) {
       case 1: launch_head(std::integral_constant<int, 1>{}); break;
