@@ -26,11 +26,13 @@ namespace mlp {
 
 inline long long round_up(long long x, long long m) { return (x + m - 1) / m * m; }
 constexpr int HB_WARPS = 8;   // head_bwd_kernel: warps (= rows in flight) per block
-// number of per-block partial-sum records of the head backward: H <= 256: one warp per row, ~2 blocks per SM;
+constexpr int HB_BLOCKS_PER_SM = 2;   // resident blocks per SM the kernel is compiled for (<= 128 registers)
+constexpr int HB_ROWS = 3;            // rows a warp has in flight per iteration
+// number of per-block partial-sum records of the head backward: H <= 256: one warp per row, HB_BLOCKS_PER_SM blocks per SM;
 // H > 256 (head_bwd_wide_kernel): row groups, so that column tiles x row groups ~ 2 blocks per SM
 inline int head_blocks(long long rows, int H) {
   if (H <= 256) {
-    long long b = (rows + HB_WARPS - 1) / HB_WARPS, cap = 2ll * sm_count();
+    long long b = (rows + HB_WARPS - 1) / HB_WARPS, cap = (long long)HB_BLOCKS_PER_SM * sm_count();
     return (int)(b < cap ? (b < 1 ? 1 : b) : cap);
   }
   const long long ct = (H + 255) / 256;
@@ -204,7 +206,7 @@ __device__ __forceinline__ float head_g(const HeadGrad& s, long long r) {
   return s.dE ? __ldg(s.dE + r) : combine_energy_grad_row(s.E, s.B, s.c1, s.coef, r);
 }
 template <int NI, bool HEAD>
-__global__ void __launch_bounds__(HB_WARPS * 32) head_bwd_kernel(const float* __restrict__ hlast, int ldh, const HeadGrad src,
+__global__ void __launch_bounds__(HB_WARPS * 32, HB_BLOCKS_PER_SM) head_bwd_kernel(const float* __restrict__ hlast, int ldh, const HeadGrad src,
                                                                  const float* __restrict__ l1v, const float* __restrict__ l2v,
                                                                  const float* __restrict__ head_w, int H, int npad,
                                                                  long long rows, int act, float* __restrict__ dz_hi,
@@ -217,32 +219,37 @@ __global__ void __launch_bounds__(HB_WARPS * 32) head_bwd_kernel(const float* __
   // columns beyond H carry zero weights and zero activations: every sum below gets exact zeros from them and dZ = 0 is
   // what the padded columns must hold, so the inner loops need no column branches (bit i of the masks = column
   // lane + 32 i is a real / a stored one)
-  float w1[NI], w2[NI], wq[NI];
+  // head weights live in shared memory (zero beyond H), the fp64 sums in registers: 3 resident blocks per SM
+  __shared__ float sw[3][NI * 32];
   double a1[NI], a2[NI], aq[NI];
   unsigned hmask = 0, nmask = 0;
+  for (int j = threadIdx.x; j < NI * 32; j += HB_WARPS * 32) {
+    sw[0][j] = j < H ? __ldg(head_w + j) : 0.f;
+    sw[1][j] = HEAD && j < H ? __ldg(head_w + H + 1 + j) : 0.f;
+    sw[2][j] = HEAD && j < H ? __ldg(head_w + 2 * (H + 1) + j) : 0.f;
+  }
 #pragma unroll
   for (int i = 0; i < NI; ++i) {
     const int j = lane + 32 * i;
-    w1[i] = w2[i] = wq[i] = 0.f;
     a1[i] = a2[i] = aq[i] = 0.;
-    if (j < H) {
-      hmask |= 1u << i;
-      w1[i] = __ldg(head_w + j);
-      if (HEAD) { w2[i] = __ldg(head_w + H + 1 + j); wq[i] = __ldg(head_w + 2 * (H + 1) + j); }
-    }
+    if (j < H) hmask |= 1u << i;
     if (j < npad) nmask |= 1u << i;
   }
+  __syncthreads();
   double sb1 = 0., sb2 = 0., sbq = 0.;
   pdl_launch_dependents();   // the dgrad GEMM sets up behind this grid
   pdl_wait();                // launched programmatically behind the last forward GEMM: head weights above, E / H_L below
-  // two rows per iteration, every load of both rows issued before the arithmetic: the kernel is latency-bound (each warp
-  // walks ~5 rows; one row at a time exposed two dependent L2 round trips per row)
-  for (long long r = (long long)blockIdx.x * HB_WARPS + warp; r < rows; r += 2 * W) {
-    const long long rr[2] = {r, r + W};
-    const bool okr[2] = {true, r + W < rows};
-    float g[2], ga[2], gb[2], h[2][NI];
+  // HB_ROWS rows per iteration, every load of all of them issued before the arithmetic: the kernel is latency-bound
+  // (each warp walks ~5 rows; one row at a time exposed two dependent L2 round trips per row)
+  constexpr int U = HB_ROWS;
+  for (long long r = (long long)blockIdx.x * HB_WARPS + warp; r < rows; r += U * W) {
+    long long rr[U];
+    bool okr[U];
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
+    for (int u = 0; u < U; ++u) { rr[u] = r + u * W; okr[u] = rr[u] < rows; }
+    float g[U], ga[U], gb[U], h[U][NI];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
       g[u] = okr[u] ? head_g(src, rr[u]) : 0.f;
       ga[u] = g[u]; gb[u] = 0.f;
       if (HEAD && okr[u]) { ga[u] = g[u] * __ldg(l2v + rr[u]); gb[u] = g[u] * __ldg(l1v + rr[u]); }
@@ -251,7 +258,7 @@ __global__ void __launch_bounds__(HB_WARPS * 32) head_bwd_kernel(const float* __
       for (int i = 0; i < NI; ++i) h[u][i] = (okr[u] && (hmask >> i & 1)) ? __ldg(hrow + 32 * i) : 0.f;
     }
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
+    for (int u = 0; u < U; ++u) {
       if (!okr[u]) continue;
       const double dga = (double)ga[u], dgb = (double)gb[u], dg = (double)g[u];
       const float g2 = 2.f * g[u];
@@ -262,10 +269,10 @@ __global__ void __launch_bounds__(HB_WARPS * 32) head_bwd_kernel(const float* __
         const double hd = (double)h[u][i];
         float dh;
         if (HEAD) {
-          dh = fmaf(ga[u], w1[i], fmaf(gb[u], w2[i], g2 * wq[i] * h[u][i]));
+          dh = fmaf(ga[u], sw[0][lane + 32 * i], fmaf(gb[u], sw[1][lane + 32 * i], g2 * sw[2][lane + 32 * i] * h[u][i]));
           a1[i] += dga * hd; a2[i] += dgb * hd; aq[i] += dg * hd * hd;
         } else {
-          dh = g[u] * w1[i];
+          dh = g[u] * sw[0][lane + 32 * i];
           a1[i] += dg * hd;
         }
         const float dz = dh * tc::act_bwd_from_h(act, h[u][i]);
