@@ -5,7 +5,8 @@ contains a hyphen).  Public surface = the reference's loss-function signatures (
 kernel-level ops (``ops``) and the fused energy MLPs (``mlp``).
 """
 from . import _lib, losses, mlp, ops, sampling  # noqa: F401
-from .losses import (FLAGS, MLE_efficient_score_matching_conjugate, anneal_ESM_scorenet_VR, dsm_fd,  # noqa: F401
+from .losses import (FLAGS, MLE_efficient_score_matching_conjugate, anneal_ESM_scorenet_VR,  # noqa: F401
+                     anneal_sliced_score_estimation_vr, dsm_fd, exact_score_matching,
                      dsm_tracetrick_FD, efficient_score_matching_conjugate, esm_scorenet_VR, fd_gradient_penalty, fd_loss, mdsm_fd,
                      mdsm_fd_nop, ncsn_anneal_ESM_scorenet, ncsn_anneal_ESM_scorenet_VR,
                      single_efficient_score_matching, single_sliced_score_matching, sliced_VR_score_matching,

@@ -71,12 +71,18 @@ def efficient_score_matching_conjugate(energy_net, samples, noise=None, eps=0.1,
 
 
 def single_efficient_score_matching(energy_net, samples, eps=0.01, noise_type="sphere", *, u=None):
-    """One-sided 2-point FD -- SSM/losses/efficient_sm.py:7-24 (sum of d^2+4d, no /eps^2)."""
-    if noise_type != "sphere":
-        raise NotImplementedError("only noise_type='sphere' is implemented on the CUDA path "
-                                  "(efficient_sm.py:10-11 'radermacher' is not part of the hot path)")
+    """One-sided 2-point FD -- SSM/losses/efficient_sm.py:7-24 (sum of d^2+4d, no /eps^2).  'sphere': eps*u/||u||
+    inside the stack kernel; 'radermacher' (the reference's spelling, :10-11): v = sign(u)*eps, handed to the stack
+    kernel as an already-scaled direction; any other value leaves the Gaussian draw unscaled, as the reference does."""
     x2 = samples.reshape(samples.shape[0], -1)
-    return _fd_energy(energy_net, x2, u=u, eps=eps, scale=1.0, mean=False, rows3=False, mode=1)[0]
+    if noise_type == "sphere":
+        return _fd_energy(energy_net, x2, u=u, eps=eps, scale=1.0, mean=False, rows3=False, mode=1)[0]
+    if u is not None:
+        u = u.reshape(x2.shape)
+    v = _projection_vectors(x2, "radermacher" if noise_type == "radermacher" else "gaussian", u)
+    if noise_type == "radermacher":
+        v = v * eps
+    return _fd_energy(energy_net, x2, v=v, eps=eps, scale=1.0, mean=False, rows3=False, mode=1)[0]
 
 
 def MLE_efficient_score_matching_conjugate(energy_net, samples, eps=0.01, mle_ratio=10, noise_type="sphere", *, u=None):
@@ -289,6 +295,50 @@ def ssm_vr(energy, x, mean=True, *, batch_size=None, u=None):
     x2 = x.reshape(bs, -1)
     per, _, _ = _ssm_hvp(energy, x2, _projection_vectors(x2, "gaussian", u), vr=True)
     return per.mean() if mean is True else per
+
+
+def anneal_sliced_score_estimation_vr(scorenet, samples, sigmas, labels=None, anneal_power=2.0, hook=None, n_particles=1,
+                                      *, u=None, dsm_noise=None):
+    """ncsnv2/losses/dsm.py:33-74: the exact (double-backward) annealed SSM-VR objective that a13 replaces.  The noise
+    and the Gaussian projections (:53; one per particle) come from kernel (1)'s Philox streams; the score net and its
+    vector-Jacobian product run in torch.  Unlike the FD forms this one is shape-correct for n_particles > 1
+    (per-particle means at :64-65)."""
+    x2, B, D = _flat(samples)
+    if labels is None:
+        labels = torch.randint(0, len(sigmas), (B,), device=samples.device)
+    if dsm_noise is None:
+        seed, offset, row0 = ops.next_draw()
+        dsm_noise = ops.philox_normal(B, D, 1, seed, offset, row0, device=samples.device)
+    if u is None:
+        seed, offset, row0 = ops.next_draw()
+        u = ops.philox_normal(n_particles * B, D, 0, seed, offset, row0, device=samples.device)
+    used = sigmas[labels].view(B, 1).to(x2.dtype)
+    xt = x2 + dsm_noise.reshape(B, D) * used
+    dup = xt.unsqueeze(0).expand(n_particles, B, D).reshape(n_particles * B, *samples.shape[1:]).detach().requires_grad_(True)
+    dup_labels = labels.unsqueeze(0).expand(n_particles, B).reshape(-1)
+    vectors = u.reshape(dup.shape)
+    grad1 = scorenet(dup, dup_labels)
+    grad2 = torch.autograd.grad(torch.sum(grad1 * vectors), dup, create_graph=True)[0]
+    loss1 = torch.sum(grad1.reshape(n_particles * B, -1) ** 2, dim=-1) / 2.0
+    loss2 = torch.sum((vectors * grad2).reshape(n_particles * B, -1), dim=-1)
+    per = (loss1.view(n_particles, B).mean(0) + loss2.view(n_particles, B).mean(0)) * used.view(B) ** anneal_power
+    if hook is not None:
+        hook(per, labels)
+    return per.mean(dim=0)
+
+
+def exact_score_matching(energy_net, samples, train=False):
+    """SSM/losses/score_matching.py:48-73: per-sample 0.5 ||grad logp||^2 + tr(Hessian logp) by one backward pass per
+    input dimension.  Evaluation metric of the DKEF runner (dkef_runner.py:373-389); no random draws and no kernel of
+    ours: D passes through the caller's torch network.  Returns the per-sample vector (detached unless train)."""
+    samples.requires_grad_(True)
+    logp = -energy_net(samples).sum()
+    grad1 = torch.autograd.grad(logp, samples, create_graph=True)[0]
+    loss = torch.norm(grad1, dim=-1) ** 2 / 2.0
+    for i in range(samples.shape[1]):
+        g = torch.autograd.grad(grad1[:, i].sum(), samples, create_graph=train, retain_graph=True)[0][:, i]
+        loss = loss + (g if train else g.detach())
+    return loss if train else loss.detach()
 
 
 # ------------------------------------------------------------------------------------------------

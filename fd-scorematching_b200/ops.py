@@ -167,6 +167,8 @@ def direction(B, D, scale, *, u=None, device=None, draw=None):
 
 def philox_normal(B, D, stream_id, seed, offset, row0=0, device="cuda"):
     lib = _lib.load()
+    if torch.device(device).type != "cuda":
+        raise _lib.FdsmError(f"philox_normal draws on the GPU (no CPU fallback); got device {device}")
     out = torch.empty((B, D), device=device, dtype=torch.float32)
     _count(1); check(lib.fdsm_philox_normal(_ptr(out), max(D, 1), B, D, stream_id, seed, offset, row0, _stream()),
           "fdsm_philox_normal")

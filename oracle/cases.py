@@ -52,6 +52,22 @@ CASES = {
                        smin=0.01, anneal_power=1.0, data="unit"),
 }
 
+# Cases added after the first GPU parity run.  Their GPU tests live in tests/test_zz_late_cases_gpu.py (collected last),
+# the CPU oracle tests and make_golden treat them like every other case.
+LATE = {
+    # a2 with noise_type='radermacher' (the reference's spelling): v = sign(u) * eps  (efficient_sm.py:10-11)
+    "a2_rad_gmm11": dict(fn="a2", net=("softplus_mlp", 11, 30), B=48, D=11, eps=0.01, data="gmm",
+                         noise_type="radermacher"),
+    # a17 ncsnv2 anneal_sliced_score_estimation_vr (ncsnv2/losses/dsm.py:33-74): labels drawn inside, Gaussian projections
+    "a17_anneal_vr_img": dict(fn="a17_anneal_vr", net=("score", (3, 8, 8), 40, 12, True), B=10, D=192, eps=0.0, L=12,
+                              smax=50.0, smin=0.01, anneal_power=2.0, n_particles=1, data="unit"),
+    "a17_anneal_vr_p2": dict(fn="a17_anneal_vr", net=("score", (3, 8, 8), 40, 12, True), B=6, D=192, eps=0.0, L=12,
+                             smax=50.0, smin=0.01, anneal_power=1.5, n_particles=2, data="unit"),
+    # a17 exact_score_matching(train=True) (SSM/losses/score_matching.py:48-73): 0.5 ||grad logp||^2 + tr(Hessian logp)
+    "a17_exact_gmm11": dict(fn="a17_exact", net=("softplus_mlp", 11, 30), B=24, D=11, eps=0.0, data="gmm"),
+}
+CASES.update(LATE)
+
 
 def geometric_sigmas(smax, smin, L):
     """ncsn anneal_runner / ncsnv2 models/__init__.py:4-17: exp(linspace(log smax, log smin, L))."""
@@ -89,7 +105,9 @@ def build(name, dtype=torch.float32):
         x = x.reshape(B, *shape)
     c["net"] = net
     c["x"] = x.to(dtype)
-    c["u"] = nets.np_randn(seed + 3, *x.shape).to(dtype)   # direction draw
+    P = c.get("n_particles", 1)
+    # direction draw (one per particle: the exact-SSM annealed loss duplicates the noised batch, ncsnv2/losses/dsm.py:43-56)
+    c["u"] = nets.np_randn(seed + 3, P * x.shape[0], *x.shape[1:]).to(dtype)
     c["n"] = nets.np_randn(seed + 4, *x.shape).to(dtype)   # DSM noise draw
     if "L" in c:
         c["sigmas"] = sig.to(dtype)

@@ -158,6 +158,36 @@ def ssm_hvp(energy_net, x, u, vr=False):
     return (loss1 + (hvp * u).sum(dim=-1)).mean()
 
 
+def anneal_ssm_vr(scorenet, x, n, u, labels, sigmas, anneal_power=2.0, n_particles=1, hook=None):
+    """a17 ncsnv2 anneal_sliced_score_estimation_vr (ncsnv2/losses/dsm.py:33-74): x~ = x + n*sigma[labels], duplicated
+    n_particles times; per row 0.5 ||s||^2 + u . d(u . s)/dx with GAUSSIAN u (the "use Rademacher" comment at :52 is not
+    what :53 does); particle mean, weight sigma**anneal_power, batch mean."""
+    B = x.shape[0]
+    used = sigmas[labels].view(B, *([1] * (x.dim() - 1)))
+    xt = x + n * used
+    dup = xt.unsqueeze(0).expand(n_particles, *x.shape).contiguous().view(-1, *x.shape[1:]).detach().requires_grad_(True)
+    dup_labels = labels.unsqueeze(0).expand(n_particles, *labels.shape).contiguous().view(-1)
+    s = scorenet(dup, dup_labels)
+    grad2 = torch.autograd.grad(torch.sum(s * u), dup, create_graph=True)[0]
+    loss1 = (s.reshape(dup.shape[0], -1) ** 2).sum(-1) / 2.0
+    loss2 = (u * grad2).reshape(dup.shape[0], -1).sum(-1)
+    per = (loss1.view(n_particles, -1).mean(0) + loss2.view(n_particles, -1).mean(0)) * used.reshape(B) ** anneal_power
+    if hook is not None:
+        hook(per, labels)
+    return per.mean()
+
+
+def exact_sm(energy_net, x):
+    """a17 exact_score_matching(train=True) (SSM/losses/score_matching.py:48-73): per sample
+    0.5 ||grad logp||^2 + sum_i d^2 logp / dx_i^2 (one backward pass per input dimension)."""
+    x = x.detach().clone().requires_grad_(True)
+    score = torch.autograd.grad(-energy_net(x).sum(), x, create_graph=True)[0]
+    per = (score ** 2).sum(-1) / 2.0
+    for i in range(x.shape[1]):
+        per = per + torch.autograd.grad(score[:, i].sum(), x, create_graph=True)[0][:, i]
+    return per
+
+
 def quadratic_energy_fd_ssm_exact(A, b, x, vhat):
     """Analytic fixture: E(x)=0.5 x^T A x + b^T x (A symmetric).  For v=eps*vhat the
     a1 loss / D == mean(0.5*(vhat^T(Ax+b))^2 - vhat^T A vhat) for ANY eps

@@ -62,6 +62,7 @@ def load_reference():
     ref.FLAGS = flags_mod.FLAGS
     ref.esm = _load(f"{REF}/SSM/losses/efficient_sm.py", "ref_ssm_efficient_sm")
     ref.sliced = _load(f"{REF}/SSM/losses/sliced_sm.py", "ref_ssm_sliced_sm")
+    ref.score_matching = _load(f"{REF}/SSM/losses/score_matching.py", "ref_ssm_score_matching")
     ref.ssm_dsm = _load(f"{REF}/SSM/losses/dsm.py", "ref_ssm_dsm", extra_path=f"{REF}/SSM")
     ref.deepebm = _load(f"{REF}/DeepEBM/ESM/loss_train.py", "ref_deepebm_loss_train", stubs=stubs)
     ref.deepebm_models = _load(f"{REF}/DeepEBM/ESM/models.py", "ref_deepebm_models", stubs=stubs)
@@ -111,7 +112,7 @@ def reference_loss(ref, c):
             return ref.deepebm.ssm_fd_nop(net, x)
     if fn == "a2":
         with Replay([u]):
-            return ref.esm.single_efficient_score_matching(net, x, eps=eps)
+            return ref.esm.single_efficient_score_matching(net, x, eps=eps, noise_type=c.get("noise_type", "sphere"))
     if fn == "a5":
         with Replay([u]):
             return ref.esm.MLE_efficient_score_matching_conjugate(net, x, eps=eps, mle_ratio=c["mle_ratio"])
@@ -137,6 +138,17 @@ def reference_loss(ref, c):
     if fn == "a13":   # labels=None -> drawn inside with torch.randint (ncsnv2/losses/dsm.py:88-91)
         with Replay([n, u], [c["labels"]]):
             return ref.ncsnv2.anneal_ESM_scorenet_VR(net, x, c["sigmas"], None, c["anneal_power"], None, 1, eps)
+    if fn == "a17_anneal_vr":   # RNG order: randint labels, noise, projections (ncsnv2/losses/dsm.py:36-53)
+        with Replay([n, u], [c["labels"]]):
+            return ref.ncsnv2.anneal_sliced_score_estimation_vr(net, x, c["sigmas"], None, c["anneal_power"], None,
+                                                                c["n_particles"])
+    if fn == "a17_exact":   # the reference accumulates into torch.zeros(B) of the DEFAULT dtype (score_matching.py:52)
+        saved = torch.get_default_dtype()
+        torch.set_default_dtype(x.dtype)
+        try:
+            return ref.score_matching.exact_score_matching(net, x, train=True).mean()
+        finally:
+            torch.set_default_dtype(saved)
     if fn == "a17_ssm":
         with Replay([u.reshape(c["B"], -1)]):
             return ref.deepebm.ssm(net, x)

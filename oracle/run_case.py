@@ -12,6 +12,8 @@ def directions(c):
     fn, eps, u = c["fn"], c["eps"], c["u"]
     if fn == "a3":
         return F.sphere_direction(u, eps, math.sqrt(c["D"]))
+    if c.get("noise_type") == "radermacher":
+        return u.sign() * eps              # SSM/losses/efficient_sm.py:10-11
     if fn == "a12":
         return F.sphere_direction(u, 0.1)  # eps hard-coded, ncsn/losses/sliced_sm.py:220
     return F.sphere_direction(u, eps)
@@ -20,6 +22,10 @@ def directions(c):
 def oracle_loss(c, net=None):
     net = net or c["net"]
     fn, x, eps, D, B = c["fn"], c["x"], c["eps"], c["D"], c["B"]
+    if fn == "a17_anneal_vr":
+        return F.anneal_ssm_vr(net, x, c["n"], c["u"], c["labels"], c["sigmas"], c["anneal_power"], c["n_particles"])
+    if fn == "a17_exact":
+        return F.exact_sm(net, x).mean()
     if fn.startswith("a17"):   # exact SSM (HVP) comparison losses: Gaussian (DeepEBM) or sign (SSM repo) projections
         xf, uf = x.reshape(B, -1), c["u"].reshape(B, -1)
         if fn in ("a17_sliced", "a17_sliced_vr"):

@@ -56,7 +56,7 @@ def test_reference_error_behaviour(fdsm):
     x = torch.randn(4, 3, 8, 8)
     with pytest.raises(RuntimeError):  # reference is only shape-correct for n_particles=1
         fdsm.anneal_ESM_scorenet_VR(lambda z, y: z, x, torch.ones(3), n_particles=2)
-    with pytest.raises(NotImplementedError):
+    with pytest.raises(fdsm._lib.FdsmError):  # sign projections are implemented (efficient_sm.py:10-11) but only on the GPU
         fdsm.single_efficient_score_matching(lambda z: z.sum(-1), torch.randn(4, 8), noise_type="radermacher")
     with pytest.raises(ValueError):
         fdsm.fd_loss(lambda z: z, x, mode="nope")

@@ -68,7 +68,7 @@ def run_adapter(fdsm, c, dev):
     raise KeyError(fn)
 
 
-@pytest.mark.parametrize("name", list(cases.CASES))
+@pytest.mark.parametrize("name", [n for n in cases.CASES if n not in cases.LATE])
 def test_adapter_matches_reference(fdsm, golden, name):
     dev = torch.device("cuda:0")
     torch.backends.cuda.matmul.allow_tf32 = False
