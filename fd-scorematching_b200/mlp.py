@@ -87,7 +87,8 @@ class FusedEnergyMLP(nn.Module):
         n = self.sizes(0).n_params
         self.flat = nn.Parameter(torch.zeros(n, device=device, dtype=torch.float32))
         self.reset_parameters(seed)
-        self._step_state = None
+        self._step_state = None     # the state of the most recent step (bench.py reads its sizes)
+        self._states = {}
         self._prep_stream = None
 
     # ---- parameter bookkeeping (reference named_parameters order) ----------------------------------------------
@@ -150,18 +151,24 @@ class FusedEnergyMLP(nn.Module):
         return _MlpFunction.apply(self.flat, x2, self)
 
     # ---- fused FD-SSM (a1 / a7): kernels (1)+(2) -> (3) fwd -> (4) fwd+bwd -> (3) bwd ---------------------------
-    def _state(self, B, device):
-        """Persistent buffers for batch size B (rows = 3B): addresses stay fixed, so the sequence is CUDA-graph capturable."""
-        st = self._step_state
-        if st is None or st["B"] != B:
-            rows = 3 * B
+    def _state(self, B, device, nrow=3):
+        """Persistent buffers for batch size B and `nrow` stacked rows per sample (3: [x, x+v, x-v]; 2: [xt+v, xt-v]):
+        addresses stay fixed, so the sequence is CUDA-graph capturable.  One state per (B, nrow), kept for the life of
+        the module: a captured graph holds raw pointers into its state, so a state is never dropped when the batch size
+        changes (last, shorter batch of an epoch) and comes back."""
+        key = (B, nrow, str(device))
+        st = self._states.get(key)
+        if st is None:
+            rows = nrow * B
             sz = self.sizes(rows)
             f = dict(device=device, dtype=torch.float32)
-            st = dict(B=B, rows=rows, sz=sz,
+            st = dict(B=B, nrow=nrow, rows=rows, sz=sz,
                       xh=torch.empty(rows, sz.in_ld, **f), xl=torch.empty(rows, sz.in_ld, **f) if self.presplit else None,
                       ws=torch.empty(sz.workspace, **f), E=torch.empty(rows, **f), dE=torch.empty(rows, **f),
+                      dot=torch.empty(B, **f) if nrow == 2 else None,
                       loss=torch.zeros((), **f), grad=torch.zeros(sz.n_params, **f))
-            self._step_state = st
+            self._states[key] = st
+        self._step_state = st
         return st
 
     def fd_ssm_loss_and_grad(self, x, eps, scale, *, u=None, v=None, draw=None, c1=2.0, mean=True, offset_dev=None):
@@ -212,6 +219,48 @@ class FusedEnergyMLP(nn.Module):
               "fdsm_mlp_backward_fd_ssm")
         return st["loss"], st["grad"]
 
+    # ---- fused FD-DSM (a9 mdsm_fd): kernels (1)+(2) noised 2-row form -> (3) fwd -> (4) DSM fwd + bwd -> (3) bwd ----------
+    def fd_dsm_loss_and_grad(self, x, sigma_b, *, eps, sigma02, loss_coe, u=None, dsm_noise=None, draw=None, offset_dev=None):
+        """DeepEBM/ESM/loss_train.py:96-118 on the fused MLP: xt = x + sigma_b * n, v = eps * u/||u||, one forward on
+        cat[xt + v, xt - v] (2B rows), loss = mean_b[((logp1 - logp2)/2 + v.(xt - x)/sigma0^2)^2 / sigma_b^2] * loss_coe *
+        D / eps^2, and its gradient w.r.t. the flat parameters.  `sigma_b` (B,) is the per-batch-position noise schedule
+        of train_dsm.py:50-57.  RNG order as in the reference: noise, then direction (injected for parity, else the two
+        Philox streams of one draw).  Returns (loss 0-dim tensor, flat gradient); both are persistent buffers."""
+        lib = _lib.load()
+        x2 = x.reshape(x.shape[0], -1)
+        B, D = x2.shape
+        st = self._state(B, x2.device, nrow=2)
+        rows, d = st["rows"], self.desc
+        s = _stream()
+        flat = self.flat.data
+        sig = sigma_b.reshape(-1).to(torch.float32)
+        if sig.numel() != B:
+            raise RuntimeError(f"sigmas has {sig.numel()} entries for batch size {B}")
+        alpha, beta, gamma = 0.5, 1.0 / float(sigma02), float(loss_coe) / float(eps) ** 2 * D
+        cur = torch.cuda.current_stream()
+        if self._prep_stream is None:
+            self._prep_stream = torch.cuda.Stream()
+        self._prep_stream.wait_stream(cur)
+        with torch.cuda.stream(self._prep_stream):
+            ops._count(1); check(lib.fdsm_mlp_prepare(C.byref(d), rows, _ptr(flat), _ptr(st["ws"]), _stream()), "fdsm_mlp_prepare")
+        ops.stack(x2, row_mask=ops.ROW_PLUS | ops.ROW_MINUS, scale=eps, direction=None if u is None else u.reshape(B, -1),
+                  normalize=True, noise=None if dsm_noise is None else dsm_noise.reshape(B, -1), sigma=sig, perturb=True,
+                  dot_mode=1, dot_out=st["dot"], out=st["xh"], out_lo=st["xl"], draw=draw, offset_dev=offset_dev,
+                  pad_ones=not self.presplit)
+        cur.wait_stream(self._prep_stream)
+        ops._count(self.n_hidden); check(lib.fdsm_mlp_forward(C.byref(d), _ptr(st["xh"]), _ptr(st["xl"]), rows, _ptr(flat),
+                                                            _ptr(st["ws"]), _ptr(st["E"]), s), "fdsm_mlp_forward")
+        ops._count(2)
+        check(lib.fdsm_combine_dsm_fwd(_ptr(st["E"]), _ptr(st["dot"]), _ptr(sig), B, alpha, beta, gamma, None, _ptr(st["loss"]), s),
+              "fdsm_combine_dsm_fwd")
+        check(lib.fdsm_combine_dsm_bwd(_ptr(st["E"]), _ptr(st["dot"]), _ptr(sig), B, alpha, beta, gamma, None, _ptr(st["dE"]), s),
+              "fdsm_combine_dsm_bwd")
+        ops._count(3 * self.n_hidden + 1)
+        check(lib.fdsm_mlp_backward(C.byref(d), _ptr(st["xh"]), _ptr(st["xl"]), rows, _ptr(flat), _ptr(st["ws"]), _ptr(st["dE"]),
+                                    _ptr(st["grad"]), 0, s), "fdsm_mlp_backward")
+        st["sig"] = sig      # keeps the schedule alive for graph replays
+        return st["loss"], st["grad"]
+
     # ---- the training step: FD-SSM loss -> backward -> (all-reduce) -> clip -> Adam, graph-replayed ----------------
     def flat_params(self):
         return self
@@ -229,9 +278,15 @@ class FusedEnergyMLP(nn.Module):
         """Learning-rate schedules (DeepEBM/ESM/inputs.py:75-90) write the device scalar the captured step reads."""
         self._opt["lr_dev"].fill_(float(lr))
 
-    def _loss_and_grad_captured(self, st, eps, scale):
+    def _loss_and_grad_captured(self, st, kind, cfg):
         o = self._opt
-        return self.fd_ssm_loss_and_grad(st["x"], eps, scale, draw=(o["seed"], 0, o["rank"] * st["B"]), offset_dev=o["step"])
+        draw = (o["seed"], 0, o["rank"] * st["B"])      # offset = device step counter; rows keyed by the GLOBAL sample index
+        if kind == "ssm":
+            eps, scale = cfg
+            return self.fd_ssm_loss_and_grad(st["x"], eps, scale, draw=draw, offset_dev=o["step"])
+        eps, sigma02, loss_coe = cfg
+        return self.fd_dsm_loss_and_grad(st["x"], st["sigma_b"], eps=eps, sigma02=sigma02, loss_coe=loss_coe, draw=draw,
+                                         offset_dev=o["step"])
 
     def _apply_update(self, st, have_sumsq=False):
         lib, o = _lib.load(), self._opt
@@ -248,14 +303,34 @@ class FusedEnergyMLP(nn.Module):
         scalar, persistent buffer).  The whole step is ONE CUDA-graph replay -- also for world > 1 when `allreduce` is the
         peer-memory kernel (ddp.PeerAllReduce); with the NCCL library collective it is two replays around the all-reduce."""
         x2 = x.reshape(x.shape[0], -1)
-        B = x2.shape[0]
-        st = self._state(B, x2.device)
+        st = self._state(x2.shape[0], x2.device)
         if "x" not in st:
             st["x"] = torch.empty_like(x2)
         scale = 1.0 / eps ** 2 if scale is None else scale
         st["x"].copy_(x2)
+        return self._train_step(st, "ssm", (float(eps), float(scale)), allreduce, distributed)
+
+    def mdsm_fd_step(self, x, sigmas, sigma02=0.01, eps=0.05, loss_coe=1e-4, allreduce=None, distributed=False):
+        """One optimisation step of DeepEBM/train_dsm.py:62-71 with loss_func = mdsm_fd (loss_train.py:96-118): `sigmas`
+        is the (B, 1) per-batch-position noise schedule of train_dsm.py:50-57 (a rank of a sharded batch passes its slice);
+        defaults = configs/default.yaml (sigma0 0.1, esm_eps 0.05, loss_coe 1e-4).  Same graph-replayed sequence as
+        fd_ssm_step with the noised 2-row stack and the DSM combine.  The reference's `tloss.item() > 1e8` skip
+        (train_dsm.py:64-66) needs a host read of the loss every step and is left to the caller."""
+        x2 = x.reshape(x.shape[0], -1)
+        B = x2.shape[0]
+        st = self._state(B, x2.device, nrow=2)
+        if "x" not in st:
+            st["x"] = torch.empty_like(x2)
+            st["sigma_b"] = torch.empty(B, device=x2.device, dtype=torch.float32)
+        if sigmas.numel() != B:
+            raise RuntimeError(f"sigmas has {sigmas.numel()} entries for batch size {B}")
+        st["x"].copy_(x2)
+        st["sigma_b"].copy_(sigmas.reshape(-1))
+        return self._train_step(st, "dsm", (float(eps), float(sigma02), float(loss_coe)), allreduce, distributed)
+
+    def _train_step(self, st, kind, cfg, allreduce, distributed):
         peer = distributed and getattr(allreduce, "fused_sumsq", False)    # ddp.PeerAllReduce: capturable, emits the sumsq
-        key = (B, float(eps), float(scale), bool(distributed), bool(peer))
+        key = (st["B"], kind, cfg, bool(distributed), bool(peer))
 
         def exchange_and_update():
             if peer:
@@ -266,7 +341,7 @@ class FusedEnergyMLP(nn.Module):
                 self._apply_update(st)
 
         if not self._opt["use_graph"]:
-            self._loss_and_grad_captured(st, eps, scale)
+            self._loss_and_grad_captured(st, kind, cfg)
             if distributed and allreduce is not None and not peer:
                 allreduce(st["grad"])
             exchange_and_update()
@@ -277,14 +352,14 @@ class FusedEnergyMLP(nn.Module):
             side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):
                 step0 = self._opt["step"].clone()
-                self._loss_and_grad_captured(st, eps, scale)
+                self._loss_and_grad_captured(st, kind, cfg)
                 self._opt["step"].copy_(step0)
             torch.cuda.current_stream().wait_stream(side)
             launches0 = ops.LAUNCHES
             g1, g2 = torch.cuda.CUDAGraph(), None
             one_graph = not distributed or peer
             with torch.cuda.graph(g1):
-                self._loss_and_grad_captured(st, eps, scale)
+                self._loss_and_grad_captured(st, kind, cfg)
                 if one_graph:
                     exchange_and_update()
             if not one_graph:

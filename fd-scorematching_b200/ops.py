@@ -88,7 +88,7 @@ def next_draw():
 # --------------------------------------------------------------------------------------------
 def stack(x, *, row_mask, scale, direction=None, normalize=True, noise=None, sigma=None, labels=None,
           perturb=True, dot_mode=0, want_v=False, want_dot=False, draw=None, out=None, out_lo=None, offset_dev=None,
-          pad_ones=False):
+          pad_ones=False, dot_out=None):
     """Fused direction sampling + normalisation + stacked-batch build (fdsm_stack).
 
     x: (B, D) fp32 CUDA.  Returns (stacked (rows*B, D) | None, v (B, D) | None, dot (B,) | None)."""
@@ -140,7 +140,12 @@ def stack(x, *, row_mask, scale, direction=None, normalize=True, noise=None, sig
     if want_v:
         v = torch.empty((B, D), device=x.device, dtype=torch.float32)
         a.v_out, a.ldv = _ptr(v), max(D, 1)
-    if want_dot:
+    if dot_out is not None:     # caller-owned (persistent) buffer: CUDA-graph replays write the same address
+        dot = _req(dot_out, "dot_out")
+        if dot.numel() != B or not dot.is_contiguous():
+            raise ValueError("dot_out must be a contiguous (B,) tensor")
+        a.dot_out = _ptr(dot)
+    elif want_dot:
         dot = torch.empty((B,), device=x.device, dtype=torch.float32)
         a.dot_out = _ptr(dot)
     seed, offset, row0 = draw if draw is not None else next_draw()

@@ -8,9 +8,18 @@ from . import ddp, losses, ops
 
 
 class FDSSMTrainer:
-    def __init__(self, net, *, eps=0.05, lr=1e-5, betas=(0.9, 0.95), clip=0.1, loss="ssm_fd", seed=1234):
+    """loss = "ssm_fd" (train_ssm.py) or "mdsm_fd" (train_dsm.py: pass the (B_global, 1) per-batch-position noise
+    schedule of train_dsm.py:50-57 as `sigmas`; each rank uses its own slice of it)."""
+
+    def __init__(self, net, *, eps=0.05, lr=1e-5, betas=(0.9, 0.95), clip=0.1, loss="ssm_fd", seed=1234, sigmas=None,
+                 sigma02=0.01, loss_coe=1e-4):
+        if loss not in ("ssm_fd", "mdsm_fd"):
+            raise ValueError("loss must be 'ssm_fd' or 'mdsm_fd'")
+        if loss == "mdsm_fd" and sigmas is None:
+            raise ValueError("mdsm_fd needs the per-batch-position noise schedule `sigmas`")
         self.net = net
         self.eps, self.clip, self.loss_name = eps, clip, loss
+        self.sigmas, self.sigma02, self.loss_coe = sigmas, sigma02, loss_coe
         self.fused = hasattr(net, "fd_ssm_step")       # mlp.FusedEnergyMLP: kernels (1)-(4) + Adam in CUDA
         rank = torch.distributed.get_rank() if ddp.is_distributed() else 0
         if self.fused:
@@ -31,10 +40,20 @@ class FDSSMTrainer:
     def step(self, x):
         B = x.shape[0]
         ops.set_row_offset(self._rank * B)
+        sig = None
+        if self.loss_name == "mdsm_fd":      # this rank's slice of the positional schedule
+            sig = self.sigmas.reshape(-1)[self._rank * B:(self._rank + 1) * B]
         if self.fused:
+            if sig is not None:
+                return self.net.mdsm_fd_step(x, sig, self.sigma02, self.eps, self.loss_coe, allreduce=self._allreduce,
+                                             distributed=ddp.is_distributed())
             return self.net.fd_ssm_step(x, eps=self.eps, allreduce=self._allreduce, distributed=ddp.is_distributed())
         self.flat.zero_grad()
-        loss = losses.ssm_fd(self.net, x, eps=self.eps, batch_size=B)
+        if sig is not None:
+            loss = losses.mdsm_fd(self.net, x, sig, self.sigma02, int(x[0].numel()), eps=self.eps, batch_size=B,
+                                  loss_coe=self.loss_coe)
+        else:
+            loss = losses.ssm_fd(self.net, x, eps=self.eps, batch_size=B)
         loss.backward()
         ddp.allreduce_mean_(self.flat.grad)
         if self.clip is not None:

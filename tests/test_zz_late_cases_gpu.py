@@ -86,3 +86,80 @@ def test_anneal_ssm_vr_philox_draws_and_hook(fdsm):
                                                                    lambda per, lab: got.append(per.detach()), 2))
     assert got[0].shape == (c["B"],) and torch.isfinite(out[0])
     assert torch.equal(out[0], out[1]) and torch.equal(got[0], got[1])
+
+
+# ---- fused FD-DSM (a9 mdsm_fd on the tcgen05 MLP) and the train_dsm.py step ---------------------------------------------
+def _fused_pair(fdsm, D, H, L, act, seed=0):
+    from oracle import nets
+    ref = nets.init_from_numpy(nets.QuadraticMLP(D, H, L, act), seed)
+    net = fdsm.mlp.FusedEnergyMLP(D, H, L, act=act, head="quadratic", device="cuda:0")
+    net.load_reference_state_dict([p.detach().float() for p in ref.parameters()])
+    return net, ref.double()
+
+
+@pytest.mark.parametrize("B,D,H,act", [(20, 48, 32, "elu"), (256, 784, 200, "nsoftplus"), (37, 100, 40, "elu")])
+def test_fused_mdsm_fd_matches_oracle(fdsm, B, D, H, act):
+    """fd_dsm_loss_and_grad (stack2-noised -> MLP forward -> DSM combine fwd+bwd -> MLP backward, all through the C ABI)
+    against the fp64 oracle of loss_train.py:96-118 on injected draws; yardstick = the same objective in torch fp32."""
+    from oracle import fd_losses, nets
+    dev = "cuda:0"
+    eps, sigma02, coe = 0.05, 0.01, 1e-4
+    net, ref = _fused_pair(fdsm, D, H, 3, act)
+    x, u, n = nets.np_rand(11, B, D), nets.np_randn(12, B, D), nets.np_randn(13, B, D)
+    sig = torch.tensor(np.linspace(0.05, 1.2, B)).view(-1, 1)
+    lr = fd_losses.mdsm_fd(ref, x, n, fd_losses.sphere_direction(u, eps), sig, sigma02, eps, coe)
+    lr.backward()
+    gr = torch.cat([p.grad.reshape(-1) for p in ref.parameters()])
+    loss, grad = net.fd_dsm_loss_and_grad(x.float().to(dev), sig.float().to(dev), eps=eps, sigma02=sigma02, loss_coe=coe,
+                                          u=u.float().to(dev), dsm_noise=n.float().to(dev))
+    torch.backends.cuda.matmul.allow_tf32 = False
+    r32 = nets.init_from_numpy(nets.QuadraticMLP(D, H, 3, act), 0).to(dev)
+    l32 = fd_losses.mdsm_fd(r32, x.float().to(dev), n.float().to(dev), fd_losses.sphere_direction(u.float().to(dev), eps),
+                            sig.float().to(dev), sigma02, eps, coe)
+    l32.backward()
+    g32 = torch.cat([p.grad.reshape(-1) for p in r32.parameters()])
+    e, e32 = _rel(loss, lr), _rel(l32, lr)
+    assert e <= max(1e-4, 3 * e32), (float(loss), float(lr), float(l32))
+    ge = float((grad.double().cpu() - gr).norm() / gr.norm())
+    ge32 = float((g32.double().cpu() - gr).norm() / gr.norm())
+    assert ge <= max(1e-4, 3 * ge32), (ge, ge32)
+    # and the module route (generic adapter around net(x)) gives the same numbers as the fused entry point
+    net.flat.grad = None
+    l2 = fdsm.losses.mdsm_fd(net, x.float().to(dev), sig.float().to(dev), sigma02, D, eps=eps, loss_coe=coe,
+                             u=u.float().to(dev), dsm_noise=n.float().to(dev))
+    l2.backward()
+    assert _rel(l2, loss) < 1e-6 and float((net.flat.grad - grad).norm() / grad.norm()) < 1e-5
+
+
+def test_mdsm_step_graph_replay_equals_eager_and_batch_sizes_alternate(fdsm):
+    """train_dsm.py step: one CUDA-graph replay == the eager launch sequence, bit for bit, also when the batch size changes
+    and comes back (each (B, rows) keeps its own buffers and graph)."""
+    dev = "cuda:0"
+    a = fdsm.mlp.FusedEnergyMLP(64, 48, 3, act="elu", device=dev, seed=2)
+    b = fdsm.mlp.FusedEnergyMLP(64, 48, 3, act="elu", device=dev, seed=2)
+    a.configure_optimizer(lr=1e-3, use_graph=True, seed=9)
+    b.configure_optimizer(lr=1e-3, use_graph=False, seed=9)
+    g = torch.Generator().manual_seed(3)
+    for B in (48, 20, 48, 48, 20):
+        x = torch.rand(B, 64, generator=g).to(dev)
+        sig = torch.linspace(0.05, 1.2, B, device=dev).view(-1, 1)
+        la, lb = a.mdsm_fd_step(x, sig), b.mdsm_fd_step(x, sig)
+        assert float(la) == float(lb) and np.isfinite(float(la))
+    # the FD-SSM step shares the optimizer state and the step counter with the DSM step
+    x = torch.rand(48, 64, generator=g).to(dev)
+    assert float(a.fd_ssm_step(x, eps=0.05)) == float(b.fd_ssm_step(x, eps=0.05))
+    assert torch.equal(a.flat.data, b.flat.data)
+    assert int(a._opt["step"]) == 6
+
+
+def test_trainer_runs_the_dsm_objective(fdsm):
+    dev = "cuda:0"
+    net = fdsm.mlp.FusedEnergyMLP(64, 48, 3, act="elu", device=dev, seed=4)
+    B = 32
+    sig = torch.logspace(np.log10(0.05), np.log10(1.2), B, device=dev).view(-1, 1)
+    from fdsm_b200.train import FDSSMTrainer
+    tr = FDSSMTrainer(net, eps=0.05, lr=1e-3, loss="mdsm_fd", sigmas=sig)
+    before = net.flat.data.clone()
+    losses = [float(tr.step(torch.rand(B, 1, 8, 8, device=dev))) for _ in range(3)]
+    assert all(np.isfinite(l) and l > 0 for l in losses)
+    assert float((net.flat.data - before).abs().max()) > 0
