@@ -89,6 +89,8 @@ PROTOTYPES = {
                                       C.c_void_p, _stream]),
     "fdsm_mlp_backward_fd_ssm": (C.c_int, [C.POINTER(MlpDesc), _f32p, _f32p, _i64, _f32p, _f32p, _f32p, _f32, _f32, _i32,
                                            _f32p, _f32p, _i32, _stream]),
+    "fdsm_mlp_backward_fd_dsm": (C.c_int, [C.POINTER(MlpDesc), _f32p, _f32p, _i64, _f32p, _f32p, _f32p, _f32p, _f32p, _f32,
+                                           _f32, _f32, _f32p, _f32p, _i32, _stream]),
 }
 
 _lib = None

@@ -43,19 +43,7 @@ __global__ void __launch_bounds__(1024) combine_dsm_fwd_kernel(const float* __re
                                                                float beta, float gamma, float* __restrict__ per_sample,
                                                                float* __restrict__ loss) {
   __shared__ float red[32];
-  float acc = 0.f;
-  for (int64_t b = threadIdx.x; b < B; b += blockDim.x) {
-    const float r = alpha * (E[B + b] - E[b]) + beta * dot[b];
-    float p = r * r;
-    if (sigma_b) {
-      const float s = sigma_b[b];
-      p = p / (s * s);
-    }
-    if (per_sample) per_sample[b] = p * gamma;
-    acc += p;
-  }
-  acc = block_sum_1024(acc, red);
-  if (threadIdx.x == 0 && loss) *loss = acc / (float)B * gamma;
+  combine_dsm_fwd_block(E, dot, sigma_b, B, alpha, beta, gamma, per_sample, loss, red);
 }
 
 __global__ void __launch_bounds__(256) combine_dsm_bwd_kernel(const float* __restrict__ E, const float* __restrict__ dot,
@@ -64,12 +52,7 @@ __global__ void __launch_bounds__(256) combine_dsm_bwd_kernel(const float* __res
                                                               float* __restrict__ dE) {
   const float c = 2.f * alpha * gamma / (float)B * (gout ? __ldg(gout) : 1.f);
   for (int64_t b = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; b < B; b += (int64_t)gridDim.x * blockDim.x) {
-    const float r = alpha * (E[B + b] - E[b]) + beta * dot[b];
-    float g = c * r;
-    if (sigma_b) {
-      const float s = sigma_b[b];
-      g = g / (s * s);
-    }
+    const float g = combine_dsm_grad(E, dot, sigma_b, B, alpha, beta, c, b);
     dE[b] = -g;
     dE[B + b] = g;
   }

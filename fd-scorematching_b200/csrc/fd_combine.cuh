@@ -52,4 +52,38 @@ __device__ __forceinline__ float combine_energy_grad_row(const float* __restrict
   return which == 1 ? coef * (q - 1.f) : coef * (-q - 1.f);
 }
 
+// ---- DSM energy form (E = energy([xt+v | xt-v]), 2B rows): r_b = alpha (E[B+b] - E[b]) + beta dot_b,
+// per_b = r_b^2 / sigma_b^2, loss = gamma mean_b per_b.  Shared by fd_combine.cu and the fused head kernels of fd_mlp.cu. ----
+__device__ __forceinline__ void combine_dsm_fwd_block(const float* __restrict__ E, const float* __restrict__ dot,
+                                                      const float* __restrict__ sigma_b, int64_t B, float alpha, float beta,
+                                                      float gamma, float* __restrict__ per_sample, float* __restrict__ loss,
+                                                      float* red) {
+  float acc = 0.f;
+  for (int64_t b = threadIdx.x; b < B; b += blockDim.x) {
+    const float r = alpha * (E[B + b] - E[b]) + beta * dot[b];
+    float p = r * r;
+    if (sigma_b) {
+      const float s = sigma_b[b];
+      p = p / (s * s);
+    }
+    if (per_sample) per_sample[b] = p * gamma;
+    acc += p;
+  }
+  acc = block_sum_1024(acc, red);
+  if (threadIdx.x == 0 && loss) *loss = acc / (float)B * gamma;
+}
+
+// dL/dE of sample b's SECOND row (row B + b); the first row (row b) gets the negative.  c = 2 alpha gamma / B (x gout).
+__device__ __forceinline__ float combine_dsm_grad(const float* __restrict__ E, const float* __restrict__ dot,
+                                                  const float* __restrict__ sigma_b, int64_t B, float alpha, float beta,
+                                                  float c, int64_t b) {
+  const float r = alpha * (__ldg(E + B + b) - __ldg(E + b)) + beta * __ldg(dot + b);
+  float g = c * r;
+  if (sigma_b) {
+    const float s = __ldg(sigma_b + b);
+    g = g / (s * s);
+  }
+  return g;
+}
+
 }  // namespace fdsm

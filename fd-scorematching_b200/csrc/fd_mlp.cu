@@ -200,10 +200,17 @@ __global__ void __launch_bounds__(256) prep_weights_kernel(const PrepArgs a) {
 // One warp per row, lanes across the columns (coalesced 128-byte row segments), grid ~ 2 blocks per SM.
 struct HeadGrad {
   const float* dE;                                    // explicit dL/dE, or NULL:
-  const float* E; long long B; float c1, coef;        // energy-form combine, rows = 3B
+  const float* E; long long B; float c1, coef;        // energy-form combine, rows = 3B (dot == NULL)
+  const float* dot; const float* sigma; float alpha, beta;   // DSM combine, rows = 2B (dot != NULL; coef = 2 alpha gamma / B)
 };
 __device__ __forceinline__ float head_g(const HeadGrad& s, long long r) {
-  return s.dE ? __ldg(s.dE + r) : combine_energy_grad_row(s.E, s.B, s.c1, s.coef, r);
+  if (s.dE) return __ldg(s.dE + r);
+  if (s.dot) {
+    const bool second = r >= s.B;
+    const float g = combine_dsm_grad(s.E, s.dot, s.sigma, s.B, s.alpha, s.beta, s.coef, second ? r - s.B : r);
+    return second ? g : -g;
+  }
+  return combine_energy_grad_row(s.E, s.B, s.c1, s.coef, r);
 }
 template <int NI, bool HEAD>
 __global__ void __launch_bounds__(HB_WARPS * 32, HB_BLOCKS_PER_SM) head_bwd_kernel(const float* __restrict__ hlast, int ldh, const HeadGrad src,
@@ -396,6 +403,7 @@ __global__ void __launch_bounds__(256) head_energy_kernel(const float* __restric
 // evaluates the energy-form combine forward (the step's loss) -- same code as fdsm_combine_energy_fwd.
 struct HeadLoss {
   const float* E; long long B; float c1, scale; int mean; float* loss;
+  const float* dot; const float* sigma; float alpha, beta, gamma;      // dot != NULL: the DSM combine forward instead
 };
 __global__ void __launch_bounds__(1024) head_finish_kernel(const double* __restrict__ partial, int nblk, int n,
                                                            float* __restrict__ ghead, int accumulate, const HeadLoss hl) {
@@ -403,7 +411,8 @@ __global__ void __launch_bounds__(1024) head_finish_kernel(const double* __restr
   __shared__ float red[32];
   const int nb = (n + 31) / 32;
   if ((int)blockIdx.x >= nb) {
-    combine_energy_fwd_block(hl.E, hl.B, 0, hl.c1, hl.scale, hl.mean, nullptr, hl.loss, red);
+    if (hl.dot) combine_dsm_fwd_block(hl.E, hl.dot, hl.sigma, hl.B, hl.alpha, hl.beta, hl.gamma, nullptr, hl.loss, red);
+    else combine_energy_fwd_block(hl.E, hl.B, 0, hl.c1, hl.scale, hl.mean, nullptr, hl.loss, red);
     return;
   }
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
@@ -713,8 +722,8 @@ extern "C" int fdsm_mlp_backward(const fdsm_mlp_desc* desc, const float* x_hi, c
                                  const float* params, float* workspace, const float* dE, float* grads, int32_t accumulate,
                                  fdsm_stream_t stream) {
   FDSM_REQUIRE(rows == 0 || dE, "fdsm_mlp_backward: dE is NULL");
-  mlp::HeadGrad hg = {dE, nullptr, 0, 0.f, 0.f};
-  mlp::HeadLoss hl = {nullptr, 0, 0.f, 0.f, 0, nullptr};
+  mlp::HeadGrad hg = {dE, nullptr, 0, 0.f, 0.f, nullptr, nullptr, 0.f, 0.f};
+  mlp::HeadLoss hl = {nullptr, 0, 0.f, 0.f, 0, nullptr, nullptr, nullptr, 0.f, 0.f, 0.f};
   return mlp::backward_impl(desc, x_hi, x_lo, rows, params, workspace, hg, hl, grads, accumulate, stream);
 }
 
@@ -724,11 +733,27 @@ extern "C" int fdsm_mlp_backward_fd_ssm(const fdsm_mlp_desc* desc, const float* 
   FDSM_REQUIRE(B >= 0 && B < (1ll << 29), "fdsm_mlp_backward_fd_ssm: bad batch size");
   FDSM_REQUIRE(B == 0 || energy, "fdsm_mlp_backward_fd_ssm: energy is NULL");
   const float coef = mean && B ? scale / (float)B : scale;
-  mlp::HeadGrad hg = {nullptr, energy, B, c1, coef};
-  mlp::HeadLoss hl = {energy, B, c1, scale, mean, B ? loss : nullptr};
+  mlp::HeadGrad hg = {nullptr, energy, B, c1, coef, nullptr, nullptr, 0.f, 0.f};
+  mlp::HeadLoss hl = {energy, B, c1, scale, mean, B ? loss : nullptr, nullptr, nullptr, 0.f, 0.f, 0.f};
   if (B == 0 && loss) {
     int rc = cuda_status(cudaMemsetAsync(loss, 0, sizeof(float), (cudaStream_t)stream), "fdsm_mlp_backward_fd_ssm");
     if (rc) return rc;
   }
   return mlp::backward_impl(desc, x_hi, x_lo, 3 * B, params, workspace, hg, hl, grads, accumulate, stream);
+}
+
+extern "C" int fdsm_mlp_backward_fd_dsm(const fdsm_mlp_desc* desc, const float* x_hi, const float* x_lo, int64_t B,
+                                        const float* params, float* workspace, const float* energy, const float* dot,
+                                        const float* sigma_b, float alpha, float beta, float gamma, float* loss, float* grads,
+                                        int32_t accumulate, fdsm_stream_t stream) {
+  FDSM_REQUIRE(B >= 0 && B < (1ll << 29), "fdsm_mlp_backward_fd_dsm: bad batch size");
+  FDSM_REQUIRE(B == 0 || (energy && dot), "fdsm_mlp_backward_fd_dsm: energy / dot is NULL");
+  const float c = B ? 2.f * alpha * gamma / (float)B : 0.f;      // as fdsm_combine_dsm_bwd with gout = 1
+  mlp::HeadGrad hg = {nullptr, energy, B, 0.f, c, dot, sigma_b, alpha, beta};
+  mlp::HeadLoss hl = {energy, B, 0.f, 0.f, 1, B ? loss : nullptr, dot, sigma_b, alpha, beta, gamma};
+  if (B == 0 && loss) {
+    int rc = cuda_status(cudaMemsetAsync(loss, 0, sizeof(float), (cudaStream_t)stream), "fdsm_mlp_backward_fd_dsm");
+    if (rc) return rc;
+  }
+  return mlp::backward_impl(desc, x_hi, x_lo, 2 * B, params, workspace, hg, hl, grads, accumulate, stream);
 }

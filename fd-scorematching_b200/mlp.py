@@ -219,7 +219,7 @@ class FusedEnergyMLP(nn.Module):
               "fdsm_mlp_backward_fd_ssm")
         return st["loss"], st["grad"]
 
-    # ---- fused FD-DSM (a9 mdsm_fd): kernels (1)+(2) noised 2-row form -> (3) fwd -> (4) DSM fwd + bwd -> (3) bwd ----------
+    # ---- fused FD-DSM (a9 mdsm_fd): kernels (1)+(2) noised 2-row form -> (3) fwd -> (4) folded into (3) bwd ------------
     def fd_dsm_loss_and_grad(self, x, sigma_b, *, eps, sigma02, loss_coe, u=None, dsm_noise=None, draw=None, offset_dev=None):
         """DeepEBM/ESM/loss_train.py:96-118 on the fused MLP: xt = x + sigma_b * n, v = eps * u/||u||, one forward on
         cat[xt + v, xt - v] (2B rows), loss = mean_b[((logp1 - logp2)/2 + v.(xt - x)/sigma0^2)^2 / sigma_b^2] * loss_coe *
@@ -250,14 +250,11 @@ class FusedEnergyMLP(nn.Module):
         cur.wait_stream(self._prep_stream)
         ops._count(self.n_hidden); check(lib.fdsm_mlp_forward(C.byref(d), _ptr(st["xh"]), _ptr(st["xl"]), rows, _ptr(flat),
                                                             _ptr(st["ws"]), _ptr(st["E"]), s), "fdsm_mlp_forward")
-        ops._count(2)
-        check(lib.fdsm_combine_dsm_fwd(_ptr(st["E"]), _ptr(st["dot"]), _ptr(sig), B, alpha, beta, gamma, None, _ptr(st["loss"]), s),
-              "fdsm_combine_dsm_fwd")
-        check(lib.fdsm_combine_dsm_bwd(_ptr(st["E"]), _ptr(st["dot"]), _ptr(sig), B, alpha, beta, gamma, None, _ptr(st["dE"]), s),
-              "fdsm_combine_dsm_bwd")
+        # DSM combine forward (loss) + analytic dE + MLP backward: one entry point, dE never materialised
         ops._count(3 * self.n_hidden + 1)
-        check(lib.fdsm_mlp_backward(C.byref(d), _ptr(st["xh"]), _ptr(st["xl"]), rows, _ptr(flat), _ptr(st["ws"]), _ptr(st["dE"]),
-                                    _ptr(st["grad"]), 0, s), "fdsm_mlp_backward")
+        check(lib.fdsm_mlp_backward_fd_dsm(C.byref(d), _ptr(st["xh"]), _ptr(st["xl"]), B, _ptr(flat), _ptr(st["ws"]), _ptr(st["E"]),
+                                           _ptr(st["dot"]), _ptr(sig), alpha, beta, gamma, _ptr(st["loss"]), _ptr(st["grad"]), 0, s),
+              "fdsm_mlp_backward_fd_dsm")
         st["sig"] = sig      # keeps the schedule alive for graph replays
         return st["loss"], st["grad"]
 

@@ -70,12 +70,15 @@ class FDSSMTrainer:
         cur = torch.cuda.current_stream()
         if self._copy_stream is None:
             self._copy_stream = torch.cuda.Stream()
-            self._bufs = [torch.empty_like(x_host, device="cuda") for _ in range(2)]
-            self._evt = [torch.cuda.Event() for _ in range(2)]
-            self._free = [torch.cuda.Event() for _ in range(2)]
-            self._i = 0
-        i = self._i
-        self._i ^= 1
+            self._staging = {}
+        key = (tuple(x_host.shape), x_host.dtype)
+        if key not in self._staging:      # one double buffer per batch shape (the last batch of an epoch may be shorter)
+            self._staging[key] = dict(bufs=[torch.empty_like(x_host, device="cuda") for _ in range(2)],
+                                      evt=[torch.cuda.Event() for _ in range(2)], free=[torch.cuda.Event() for _ in range(2)], i=0)
+        sg = self._staging[key]
+        self._bufs, self._evt, self._free = sg["bufs"], sg["evt"], sg["free"]
+        i = sg["i"]
+        sg["i"] ^= 1
         with torch.cuda.stream(self._copy_stream):
             self._copy_stream.wait_event(self._free[i])      # previous consumer of this buffer is done
             self._bufs[i].copy_(x_host, non_blocking=True)

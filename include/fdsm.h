@@ -219,6 +219,17 @@ int fdsm_mlp_backward_fd_ssm(const fdsm_mlp_desc* desc, const float* x_hi, const
                              const float* params, float* workspace, const float* energy, float c1, float scale,
                              int32_t mean, float* loss, float* grads, int32_t accumulate, fdsm_stream_t stream);
 
+/* FD-DSM energy form (a9: DeepEBM/ESM/loss_train.py:109-117; a3/a6 through alpha/beta/gamma as in fdsm_combine_dsm_fwd)
+ * with the combine folded into the backward: `energy` = the forward's output on [xt+v | xt-v] (2B rows), `dot` = the
+ * per-sample v.(xt - x) (or v.noise) that fdsm_stack wrote, `sigma_b` = per-sample sigma (NULL: no 1/sigma^2 weight).
+ *   *loss = gamma * mean_b (alpha (E[B+b] - E[b]) + beta dot_b)^2 / sigma_b^2   (same arithmetic as fdsm_combine_dsm_fwd)
+ *   grads (+)= dloss/dparams, dE taken analytically inside the head-backward kernel (as fdsm_combine_dsm_bwd).
+ * Replaces the launches combine_dsm_fwd + combine_dsm_bwd + backward(dE).  loss may be NULL. */
+int fdsm_mlp_backward_fd_dsm(const fdsm_mlp_desc* desc, const float* x_hi, const float* x_lo, int64_t B,
+                             const float* params, float* workspace, const float* energy, const float* dot,
+                             const float* sigma_b, float alpha, float beta, float gamma, float* loss, float* grads,
+                             int32_t accumulate, fdsm_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------
  * Optimizer step on the flat parameter vector (the reference's host loop, DeepEBM/train_ssm.py:65-70:
  * clip_grad_norm_(params, clip) then Adam.step()).  Per-step scalars come from device memory so the

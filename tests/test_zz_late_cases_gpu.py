@@ -163,3 +163,36 @@ def test_trainer_runs_the_dsm_objective(fdsm):
     losses = [float(tr.step(torch.rand(B, 1, 8, 8, device=dev))) for _ in range(3)]
     assert all(np.isfinite(l) and l > 0 for l in losses)
     assert float((net.flat.data - before).abs().max()) > 0
+
+
+@pytest.mark.parametrize("D,H,L,act,B", [(64, 48, 3, "nsoftplus", 100), (784, 200, 3, "elu", 4096), (48, 300, 2, "elu", 33)])
+def test_fused_dsm_combine_backward_equals_explicit_sequence(fdsm, D, H, L, act, B):
+    """fdsm_mlp_backward_fd_dsm (DSM combine forward + analytic dE + MLP backward in one entry point) against the explicit
+    sequence combine_dsm_fwd -> combine_dsm_bwd -> fdsm_mlp_backward(dE) on the same workspace: loss and gradient are
+    bit-identical (same arithmetic, fixed-order sums), and a second call reproduces them."""
+    import ctypes as C
+    from fdsm_b200 import _lib
+    from fdsm_b200.mlp import _ptr, _stream
+    dev = "cuda:0"
+    lib = _lib.load()
+    net = fdsm.mlp.FusedEnergyMLP(D, H, L, act=act, head="quadratic", device=dev, seed=5)
+    x, u, n = torch.rand(B, D, device=dev), torch.randn(B, D, device=dev), torch.randn(B, D, device=dev)
+    sig = torch.linspace(0.05, 1.2, B, device=dev)
+    eps, sigma02, coe = 0.05, 0.01, 1e-4
+    kw = dict(eps=eps, sigma02=sigma02, loss_coe=coe, u=u, dsm_noise=n)
+    loss, grad = net.fd_dsm_loss_and_grad(x, sig, **kw)
+    loss1, grad1 = loss.clone(), grad.clone()
+    st = net._step_state
+    assert st["rows"] == 2 * B
+    alpha, beta, gamma = 0.5, 1.0 / sigma02, coe / eps ** 2 * D
+    l2, dE, g2 = torch.zeros((), device=dev), torch.empty(2 * B, device=dev), torch.empty_like(grad)
+    s = _stream()
+    _lib.check(lib.fdsm_combine_dsm_fwd(_ptr(st["E"]), _ptr(st["dot"]), _ptr(sig), B, alpha, beta, gamma, None, _ptr(l2), s), "fwd")
+    _lib.check(lib.fdsm_combine_dsm_bwd(_ptr(st["E"]), _ptr(st["dot"]), _ptr(sig), B, alpha, beta, gamma, None, _ptr(dE), s), "bwd")
+    _lib.check(lib.fdsm_mlp_backward(C.byref(net.desc), _ptr(st["xh"]), _ptr(st["xl"]), 2 * B, _ptr(net.flat.data), _ptr(st["ws"]),
+                                     _ptr(dE), _ptr(g2), 0, s), "mlp_bwd")
+    torch.cuda.synchronize()
+    assert float(loss1) == float(l2)
+    assert torch.equal(grad1, g2)
+    loss3, grad3 = net.fd_dsm_loss_and_grad(x, sig, **kw)
+    assert float(loss3) == float(loss1) and torch.equal(grad3, grad1)
