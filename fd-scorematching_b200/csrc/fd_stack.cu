@@ -55,13 +55,17 @@ __device__ __forceinline__ float4 mask_tail(float4 v, int j, int D) {
 template <bool VEC>
 __device__ __forceinline__ float4 raw_direction(const fdsm_stack_args& a, int64_t b, int j) {
   if (a.dir) return load4<VEC>(a.dir + b * a.lddir, j, (int)a.D);
-  return mask_tail(philox_normal4(a.seed, a.offset, STREAM_DIRECTION, a.row0 + (uint64_t)b, (uint32_t)j), j, (int)a.D);
+  const float4 n = philox_normal4(a.seed, a.offset, STREAM_DIRECTION, a.row0 + (uint64_t)b, (uint32_t)j);
+  if constexpr (VEC) return n;          // the vector path requires D % 4 == 0: no partial chunk
+  return mask_tail(n, j, (int)a.D);
 }
 
 template <bool VEC>
 __device__ __forceinline__ float4 raw_noise(const fdsm_stack_args& a, int64_t b, int j) {
   if (a.noise) return load4<VEC>(a.noise + b * a.ldnoise, j, (int)a.D);
-  return mask_tail(philox_normal4(a.seed, a.offset, STREAM_NOISE, a.row0 + (uint64_t)b, (uint32_t)j), j, (int)a.D);
+  const float4 n = philox_normal4(a.seed, a.offset, STREAM_NOISE, a.row0 + (uint64_t)b, (uint32_t)j);
+  if constexpr (VEC) return n;
+  return mask_tail(n, j, (int)a.D);
 }
 
 // one stacked row chunk: plain fp32, or TF32 hi/lo halves when the batch feeds the tensor-core MLP
@@ -86,8 +90,15 @@ __device__ __forceinline__ float4 normalise(float4 d, float nrm, float scale) {
                      __fmul_rn(__fdiv_rn(d.z, nrm), scale), __fmul_rn(__fdiv_rn(d.w, nrm), scale));
 }
 
-template <int G, bool VEC, bool CACHE>
+// PLAIN: the training-step configuration (Philox direction, no noise / injected direction / hi-lo split / v / dot output,
+// all three rows, 16-byte aligned rows): every runtime mode test below folds away and the row loop is straight-line code.
+// Same arithmetic in the same order as the general instantiation: the outputs are bit-identical.
+template <int G, bool VEC, bool CACHE, bool PLAIN = false>
 __global__ void __launch_bounds__(kBlock) stack_kernel(fdsm_stack_args a) {
+  if constexpr (PLAIN) {
+    a.dir = nullptr; a.noise = nullptr; a.sigma = nullptr; a.labels = nullptr; a.out_lo = nullptr; a.v_out = nullptr;
+    a.dot_out = nullptr; a.row_mask = 7; a.normalize_dir = 1;
+  }
   pdl_launch_dependents();   // the GEMM that consumes the stacked rows sets up (barriers, TMEM) while this grid runs
   if (a.offset_dev) a.offset += __ldg(reinterpret_cast<const unsigned long long*>(a.offset_dev));
   constexpr int RPB = kBlock / G;
@@ -226,6 +237,11 @@ __global__ void __launch_bounds__(kBlock) philox_normal_kernel(float* out, int64
 
 template <int G>
 int launch_g(const fdsm_stack_args& a, bool vec, bool cache, int grid, cudaStream_t st) {
+  const bool plain = vec && cache && !a.dir && !a.sigma && !a.out_lo && !a.v_out && !a.dot_out && a.row_mask == 7 && a.x;
+  if (plain) {
+    stack_kernel<G, true, true, true><<<grid, kBlock, 0, st>>>(a);
+    FDSM_LAUNCH_CHECK("fdsm_stack");
+  }
   if (vec) {
     if (cache) stack_kernel<G, true, true><<<grid, kBlock, 0, st>>>(a);
     else stack_kernel<G, true, false><<<grid, kBlock, 0, st>>>(a);
