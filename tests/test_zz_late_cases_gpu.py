@@ -196,3 +196,46 @@ def test_fused_dsm_combine_backward_equals_explicit_sequence(fdsm, D, H, L, act,
     assert torch.equal(grad1, g2)
     loss3, grad3 = net.fd_dsm_loss_and_grad(x, sig, **kw)
     assert float(loss3) == float(loss1) and torch.equal(grad3, grad1)
+
+
+# ---- stack kernel: the compile-time specialisations must reproduce the general instantiation bit for bit ---------------
+@pytest.mark.parametrize("B,D", [(32, 784), (5, 3072), (128, 3072), (7, 64), (3, 16)])
+@pytest.mark.parametrize("use_labels", [False, True])
+@pytest.mark.parametrize("want_v,want_dot,perturb,dot_mode", [(True, True, True, 1), (False, False, True, 0), (False, True, False, 0),
+                                                              (True, False, True, 1)])
+def test_stack_noised_specialisation_equals_general_kernel(fdsm, B, D, use_labels, want_v, want_dot, perturb, dot_mode):
+    """Production-mode noised 2-row form (Philox direction + Philox noise: MODE_NOISED2 of fd_stack.cu) against the
+    general instantiation, which is what runs when the same noise is INJECTED (noise=) -- the direction stays in-kernel
+    Philox in both, so every output must be bit-identical."""
+    dev = "cuda:0"
+    g = torch.Generator().manual_seed(B * 7 + D)
+    x = torch.rand(B, D, generator=g).to(dev)
+    draw = (4242, 17, 1000)
+    if use_labels:
+        sigma = torch.exp(torch.linspace(np.log(50.0), np.log(0.01), 12)).to(dev)
+        labels = torch.randint(0, 12, (B,), generator=g).to(dev)
+    else:
+        sigma, labels = torch.linspace(0.05, 1.2, B).to(dev), None
+    kw = dict(row_mask=6, scale=0.1, sigma=sigma, labels=labels, perturb=perturb, dot_mode=dot_mode, want_v=want_v,
+              want_dot=want_dot, draw=draw)
+    out, v, dot = fdsm.ops.stack(x, **kw)
+    n = fdsm.ops.philox_normal(B, D, 1, *draw)
+    out2, v2, dot2 = fdsm.ops.stack(x, noise=n, **kw)
+    assert torch.equal(out, out2)
+    if want_v:
+        assert torch.equal(v, v2)
+    if want_dot:
+        assert torch.equal(dot, dot2)
+
+
+@pytest.mark.parametrize("B,D", [(32, 784), (4096, 784), (6, 3072), (3, 16)])
+def test_stack_energy_specialisation_equals_general_kernel(fdsm, B, D):
+    """MODE_ENERGY3 (three rows, Philox direction, nothing else) against the general instantiation, reached by also asking
+    for v: rows bit-identical, and x + v / x - v reproduce them."""
+    dev = "cuda:0"
+    x = torch.rand(B, D, device=dev)
+    draw = (77, 3, 0)
+    out, _, _ = fdsm.ops.stack(x, row_mask=7, scale=0.05, draw=draw)
+    out2, v, _ = fdsm.ops.stack(x, row_mask=7, scale=0.05, draw=draw, want_v=True)
+    assert torch.equal(out, out2)
+    assert torch.equal(out[:B], x) and torch.equal(out[B:2 * B], x + v) and torch.equal(out[2 * B:], x - v)
