@@ -219,7 +219,13 @@ def main():
     else:
         net = TorchQuadraticMLP(D, HID, NHID).to(dev)
         network = "torch nn.Linear (cuBLAS fp32) between our FD kernels"
-    tr = FDSSMTrainer(net, eps=EPS, lr=LR, betas=BETAS, clip=CLIP, seed=1234)
+    affinity0 = os.sched_getaffinity(0) if hasattr(os, "sched_getaffinity") else None
+    if world == 1 and not args.no_cpu_baseline:
+        # start torch's intra-op worker threads NOW, while this thread may still run on every core: workers inherit the
+        # creating thread's CPU mask, and the trainer below narrows this thread's mask to the GPU's NUMA node
+        torch.set_num_threads(os.cpu_count() or 1)
+        float((torch.ones(1 << 22) * 2.0).sum())
+    tr = FDSSMTrainer(net, eps=EPS, lr=LR, betas=BETAS, clip=CLIP, seed=1234)   # binds this thread to the GPU's NUMA node
 
     gen = torch.Generator(device=dev).manual_seed(1234 + rank)
     pool = [synth_batch(gen, B_PER_GPU, dev) for _ in range(POOL)]
@@ -361,7 +367,10 @@ def main():
         }
         if use_fused:
             out["roofline_fd_kernel"] = fd_roof
+        out["config"]["host_thread_cpus"] = ("gpu-local: " + str(len(tr.host_cpus))) if tr.host_cpus else "unbound"
         if world == 1 and not args.no_cpu_baseline:
+            if affinity0 is not None:
+                os.sched_setaffinity(0, affinity0)   # the CPU baseline uses every host core the process may run on
             out["cpu_baseline"] = cpu_baseline()
         print(json.dumps(out))
     if world > 1:

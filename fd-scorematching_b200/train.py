@@ -2,9 +2,43 @@
 loss -> zero_grad -> backward -> clip_grad_norm_ -> Adam step, data-parallel over ranks.
 
 This is the call a user makes (`bench.py`'s e2e leg goes through `step_from_host`)."""
+import os
+import sys
+
 import torch
 
 from . import ddp, losses, ops
+
+
+def bind_host_thread_to_gpu_node(device_index):
+    """Pin the calling host thread to the CPUs NVML reports as local to the GPU (its NUMA node), so that the pinned
+    staging buffers of `step_from_host` -- allocated by this thread -- and the launch path sit on the socket the GPU's
+    PCIe root hangs off: a remote-socket staging buffer costs H2D bandwidth.  Returns the CPU set applied, or None when
+    nothing was changed (NVML missing, FDSM_NUMA_BIND=0, or the local CPUs are outside this process's cpuset).  Never
+    raises: binding is an optimisation of the host side, not a requirement."""
+    if os.environ.get("FDSM_NUMA_BIND", "1") == "0" or not hasattr(os, "sched_setaffinity"):
+        return None
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        try:
+            uuid = str(torch.cuda.get_device_properties(device_index).uuid)
+            handle = pynvml.nvmlDeviceGetHandleByUUID(uuid if uuid.startswith("GPU-") else "GPU-" + uuid)
+        except Exception:
+            handle = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+        ncpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(handle, (ncpu + 63) // 64)
+        local = {64 * w + b for w, m in enumerate(words) for b in range(64) if (int(m) >> b) & 1}
+        allowed = os.sched_getaffinity(0)
+        cpus = local & allowed
+        if not cpus or cpus == allowed:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return cpus
+    except Exception as e:   # noqa: BLE001 -- see docstring
+        if os.environ.get("FDSM_DEBUG"):
+            print(f"fdsm_b200: host thread not bound to the GPU's NUMA node ({type(e).__name__}: {e})", file=sys.stderr)
+        return None
 
 
 class FDSSMTrainer:
@@ -18,6 +52,8 @@ class FDSSMTrainer:
         if loss == "mdsm_fd" and sigmas is None:
             raise ValueError("mdsm_fd needs the per-batch-position noise schedule `sigmas`")
         self.net = net
+        dev = next(net.parameters()).device
+        self.host_cpus = bind_host_thread_to_gpu_node(dev.index if dev.index is not None else 0) if dev.type == "cuda" else None
         self.eps, self.clip, self.loss_name = eps, clip, loss
         self.sigmas, self.sigma02, self.loss_coe = sigmas, sigma02, loss_coe
         self.fused = hasattr(net, "fd_ssm_step")       # mlp.FusedEnergyMLP: kernels (1)-(4) + Adam in CUDA

@@ -101,3 +101,52 @@ def test_flat_params_alignment_and_views():
     flat.flat.mul_(2.0)
     for p, b in zip(net.parameters(), before):
         assert torch.equal(p, 2 * b)          # parameters are views into the bucket
+
+
+def test_numa_binding_is_optional_and_never_raises(fdsm, monkeypatch):
+    """bind_host_thread_to_gpu_node: no NVML (this container) or FDSM_NUMA_BIND=0 -> returns None, affinity untouched."""
+    import os
+    from fdsm_b200.train import bind_host_thread_to_gpu_node
+    before = os.sched_getaffinity(0)
+    assert bind_host_thread_to_gpu_node(0) is None or os.sched_getaffinity(0) <= before
+    os.sched_setaffinity(0, before)
+    monkeypatch.setenv("FDSM_NUMA_BIND", "0")
+    assert bind_host_thread_to_gpu_node(0) is None
+    assert os.sched_getaffinity(0) == before
+
+
+def test_trainer_rejects_unknown_objectives(fdsm):
+    import pytest
+    from fdsm_b200.train import FDSSMTrainer
+    with pytest.raises(ValueError):
+        FDSSMTrainer(object(), loss="nope")
+    with pytest.raises(ValueError):
+        FDSSMTrainer(object(), loss="mdsm_fd")      # needs the positional noise schedule
+
+
+def test_numa_binding_decodes_the_nvml_mask(fdsm, monkeypatch):
+    """With a stub NVML reporting CPUs {0, 2} as GPU-local, the calling thread ends up on exactly those of them it may use."""
+    import os
+    import sys
+    import types
+    from fdsm_b200.train import bind_host_thread_to_gpu_node
+    before = os.sched_getaffinity(0)
+    if not {0, 2} <= before or before == {0, 2}:
+        import pytest
+        pytest.skip("this process may not run on CPUs 0 and 2 (or on nothing else)")
+    stub = types.ModuleType("pynvml")
+    stub.nvmlInit = lambda: None
+    stub.nvmlDeviceGetHandleByUUID = lambda u: (_ for _ in ()).throw(RuntimeError("no such uuid"))
+    stub.nvmlDeviceGetHandleByIndex = lambda i: ("handle", i)
+    stub.nvmlDeviceGetCpuAffinity = lambda h, n: [0b0101] + [0] * (n - 1)
+    monkeypatch.setitem(sys.modules, "pynvml", stub)
+    monkeypatch.delenv("FDSM_NUMA_BIND", raising=False)
+    try:
+        assert bind_host_thread_to_gpu_node(0) == {0, 2}
+        assert os.sched_getaffinity(0) == {0, 2}
+        # GPU-local CPUs outside the cpuset: nothing changes
+        stub.nvmlDeviceGetCpuAffinity = lambda h, n: [0] * (n - 1) + [1 << 63]
+        os.sched_setaffinity(0, before)
+        assert bind_host_thread_to_gpu_node(0) is None and os.sched_getaffinity(0) == before
+    finally:
+        os.sched_setaffinity(0, before)
