@@ -78,7 +78,9 @@ class FDSSMTrainer:
         ops.set_row_offset(self._rank * B)
         sig = None
         if self.loss_name == "mdsm_fd":      # this rank's slice of the positional schedule
-            sig = self.sigmas.reshape(-1)[self._rank * B:(self._rank + 1) * B]
+            sig = ddp.shard_sigmas(self.sigmas.reshape(-1))
+            if sig.numel() != B:
+                raise RuntimeError(f"the sigma schedule gives this rank {sig.numel()} entries for a local batch of {B}")
         if self.fused:
             if sig is not None:
                 return self.net.mdsm_fd_step(x, sig, self.sigma02, self.eps, self.loss_coe, allreduce=self._allreduce,
