@@ -44,8 +44,9 @@ def is_distributed():
 
 def shard_range(global_batch, rank=None, world=None):
     """Rank r owns samples [r*b, (r+1)*b) of the global batch; all rows of a sample stay on one rank."""
-    rank = dist.get_rank() if rank is None else rank
-    world = dist.get_world_size() if world is None else world
+    initialised = dist.is_available() and dist.is_initialized()     # a single process owns the whole batch
+    rank = (dist.get_rank() if initialised else 0) if rank is None else rank
+    world = (dist.get_world_size() if initialised else 1) if world is None else world
     if global_batch % world:
         raise ValueError(f"global batch {global_batch} not divisible by world size {world}")
     b = global_batch // world

@@ -150,3 +150,11 @@ def test_numa_binding_decodes_the_nvml_mask(fdsm, monkeypatch):
         assert bind_host_thread_to_gpu_node(0) is None and os.sched_getaffinity(0) == before
     finally:
         os.sched_setaffinity(0, before)
+
+
+def test_single_process_owns_the_whole_batch():
+    """No process group: shard_range / shard_sigmas give the full range (FDSSMTrainer at N = 1 goes through them)."""
+    from fdsm_b200 import ddp
+    assert ddp.shard_range(12) == (0, 12)
+    s = torch.linspace(0.1, 0.8, 8)
+    assert torch.equal(ddp.shard_sigmas(s), s)
