@@ -158,3 +158,43 @@ def test_single_process_owns_the_whole_batch():
     assert ddp.shard_range(12) == (0, 12)
     s = torch.linspace(0.1, 0.8, 8)
     assert torch.equal(ddp.shard_sigmas(s), s)
+
+
+def test_trainer_hands_the_dsm_step_its_sigma_slice(fdsm):
+    """FDSSMTrainer(loss='mdsm_fd') host logic with a stand-in for the fused network: the step receives the batch, this
+    process's slice of the positional sigma schedule and the DeepEBM defaults."""
+    from fdsm_b200.train import FDSSMTrainer
+
+    class Net(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.flat = torch.nn.Parameter(torch.zeros(8))
+            self.calls = []
+
+        def flat_params(self):
+            return self
+
+        def configure_optimizer(self, **kw):
+            self.opt = kw
+
+        def fd_ssm_step(self, x, eps, allreduce=None, distributed=False):
+            self.calls.append(("ssm", x.shape, eps, distributed))
+            return torch.zeros(())
+
+        def mdsm_fd_step(self, x, sigmas, sigma02, eps, loss_coe, allreduce=None, distributed=False):
+            self.calls.append(("dsm", x.shape, sigmas.clone(), sigma02, eps, loss_coe, distributed))
+            return torch.zeros(())
+
+    sig = torch.linspace(0.05, 1.2, 6).view(-1, 1)
+    net = Net()
+    tr = FDSSMTrainer(net, eps=0.05, loss="mdsm_fd", sigmas=sig, sigma02=0.01, loss_coe=1e-4)
+    assert tr.host_cpus is None                       # CPU parameters: no GPU to be local to
+    tr.step(torch.rand(6, 1, 4, 4))
+    kind, shape, s, sigma02, eps, coe, distributed = net.calls[0]
+    assert kind == "dsm" and shape == (6, 1, 4, 4) and torch.equal(s, sig.view(-1)) and not distributed
+    assert (sigma02, eps, coe) == (0.01, 0.05, 1e-4)
+    with pytest.raises(RuntimeError):                 # schedule and batch disagree
+        tr.step(torch.rand(5, 1, 4, 4))
+    tr2 = FDSSMTrainer(net, eps=0.05)
+    tr2.step(torch.rand(6, 16))
+    assert net.calls[-1][0] == "ssm"
