@@ -6,7 +6,8 @@ kernel-level ops (``ops``) and the fused energy MLPs (``mlp``).
 """
 from . import _lib, losses, mlp, ops, sampling  # noqa: F401
 from .losses import (FLAGS, MLE_efficient_score_matching_conjugate, anneal_ESM_scorenet_VR,  # noqa: F401
-                     anneal_sliced_score_estimation_vr, dsm_fd, exact_score_matching,
+                     anneal_sliced_score_estimation_vr, deepebm_exact_score_matching, dsm_fd, exact_score_matching,
+                     mdsm_baseline, mdsm_tracetrick,
                      dsm_tracetrick_FD, efficient_score_matching_conjugate, esm_scorenet_VR, fd_gradient_penalty, fd_loss, mdsm_fd,
                      mdsm_fd_nop, ncsn_anneal_ESM_scorenet, ncsn_anneal_ESM_scorenet_VR,
                      single_efficient_score_matching, single_sliced_score_matching, sliced_VR_score_matching,

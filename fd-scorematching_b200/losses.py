@@ -341,6 +341,47 @@ def exact_score_matching(energy_net, samples, train=False):
     return loss if train else loss.detach()
 
 
+def _mdsm_exact(energy, x_real, sigmas, sigma02, dim, mean, projected, batch_size, loss_coe, u, dsm_noise):
+    coe = FLAGS.loss_coe if loss_coe is None else loss_coe
+    bs = batch_size or FLAGS.batch_size or x_real.shape[0]
+    x2 = x_real.reshape(bs, dim)
+    if dsm_noise is None:
+        seed, offset, row0 = ops.next_draw()
+        dsm_noise = ops.philox_normal(bs, dim, 1, seed, offset, row0, device=x2.device)
+        if projected and u is None:       # same draw, the other Philox stream
+            u = ops.philox_normal(bs, dim, 0, seed, offset, row0, device=x2.device)
+    x_noisy = (x2 + sigmas * dsm_noise.reshape(bs, dim)).detach().requires_grad_()
+    grad_x = torch.autograd.grad(energy(x_noisy).sum(), x_noisy, create_graph=True)[0]
+    r = (x2 - x_noisy) / sigma02 + grad_x
+    if projected:
+        if u is None:
+            u = _projection_vectors(x2, "gaussian", None)
+        per = torch.sum(r * u.reshape(bs, dim).detach(), dim=-1) ** 2
+    else:
+        per = torch.sum(r ** 2, dim=-1)
+    per = per * (coe / (sigmas.view(-1) ** 2))
+    return per.mean() if mean is True else per
+
+
+def mdsm_baseline(energy, x_real, sigmas, sigma02, dim, mean=True, *, batch_size=None, loss_coe=None, dsm_noise=None):
+    """DeepEBM/ESM/loss_train.py:29-44: the multiscale DSM objective mdsm_fd approximates, and train_dsm.py's evaluation
+    loss (inputs.py:126-134).  One autograd pass over the input through the caller's network; the noise comes from
+    kernel (1)'s Philox noise stream."""
+    return _mdsm_exact(energy, x_real, sigmas, sigma02, dim, mean, False, batch_size, loss_coe, None, dsm_noise)
+
+
+def mdsm_tracetrick(energy, x_real, sigmas, sigma02, dim, mean=True, *, batch_size=None, loss_coe=None, u=None, dsm_noise=None):
+    """DeepEBM/ESM/loss_train.py:47-63: mdsm_baseline with the residual projected on one Gaussian direction before
+    squaring.  RNG order: noise, then projection."""
+    return _mdsm_exact(energy, x_real, sigmas, sigma02, dim, mean, True, batch_size, loss_coe, u, dsm_noise)
+
+
+def deepebm_exact_score_matching(energy_net, samples, dim):
+    """DeepEBM/ESM/loss_train.py:11-26 (test_exact_sm.py's evaluator): mean over the batch of exact_score_matching on
+    samples.view(-1, dim); a detached scalar."""
+    return exact_score_matching(energy_net, samples.reshape(-1, dim), train=False).mean()
+
+
 # ------------------------------------------------------------------------------------------------
 # N4: GAN_FD's one-sided finite-difference gradient penalty (GAN_FD/library/trainer_fd.py:57-73 real data, :82-100 fake)
 # ------------------------------------------------------------------------------------------------

@@ -65,6 +65,14 @@ LATE = {
                              smax=50.0, smin=0.01, anneal_power=1.5, n_particles=2, data="unit"),
     # a17 exact_score_matching(train=True) (SSM/losses/score_matching.py:48-73): 0.5 ||grad logp||^2 + tr(Hessian logp)
     "a17_exact_gmm11": dict(fn="a17_exact", net=("softplus_mlp", 11, 30), B=24, D=11, eps=0.0, data="gmm"),
+    # the rest of DeepEBM's loss table (ESM/inputs.py:96-136): the non-FD multiscale DSM losses a9 is compared with (and
+    # evaluated by: get_eval_loss) and the offline exact-SM evaluator of test_exact_sm.py
+    "a17_mdsm_baseline_d48": dict(fn="a17_mdsm_baseline", net=("quadratic_mlp", 48, 32, 3, "elu"), B=20, D=48, eps=0.0,
+                                  sigma02=0.01, loss_coe=1e-4, min_noise=0.05, max_noise=1.2, data="unit"),
+    "a17_mdsm_tracetrick_d48": dict(fn="a17_mdsm_tracetrick", net=("quadratic_mlp", 48, 32, 3, "elu"), B=20, D=48, eps=0.0,
+                                    sigma02=0.01, loss_coe=1e-4, min_noise=0.05, max_noise=1.2, data="unit"),
+    "a17_exact_deepebm_d16": dict(fn="a17_exact_deepebm", net=("quadratic_mlp", 16, 24, 2, "nsoftplus"), B=10, D=16, eps=0.0,
+                                  data="unit", view=(1, 4, 4)),
 }
 CASES.update(LATE)
 
@@ -112,7 +120,7 @@ def build(name, dtype=torch.float32):
     if "L" in c:
         c["sigmas"] = sig.to(dtype)
         c["labels"] = nets.np_randint(seed + 5, c["L"], B)
-    if c["fn"] in ("a9", "a10"):
+    if c["fn"] in ("a9", "a10", "a17_mdsm_baseline", "a17_mdsm_tracetrick"):
         import numpy as np
         c["sig_b"] = torch.tensor(np.linspace(c["min_noise"], c["max_noise"], B)).view(-1, 1).to(dtype)
     return c

@@ -188,6 +188,19 @@ def exact_sm(energy_net, x):
     return per
 
 
+def mdsm_exact(energy_net, x, n, sigmas, sigma02, loss_coe, projection=None):
+    """a17 DeepEBM mdsm_baseline (loss_train.py:29-44) and, with `projection`, mdsm_tracetrick (:47-63): the multiscale
+    denoising score matching objective that mdsm_fd approximates -- ((x - xt)/sigma0^2 + grad E(xt)) squared (or its
+    squared projection), weighted loss_coe / sigma_b^2, batch mean."""
+    B = x.shape[0]
+    xf = x.reshape(B, -1)
+    xt = (xf + sigmas * n.reshape(B, -1)).detach().requires_grad_(True)
+    grad_x = torch.autograd.grad(energy_net(xt).sum(), xt, create_graph=True)[0]
+    r = (xf - xt) / sigma02 + grad_x
+    per = (r ** 2).sum(-1) if projection is None else ((r * projection.reshape(B, -1)).sum(-1)) ** 2
+    return (per * (loss_coe / sigmas.view(-1) ** 2)).mean()
+
+
 def quadratic_energy_fd_ssm_exact(A, b, x, vhat):
     """Analytic fixture: E(x)=0.5 x^T A x + b^T x (A symmetric).  For v=eps*vhat the
     a1 loss / D == mean(0.5*(vhat^T(Ax+b))^2 - vhat^T A vhat) for ANY eps

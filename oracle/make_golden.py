@@ -149,6 +149,19 @@ def reference_loss(ref, c):
             return ref.score_matching.exact_score_matching(net, x, train=True).mean()
         finally:
             torch.set_default_dtype(saved)
+    if fn == "a17_mdsm_baseline":
+        with Replay([n]):
+            return ref.deepebm.mdsm_baseline(net, x, c["sig_b"], c["sigma02"], c["D"])
+    if fn == "a17_mdsm_tracetrick":
+        with Replay([n, u]):
+            return ref.deepebm.mdsm_tracetrick(net, x, c["sig_b"], c["sigma02"], c["D"])
+    if fn == "a17_exact_deepebm":   # returns a detached mean (loss_train.py:20-26): value only, the gradient entry stays zero
+        saved = torch.get_default_dtype()
+        torch.set_default_dtype(x.dtype)
+        try:
+            return ref.deepebm.exact_score_matching(net, x, c["D"])
+        finally:
+            torch.set_default_dtype(saved)
     if fn == "a17_ssm":
         with Replay([u.reshape(c["B"], -1)]):
             return ref.deepebm.ssm(net, x)
@@ -175,7 +188,8 @@ def main():
             for p in c["net"].parameters():
                 p.grad = None
             loss = reference_loss(ref, c)
-            loss.backward()
+            if loss.requires_grad:
+                loss.backward()
             rec[f"loss_{tag}"] = loss.detach().double().numpy()
             rec[f"grad_{tag}"] = cases.flat_grad(c["net"]).double().numpy()
             # restatement check at generation time too (the CPU test suite repeats it)

@@ -26,6 +26,12 @@ def oracle_loss(c, net=None):
         return F.anneal_ssm_vr(net, x, c["n"], c["u"], c["labels"], c["sigmas"], c["anneal_power"], c["n_particles"])
     if fn == "a17_exact":
         return F.exact_sm(net, x).mean()
+    if fn == "a17_exact_deepebm":      # loss_train.py:11-26: the same quantity on samples.view(-1, dim), mean
+        return F.exact_sm(net, x.reshape(B, -1)).mean().detach()   # an evaluator: value only
+    if fn == "a17_mdsm_baseline":
+        return F.mdsm_exact(net, x, c["n"], c["sig_b"], c["sigma02"], c["loss_coe"])
+    if fn == "a17_mdsm_tracetrick":    # RNG order: noise, then projection (loss_train.py:49-50)
+        return F.mdsm_exact(net, x, c["n"], c["sig_b"], c["sigma02"], c["loss_coe"], projection=c["u"])
     if fn.startswith("a17"):   # exact SSM (HVP) comparison losses: Gaussian (DeepEBM) or sign (SSM repo) projections
         xf, uf = x.reshape(B, -1), c["u"].reshape(B, -1)
         if fn in ("a17_sliced", "a17_sliced_vr"):
@@ -65,7 +71,8 @@ def loss_and_grad(c, net=None):
     for p in net.parameters():
         p.grad = None
     loss = oracle_loss(c, net)
-    loss.backward()
+    if loss.requires_grad:
+        loss.backward()
     g = torch.cat([(p.grad if p.grad is not None else torch.zeros_like(p)).reshape(-1)
                    for p in net.parameters()])
     return loss.detach(), g

@@ -32,6 +32,12 @@ def run_late_adapter(L, c, dev):
                                                    c["n_particles"], u=u, dsm_noise=n)
     if fn == "a17_exact":
         return L.exact_score_matching(net, x, train=True).mean()
+    if fn == "a17_exact_deepebm":
+        return L.deepebm_exact_score_matching(net, x, c["D"])
+    if fn == "a17_mdsm_baseline":
+        return L.mdsm_baseline(net, x, c["sig_b"].to(dev), c["sigma02"], c["D"], loss_coe=c["loss_coe"], dsm_noise=n)
+    if fn == "a17_mdsm_tracetrick":
+        return L.mdsm_tracetrick(net, x, c["sig_b"].to(dev), c["sigma02"], c["D"], loss_coe=c["loss_coe"], u=u, dsm_noise=n)
     raise KeyError(fn)
 
 
@@ -41,7 +47,8 @@ def test_late_adapter_matches_reference(fdsm, golden, name):
     torch.backends.cuda.matmul.allow_tf32 = False
     c = cases.build(name, torch.float32)
     loss = run_late_adapter(fdsm.losses, c, dev)
-    loss.backward()
+    if loss.requires_grad:
+        loss.backward()
     grad = cases.flat_grad(c["net"]).cpu().numpy()
     l32, l64 = golden[f"{name}/loss_f32"], golden[f"{name}/loss_f64"]
     g32, g64 = golden[f"{name}/grad_f32"], golden[f"{name}/grad_f64"]
