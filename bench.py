@@ -329,8 +329,9 @@ def main():
                    "avg_launch_us": kus, "in_step_eager_launch_us": savg * 1e3,
                    "traffic": ncu.get("stack_dram_bytes_per_launch"),
                    "note": "graph-timed launches on rotating inputs; 38.5 MB of output stay in the 126 MB L2 for the GEMM "
-                           "that follows, so DRAM traffic is below the algorithmic bytes (the kernel is issue-bound: "
-                           "Philox4x32-10 + Box-Muller per float4)"}
+                           "that follows, so DRAM traffic is below the algorithmic bytes; what bounds the launch is "
+                           "instruction issue (Philox4x32-10 + Box-Muller per float4), hence the compile-time "
+                           "specialisation of this configuration (fd_stack.cu MODE_ENERGY3)"}
     if roof is None:
         # generic mode: the dominant kernel of ours is the fused direction+stack build (HBM-bound)
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
