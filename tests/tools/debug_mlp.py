@@ -4,7 +4,7 @@ import sys
 
 import torch
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 import fdsm_b200 as fdsm  # noqa: E402
 from oracle import fd_losses, nets  # noqa: E402
