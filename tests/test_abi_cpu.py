@@ -63,6 +63,10 @@ def test_reference_error_behaviour(fdsm):
 
 
 def test_product_never_imports_oracle():
+    for fn in os.listdir(os.path.join(ROOT, "scripts")):      # measurement scripts time the product: no checker in them
+        if fn.endswith(".py"):
+            txt = open(os.path.join(ROOT, "scripts", fn)).read()
+            assert not re.search(r"^\s*(from|import)\s+oracle\b", txt, flags=re.M), f"scripts/{fn} imports oracle/"
     pkg = os.path.join(ROOT, "fd-scorematching_b200")
     for dp, _, fns in os.walk(pkg):
         for fn in fns:
