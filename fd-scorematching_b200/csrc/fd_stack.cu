@@ -247,7 +247,9 @@ __global__ void __launch_bounds__(kBlock) philox_normal_kernel(float* out, int64
 
 template <int G>
 int launch_g(const fdsm_stack_args& a, bool vec, bool cache, int grid, cudaStream_t st) {
-  if (vec && cache && !a.dir && !a.out_lo && a.x) {
+  // FDSM_STACK_SPECIALISE=0 (read once) routes everything through the general instantiation: A/B timing, bisecting
+  static const bool specialise = [] { const char* e = getenv("FDSM_STACK_SPECIALISE"); return !(e && e[0] == '0'); }();
+  if (specialise && vec && cache && !a.dir && !a.out_lo && a.x) {
     if (!a.sigma && !a.v_out && !a.dot_out && a.row_mask == 7) {
       stack_kernel<G, true, true, MODE_ENERGY3><<<grid, kBlock, 0, st>>>(a);
       FDSM_LAUNCH_CHECK("fdsm_stack");
