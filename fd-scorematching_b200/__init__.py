@@ -4,7 +4,7 @@ Import as ``fdsm_b200`` (see the ``fdsm_b200.py`` shim at the repo root; the dir
 contains a hyphen).  Public surface = the reference's loss-function signatures (``losses``), the
 kernel-level ops (``ops``) and the fused energy MLPs (``mlp``).
 """
-from . import _lib, losses, mlp, ops, sampling  # noqa: F401
+from . import _lib, losses, mlp, nets, ops, sampling  # noqa: F401
 from .losses import (FLAGS, MLE_efficient_score_matching_conjugate, anneal_ESM_scorenet_VR,  # noqa: F401
                      anneal_sliced_score_estimation_vr, deepebm_exact_score_matching, dsm_fd, exact_score_matching,
                      mdsm_baseline, mdsm_tracetrick,

@@ -58,6 +58,8 @@ class MlpDesc(C.Structure):
                 ("presplit", _i32)]
 
 
+ABI_VERSION = 5    # FDSM_ABI_VERSION of include/fdsm.h
+
 # name -> (restype, argtypes); must list every symbol include/fdsm.h declares
 PROTOTYPES = {
     "fdsm_version": (C.c_int, []),
@@ -72,6 +74,7 @@ PROTOTYPES = {
     "fdsm_combine_dsm_bwd": (C.c_int, [_f32p, _f32p, _f32p, _i64, _f32, _f32, _f32, _f32p, _f32p, _stream]),
     "fdsm_combine_score": (C.c_int, [_f32p, _i64, _f32p, _i64, _f32p, C.c_void_p, _f32, _i64, _i64, _f32, _i32,
                                      _f32p, _f32p, _f32p, _f32p, _i64, _stream]),
+    "fdsm_scale_unless_one": (C.c_int, [_f32p, _i64, _f32p, _stream]),
     "fdsm_tf32_split": (C.c_int, [_f32p, _i64, _i64, _i64, _f32p, _f32p, _i64, _i64, _i32, _stream]),
     "fdsm_tc_gemm": (C.c_int, [C.POINTER(GemmArgs), _stream]),
     "fdsm_grad_sumsq": (C.c_int, [_f32p, _i64, _f32p, C.c_void_p, _stream]),
@@ -114,8 +117,8 @@ def load():
     for name, (res, args) in PROTOTYPES.items():
         fn = getattr(lib, name)  # AttributeError if the symbol is missing
         fn.restype, fn.argtypes = res, args
-    if lib.fdsm_version() != 4:
-        raise FdsmError(f"libfdsm ABI version {lib.fdsm_version()} != 4")
+    if lib.fdsm_version() != ABI_VERSION:
+        raise FdsmError(f"libfdsm ABI version {lib.fdsm_version()} != {ABI_VERSION} (stale build: run __graft_entry__.build())")
     _lib = lib
     return lib
 

@@ -151,6 +151,20 @@ __global__ void __launch_bounds__(1024) mean_kernel(const float* __restrict__ pe
   if (threadIdx.x == 0) *out = acc / (float)B;
 }
 
+// data *= *g unless *g == 1 (the usual root-loss case: every block reads the scalar and leaves -- no traffic)
+__global__ void __launch_bounds__(256) scale_unless_one_kernel(float* __restrict__ data, int64_t n, const float* __restrict__ g) {
+  const float c = __ldg(g);
+  if (c == 1.f) return;
+  const int64_t n4 = aligned16(data) ? n >> 2 : 0;
+  float4* d4 = reinterpret_cast<float4*>(data);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    float4 v = d4[i];
+    v.x *= c; v.y *= c; v.z *= c; v.w *= c;
+    d4[i] = v;
+  }
+  for (int64_t i = 4 * n4 + blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) data[i] *= c;
+}
+
 template <int G>
 void launch_score(const ScoreArgs& a, bool vec, int grid, cudaStream_t st) {
   if (vec) combine_score_kernel<G, true><<<grid, kBlock, 0, st>>>(a);
@@ -238,4 +252,13 @@ extern "C" int fdsm_combine_score(const float* s, int64_t lds, const float* v, i
     FDSM_LAUNCH_CHECK("fdsm_combine_score(mean)");
   }
   return FDSM_OK;
+}
+
+extern "C" int fdsm_scale_unless_one(float* data, int64_t n, const float* g, fdsm_stream_t stream) {
+  FDSM_REQUIRE(n >= 0, "fdsm_scale_unless_one: n < 0");
+  if (n == 0) return FDSM_OK;
+  FDSM_REQUIRE(data && g, "fdsm_scale_unless_one: NULL pointer");
+  const int64_t want = (n / 4 + 255) / 256 + 1, cap = (int64_t)sm_count() * 8;
+  scale_unless_one_kernel<<<(int)(want < cap ? want : cap), 256, 0, (cudaStream_t)stream>>>(data, n, g);
+  FDSM_LAUNCH_CHECK("fdsm_scale_unless_one");
 }

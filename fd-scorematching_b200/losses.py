@@ -86,11 +86,18 @@ def single_efficient_score_matching(energy_net, samples, eps=0.01, noise_type="s
 
 
 def MLE_efficient_score_matching_conjugate(energy_net, samples, eps=0.01, mle_ratio=10, noise_type="sphere", *, u=None):
-    """SSM/losses/efficient_sm.py:101-123: c1 = mle_ratio, summed, no /eps^2."""
-    if noise_type != "sphere":
-        raise NotImplementedError("only noise_type='sphere' is implemented on the CUDA path")
+    """SSM/losses/efficient_sm.py:101-123: c1 = mle_ratio, summed, no /eps^2.  noise_type as in
+    single_efficient_score_matching (:105-110): 'sphere' = eps*u/||u||, 'radermacher' = sign(u)*eps, anything else
+    leaves the Gaussian draw unscaled."""
     x2 = samples.reshape(samples.shape[0], -1)
-    return _fd_energy(energy_net, x2, u=u, eps=eps, scale=1.0, c1=mle_ratio, mean=False)[0]
+    if noise_type == "sphere":
+        return _fd_energy(energy_net, x2, u=u, eps=eps, scale=1.0, c1=mle_ratio, mean=False)[0]
+    if u is not None:
+        u = u.reshape(x2.shape)
+    v = _projection_vectors(x2, "radermacher" if noise_type == "radermacher" else "gaussian", u)
+    if noise_type == "radermacher":
+        v = v * eps
+    return _fd_energy(energy_net, x2, v=v, eps=eps, scale=1.0, c1=mle_ratio, mean=False)[0]
 
 
 def ssm_fd(energy, samples, *, eps=None, batch_size=None, u=None):

@@ -3,8 +3,8 @@
 (``fdsm_mlp_*``, include/fdsm.h).  No torch matmul, no fallback.
 
 Two ways in:
-  * ``net(x)`` -- an ``nn.Module`` drop-in for the reference's energy networks: works with every energy-form loss
-    adapter in ``losses`` (generic mode); parameters live in ONE flat ``nn.Parameter`` laid out in the reference's
+  * ``net(x)`` -- an ``nn.Module`` drop-in for the reference's energy networks: works with every energy-form FD loss
+    adapter in ``losses`` (generic mode; the a17 comparison losses differentiate w.r.t. x and need a torch module); parameters live in ONE flat ``nn.Parameter`` laid out in the reference's
     ``named_parameters()`` order, so ``load_reference_state_dict`` accepts the reference's checkpoints.
   * ``net.fd_ssm_loss_and_grad(x, eps, scale)`` -- the fused FD-SSM step: stack build (hi/lo TF32 operands written
     directly by kernel (1)+(2)), MLP forward, combine forward+backward (kernel (4)), MLP backward.
@@ -43,6 +43,11 @@ class _MlpFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, flat, x2, net):
         lib = _lib.load()
+        if x2.requires_grad:
+            # the backward emits parameter gradients only (the FD objectives never differentiate w.r.t. the samples):
+            # a caller that needs dE/dx (the exact-SSM comparison losses, a GAN generator) must not get silence
+            raise NotImplementedError("FusedEnergyMLP does not provide the gradient with respect to its input; use a torch "
+                                      "module for losses that differentiate through x (ssm, ssm_vr, exact_score_matching)")
         rows = x2.shape[0]
         sz = net.sizes(rows)
         xh, xl = ops.tf32_split(x2, out_cols=sz.in_ld, ones_col=True, raw=not net.presplit)

@@ -189,6 +189,7 @@ class CombineEnergy(torch.autograd.Function):
     @staticmethod
     def forward(ctx, E, B, mode, c1, scale, mean, want_per_sample):
         lib = _lib.load()
+        ctx.e_shape = tuple(E.shape)      # (N,) or (N, 1): the backward returns the gradient in the caller's shape
         E = _req(E, "energy output").contiguous().view(-1)
         rows = 3 if mode == 0 else 2
         if E.numel() != rows * B:
@@ -213,7 +214,7 @@ class CombineEnergy(torch.autograd.Function):
         dE = torch.empty_like(E)
         _count(1); check(lib.fdsm_combine_energy_bwd(_ptr(E), B, mode, c1, scale, mean, _ptr(gout), _ptr(dE), _stream()),
               "fdsm_combine_energy_bwd")
-        return dE, None, None, None, None, None, None
+        return dE.view(ctx.e_shape), None, None, None, None, None, None
 
 
 class CombineDsm(torch.autograd.Function):
@@ -222,6 +223,7 @@ class CombineDsm(torch.autograd.Function):
     @staticmethod
     def forward(ctx, E, dot, sigma_b, B, alpha, beta, gamma):
         lib = _lib.load()
+        ctx.e_shape = tuple(E.shape)
         E = _req(E, "energy output").contiguous().view(-1)
         if E.numel() != 2 * B:
             raise ValueError(f"energy net returned {E.numel()} values for a stacked batch of {2 * B} rows")
@@ -241,11 +243,15 @@ class CombineDsm(torch.autograd.Function):
         dE = torch.empty_like(E)
         _count(1); check(lib.fdsm_combine_dsm_bwd(_ptr(E), _ptr(dot), _ptr(sigma_b), B, alpha, beta, gamma, _ptr(gout), _ptr(dE),
                                        _stream()), "fdsm_combine_dsm_bwd")
-        return dE, None, None, None, None, None, None
+        return dE.view(ctx.e_shape), None, None, None, None, None, None
 
 
 class CombineScore(torch.autograd.Function):
-    """loss = mean_b w_b * sum_d[(s1+s2)^2/8 + (s1-s2) v k]  (or the projected non-VR form)."""
+    """loss = mean_b w_b * sum_d[(s1+s2)^2/8 + (s1-s2) v k]  (or the projected non-VR form).
+
+    When the score output needs a gradient, the forward launch is the kernel's fused fwd+bwd pass (R s1, s2, v; W ds1,
+    ds2 = 20*D bytes per sample): ds is written for an upstream gradient of 1 and the backward
+    only rescales it when the upstream gradient differs from 1 (fdsm_scale_unless_one: a scalar test per block)."""
 
     @staticmethod
     def forward(ctx, s, v, sigma, labels, power, B, D, k, projected, want_per_sample):
@@ -256,25 +262,24 @@ class CombineScore(torch.autograd.Function):
         s2d, lds = _rows(s2d, "score output")
         loss = torch.empty((), device=s.device, dtype=torch.float32)
         per = torch.empty((B,), device=s.device, dtype=torch.float32)
+        ds = torch.empty((2 * B, D), device=s.device, dtype=torch.float32) if ctx.needs_input_grad[0] else None
         _count(2); check(lib.fdsm_combine_score(_ptr(s2d), lds, _ptr(v), max(D, 1), _ptr(sigma), _ptr(labels), power, B, D, k,
-                                     int(projected), None, _ptr(per), _ptr(loss), None, 0, _stream()),
-              "fdsm_combine_score(fwd)")
-        ctx.save_for_backward(s2d, v, sigma, labels)
-        ctx.cfg = (power, B, D, k, int(projected), tuple(s.shape), lds)
+                                     int(projected), None, _ptr(per), _ptr(loss), _ptr(ds), max(D, 1), _stream()),
+              "fdsm_combine_score(fwd+bwd)" if ds is not None else "fdsm_combine_score(fwd)")
+        ctx.ds, ctx.shape = ds, tuple(s.shape)
         ctx.mark_non_differentiable(per)
         return loss, per
 
     @staticmethod
     def backward(ctx, gout, _gper):
         lib = _lib.load()
-        s2d, v, sigma, labels = ctx.saved_tensors
-        power, B, D, k, projected, shape, lds = ctx.cfg
+        ds, ctx.ds = ctx.ds, None      # consumed: a second backward through the same graph is an error, as in torch
+        if ds is None:
+            raise RuntimeError("CombineScore.backward: the gradient buffer was already consumed (retain_graph is not "
+                               "supported on the fused combine) or the score output did not require grad")
         gout = gout.contiguous().float()
-        ds = torch.empty((2 * B, D), device=s2d.device, dtype=torch.float32)
-        _count(1); check(lib.fdsm_combine_score(_ptr(s2d), lds, _ptr(v), max(D, 1), _ptr(sigma), _ptr(labels), power, B, D, k,
-                                     projected, _ptr(gout), None, None, _ptr(ds), max(D, 1), _stream()),
-              "fdsm_combine_score(bwd)")
-        return ds.view(shape), None, None, None, None, None, None, None, None, None
+        _count(1); check(lib.fdsm_scale_unless_one(_ptr(ds), ds.numel(), _ptr(gout), _stream()), "fdsm_scale_unless_one")
+        return ds.view(ctx.shape), None, None, None, None, None, None, None, None, None
 
 
 def combine_score_fused(s2d, v, *, k, sigma=None, labels=None, power=2.0, projected=False):

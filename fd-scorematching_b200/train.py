@@ -46,7 +46,7 @@ class FDSSMTrainer:
     schedule of train_dsm.py:50-57 as `sigmas`; each rank uses its own slice of it)."""
 
     def __init__(self, net, *, eps=0.05, lr=1e-5, betas=(0.9, 0.95), clip=0.1, loss="ssm_fd", seed=1234, sigmas=None,
-                 sigma02=0.01, loss_coe=1e-4):
+                 sigma02=0.01, loss_coe=1e-4, scale=None):
         if loss not in ("ssm_fd", "mdsm_fd"):
             raise ValueError("loss must be 'ssm_fd' or 'mdsm_fd'")
         if loss == "mdsm_fd" and sigmas is None:
@@ -56,6 +56,7 @@ class FDSSMTrainer:
         self.host_cpus = bind_host_thread_to_gpu_node(dev.index if dev.index is not None else 0) if dev.type == "cuda" else None
         self.eps, self.clip, self.loss_name = eps, clip, loss
         self.sigmas, self.sigma02, self.loss_coe = sigmas, sigma02, loss_coe
+        self.scale = scale      # None: 1/eps^2 (loss_train.py:232); efficient_sm.py:71 uses D/eps^2
         self.fused = hasattr(net, "fd_ssm_step")       # mlp.FusedEnergyMLP: kernels (1)-(4) + Adam in CUDA
         rank = torch.distributed.get_rank() if ddp.is_distributed() else 0
         if self.fused:
@@ -85,13 +86,16 @@ class FDSSMTrainer:
             if sig is not None:
                 return self.net.mdsm_fd_step(x, sig, self.sigma02, self.eps, self.loss_coe, allreduce=self._allreduce,
                                              distributed=ddp.is_distributed())
-            return self.net.fd_ssm_step(x, eps=self.eps, allreduce=self._allreduce, distributed=ddp.is_distributed())
+            return self.net.fd_ssm_step(x, eps=self.eps, allreduce=self._allreduce, distributed=ddp.is_distributed(),
+                                        scale=self.scale)
         self.flat.zero_grad()
         if sig is not None:
             loss = losses.mdsm_fd(self.net, x, sig, self.sigma02, int(x[0].numel()), eps=self.eps, batch_size=B,
                                   loss_coe=self.loss_coe)
         else:
             loss = losses.ssm_fd(self.net, x, eps=self.eps, batch_size=B)
+            if self.scale is not None:
+                loss = loss * (self.scale * self.eps ** 2)
         loss.backward()
         ddp.allreduce_mean_(self.flat.grad)
         if self.clip is not None:
@@ -126,3 +130,77 @@ class FDSSMTrainer:
         self._free[i].record(cur)
         loss_host.copy_(loss, non_blocking=True)
         return loss_host
+
+
+class GenericFDTrainer:
+    """The same hot loop for ANY network in generic mode (configs 3-5: Res18Quadratic, CondRefineNetDilated, NCSNv2 --
+    or the caller's own module): `loss_fn(net, x) -> scalar` is one of the adapters in `losses` (kernels (1)+(2) and (4)
+    of ours around the caller's torch network), then zero_grad / backward / ONE all-reduce of the flat gradient / optional
+    global-norm clip / Adam / optional EMA (ncsnv2/runners/ncsn_esm_runner.py:146-151) -- the last three each ONE launch on
+    the flat parameter vector (`ddp.FlatParams`)."""
+
+    def __init__(self, net, loss_fn, *, lr=1e-4, betas=(0.9, 0.999), clip=None, ema_rate=None, seed=1234):
+        self.net, self.loss_fn, self.clip = net, loss_fn, clip
+        self.flat = ddp.FlatParams(net)
+        self.opt = torch.optim.Adam([self.flat.flat], lr=lr, betas=betas, fused=self.flat.flat.is_cuda)
+        self.flat.flat.grad = self.flat.grad
+        ddp.broadcast_params_(self.flat.flat.data)
+        self.ema_rate = ema_rate
+        self.ema_shadow = self.flat.flat.data.clone() if ema_rate else None
+        self._rank = torch.distributed.get_rank() if ddp.is_distributed() else 0
+        ops.manual_seed(seed)
+        self._h2d = None
+
+    def step(self, x):
+        ops.set_row_offset(self._rank * x.shape[0])
+        self.flat.zero_grad()
+        loss = self.loss_fn(self.net, x)
+        loss.backward()
+        ddp.allreduce_mean_(self.flat.grad)
+        if self.clip:
+            nrm = torch.linalg.vector_norm(self.flat.grad)
+            self.flat.grad.mul_(torch.clamp(self.clip / (nrm + 1e-6), max=1.0))
+        self.opt.step()
+        if self.ema_shadow is not None:
+            ops.ema_update(self.ema_shadow, self.flat.flat.data, self.ema_rate)
+        return loss.detach()
+
+    def step_from_host(self, x_host, loss_host):
+        """Pinned host batch -> device (copy stream, double-buffered) -> step -> async D2H of the loss."""
+        if self._h2d is None:
+            self._h2d = HostStager()
+        x = self._h2d.stage(x_host)
+        loss = self.step(x)
+        self._h2d.release()
+        loss_host.copy_(loss, non_blocking=True)
+        return loss_host
+
+
+class HostStager:
+    """Double-buffered pinned-host -> device staging on a copy stream (one pair of device buffers per batch shape)."""
+
+    def __init__(self):
+        self.stream = torch.cuda.Stream()
+        self.slots = {}
+        self._last = None
+
+    def stage(self, x_host):
+        cur = torch.cuda.current_stream()
+        key = (tuple(x_host.shape), x_host.dtype)
+        if key not in self.slots:
+            self.slots[key] = dict(bufs=[torch.empty_like(x_host, device="cuda") for _ in range(2)],
+                                   ready=[torch.cuda.Event() for _ in range(2)], free=[torch.cuda.Event() for _ in range(2)], i=0)
+        sg = self.slots[key]
+        i = sg["i"]
+        sg["i"] ^= 1
+        with torch.cuda.stream(self.stream):
+            self.stream.wait_event(sg["free"][i])
+            sg["bufs"][i].copy_(x_host, non_blocking=True)
+            sg["ready"][i].record(self.stream)
+        cur.wait_event(sg["ready"][i])
+        self._last = (sg, i)
+        return sg["bufs"][i]
+
+    def release(self):
+        sg, i = self._last
+        sg["free"][i].record(torch.cuda.current_stream())

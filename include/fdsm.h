@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define FDSM_ABI_VERSION 4
+#define FDSM_ABI_VERSION 5
 
 #define FDSM_OK 0
 #define FDSM_ERR_INVALID_ARGUMENT (-1)
@@ -137,6 +137,11 @@ int fdsm_combine_score(const float* s, int64_t lds, const float* v, int64_t ldv,
                        const int64_t* labels, float power, int64_t B, int64_t D, float k, int32_t projected,
                        const float* gout, float* per_sample, float* loss, float* ds, int64_t ldds,
                        fdsm_stream_t stream);
+/* data[0..n) *= g[0] unless g[0] == 1 (device scalar; no host read, graph-capturable).  The autograd wrapper of the
+ * fused pass above computes ds for an upstream gradient of 1 inside the FORWARD launch and applies the actual upstream
+ * gradient here: for the usual `loss.backward()` on the returned loss every block reads the scalar and exits, so the
+ * score-form combine moves 20*D bytes per sample instead of the 32*D of a forward launch plus a backward launch. */
+int fdsm_scale_unless_one(float* data, int64_t n, const float* g, fdsm_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------
  * Kernel (3) building blocks: TF32 hi/lo operand split and the tcgen05/TMEM GEMM fed by TMA.

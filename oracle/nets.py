@@ -130,3 +130,29 @@ def np_rand(seed, *shape):
 def np_randint(seed, high, n):
     import numpy as np
     return torch.from_numpy(np.random.RandomState(seed).randint(0, high, size=(n,))).long()
+
+
+def init_by_name(module, seed):
+    """Deterministic init that does not depend on parameter ORDER: every floating-point parameter is drawn from a numpy
+    MT19937 stream keyed by (seed, crc32(name)).  Used where the same state must be given to the reference's module and
+    to fdsm_b200.nets (whose registration order differs).  Ranges: weights with >= 2 dims U(+-1/sqrt(fan_in)) (torch's
+    conv / linear default bound); normaliser scales (alpha, gamma, LayerNorm weight, the first two thirds of an
+    InstanceNorm++ embedding row) U(0.9, 1.1); every other vector U(+-0.05)."""
+    import zlib
+    import numpy as np
+    with torch.no_grad():
+        for name, p in sorted(module.named_parameters()):
+            rs = np.random.RandomState((seed * 1000003 + zlib.crc32(name.encode())) % (2 ** 31))
+            leaf = name.rsplit(".", 1)[-1]
+            if name.endswith("embed.weight"):
+                c = p.shape[1] // 3
+                vals = np.concatenate([rs.uniform(0.9, 1.1, (p.shape[0], 2 * c)), rs.uniform(-0.05, 0.05, (p.shape[0], c))], 1)
+            elif leaf in ("alpha", "gamma") or (leaf == "weight" and p.dim() == 3):   # LayerNorm([C, H, W]).weight
+                vals = rs.uniform(0.9, 1.1, tuple(p.shape))
+            elif p.dim() >= 2:
+                bound = 1.0 / math.sqrt(max(int(np.prod(p.shape[1:])), 1))
+                vals = rs.uniform(-bound, bound, tuple(p.shape))
+            else:
+                vals = rs.uniform(-0.05, 0.05, tuple(p.shape))
+            p.copy_(torch.from_numpy(vals).to(p.dtype))
+    return module

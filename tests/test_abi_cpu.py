@@ -27,7 +27,8 @@ def test_library_exports_every_declared_symbol(fdsm):
     for s in syms:
         assert hasattr(lib, s), f"libfdsm.so does not export {s}"
     assert syms == set(fdsm._lib.PROTOTYPES), "ctypes prototype table out of sync with include/*.h"
-    assert lib.fdsm_version() == 4
+    hdr = open(os.path.join(ROOT, "include", "fdsm.h")).read()
+    assert lib.fdsm_version() == int(re.search(r"#define FDSM_ABI_VERSION (\d+)", hdr).group(1)) == fdsm._lib.ABI_VERSION
 
 
 def test_stack_args_struct_matches_header(fdsm):
@@ -43,6 +44,17 @@ def test_stack_args_struct_matches_header(fdsm):
         for part in decl.split(","):
             fields.append(re.findall(r"([A-Za-z_0-9]+)\s*$", part.strip())[0])
     assert fields == [f[0] for f in fdsm._lib.StackArgs._fields_]
+
+
+def test_integration_doc_struct_matches_header(fdsm):
+    """The ctypes mirror a maintainer would paste from INTEGRATION.md has the fields (names, order, ctypes) of _lib.py's."""
+    txt = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    body = txt[txt.index("class StackArgs(C.Structure):"):]
+    body = body[body.index("_fields_ = ["):body.index("]\n") + 1]
+    doc = re.findall(r'\("([A-Za-z_0-9]+)",\s*C\.(c_[a-z0-9_]+)\)', body)
+    # same names in the same order, each field of the same size and kind (pointer / integer / float)
+    kind = lambda t: ("p" if t in (ctypes.c_void_p, fdsm._lib._f32p) else "f" if t is ctypes.c_float else "i", ctypes.sizeof(t))
+    assert [(n, kind(getattr(ctypes, t))) for n, t in doc] == [(n, kind(t)) for n, t in fdsm._lib.StackArgs._fields_]
 
 
 def test_no_cpu_fallback(fdsm):
