@@ -316,8 +316,15 @@ def main():
 
     use_fused = args.network in ("auto", "fused")
     if use_fused:
-        net = fdsm.mlp.FusedEnergyMLP(D, HID, NHID, act=ACT, head="quadratic", device=dev, seed=1234)
-        network = "fused tcgen05 3xTF32 MLP (ours): kernels (1)-(4) + clip + Adam, one CUDA-graph replay per step"
+        net = fdsm.mlp.FusedEnergyMLP(D, HID, NHID, act=ACT, head="quadratic", device=dev, seed=1234,
+                                      formulation=os.environ.get("FDSM_BENCH_FORMULATION", "auto"),
+                                      jet_passes=int(os.environ.get("FDSM_BENCH_JET_PASSES", "2")))
+        if net.formulation == "jet":
+            network = (f"fused difference-propagating chain (ours): Philox direction + tcgen05 forward / head / combine / dgrad in one "
+                       f"kernel (weights TF32 hi+lo, {net.jet_passes} pass), split-K tcgen05 weight gradients, clip + Adam; one "
+                       f"CUDA-graph replay per step")
+        else:
+            network = "fused tcgen05 3xTF32 MLP (ours): kernels (1)-(4) + clip + Adam, one CUDA-graph replay per step"
     else:
         net = TorchQuadraticMLP(D, HID, NHID).to(dev)
         network = "torch nn.Linear (cuBLAS fp32) between our FD kernels"
@@ -401,14 +408,15 @@ def main():
         # Kernel time = 20 launches on rotating batches inside one CUDA graph between two events (no host launch gaps);
         # the in-step eager launch of the un-graphed pass above is reported next to it.
         sms = sorted(a.elapsed_time(b) for a, b in sev)
-        savg = sum(sms) / len(sms)
-        st = net._step_state
+        savg = sum(sms) / len(sms) if sms else None
+        # rotating OUTPUT buffers as well (4 x 38.5 MB > the 126 MB L2): the stores of one launch cannot stay L2-resident
+        # for the next, so the figure is an HBM figure
+        outs = [torch.empty(3 * B_PER_GPU, D, device=dev) for _ in range(4)]
         gs = torch.cuda.Stream()
         gs.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(gs):
             def stack_once(i):
-                ops.stack(pool[i % POOL], row_mask=7, scale=EPS, out=st["xh"], out_lo=st["xl"], draw=(1234, i, 0),
-                          pad_ones=not net.presplit)
+                ops.stack(pool[i % POOL], row_mask=7, scale=EPS, out=outs[i % 4], draw=(1234, i, 0))
             stack_once(0)
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g, stream=gs):
@@ -425,15 +433,12 @@ def main():
         torch.cuda.current_stream().wait_stream(gs)
         kus = ge0.elapsed_time(ge1) * 1e3 / 100
         alg = 16.0 * D * B_PER_GPU          # R x (4D) + W 3 rows (12D) bytes per sample, SURVEY.md §8d
-        fd_roof = {"kernel": "fdsm_stack (Philox direction + L2 norm + [x, x+v, x-v] build, GEMM-padded rows)",
+        fd_roof = {"kernel": "fdsm_stack (Philox direction + L2 norm + [x, x+v, x-v] build; kernels (1)+(2) of the generic mode)",
                    "bound": "hbm", "achieved": alg / (kus * 1e-6) / 1e9, "peak": pk["hbm_gbs"], "unit": "GB/s",
                    "frac": alg / (kus * 1e-6) / 1e9 / pk["hbm_gbs"], "algorithmic_bytes_per_launch": alg,
-                   "avg_launch_us": kus, "in_step_eager_launch_us": savg * 1e3,
+                   "avg_launch_us": kus, "in_step_eager_launch_us": savg * 1e3 if savg else None,
                    "traffic": ncu.get("stack_dram_bytes_per_launch"),
-                   "note": "graph-timed launches on rotating inputs; 38.5 MB of output stay in the 126 MB L2 for the GEMM "
-                           "that follows, so DRAM traffic is below the algorithmic bytes; what bounds the launch is "
-                           "instruction issue (Philox4x32-10 + Box-Muller per float4), hence the compile-time "
-                           "specialisation of this configuration (fd_stack.cu MODE_ENERGY3)"}
+                   "note": "graph-timed launches, rotating inputs (205 MB) AND outputs (154 MB), both larger than L2"}
     if roof is None:
         # generic mode: the dominant kernel of ours is the fused direction+stack build (HBM-bound)
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]

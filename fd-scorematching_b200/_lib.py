@@ -41,6 +41,21 @@ class StackArgs(C.Structure):
     ]
 
 
+class JetArgs(C.Structure):
+    """Mirror of `fdsm_jet_args` (include/fdsm.h)."""
+    _fields_ = [
+        ("x", _f32p), ("ldx", _i64), ("B", _i64),
+        ("dir", _f32p), ("lddir", _i64),
+        ("normalize_dir", _i32), ("dir_scale", _f32),
+        ("seed", _u64), ("offset", _u64), ("row0", _u64),
+        ("offset_dev", C.c_void_p),
+        ("params", _f32p), ("workspace", _f32p),
+        ("c1", _f32), ("scale", _f32), ("mean", _i32),
+        ("loss", _f32p), ("grads", _f32p), ("accumulate", _i32),
+        ("ev_chain_start", C.c_void_p), ("ev_chain_stop", C.c_void_p),
+    ]
+
+
 class GemmArgs(C.Structure):
     """Mirror of `fdsm_gemm_args` (include/fdsm.h)."""
     _fields_ = [
@@ -84,6 +99,9 @@ PROTOTYPES = {
     "fdsm_mlp_prepare": (C.c_int, [C.POINTER(MlpDesc), _i64, _f32p, _f32p, _stream]),
     "fdsm_mlp_forward": (C.c_int, [C.POINTER(MlpDesc), _f32p, _f32p, _i64, _f32p, _f32p, _f32p, _stream]),
     "fdsm_mlp_backward": (C.c_int, [C.POINTER(MlpDesc), _f32p, _f32p, _i64, _f32p, _f32p, _f32p, _f32p, _i32, _stream]),
+    "fdsm_jet_supported": (C.c_int, [C.POINTER(MlpDesc)]),
+    "fdsm_jet_sizes": (C.c_int, [C.POINTER(MlpDesc), _i64, C.POINTER(_i64), C.POINTER(_i64), C.POINTER(_i64)]),
+    "fdsm_jet_fd_ssm": (C.c_int, [C.POINTER(MlpDesc), C.POINTER(JetArgs), _stream]),
     "fdsm_langevin_step": (C.c_int, [_f32p, _i64, _f32p, _i64, _f32p, _i64, _f32p, _i64, _i64, _i64, _f32, _f32, _u64, _u64, _u64,
                                      _stream]),
     "fdsm_ema_update": (C.c_int, [_f32p, _f32p, _i64, _f32, _f32, _stream]),

@@ -20,6 +20,7 @@
 
 #include "tc_gemm_host.cuh"
 #include "fd_combine.cuh"
+#include "fd_chain.cuh"
 
 namespace fdsm {
 namespace mlp {
@@ -757,3 +758,5 @@ extern "C" int fdsm_mlp_backward_fd_dsm(const fdsm_mlp_desc* desc, const float* 
   }
   return mlp::backward_impl(desc, x_hi, x_lo, 2 * B, params, workspace, hg, hl, grads, accumulate, stream);
 }
+
+#include "fd_jet_host.inc"

@@ -17,7 +17,7 @@ import torch
 import torch.nn as nn
 
 from . import _lib, ops
-from ._lib import MlpDesc, check
+from ._lib import JetArgs, MlpDesc, check
 
 ACTS = {"softplus": 1, "nsoftplus": 2, "elu": 3}
 
@@ -77,7 +77,11 @@ class _MlpFunction(torch.autograd.Function):
 
 class FusedEnergyMLP(nn.Module):
     def __init__(self, in_dim, hidden, n_hidden=3, act="nsoftplus", head="quadratic", device="cuda", seed=None, passes=3,
-                 presplit=False):
+                 presplit=False, formulation="auto", jet_passes=2):
+        """formulation of the fused FD-SSM step (`fd_ssm_loss_and_grad` / `fd_ssm_step`): "jet" = the difference-
+        propagating chain kernel (csrc/fd_chain.cuh; hidden <= 223, n_hidden <= 5), "stacked" = the reference's stacked batch
+        [x | x+v | x-v] through the 3xTF32 GEMM launches, "auto" = jet where supported.  `jet_passes`: 2 = weights as TF32
+        hi + lo (default), 1 = weights rounded to TF32.  `passes` / `presplit` configure the stacked path and `net(x)`."""
         super().__init__()
         if act not in ACTS:
             raise ValueError(f"act must be one of {sorted(ACTS)}")
@@ -88,6 +92,14 @@ class FusedEnergyMLP(nn.Module):
         # presplit=True: hi/lo halves are materialised in HBM by the producing kernels (twice the traffic)
         self.presplit = bool(presplit) or passes != 3
         self.desc = MlpDesc(in_dim, hidden, n_hidden, ACTS[act], 1 if head == "quadratic" else 0, passes, int(self.presplit))
+        if formulation not in ("auto", "jet", "stacked"):
+            raise ValueError("formulation must be 'auto', 'jet' or 'stacked'")
+        self.jet_desc = MlpDesc(in_dim, hidden, n_hidden, ACTS[act], 1 if head == "quadratic" else 0, int(jet_passes), 0)
+        jet_ok = bool(_lib.load().fdsm_jet_supported(C.byref(self.jet_desc)))
+        if formulation == "jet" and not jet_ok:
+            raise ValueError("the chain kernel supports hidden <= 223 and n_hidden <= 5")
+        self.formulation = "jet" if (formulation in ("auto", "jet") and jet_ok) else "stacked"
+        self.jet_passes = int(jet_passes)
         self._sizes = {}
         n = self.sizes(0).n_params
         self.flat = nn.Parameter(torch.zeros(n, device=device, dtype=torch.float32))
@@ -176,10 +188,61 @@ class FusedEnergyMLP(nn.Module):
         self._step_state = st
         return st
 
+    def _jet_state(self, B, device):
+        key = ("jet", B, str(device))
+        st = self._states.get(key)
+        if st is None:
+            n, w = C.c_int64(), C.c_int64()
+            offs = (C.c_int64 * (8 + 4 * self.n_hidden))()
+            check(_lib.load().fdsm_jet_sizes(C.byref(self.jet_desc), B, C.byref(n), C.byref(w), offs), "fdsm_jet_sizes")
+            f = dict(device=device, dtype=torch.float32)
+            st = dict(B=B, nrow=3, rows=3 * B, jet=True, offsets=list(offs), ws=torch.zeros(w.value, **f), loss=torch.zeros((), **f),
+                      grad=torch.zeros(n.value, **f), xh=None, xl=None)
+            self._states[key] = st
+        self._step_state = st
+        return st
+
+    def _jet_loss_and_grad(self, x2, eps, scale, u, v, draw, c1, mean, offset_dev):
+        """The same loss and gradient through the difference-propagating chain kernel (fdsm_jet_fd_ssm)."""
+        lib = _lib.load()
+        B, D = x2.shape
+        st = self._jet_state(B, x2.device)
+        x2 = ops._req(x2, "samples")
+        x2, ldx = ops._rows(x2, "samples")
+        a = JetArgs()
+        a.x, a.ldx, a.B = _ptr(x2), ldx, B
+        keep = [x2]
+        d = v if v is not None else u
+        if d is not None:
+            d, ldd = ops._rows(ops._req(d.reshape(B, -1), "direction"), "direction")
+            a.dir, a.lddir = _ptr(d), ldd
+            keep.append(d)
+        a.normalize_dir, a.dir_scale = int(v is None), float(eps if v is None else 1.0)
+        seed, offset, row0 = draw if draw is not None else ops.next_draw()
+        a.seed, a.offset, a.row0 = seed, offset, row0
+        if offset_dev is not None:
+            a.offset_dev = _ptr(offset_dev)
+        a.params, a.workspace = _ptr(self.flat.data), _ptr(st["ws"])
+        a.c1, a.scale, a.mean = float(c1), float(scale), int(mean)
+        a.loss, a.grads, a.accumulate = _ptr(st["loss"]), _ptr(st["grad"]), 0
+        hook = ops.PROFILE_HOOK
+        if hook is not None:   # bench.py: CUDA events around the chain kernel, recorded by the library on the launching stream
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); e1.record()        # creates the underlying cudaEvent_t handles
+            a.ev_chain_start, a.ev_chain_stop = C.c_void_p(e0.cuda_event), C.c_void_p(e1.cuda_event)
+        ops._count(4 + 2 * self.n_hidden)     # prep, inputs, chain, finish + per layer: weight-gradient GEMM and its reduce
+        check(lib.fdsm_jet_fd_ssm(C.byref(self.jet_desc), C.byref(a), _stream()), "fdsm_jet_fd_ssm")
+        if hook is not None:
+            hook.append((e0, e1))
+        st["_keep"] = keep
+        return st["loss"], st["grad"]
+
     def fd_ssm_loss_and_grad(self, x, eps, scale, *, u=None, v=None, draw=None, c1=2.0, mean=True, offset_dev=None):
         """loss = scale * mean_b[(E2-E3)^2/8 - E2 - E3 + c1 E1] on the stacked batch [x, x+v, x-v] and its gradient
         w.r.t. the flat parameters (SSM/losses/efficient_sm.py:47-73 with scale = D/eps^2; DeepEBM/ESM/loss_train.py:
         212-234 with scale = 1/eps^2).  Returns (loss 0-dim tensor, flat gradient); both are persistent buffers."""
+        if self.formulation == "jet":
+            return self._jet_loss_and_grad(x.reshape(x.shape[0], -1), eps, scale, u, v, draw, c1, mean, offset_dev)
         lib = _lib.load()
         x2 = x.reshape(x.shape[0], -1)
         B = x2.shape[0]
@@ -305,7 +368,7 @@ class FusedEnergyMLP(nn.Module):
         scalar, persistent buffer).  The whole step is ONE CUDA-graph replay -- also for world > 1 when `allreduce` is the
         peer-memory kernel (ddp.PeerAllReduce); with the NCCL library collective it is two replays around the all-reduce."""
         x2 = x.reshape(x.shape[0], -1)
-        st = self._state(x2.shape[0], x2.device)
+        st = self._jet_state(x2.shape[0], x2.device) if self.formulation == "jet" else self._state(x2.shape[0], x2.device)
         if "x" not in st:
             st["x"] = torch.empty_like(x2)
         scale = 1.0 / eps ** 2 if scale is None else scale
@@ -391,6 +454,22 @@ class FusedEnergyMLP(nn.Module):
             return None
         ms = sorted(a.elapsed_time(b) for a, b in events)
         avg = sum(ms) / len(ms)
+        if self.formulation == "jet":
+            B, D, H, L = self._step_state["B"], self.in_dim, self.hidden, self.n_hidden
+            fwd = 2.0 * (2 * B * D * H + 3 * B * H * H * (L - 1))          # layer 0 on the 2B rows [x | v], the rest on 3B
+            dgrad = 2.0 * 3 * B * H * H * (L - 1)
+            flops = fwd + dgrad
+            ach = flops / (avg * 1e-3) / 1e12
+            peak = peaks["bf16_tflops"] / 2.0
+            return {"kernel": f"fdsm::jet::chain_kernel (tcgen05 kind::tf32, TMA-fed, weights as TF32 hi+lo = {self.jet_passes} MMA "
+                              f"pass(es); all {L} forward layers + head + combine + {L - 1} dgrad GEMMs in one launch)",
+                    "bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": None,
+                    "peak_kind": f"{peaks_kind} dense bf16 burst / 2 (TF32 kind)", "passes": self.jet_passes,
+                    "executed_tf32_tflops": ach * self.jet_passes, "executed_frac": ach * self.jet_passes / peak,
+                    "algorithmic_flops_per_launch": flops, "avg_launch_us": avg * 1e3, "launches_timed": len(ms),
+                    "stacked_formulation_flops": 2.0 * 3 * B * (D * H + (L - 1) * H * H) + dgrad,
+                    "note": "achieved counts the 2*M*N*K of OUR formulation (layer 0 contracts the 2B rows [x | v]); the "
+                            "reference's stacked evaluation of the same quantities needs stacked_formulation_flops"}
         rows = self._step_state["rows"]
         per_launch_flops = self.forward_flops(rows) / self.n_hidden
         per_launch_s = avg * 1e-3 / self.n_hidden

@@ -86,8 +86,8 @@ class FDSSMTrainer:
             if sig is not None:
                 return self.net.mdsm_fd_step(x, sig, self.sigma02, self.eps, self.loss_coe, allreduce=self._allreduce,
                                              distributed=ddp.is_distributed())
-            return self.net.fd_ssm_step(x, eps=self.eps, allreduce=self._allreduce, distributed=ddp.is_distributed(),
-                                        scale=self.scale)
+            kw = {} if self.scale is None else {"scale": self.scale}
+            return self.net.fd_ssm_step(x, eps=self.eps, allreduce=self._allreduce, distributed=ddp.is_distributed(), **kw)
         self.flat.zero_grad()
         if sig is not None:
             loss = losses.mdsm_fd(self.net, x, sig, self.sigma02, int(x[0].numel()), eps=self.eps, batch_size=B,

@@ -236,6 +236,42 @@ int fdsm_mlp_backward_fd_dsm(const fdsm_mlp_desc* desc, const float* x_hi, const
                              int32_t accumulate, fdsm_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Kernel (3) in difference-propagating form: the whole FD-SSM energy-form loss (a1 / a5 / a7) AND its parameter gradient
+ * for the energy MLPs above in one call -- direction sampling, forward, head + combine, backward.
+ *
+ * Instead of the stacked batch [x | x+v | x-v] the network carries, per sample, (h0, a, b) with h(x+-v) = h0 + b +- a
+ * (a = odd part ~ eps, b = even part ~ eps^2; csrc/fd_jet.cuh): the same three function values the reference evaluates
+ * (DeepEBM/ESM/loss_train.py:222-223, SSM/losses/efficient_sm.py:59-60), with rounding relative to the differences, so
+ * single TF32 operands keep loss and gradient within ~1e-4 of the float64 value where the reference's own fp32 stacked
+ * arithmetic is off by 1e-2 .. 1 at the BASELINE configs.  One launch (csrc/fd_chain.cuh) runs every layer forward, the head,
+ * the per-sample loss and all data-gradient GEMMs for a tile of samples; the weight gradients follow as split-K GEMMs.
+ *   *loss = scale * mean_b|sum_b [ (E+ - E-)^2/8 - (E+ + E- - 2 E0) + (c1 - 2) E0 ]
+ *   grads (+)= dloss/dparams   (flat, the layout of fdsm_mlp_*)
+ * desc->passes: 1 = weights rounded to TF32 (one MMA pass); any other value = weights as TF32 hi + lo (two passes,
+ * default).  desc->presplit is ignored.  Supported: hidden <= 223, n_hidden <= 5 (fdsm_jet_supported).
+ * Deterministic: fixed-order tile, split-K and head reductions.  Graph-capturable (uses internal side streams by
+ * event fork/join).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct fdsm_jet_args {
+  const float* x; int64_t ldx; int64_t B;   /* samples (B, D)                                                          */
+  const float* dir; int64_t lddir;          /* injected direction (B, D) or NULL => Philox stream 0 (as fdsm_stack)     */
+  int32_t normalize_dir; float dir_scale;   /* 1: v = dir/||dir|| * dir_scale ; 0: v = dir as given (dir != NULL)       */
+  uint64_t seed, offset, row0;              /* Philox key / draw counter / global index of local row 0                  */
+  const uint64_t* offset_dev;               /* optional device counter added to `offset` (graph replay)                 */
+  const float* params; float* workspace;    /* flat parameters ; fdsm_jet_sizes() floats, 16-byte aligned                */
+  float c1, scale; int32_t mean;
+  float* loss; float* grads; int32_t accumulate;   /* loss may be NULL                                                  */
+  void* ev_chain_start; void* ev_chain_stop;       /* optional cudaEvent_t pair recorded on `stream` around the chain kernel
+                                                      (measurement: bench.py's roofline of the dominant kernel)         */
+} fdsm_jet_args;
+int fdsm_jet_supported(const fdsm_mlp_desc* desc);
+/* offsets (optional, >= 8 + 4 * n_hidden entries): test view of the workspace -- [0] samples per tile S, [1] padded rows per
+ * stream Bp, [2] npad, [3] kpad0, [4] kpadh, [5] XV offset, [6] passes, [7] tiles, then per layer l: [8+4l] Wt_l,
+ * [9+4l] H_l (l >= 1), [10+4l] dZ_l (float offsets), [11+4l] split-K count of the weight-gradient GEMM. */
+int fdsm_jet_sizes(const fdsm_mlp_desc* desc, int64_t B, int64_t* n_params, int64_t* workspace_floats, int64_t* offsets);
+int fdsm_jet_fd_ssm(const fdsm_mlp_desc* desc, const fdsm_jet_args* args, fdsm_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
  * Optimizer step on the flat parameter vector (the reference's host loop, DeepEBM/train_ssm.py:65-70:
  * clip_grad_norm_(params, clip) then Adam.step()).  Per-step scalars come from device memory so the
  * step replays from one CUDA graph.

@@ -203,3 +203,20 @@ def fd_ssm_jet(net, x, v, scale, c1=2.0, reduce="mean", tf32=False):
     E0, dE, sE = energy_jet(net, x, v, tf32)
     per = dE * dE / 8.0 - sE + (c1 - 2.0) * E0
     return (per.mean() if reduce == "mean" else per.sum()) * scale
+
+
+def mlp_jet_trace(layers, act, x, v, tf32=False):
+    """mlp_jet that also returns, per layer, the pre-activation streams (z0, P, Q) -- with retain_grad() set, so that after
+    a backward their .grad are the (dz0, dP, dQ) the chain kernel stores -- and the outputs (h0, a, b)."""
+    h0, a, b = x, v, None
+    pre, post = [], []
+    for W, bias in layers:
+        z0 = linear(h0, W, bias, tf32)
+        P = linear(a, W, None, tf32)
+        Q = linear(b, W, None, tf32) if b is not None else torch.zeros_like(P, requires_grad=True)
+        for t in (z0, P, Q):
+            t.retain_grad()
+        h0, a, b = act_jet(act, z0, P, Q)
+        pre.append((z0, P, Q))
+        post.append((h0, a, b))
+    return pre, post
