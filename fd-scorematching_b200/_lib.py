@@ -52,7 +52,7 @@ class JetArgs(C.Structure):
         ("params", _f32p), ("workspace", _f32p),
         ("c1", _f32), ("scale", _f32), ("mean", _i32),
         ("loss", _f32p), ("grads", _f32p), ("accumulate", _i32),
-        ("ev_chain_start", C.c_void_p), ("ev_chain_stop", C.c_void_p),
+        ("ev_chain_start", C.c_void_p), ("ev_chain_stop", C.c_void_p), ("trace", C.c_void_p),
     ]
 
 

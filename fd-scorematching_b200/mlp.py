@@ -225,6 +225,8 @@ class FusedEnergyMLP(nn.Module):
         a.params, a.workspace = _ptr(self.flat.data), _ptr(st["ws"])
         a.c1, a.scale, a.mean = float(c1), float(scale), int(mean)
         a.loss, a.grads, a.accumulate = _ptr(st["loss"]), _ptr(st["grad"]), 0
+        if ops.CHAIN_TRACE is not None:      # scripts/chain_trace.py: int64 tensor (tiles, 38) of %globaltimer stamps
+            a.trace = _ptr(ops.CHAIN_TRACE)
         hook = ops.PROFILE_HOOK
         if hook is not None:   # bench.py: CUDA events around the chain kernel, recorded by the library on the launching stream
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

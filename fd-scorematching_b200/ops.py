@@ -16,6 +16,7 @@ from ._lib import ROW_MINUS, ROW_PLUS, ROW_X, StackArgs, check
 LAUNCHES = 0          # kernels launched through the C ABI by this process (bench.py "gpu_launches")
 PROFILE_HOOK = None   # bench.py: list collecting (start, end) CUDA events around the dominant kernel
 PROFILE_HOOK_STACK = None   # same, around the fused direction + stack-build kernel
+CHAIN_TRACE = None          # scripts/chain_trace.py: int64 CUDA tensor receiving the chain kernel's per-CTA phase stamps
 
 
 def _count(n):

@@ -263,11 +263,14 @@ typedef struct fdsm_jet_args {
   float* loss; float* grads; int32_t accumulate;   /* loss may be NULL                                                  */
   void* ev_chain_start; void* ev_chain_stop;       /* optional cudaEvent_t pair recorded on `stream` around the chain kernel
                                                       (measurement: bench.py's roofline of the dominant kernel)         */
+  void* trace;                                     /* optional debug buffer: tiles x 38 uint64 %globaltimer stamps of the chain
+                                                      kernel's phases (scripts/chain_trace.py); NULL in production      */
 } fdsm_jet_args;
 int fdsm_jet_supported(const fdsm_mlp_desc* desc);
 /* offsets (optional, >= 8 + 4 * n_hidden entries): test view of the workspace -- [0] samples per tile S, [1] padded rows per
  * stream Bp, [2] npad, [3] kpad0, [4] kpadh, [5] XV offset, [6] passes, [7] tiles, then per layer l: [8+4l] Wt_l,
- * [9+4l] H_l (l >= 1), [10+4l] dZ_l (float offsets), [11+4l] split-K count of the weight-gradient GEMM. */
+ * [9+4l] H_l (l >= 1; [9] = CTAs per cluster of the chain kernel), [10+4l] dZ_l (float offsets), [11+4l] split-K count of
+ * the weight-gradient GEMM. */
 int fdsm_jet_sizes(const fdsm_mlp_desc* desc, int64_t B, int64_t* n_params, int64_t* workspace_floats, int64_t* offsets);
 int fdsm_jet_fd_ssm(const fdsm_mlp_desc* desc, const fdsm_jet_args* args, fdsm_stream_t stream);
 
