@@ -15,14 +15,21 @@
 // the weight-gradient GEMMs) -- while the epilogue warps are still on block j+1, so after phase 0 the tensor pipe and the
 // weight stream run under the epilogue instead of between epilogues.
 //
-// Weights reach the CTAs by cluster multicast (CL = 1, 2 or 4 CTAs per cluster): every CTA of a cluster walks the same
-// weight stream, so each loads 1/CL of a ring slot and multicasts it to all -- the L2 read traffic of the weight stream,
-// which bounds the un-clustered kernel (every CTA re-reads every W), drops by CL.
+// What bounds the weight stream is the L2 -> SM delivery rate (every CTA walks all weights: ~3 MB per CTA as hi + lo,
+// x 128 CTAs against the chip's ~6300 B/clk L2 throughput), so the weights travel ONCE, as plain fp32: tcgen05 kind::tf32
+// ignores the 13 low mantissa bits, i.e. the raw tile IS the hi operand; once the hi MMAs of a slot have completed, the
+// epilogue warps -- idle during phase 0 -- overwrite the slot IN PLACE with lo = x - trunc(x) and the lo MMAs follow, one
+// k-block behind the hi MMAs.  Later phases stream under the epilogues, where the delivery rate is not the limit and the
+// epilogue warps are busy: there the weights come as two TMA copies, hi and lo (PASSES = 2; PASSES = 1 ships
+// round-to-nearest TF32 weights and issues the hi MMAs only).  With CL > 1 the CTAs of a cluster split each slot's TMA
+// boxes and multicast them.
 //
-// Shared memory: A region NA x 16 KB (NA = ceil32(H+1)/32 k-blocks; the TMA ring of phase 0, then the resident operand)
-// + W ring 3 x 28 KB (one k-block of W_hi or W_lo per slot) + head weights / head-gradient records.  TMEM: one
-// 128 x npad fp32 accumulator.  Warps 0..15 run the epilogues (warp w owns samples w, w+16, ...; lane = column mod 32);
-// warp 16 lane 0 = TMA producer, warp 17 lane 0 = MMA + TMA-store issuer; warp 2 also allocates TMEM.
+// Shared memory: A region NA x (3 S x 128 B) (NA = ceil32(H+1)/32 k-blocks; the TMA ring of phase 0, then the resident
+// operand; the 128-row MMA reads past the 3 S rows of a block into the next one: those accumulator rows are never read)
+// + W ring (nraw x 28 KB, one k-block each) + head weights / head-gradient records.
+// TMEM: one 128 x npad fp32 accumulator.  Warps 0..15 run the epilogues (warp w owns samples w, w+16, ...; lane = column
+// mod 32; two samples at a time for instruction-level parallelism); warp 16 lane 0 = TMA producer, warp 17 lane 0 = MMA +
+// TMA-store issuer; warp 2 also allocates TMEM.
 #pragma once
 #include "fd_jet.cuh"
 
@@ -31,19 +38,21 @@ namespace jet {
 
 constexpr int MAXL = 5;              // hidden layers the chain supports (CUtensorMap budget of the parameter space)
 constexpr int EPI_WARPS = 16, EPI_T = EPI_WARPS * 32;
-constexpr int CT = EPI_T + 64;       // + producer warp + MMA/store warp
-constexpr int WSLOTS = 3, WSLOT_BYTES = 28672;   // 7 boxes of 32 x 32 fp32 (4 KB each)
+constexpr int PROD_WARP = 16, MMA_WARP = 17;
+constexpr int CT = EPI_T + 64;
+constexpr int MAX_RAW = 5, WSLOT_BYTES = 28672;   // slot = 7 boxes of 32 x 32 fp32 (4 KB each)
 constexpr int MAX_NA = 7;            // ceil32(H+1) <= 224
 constexpr int MAX_S = 40, MAX_SPW = (MAX_S + EPI_WARPS - 1) / EPI_WARPS;   // samples per tile / per epilogue warp
-constexpr int A_KB_BYTES = 128 * 128;   // one k-block of the A operand: 128 rows x 32 fp32
 constexpr int HWS = 224;             // head-weight row stride in shared memory
 constexpr int HREC = 3 * HWS + 4;    // one head-gradient record: [gw1 | gw2 | gwq | gb1 gb2 gbq .]
 constexpr int NCOEF = 12;            // per-sample head-gradient coefficients kept in shared memory between the two passes
-constexpr int NBARS = 2 * MAX_NA + 2 * WSLOTS + 1 + MAX_NA;
+constexpr int NBARS = 2 * MAX_NA + 4 * MAX_RAW + 1 + MAX_NA;
+constexpr int CHAIN_MISC_BYTES = (3 * HWS + 4 * HREC + MAX_S * NCOEF) * 4 + NBARS * 8 + 16 + EPI_WARPS * 4 + 64;
 
 struct alignas(64) ChainParams {
   CUtensorMap t_in;                  // [2 Bp x kpad0]  rows [x | v]                          (load, box {32, S})
-  CUtensorMap t_wf[MAXL];            // Wt_l [2 kpad_l x npad] (hi rows, then lo rows), MN-major view (load, box {32, 32})
+  CUtensorMap t_wf[MAXL];            // Wt_l [kpad_0 x npad] fp32 (l = 0) / [2 kpad_l x npad] hi rows, lo rows (l >= 1),
+                                     //   MN-major view                                      (load, box {32, 32})
   CUtensorMap t_wb[MAXL];            // the same memory, K-major view for the dgrad          (load, box {32, 32})
   CUtensorMap t_h[MAXL];             // H_l [3 Bp x kpadh], l = 1..L-1                       (store, box {32, S})
   CUtensorMap t_dz[MAXL];            // dZ_l [3 Bp x npad] (l = 0: 2 Bp rows)                (store, box {32, S})
@@ -52,6 +61,7 @@ struct alignas(64) ChainParams {
   float* loss_part;                  // [tiles]   sum over the tile's samples of the per-sample loss (unscaled)
   float* head_part;                  // [tiles][head_n]  head-parameter gradient of the tile
   int B, Bp, S, H, L, npad, kpad0, kpadh, head;
+  int ablk, nraw;                    // bytes of one A k-block (3 S x 128), slots of the weight ring
   float act_offset;                  // ln 2 for the normalised softplus
   float c1, coef;                    // loss_b = dE^2/8 - sE + (c1 - 2) E0 ; dL/dloss_b = coef (= scale / B or scale)
   unsigned long long* trace;         // debug: per-CTA %globaltimer stamps [tile][TRACE_N] (NULL in production)
@@ -66,19 +76,159 @@ __device__ __forceinline__ void stamp(const ChainParams& p, int slot) {   // epi
   if (p.trace && threadIdx.x == 96) stamp_now(p, slot);
 }
 
-__host__ __device__ constexpr int chain_smem_bytes(int NA) {
-  return 1024 + NA * A_KB_BYTES + WSLOTS * WSLOT_BYTES + 3 * HWS * 4 + 4 * HREC * 4 + MAX_S * NCOEF * 4 + NBARS * 8 + 16 + EPI_WARPS * 4 + 64;
-}
-
-// ---- shared-memory addressing of the A operand (K-major, 128-byte swizzle): element (row, col) ---------------------------
-__device__ __forceinline__ uint32_t a_off(int row, int col) {
-  return (uint32_t)((col >> 5) * A_KB_BYTES + row * 128 + (((((col & 31) >> 2) ^ (row & 7)) << 4) | ((col & 3) << 2)));
+// the last A block's 128-row MMA reads up to 16 KB from its base: the weight rings behind it cover the overrun
+__host__ __device__ constexpr int chain_smem_bytes(int NA, int ablk, int nslots) {
+  return 1024 + NA * ablk + nslots * WSLOT_BYTES + CHAIN_MISC_BYTES;
 }
 
 __device__ __forceinline__ void tma_store_2d(const void* tmap, uint32_t src, int32_t c0, int32_t c1) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
                ::"l"((uint64_t)tmap), "r"(src), "r"(c0), "r"(c1)
                : "memory");
+}
+__device__ __forceinline__ float lds(const uint8_t* p) { return *reinterpret_cast<const float*>(p); }
+__device__ __forceinline__ void sts(uint8_t* p, float v) { *reinterpret_cast<float*>(p) = v; }
+
+// ---- epilogue bodies: TWO samples of one column at once (the epilogues are bound by instruction issue and by the latency of
+// ---- one element's dependency chain; e[n] = address of sample n's h0-stream element in the block, the a / b streams sit
+// ---- `sst` and 2 `sst` bytes further; v1 = the second sample exists -- otherwise e[1] = e[0] and nothing is stored for it).
+// ---- Columns >= H need no masking: their pre-activations are exact zeros (zero-padded weight columns, zero-filled by the
+// ---- dump beyond npad), everything computed from them is finite, and every consumer multiplies it by a zero weight row /
+// ---- column or ignores it -- except column H of a hidden layer's output, the ones column that carries the next bias.
+template <int ACT>
+__device__ __forceinline__ void epi_fwd_hidden(uint8_t* const (&e)[2], bool v1, int sst, bool ones, float off) {
+  float z[2], P[2], Q[2];
+  Jet o[2];
+#pragma unroll
+  for (int n = 0; n < 2; ++n) { z[n] = lds(e[n]); P[n] = lds(e[n] + sst); Q[n] = lds(e[n] + 2 * sst); }
+  jet_fwd_n<ACT, 2>(z, P, Q, off, o);
+#pragma unroll
+  for (int n = 0; n < 2; ++n) {
+    if (n == 0 || v1) {
+      sts(e[n], ones ? 1.f : tf32r(o[n].h0));
+      sts(e[n] + sst, tf32r(o[n].a));
+      sts(e[n] + 2 * sst, tf32r(o[n].b));
+    }
+  }
+}
+
+// last forward layer, pass 1: jets (kept unrounded in place) and the head's nine sums per sample
+template <int ACT>
+__device__ __forceinline__ void epi_head_pass1(uint8_t* const (&e0)[2], bool v1, int sst, int ablk, int NA, int lane, const float* hw,
+                                               bool quad, float off, float (&sum)[2][9]) {
+#pragma unroll
+  for (int n = 0; n < 2; ++n)
+#pragma unroll
+    for (int q = 0; q < 9; ++q) sum[n][q] = 0.f;
+#pragma unroll 1
+  for (int j = 0; j < NA; ++j) {
+    const int c = lane + 32 * j;
+    const float w1 = hw[c], w2 = hw[HWS + c], wq = hw[2 * HWS + c];      // zero beyond H
+    float z[2], P[2], Q[2];
+    Jet o[2];
+#pragma unroll
+    for (int n = 0; n < 2; ++n) {
+      const uint8_t* e = e0[n] + j * ablk;
+      z[n] = lds(e); P[n] = lds(e + sst); Q[n] = lds(e + 2 * sst);
+    }
+    jet_fwd_n<ACT, 2>(z, P, Q, off, o);
+#pragma unroll
+    for (int n = 0; n < 2; ++n) {
+      uint8_t* e = e0[n] + j * ablk;
+      if (n == 0 || v1) { sts(e, o[n].h0); sts(e + sst, o[n].a); sts(e + 2 * sst, o[n].b); }   // for this lane, in pass 2
+      sum[n][0] = fmaf(w1, o[n].h0, sum[n][0]); sum[n][1] = fmaf(w1, o[n].a, sum[n][1]); sum[n][2] = fmaf(w1, o[n].b, sum[n][2]);
+      if (quad) {
+        sum[n][3] = fmaf(w2, o[n].h0, sum[n][3]); sum[n][4] = fmaf(w2, o[n].a, sum[n][4]); sum[n][5] = fmaf(w2, o[n].b, sum[n][5]);
+        sum[n][6] = fmaf(wq, o[n].a * (o[n].b + o[n].h0), sum[n][6]);
+        sum[n][7] = fmaf(wq, fmaf(o[n].b, o[n].b, fmaf(o[n].a, o[n].a, 2.f * o[n].h0 * o[n].b)), sum[n][7]);
+        sum[n][8] = fmaf(wq, o[n].h0 * o[n].h0, sum[n][8]);
+      }
+    }
+  }
+#pragma unroll
+  for (int n = 0; n < 2; ++n)
+#pragma unroll
+    for (int q = 0; q < 9; ++q)
+      if (q < 3 || quad) sum[n][q] = warp_sum(sum[n][q]);
+}
+
+// from the nine sums of a sample: its loss term and the coefficients of the head backward (oracle/jet.py quadratic_head_jet)
+//   cs[0..3] = G1h G1a G1b gd   cs[4..7] = G2h G2a G2b gs   cs[8] = ge
+__device__ __forceinline__ float head_sample(const float (&sum)[9], bool quad, float b1, float b2, float bq, float c1, float cf,
+                                             bool lane0, float* cs, float& gb1, float& gb2, float& gbq) {
+  const float l1 = sum[0] + b1, A1 = sum[1], B1 = sum[2], l2 = sum[3] + b2, A2 = sum[4], B2 = sum[5];
+  float dE, sE, E0;
+  if (quad) {
+    dE = 2.f * (A1 * (l2 + B2) + A2 * (l1 + B1)) + 4.f * sum[6];
+    sE = 2.f * (l1 * B2 + B1 * l2 + B1 * B2 + A1 * A2) + 2.f * sum[7];
+    E0 = fmaf(l1, l2, sum[8]) + bq;
+  } else {
+    dE = 2.f * A1; sE = 2.f * B1; E0 = l1;
+  }
+  const float gd = cf * dE * 0.25f, gs = -cf, ge = cf * (c1 - 2.f);
+  float G1h, G2h, G1a, G2a, G1b, G2b;
+  if (quad) {
+    G1h = 2.f * (gd * A2 + gs * B2) + ge * l2; G2h = 2.f * (gd * A1 + gs * B1) + ge * l1;
+    G1a = 2.f * (gd * (l2 + B2) + gs * A2);     G2a = 2.f * (gd * (l1 + B1) + gs * A1);
+    G1b = 2.f * (gd * A2 + gs * (l2 + B2));     G2b = 2.f * (gd * A1 + gs * (l1 + B1));
+  } else {
+    G1h = ge; G1a = 2.f * gd; G1b = 2.f * gs; G2h = G2a = G2b = 0.f;
+  }
+  gb1 += G1h; gb2 += G2h; gbq += ge;
+  if (lane0) {
+    float4* c4 = reinterpret_cast<float4*>(cs);
+    c4[0] = make_float4(G1h, G1a, G1b, gd);
+    c4[1] = make_float4(G2h, G2a, G2b, gs);
+    c4[2] = make_float4(ge, 0.f, 0.f, 0.f);
+  }
+  return dE * dE * 0.125f - sE + (c1 - 2.f) * E0;
+}
+
+// last forward layer, pass 2, one block: gradient w.r.t. the jets, head-weight gradient terms, activation backward -> dZ
+template <int ACT>
+__device__ __forceinline__ void epi_head_pass2(uint8_t* const (&e)[2], bool v1, int sst, float w1, float w2, float wq,
+                                               const float* const (&cs)[2], bool quad, float off, float& gw1, float& gw2, float& gwq) {
+  Jet o[2];
+  float g0[2], ga[2], gb[2], dz0[2], dP[2], dQ[2];
+#pragma unroll
+  for (int n = 0; n < 2; ++n) {
+    const float4 k1 = reinterpret_cast<const float4*>(cs[n])[0], k2 = reinterpret_cast<const float4*>(cs[n])[1];
+    const float ge = cs[n][8];
+    const float G1h = k1.x, G1a = k1.y, G1b = k1.z, gd = k1.w, G2h = k2.x, G2a = k2.y, G2b = k2.z, gs = k2.w;
+    o[n] = Jet{lds(e[n]), lds(e[n] + sst), lds(e[n] + 2 * sst)};
+    g0[n] = G1h * w1; ga[n] = G1a * w1; gb[n] = G1b * w1;
+    const float use = (n == 0 || v1) ? 1.f : 0.f;      // the stand-in second sample adds nothing to the weight gradients
+    gw1 += use * (G1h * o[n].h0 + G1a * o[n].a + G1b * o[n].b);
+    if (quad) {
+      g0[n] += G2h * w2 + wq * (4.f * gd * o[n].a + 4.f * gs * o[n].b + 2.f * ge * o[n].h0);
+      ga[n] += G2a * w2 + wq * 4.f * (gd * (o[n].b + o[n].h0) + gs * o[n].a);
+      gb[n] += G2b * w2 + wq * 4.f * (gd * o[n].a + gs * (o[n].b + o[n].h0));
+      gw2 += use * (G2h * o[n].h0 + G2a * o[n].a + G2b * o[n].b);
+      gwq += use * (4.f * gd * o[n].a * (o[n].b + o[n].h0) +
+                    2.f * gs * fmaf(o[n].b, o[n].b, fmaf(o[n].a, o[n].a, 2.f * o[n].h0 * o[n].b)) + ge * o[n].h0 * o[n].h0);
+    }
+  }
+  jet_bwd_n<ACT, 2>(o, off, g0, ga, gb, dz0, dP, dQ);
+#pragma unroll
+  for (int n = 0; n < 2; ++n)
+    if (n == 0 || v1) { sts(e[n], tf32r(dz0[n])); sts(e[n] + sst, tf32r(dP[n])); sts(e[n] + 2 * sst, tf32r(dQ[n])); }
+}
+
+// dgrad epilogue, one block: rows hold dL/dH_l as (g0, ga, gb); H_l (hp[n]: the sample's h0 element in HBM / L2; the a / b
+// streams `hstride` floats further) -> dZ_{l-1}
+template <int ACT>
+__device__ __forceinline__ void epi_dgrad(uint8_t* const (&e)[2], bool v1, int sst, const float* const (&hp)[2], long long hstride,
+                                          float off) {
+  Jet o[2];
+  float g0[2], ga[2], gb[2], dz0[2], dP[2], dQ[2];
+#pragma unroll
+  for (int n = 0; n < 2; ++n) o[n] = Jet{__ldcg(hp[n]), __ldcg(hp[n] + hstride), __ldcg(hp[n] + 2 * hstride)};
+#pragma unroll
+  for (int n = 0; n < 2; ++n) { g0[n] = lds(e[n]); ga[n] = lds(e[n] + sst); gb[n] = lds(e[n] + 2 * sst); }
+  jet_bwd_n<ACT, 2>(o, off, g0, ga, gb, dz0, dP, dQ);
+#pragma unroll
+  for (int n = 0; n < 2; ++n)
+    if (n == 0 || v1) { sts(e[n], tf32r(dz0[n])); sts(e[n] + sst, tf32r(dP[n])); sts(e[n] + 2 * sst, tf32r(dQ[n])); }
 }
 
 template <int ACT, int PASSES, int CL>
@@ -88,22 +238,24 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
   uint8_t* gen = smem_raw + (base - raw);
-  const int NA = p.kpadh >> 5;
+  const int NA = p.kpadh >> 5, ablk = p.ablk, nraw = p.nraw;
   const uint32_t a_base = base;
-  const uint32_t w_base = base + NA * A_KB_BYTES;
+  const uint32_t w_base = base + NA * ablk;
   uint8_t* a_gen = gen;
-  uint8_t* w_gen = gen + NA * A_KB_BYTES;
-  float* hw = reinterpret_cast<float*>(w_gen + WSLOTS * WSLOT_BYTES);          // [3][HWS]    head weights
+  uint8_t* w_gen = gen + NA * ablk;
+  float* hw = reinterpret_cast<float*>(w_gen + nraw * WSLOT_BYTES);    // [3][HWS]    head weights
   float* hrec = hw + 3 * HWS;                                                  // [4][HREC]   head-gradient records
   float* coef_s = hrec + 4 * HREC;                                             // [MAX_S][NCOEF]
   uint8_t* bars_gen = reinterpret_cast<uint8_t*>(coef_s + MAX_S * NCOEF);
-  const uint32_t bars = w_base + WSLOTS * WSLOT_BYTES + (3 * HWS + 4 * HREC + MAX_S * NCOEF) * 4;
+  const uint32_t bars = w_base + nraw * WSLOT_BYTES + (3 * HWS + 4 * HREC + MAX_S * NCOEF) * 4;
   auto a_full = [&](int s) { return bars + 8u * s; };
   auto a_empty = [&](int s) { return bars + 8u * (MAX_NA + s); };
   auto w_full = [&](int s) { return bars + 8u * (2 * MAX_NA + s); };
-  auto w_empty = [&](int s) { return bars + 8u * (2 * MAX_NA + WSLOTS + s); };
-  const uint32_t acc_full = bars + 8u * (2 * MAX_NA + 2 * WSLOTS);
-  auto a_ready = [&](int j) { return bars + 8u * (2 * MAX_NA + 2 * WSLOTS + 1 + j); };
+  auto w_empty = [&](int s) { return bars + 8u * (2 * MAX_NA + MAX_RAW + s); };
+  auto hi_done = [&](int s) { return bars + 8u * (2 * MAX_NA + 2 * MAX_RAW + s); };     // the slot's hi MMAs have completed
+  auto lo_full = [&](int s) { return bars + 8u * (2 * MAX_NA + 3 * MAX_RAW + s); };     // the slot now holds lo
+  const uint32_t acc_full = bars + 8u * (2 * MAX_NA + 4 * MAX_RAW);
+  auto a_ready = [&](int j) { return bars + 8u * (2 * MAX_NA + 4 * MAX_RAW + 1 + j); };
   volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(bars_gen + 8 * NBARS);
   float* red = reinterpret_cast<float*>(bars_gen + 8 * NBARS + 16);            // [EPI_WARPS] loss partials
 
@@ -120,13 +272,15 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
   if (p.trace && threadIdx.x == 96) stamp_now(p, 0);
   if (threadIdx.x == 0) {
     for (int s = 0; s < MAX_NA; ++s) { mbar_init(a_full(s), 1); mbar_init(a_empty(s), 1); mbar_init(a_ready(s), EPI_WARPS); }
-    for (int s = 0; s < WSLOTS; ++s) { mbar_init(w_full(s), 1); mbar_init(w_empty(s), CL); }
+    for (int s = 0; s < MAX_RAW; ++s) {
+      mbar_init(w_full(s), 1); mbar_init(w_empty(s), CL); mbar_init(hi_done(s), 1); mbar_init(lo_full(s), EPI_WARPS);
+    }
     mbar_init(acc_full, 2);          // the MMAs' commit + the store thread (earlier TMA stores have left shared memory)
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc(smem_u32((const void*)tmem_ptr_smem), 256);
-  // zero the A region: rows the TMA boxes never touch (the b stream of the input layer, rows >= 3S) must read as zero
-  for (int i = threadIdx.x; i < NA * A_KB_BYTES / 16; i += CT) reinterpret_cast<float4*>(a_gen)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  // zero the A region: rows the TMA boxes never touch (the b stream of the input layer) must read as zero
+  for (int i = threadIdx.x; i < NA * ablk / 16; i += CT) reinterpret_cast<float4*>(a_gen)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   {  // head weights, zero beyond H
     const int nh = p.head ? 3 : 1;
     for (int i = threadIdx.x; i < 3 * HWS; i += CT) {
@@ -142,7 +296,7 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
   const uint32_t tmem_base = *tmem_ptr_smem;
   stamp(p, 1);
 
-  if (warp == EPI_WARPS) {
+  if (warp == PROD_WARP) {
     // ===== TMA producer (one thread): the weight stream of every phase back to back, plus phase 0's A operand ============
     if (lane == 0) {
       int ws = 0; uint32_t wph = 0;
@@ -150,33 +304,35 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
         const bool fwd = g < L;
         const int layer = fwd ? g : 2 * L - 1 - g;
         const int nkb = fwd ? (g == 0 ? nkb0 : NA) : nbx;
-        const int kpad_l = layer == 0 ? p.kpad0 : p.kpadh;
+        const CUtensorMap* tw = fwd ? &p.t_wf[layer] : &p.t_wb[layer];
         for (int kb = 0; kb < nkb; ++kb) {
           if (g == 0) {
             const int as = kb % NA;
-            mbar_wait(a_empty(as), ((kb / NA) & 1) ^ 1u);
+            mbar_wait_parked(a_empty(as), ((kb / NA) & 1) ^ 1u);
             mbar_arrive_expect_tx(a_full(as), (uint32_t)(2 * S * 128));
-            tma_load_2d(a_base + as * A_KB_BYTES, &p.t_in, a_full(as), kb * 32, tile * S);
-            tma_load_2d(a_base + as * A_KB_BYTES + S * 128, &p.t_in, a_full(as), kb * 32, p.Bp + tile * S);
+            tma_load_2d(a_base + as * ablk, &p.t_in, a_full(as), kb * 32, tile * S);
+            tma_load_2d(a_base + as * ablk + S * 128, &p.t_in, a_full(as), kb * 32, p.Bp + tile * S);
           }
-          for (int ps = 0; ps < PASSES; ++ps) {
-            mbar_wait(w_empty(ws), wph ^ 1u);           // every CTA of the cluster has finished reading this slot
+          // phase 0: one slot per k-block (fp32; lo is derived on chip);  later phases with PASSES = 2: hi slot, lo slot
+          const int ncopy = (PASSES == 2 && g > 0) ? 2 : 1;
+          const int kpad_l = layer == 0 ? p.kpad0 : p.kpadh;
+          for (int ps = 0; ps < ncopy; ++ps) {
+            mbar_wait_parked(w_empty(ws), wph ^ 1u);           // every CTA of the cluster has finished with this slot
             mbar_arrive_expect_tx(w_full(ws), (uint32_t)nbx * 4096u);
             const uint32_t dst = w_base + ws * WSLOT_BYTES;
             for (int i = 0; i < nbx; ++i) {
               if (CL > 1 && (uint32_t)(i % CL) != crank) continue;
               // forward (W MN-major: box = 32 outputs x 32 k):  (32 i, k-block);  dgrad (K-major: 32 k x 32 rows): (k-block, 32 i)
               const int c0 = fwd ? 32 * i : 32 * kb, c1 = ps * kpad_l + (fwd ? 32 * kb : 32 * i);
-              const CUtensorMap* tw = fwd ? &p.t_wf[layer] : &p.t_wb[layer];
               if (CL > 1) tma_load_2d_mc(dst + i * 4096, tw, w_full(ws), c0, c1, CMASK);
               else tma_load_2d(dst + i * 4096, tw, w_full(ws), c0, c1);
             }
-            if (++ws == WSLOTS) { ws = 0; wph ^= 1u; }
+            if (++ws == nraw) { ws = 0; wph ^= 1u; }
           }
         }
       }
     }
-  } else if (warp == EPI_WARPS + 1) {
+  } else if (warp == MMA_WARP) {
     // ===== MMA issuer + TMA-store issuer (one thread) =====================================================================
     if (lane == 0) {
       int ws = 0; uint32_t wph = 0;
@@ -187,37 +343,68 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
         if (ge < L - 1) tm = &p.t_h[ge + 1];
         else if (ge == L - 1) { tm = &p.t_dz[L - 1]; nstream = L == 1 ? 2 : 3; }
         else { const int lay = 2 * L - 1 - ge; tm = &p.t_dz[lay - 1]; nstream = lay == 1 ? 2 : 3; }
-        for (int s = 0; s < nstream; ++s) tma_store_2d(tm, a_base + kb * A_KB_BYTES + s * S * 128, kb * 32, s * p.Bp + tile * S);
+        for (int s = 0; s < nstream; ++s) tma_store_2d(tm, a_base + kb * ablk + s * S * 128, kb * 32, s * p.Bp + tile * S);
       };
       for (int g = 0; g < nphase; ++g) {
         const bool fwd = g < L;
         const int nkb = fwd ? (g == 0 ? nkb0 : NA) : nbx;
         const uint32_t idesc = make_idesc_tf32(128, npad, tc::MAJOR_K, fwd ? tc::MAJOR_MN : tc::MAJOR_K);
         const uint32_t b_lbo = fwd ? 4096u : 16u, b_sbo = fwd ? 512u : 1024u, b_step = fwd ? 1024u : 32u, b_lay = fwd ? 1u : 2u;
-        for (int kb = 0; kb < nkb; ++kb) {
-          const int as = g == 0 ? kb % NA : kb;
-          if (g == 0) {
-            mbar_wait(a_full(as), (kb / NA) & 1);
-          } else {
-            mbar_wait(a_ready(kb), (g - 1) & 1);        // the epilogue has finished this k-block of the operand
-            store_block(g - 1, kb);
-          }
-          tc_fence_after();
-          for (int ps = 0; ps < PASSES; ++ps) {
-            mbar_wait(w_full(ws), wph);
-            tc_fence_after();
-            const uint32_t bsl = w_base + ws * WSLOT_BYTES;
+        auto mmas = [&](int as_, int slot, bool first) {
 #pragma unroll
-            for (int k8 = 0; k8 < 4; ++k8) {
-              const uint64_t da = make_smem_desc(a_base + as * A_KB_BYTES + k8 * 32, 16u, 1024u, 2u);
-              const uint64_t db = make_smem_desc(bsl + k8 * b_step, b_lbo, b_sbo, b_lay);
-              mma_tf32_ss(tmem_base, da, db, idesc, (kb > 0 || ps > 0 || k8 > 0) ? 1u : 0u);
-            }
-            if (CL > 1) tc_commit_mc(w_empty(ws), CMASK);
-            else tc_commit(w_empty(ws));
-            if (++ws == WSLOTS) { ws = 0; wph ^= 1u; }
+          for (int k8 = 0; k8 < 4; ++k8) {
+            const uint64_t da = make_smem_desc(a_base + as_ * ablk + k8 * 32, 16u, 1024u, 2u);
+            const uint64_t db = make_smem_desc(w_base + slot * WSLOT_BYTES + k8 * b_step, b_lbo, b_sbo, b_lay);
+            mma_tf32_ss(tmem_base, da, db, idesc, (first && k8 == 0) ? 0u : 1u);
           }
-          if (g == 0) tc_commit(a_empty(as));
+        };
+        auto release = [&](int slot) {
+          if (CL > 1) tc_commit_mc(w_empty(slot), CMASK);
+          else tc_commit(w_empty(slot));
+        };
+        if (g == 0 && PASSES == 2) {
+          // phase 0: the lo MMAs of a k-block run one k-block behind its hi MMAs (the in-place conversion gets that long);
+          // with a single A slot the operand of k-block kb must be released before kb + 1 can land: no lag then
+          const bool lag = NA >= 2;
+          int pws = 0, pas = 0; uint32_t pph = 0;
+          auto lo_mmas = [&]() {
+            mbar_wait_parked(lo_full(pws), pph);
+            tc_fence_after();
+            mmas(pas, pws, false);
+            release(pws);
+            tc_commit(a_empty(pas));
+          };
+          for (int kb = 0; kb < nkb; ++kb) {
+            const int as = kb % NA;
+            mbar_wait_parked(a_full(as), (kb / NA) & 1);
+            mbar_wait_parked(w_full(ws), wph);
+            tc_fence_after();
+            mmas(as, ws, kb == 0);
+            tc_commit(hi_done(ws));
+            if (lag && kb > 0) lo_mmas();
+            pws = ws; pas = as; pph = wph;
+            if (!lag) lo_mmas();
+            if (++ws == nraw) { ws = 0; wph ^= 1u; }
+          }
+          if (lag) lo_mmas();
+        } else {
+          for (int kb = 0; kb < nkb; ++kb) {
+            const int as = g == 0 ? kb % NA : kb;
+            if (g == 0) {
+              mbar_wait_parked(a_full(as), (kb / NA) & 1);
+            } else {
+              mbar_wait_parked(a_ready(kb), (g - 1) & 1);      // the epilogue has finished this k-block of the operand
+              store_block(g - 1, kb);
+            }
+            for (int ps = 0; ps < PASSES; ++ps) {
+              mbar_wait_parked(w_full(ws), wph);
+              tc_fence_after();
+              mmas(as, ws, kb == 0 && ps == 0);
+              release(ws);
+              if (++ws == nraw) { ws = 0; wph ^= 1u; }
+            }
+            if (g == 0) tc_commit(a_empty(as));
+          }
         }
         if (p.trace) stamp_now(p, 5 + 4 * g);            // phase g's MMAs issued
         tc_commit(acc_full);
@@ -235,7 +422,7 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
         mbar_arrive(acc_full);
       }
       for (int kb = 0; kb < nbx; ++kb) {                  // output of the last epilogue (dZ_0, or dZ_{L-1} when L = 1)
-        mbar_wait(a_ready(kb), (nphase - 1) & 1);
+        mbar_wait_parked(a_ready(kb), (nphase - 1) & 1);
         store_block(nphase - 1, kb);
       }
       asm volatile("cp.async.bulk.commit_group;" ::: "memory");
@@ -244,16 +431,40 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
   } else {
     // ===== epilogue warps ==================================================================================================
     const float off = p.act_offset;
-    auto A = [&](int row, int col) -> float& { return *reinterpret_cast<float*>(a_gen + a_off(row, col)); };
+    const int sst = S * 128;                            // byte distance between the h0 / a / b rows of a sample
+    const int spw = (S - warp + EPI_WARPS - 1) / EPI_WARPS;   // samples of this warp: i = warp + 16 k, k < spw (0..3)
+    // element (sample i, column lane + 32 j) of the A region: eb[k] + j * ablk.  S is a multiple of 8, so the three rows of
+    // a sample share the swizzle term (row & 7 = i & 7)
+    auto ebase = [&](int i) { return a_gen + i * 128 + ((((lane >> 2) ^ (i & 7)) << 4) | ((lane & 3) << 2)); };
     auto publish = [&](int j) {      // this warp's part of k-block j is final: visible to the tensor core and the TMA unit
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(a_ready(j));
     };
+    if (PASSES == 2) {
+      // phase 0: these warps have nothing else to do -- they turn every weight slot into its lo part once its hi MMAs are done
+      const int nvec = nbx * 256;                       // float4s of a slot
+      int ws = 0; uint32_t wph = 0;
+      for (int kb = 0; kb < nkb0; ++kb) {
+        mbar_wait_parked(w_full(ws), wph);              // (the TMA's writes, acquired by this thread too)
+        mbar_wait_parked(hi_done(ws), wph);
+        float4* slot = reinterpret_cast<float4*>(w_gen + ws * WSLOT_BYTES);
+        // lo = x - trunc(x): exact in fp32; the tensor core truncates it to TF32 (2^-21 of x)
+        auto lo = [](float x) { return x - __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); };
+        for (int v = threadIdx.x; v < nvec; v += EPI_T) {
+          const float4 x = slot[v];
+          slot[v] = make_float4(lo(x.x), lo(x.y), lo(x.z), lo(x.w));
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(lo_full(ws));
+        if (++ws == nraw) { ws = 0; wph ^= 1u; }
+      }
+    }
     for (int g = 0; g < nphase; ++g) {
       const bool fwd = g < L;
       const int layer = fwd ? g : 2 * L - 1 - g;
-      mbar_wait(acc_full, g & 1);
+      mbar_wait_parked(acc_full, g & 1);
       tc_fence_after();
       stamp(p, 2 + 4 * g);         // accumulator complete
       // -- dump: accumulator rows -> A region (raw pre-activations / data gradients, fp32, swizzled K-major layout) --------
@@ -263,36 +474,36 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
         const int nch = npad >> 3, per = (nch + 3) >> 2;
         const int c0 = part * per, c1 = min(nch, c0 + per);
         const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16);
+        uint8_t* rbase = a_gen + row * 128;
         for (int ch = c0; ch < c1; ++ch) {
           float v[8];
           tmem_ld_32x8(trow + (uint32_t)(ch * 8), v);
           if (row < 3 * S) {
-            const int col = ch * 8;
-            *reinterpret_cast<float4*>(a_gen + a_off(row, col)) = make_float4(v[0], v[1], v[2], v[3]);
-            *reinterpret_cast<float4*>(a_gen + a_off(row, col + 4)) = make_float4(v[4], v[5], v[6], v[7]);
+            uint8_t* bp = rbase + (ch >> 2) * ablk;
+            const int k16 = (ch & 3) * 2;               // 16-byte chunk of the 128-byte row
+            *reinterpret_cast<float4*>(bp + ((k16 ^ (row & 7)) << 4)) = make_float4(v[0], v[1], v[2], v[3]);
+            *reinterpret_cast<float4*>(bp + (((k16 + 1) ^ (row & 7)) << 4)) = make_float4(v[4], v[5], v[6], v[7]);
           }
         }
       }
+      if (warp < 4 && threadIdx.x < 3 * S)            // columns [npad, kpadh): exact zeros (see the epilogue bodies)
+        for (int c = npad; c < p.kpadh; c += 4)
+          *reinterpret_cast<float4*>(a_gen + (c >> 5) * ablk + threadIdx.x * 128 + ((((c & 31) >> 2) ^ (threadIdx.x & 7)) << 4)) =
+              make_float4(0.f, 0.f, 0.f, 0.f);
       tc_fence_before();
       named_bar_sync(1, EPI_T);
       stamp(p, 3 + 4 * g);         // dump done
       if (fwd && g < L - 1) {
         // -- hidden layer: jets, block by block -----------------------------------------------------------------------------
+#pragma unroll 1
         for (int j = 0; j < NA; ++j) {
-          const int c = lane + 32 * j;
-#pragma unroll
-          for (int k = 0; k < MAX_SPW; ++k) {
-            const int i = warp + EPI_WARPS * k;
-            if (i < S) {
-              Jet o = {0.f, 0.f, 0.f};
-              if (c < H) {
-                o = jet_fwd<ACT>(A(i, c), A(S + i, c), A(2 * S + i, c), off);
-                o.h0 = tf32r(o.h0); o.a = tf32r(o.a); o.b = tf32r(o.b);
-              } else if (c == H) {
-                o.h0 = 1.f;             // the ones column: folds the next layer's bias into its GEMM (h0 stream only)
-              }
-              A(i, c) = o.h0; A(S + i, c) = o.a; A(2 * S + i, c) = o.b;
-            }
+          const bool ones = lane + 32 * j == H;
+#pragma unroll 1
+          for (int k0 = 0; k0 < spw; k0 += 2) {
+            const bool v1 = k0 + 1 < spw;
+            uint8_t* e0 = ebase(warp + EPI_WARPS * k0) + j * ablk;
+            uint8_t* e[2] = {e0, v1 ? e0 + EPI_WARPS * 128 : e0};     // 16 rows further: same row & 7, same swizzle term
+            epi_fwd_hidden<ACT>(e, v1, sst, ones, off);
           }
           publish(j);
         }
@@ -301,105 +512,53 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
         const bool quad = p.head != 0;
         const float b1 = __ldg(p.head_w + H), b2 = quad ? __ldg(p.head_w + 2 * H + 1) : 0.f, bq = quad ? __ldg(p.head_w + 3 * H + 2) : 0.f;
         float gb1 = 0.f, gb2 = 0.f, gbq = 0.f, loss_acc = 0.f;
-        // pass 1, sample by sample: jets (kept unrounded in place), the head's nine sums, the per-sample coefficients
-        for (int i = warp; i < S; i += EPI_WARPS) {
-          float l1 = 0.f, l2 = 0.f, A1 = 0.f, A2 = 0.f, B1 = 0.f, B2 = 0.f, qha = 0.f, qs = 0.f, q0 = 0.f;
-          for (int j = 0; j < NA; ++j) {
-            const int c = lane + 32 * j;
-            Jet o = {0.f, 0.f, 0.f};
-            if (c < H) o = jet_fwd<ACT>(A(i, c), A(S + i, c), A(2 * S + i, c), off);
-            A(i, c) = o.h0; A(S + i, c) = o.a; A(2 * S + i, c) = o.b;
-            const float w1 = hw[c], w2 = hw[HWS + c], wq = hw[2 * HWS + c];
-            l1 = fmaf(w1, o.h0, l1); A1 = fmaf(w1, o.a, A1); B1 = fmaf(w1, o.b, B1);
-            if (quad) {
-              l2 = fmaf(w2, o.h0, l2); A2 = fmaf(w2, o.a, A2); B2 = fmaf(w2, o.b, B2);
-              qha = fmaf(wq, o.a * (o.b + o.h0), qha);
-              qs = fmaf(wq, fmaf(o.b, o.b, fmaf(o.a, o.a, 2.f * o.h0 * o.b)), qs);
-              q0 = fmaf(wq, o.h0 * o.h0, q0);
-            }
-          }
-          l1 = warp_sum(l1); A1 = warp_sum(A1); B1 = warp_sum(B1);
-          if (quad) {
-            l2 = warp_sum(l2); A2 = warp_sum(A2); B2 = warp_sum(B2);
-            qha = warp_sum(qha); qs = warp_sum(qs); q0 = warp_sum(q0);
-          }
-          l1 += b1; l2 += b2;
-          float dE, sE, E0;
-          if (quad) {
-            dE = 2.f * (A1 * (l2 + B2) + A2 * (l1 + B1)) + 4.f * qha;
-            sE = 2.f * (l1 * B2 + B1 * l2 + B1 * B2 + A1 * A2) + 2.f * qs;
-            E0 = fmaf(l1, l2, q0) + bq;
-          } else {
-            dE = 2.f * A1; sE = 2.f * B1; E0 = l1;
-          }
+        auto sample_done = [&](const float (&sum)[9], int i) {
           const bool valid = tile * S + i < p.B;
-          const float cf = valid ? p.coef : 0.f;
-          if (valid) loss_acc += dE * dE * 0.125f - sE + (p.c1 - 2.f) * E0;
-          const float gd = cf * dE * 0.25f, gs = -cf, ge = cf * (p.c1 - 2.f);
-          // coefficients of w1 / w2 in dL/dh0, dL/da, dL/db (quadratic head) -- see oracle/jet.py quadratic_head_jet
-          float G1h, G2h, G1a, G2a, G1b, G2b;
-          if (quad) {
-            G1h = 2.f * (gd * A2 + gs * B2) + ge * l2; G2h = 2.f * (gd * A1 + gs * B1) + ge * l1;
-            G1a = 2.f * (gd * (l2 + B2) + gs * A2);     G2a = 2.f * (gd * (l1 + B1) + gs * A1);
-            G1b = 2.f * (gd * A2 + gs * (l2 + B2));     G2b = 2.f * (gd * A1 + gs * (l1 + B1));
-          } else {
-            G1h = ge; G1a = 2.f * gd; G1b = 2.f * gs; G2h = G2a = G2b = 0.f;
-          }
-          gb1 += G1h; gb2 += G2h; gbq += ge;
-          if (lane == 0) {
-            float4* cs = reinterpret_cast<float4*>(coef_s + i * NCOEF);
-            cs[0] = make_float4(G1h, G1a, G1b, gd);
-            cs[1] = make_float4(G2h, G2a, G2b, gs);
-            cs[2] = make_float4(ge, 0.f, 0.f, 0.f);
-          }
+          const float l = head_sample(sum, quad, b1, b2, bq, p.c1, valid ? p.coef : 0.f, lane == 0, coef_s + i * NCOEF, gb1, gb2, gbq);
+          if (valid) loss_acc += l;
+        };
+#pragma unroll 1
+        for (int k0 = 0; k0 < spw; k0 += 2) {
+          const bool v1 = k0 + 1 < spw;
+          const int i0 = warp + EPI_WARPS * k0;
+          uint8_t* e0 = ebase(i0);
+          uint8_t* e[2] = {e0, v1 ? e0 + EPI_WARPS * 128 : e0};
+          float sum[2][9];
+          epi_head_pass1<ACT>(e, v1, sst, ablk, NA, lane, hw, quad, off, sum);
+          sample_done(sum[0], i0);
+          if (v1) sample_done(sum[1], i0 + EPI_WARPS);
         }
         __syncwarp();
-        // pass 2, block by block: gradient w.r.t. the jets, head-weight gradients, activation backward
+        // pass 2, block by block (the per-column head-weight sums go to a runtime-indexed, i.e. local-memory, array)
         float gw1[MAX_NA], gw2[MAX_NA], gwq[MAX_NA];
-#pragma unroll
-        for (int j = 0; j < MAX_NA; ++j) {
-          gw1[j] = gw2[j] = gwq[j] = 0.f;
-          if (j < NA) {
-            const int c = lane + 32 * j;
-            const float w1 = hw[c], w2 = hw[HWS + c], wq = hw[2 * HWS + c];
-#pragma unroll
-            for (int k = 0; k < MAX_SPW; ++k) {
-              const int i = warp + EPI_WARPS * k;
-              if (i < S) {
-                const float4* cs = reinterpret_cast<const float4*>(coef_s + i * NCOEF);
-                const float4 k1 = cs[0], k2 = cs[1];
-                const float G1h = k1.x, G1a = k1.y, G1b = k1.z, gd = k1.w, G2h = k2.x, G2a = k2.y, G2b = k2.z, gs = k2.w;
-                const float ge = coef_s[i * NCOEF + 8];
-                const Jet o = {A(i, c), A(S + i, c), A(2 * S + i, c)};
-                float g0 = G1h * w1, ga = G1a * w1, gb = G1b * w1;
-                gw1[j] += G1h * o.h0 + G1a * o.a + G1b * o.b;
-                if (quad) {
-                  g0 += G2h * w2 + wq * (4.f * gd * o.a + 4.f * gs * o.b + 2.f * ge * o.h0);
-                  ga += G2a * w2 + wq * 4.f * (gd * (o.b + o.h0) + gs * o.a);
-                  gb += G2b * w2 + wq * 4.f * (gd * o.a + gs * (o.b + o.h0));
-                  gw2[j] += G2h * o.h0 + G2a * o.a + G2b * o.b;
-                  gwq[j] += 4.f * gd * o.a * (o.b + o.h0) + 2.f * gs * fmaf(o.b, o.b, fmaf(o.a, o.a, 2.f * o.h0 * o.b)) + ge * o.h0 * o.h0;
-                }
-                float dz0 = 0.f, dP = 0.f, dQ = 0.f;
-                if (c < H) jet_bwd<ACT>(o, off, g0, ga, gb, dz0, dP, dQ);
-                A(i, c) = tf32r(dz0); A(S + i, c) = tf32r(dP); A(2 * S + i, c) = tf32r(dQ);
-              }
-            }
-            publish(j);
+#pragma unroll 1
+        for (int j = 0; j < NA; ++j) {
+          const int c = lane + 32 * j;
+          const float w1 = hw[c], w2 = hw[HWS + c], wq = hw[2 * HWS + c];
+          float s1 = 0.f, s2 = 0.f, sq = 0.f;
+#pragma unroll 1
+          for (int k0 = 0; k0 < spw; k0 += 2) {
+            const bool v1 = k0 + 1 < spw;
+            const int i0 = warp + EPI_WARPS * k0;
+            uint8_t* e0 = ebase(i0) + j * ablk;
+            uint8_t* e[2] = {e0, v1 ? e0 + EPI_WARPS * 128 : e0};
+            const float* c0 = coef_s + i0 * NCOEF;
+            const float* cs[2] = {c0, v1 ? c0 + EPI_WARPS * NCOEF : c0};
+            epi_head_pass2<ACT>(e, v1, sst, w1, w2, wq, cs, quad, off, s1, s2, sq);
           }
+          gw1[j] = s1; gw2[j] = s2; gwq[j] = sq;
+          publish(j);
         }
         // tile sums in a fixed order: four rounds of four warps add their partial sums into record (warp & 3)
         if (lane == 0) red[warp] = loss_acc;
         for (int r = 0; r < EPI_WARPS / 4; ++r) {
           if ((warp >> 2) == r) {
             float* rec = hrec + (warp & 3) * HREC;
-#pragma unroll
-            for (int j = 0; j < MAX_NA; ++j) {
-              if (j < NA) {
-                const int c = lane + 32 * j;
-                if (r == 0) { rec[c] = gw1[j]; rec[HWS + c] = gw2[j]; rec[2 * HWS + c] = gwq[j]; }
-                else { rec[c] += gw1[j]; rec[HWS + c] += gw2[j]; rec[2 * HWS + c] += gwq[j]; }
-              }
+#pragma unroll 1
+            for (int j = 0; j < NA; ++j) {
+              const int c = lane + 32 * j;
+              if (r == 0) { rec[c] = gw1[j]; rec[HWS + c] = gw2[j]; rec[2 * HWS + c] = gwq[j]; }
+              else { rec[c] += gw1[j]; rec[HWS + c] += gw2[j]; rec[2 * HWS + c] += gwq[j]; }
             }
             if (lane == 0) {
               if (r == 0) { rec[3 * HWS] = gb1; rec[3 * HWS + 1] = gb2; rec[3 * HWS + 2] = gbq; }
@@ -422,28 +581,19 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
         }
       } else {
         // -- dgrad epilogue of layer `layer`: rows hold dL/dH_layer as (g0, ga, gb); H_layer comes back from L2 --------------
-        const float* hsrc = p.h[layer];
-        const long long ldh = p.kpadh, sstride = (long long)p.Bp * ldh;
+        const long long ldh = p.kpadh, hstride = (long long)p.Bp * ldh;
+        const float* hcol = p.h[layer] + (long long)(tile * S) * ldh + lane;
+#pragma unroll 1
         for (int j = 0; j < NA; ++j) {
-          const int c = lane + 32 * j;
-          Jet o[MAX_SPW];
-#pragma unroll
-          for (int k = 0; k < MAX_SPW; ++k) {
-            const int i = warp + EPI_WARPS * k;
-            o[k] = Jet{0.f, 0.f, 0.f};
-            if (i < S && c < H) {
-              const float* hp = hsrc + (long long)(tile * S + i) * ldh + c;
-              o[k] = Jet{__ldcg(hp), __ldcg(hp + sstride), __ldcg(hp + 2 * sstride)};
-            }
-          }
-#pragma unroll
-          for (int k = 0; k < MAX_SPW; ++k) {
-            const int i = warp + EPI_WARPS * k;
-            if (i < S) {
-              float dz0 = 0.f, dP = 0.f, dQ = 0.f;
-              if (c < H) jet_bwd<ACT>(o[k], off, A(i, c), A(S + i, c), A(2 * S + i, c), dz0, dP, dQ);
-              A(i, c) = tf32r(dz0); A(S + i, c) = tf32r(dP); A(2 * S + i, c) = tf32r(dQ);
-            }
+#pragma unroll 1
+          for (int k0 = 0; k0 < spw; k0 += 2) {
+            const bool v1 = k0 + 1 < spw;
+            const int i0 = warp + EPI_WARPS * k0;
+            uint8_t* e0 = ebase(i0) + j * ablk;
+            uint8_t* e[2] = {e0, v1 ? e0 + EPI_WARPS * 128 : e0};
+            const float* h0 = hcol + i0 * ldh + 32 * j;
+            const float* hp[2] = {h0, v1 ? h0 + EPI_WARPS * ldh : h0};
+            epi_dgrad<ACT>(e, v1, sst, hp, hstride, off);
           }
           publish(j);
         }

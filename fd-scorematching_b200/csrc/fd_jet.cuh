@@ -33,27 +33,30 @@ __device__ __forceinline__ float lg2a(float x) {
   asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
-// 1/d with one Newton step on the MUFU seed (relative error ~1e-7)
-__device__ __forceinline__ float rcp_n(float d) {
+// 1/d: the MUFU reciprocal (relative error <= 2^-23)
+__device__ __forceinline__ float rcp_a(float d) {
   float r;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d));
-  return fmaf(fmaf(-d, r, 1.f), r, r);
+  return r;
 }
-// e^x - 1: degree-7 Taylor for |x| <= 0.35 (relative error < 2e-8), MUFU exponential minus one beyond (< 1e-6 there)
-__device__ __forceinline__ float expm1_j(float x) {
+// e^x - 1 for |x| <= SMALL: degree-7 Taylor (relative error < 1e-8 on that range); no MUFU
+constexpr float SMALL = 0.25f;
+__device__ __forceinline__ float expm1_s(float x) {
   float p = 1.984127e-4f;
   p = fmaf(p, x, 1.3888889e-3f);
   p = fmaf(p, x, 8.3333333e-3f);
   p = fmaf(p, x, 4.1666667e-2f);
   p = fmaf(p, x, 1.6666667e-1f);
   p = fmaf(p, x, 0.5f);
-  p = fmaf(p * x, x, x);
-  const float e = ex2a(x * LOG2E) - 1.f;
-  return fabsf(x) <= 0.35f ? p : e;
+  return fmaf(p * x, x, x);
 }
-// log(1 + t), t > -1: 2 atanh(t / (2 + t)) as an odd polynomial for t in [-0.5, 1] (relative error < 1e-7), MUFU beyond
-__device__ __forceinline__ float log1p_j(float t) {
-  const float s = t * rcp_n(2.f + t);
+// e^x - 1, any x: the polynomial where it holds, MUFU exponential minus one beyond (< 1e-6 there)
+__device__ __forceinline__ float expm1_j(float x) {
+  return fabsf(x) <= 0.35f ? expm1_s(x) : ex2a(x * LOG2E) - 1.f;
+}
+// log(1 + n/d) = 2 atanh(n / (2d + n)) as an odd polynomial: relative error < 1e-7 for n/d in [-0.55, 1.1] (|s| <= 0.36)
+__device__ __forceinline__ float log1p_ratio(float n, float d) {
+  const float s = n * rcp_a(fmaf(2.f, d, n));
   const float u = s * s;
   float q = 0.076923077f;
   q = fmaf(q, u, 0.090909091f);
@@ -62,9 +65,11 @@ __device__ __forceinline__ float log1p_j(float t) {
   q = fmaf(q, u, 0.2f);
   q = fmaf(q, u, 0.33333334f);
   const float s2 = s + s;
-  const float poly = fmaf(s2 * u, q, s2);
-  const float big = lg2a(1.f + t) * LN2;
-  return (t >= -0.5f && t <= 1.f) ? poly : big;
+  return fmaf(s2 * u, q, s2);
+}
+// log(1 + t), any t > -1
+__device__ __forceinline__ float log1p_j(float t) {
+  return (t >= -0.5f && t <= 1.f) ? log1p_ratio(t, 1.f) : lg2a(1.f + t) * LN2;
 }
 __device__ __forceinline__ float tf32r(float x) { return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u); }
 
@@ -72,10 +77,11 @@ struct Jet { float h0, a, b; };
 
 // quantities of one small argument d shared by the closed forms: expm1(d), expm1(-d), sinh d, cosh d - 1
 struct Hyp { float em, emn, sinh, coshm1; };
+template <bool SMALL_ARG>
 __device__ __forceinline__ Hyp hyp(float d) {
   Hyp r;
-  r.em = expm1_j(d);
-  const float inv = rcp_n(1.f + r.em);     // e^-d
+  r.em = SMALL_ARG ? expm1_s(d) : expm1_j(d);
+  const float inv = rcp_a(1.f + r.em);     // e^-d
   r.emn = -r.em * inv;
   r.sinh = 0.5f * (r.em - r.emn);          // opposite signs: no cancellation
   r.coshm1 = 0.5f * r.em * r.em * inv;     // (e^d - 1)^2 / (2 e^d)
@@ -92,29 +98,37 @@ enum : int { JACT_SOFTPLUS = 0, JACT_ELU = 1 };
 __device__ __forceinline__ float softplus_j(float z) {
   return fmaxf(z, 0.f) + log1p_j(ex2a(-fabsf(z) * LOG2E));
 }
-__device__ __forceinline__ Jet softplus_jet_fwd(float z0, float P, float Q, float offset) {
-  if (fmaxf(fabsf(P), fabsf(Q)) > 0.5f) {
-    // a perturbation response this large (eps far beyond the reference's 0.01 .. 0.1, or exploding weights) leaves the
-    // regime the closed forms are conditioned for: the three softplus values are O(1) apart, combine them directly
-    Jet o;
-    const float s0 = softplus_j(z0), sp = softplus_j(z0 + Q + P), sm = softplus_j(z0 + Q - P);
-    o.h0 = s0 - offset;
-    o.a = 0.5f * (sp - sm);
-    o.b = 0.5f * ((sp - s0) + (sm - s0));
-    return o;
-  }
+// A perturbation response beyond SMALL (eps far above the reference's 0.01 .. 0.1, or exploding weights) leaves the
+// regime the closed forms are conditioned for: the three softplus values are O(1) apart, combine them directly.
+// Out of line: rare, and the epilogue loops must stay small enough for the instruction cache.
+__device__ __noinline__ void softplus_jet_fwd_large(float z0, float P, float Q, float offset, Jet* out) {
+  const float s0 = softplus_j(z0), sp = softplus_j(z0 + Q + P), sm = softplus_j(z0 + Q - P);
+  out->h0 = s0 - offset;
+  out->a = 0.5f * (sp - sm);
+  out->b = 0.5f * ((sp - s0) + (sm - s0));
+}
+// main path: |P|, |Q| <= SMALL, every expm1 / log1p below is a short polynomial (6 MUFU operations in all)
+__device__ __forceinline__ Jet softplus_jet_fwd_small(float z0, float P, float Q, float offset) {
   const float t = ex2a(-fabsf(z0) * LOG2E);          // e^-|z0|
-  const float r = rcp_n(1.f + t);
+  const float r = rcp_a(1.f + t);
   const float s0 = z0 >= 0.f ? r : t * r, e0 = z0 >= 0.f ? t * r : r;
   Jet o;
-  o.h0 = fmaxf(z0, 0.f) + log1p_j(t) - offset;
-  const Hyp hp = hyp(P);
-  const float emq = expm1_j(Q), eq = 1.f + emq;
+  o.h0 = fmaf(lg2a(1.f + t), LN2, fmaxf(z0, 0.f)) - offset;
+  const Hyp hp = hyp<true>(P);
+  const float emq = expm1_s(Q), eq = 1.f + emq;
   const float em = hp.emn + emq + hp.emn * emq;      // expm1(Q - P)
-  o.a = 0.5f * log1p_j(2.f * s0 * eq * hp.sinh * rcp_n(1.f + s0 * em));
+  o.a = 0.5f * log1p_ratio(2.f * s0 * eq * hp.sinh, fmaf(s0, em, 1.f));
   const float S = 2.f * fmaf(emq, 1.f + hp.coshm1, hp.coshm1);
-  o.b = 0.5f * log1p_j(s0 * fmaf(e0, S, s0 * emq * (2.f + emq)));
+  o.b = 0.5f * log1p_ratio(s0 * fmaf(e0, S, s0 * emq * (2.f + emq)), 1.f);
   return o;
+}
+__device__ __forceinline__ Jet softplus_jet_fwd(float z0, float P, float Q, float offset) {
+  if (fmaxf(fabsf(P), fabsf(Q)) > SMALL) {
+    Jet o;
+    softplus_jet_fwd_large(z0, P, Q, offset, &o);
+    return o;
+  }
+  return softplus_jet_fwd_small(z0, P, Q, offset);
 }
 // backward from the OUTPUTS: softplus(z+-) = sp0 + b +- a and sigmoid = 1 - exp(-softplus), e0 = exp(-sp0):
 //   S1 = (s'(z+) - s'(z-))/2 = e0 e^-b sinh a     S2 = (s'(z+) + s'(z-))/2 - s'(z0) = -e0 (expm1(-b) cosh a + cosh a - 1)
@@ -126,38 +140,50 @@ __device__ __forceinline__ void jet_bwd_apply(float d0, float S1, float S2, floa
   dP = fmaf(Sm, ga, S1 * gb);
   dQ = fmaf(Sm, gb, S1 * ga);
 }
+__device__ __noinline__ void softplus_jet_bwd_large(float sp0, float e0, float a, float b, float* s0, float* S1, float* S2) {
+  *s0 = -expm1_j(-sp0);
+  const Hyp ha = hyp<false>(a);
+  const float emb = expm1_j(-b);
+  *S1 = e0 * (1.f + emb) * ha.sinh;
+  *S2 = -e0 * fmaf(emb, 1.f + ha.coshm1, ha.coshm1);
+}
+__device__ __forceinline__ void softplus_jet_bwd_small(const Jet& o, float offset, float g0, float ga, float gb, float& dz0,
+                                                       float& dP, float& dQ) {
+  const float e0 = ex2a(-(o.h0 + offset) * LOG2E);
+  const Hyp ha = hyp<true>(o.a);
+  const float emb = expm1_s(-o.b);
+  jet_bwd_apply(1.f - e0, e0 * (1.f + emb) * ha.sinh, -e0 * fmaf(emb, 1.f + ha.coshm1, ha.coshm1), g0, ga, gb, dz0, dP, dQ);
+}
 __device__ __forceinline__ void softplus_jet_bwd(const Jet& o, float offset, float g0, float ga, float gb, float& dz0, float& dP,
                                                  float& dQ) {
-  const float sp0 = o.h0 + offset;
-  const float e0 = ex2a(-sp0 * LOG2E);
-  const float s0 = -expm1_j(-sp0);
-  const Hyp ha = hyp(o.a);
-  const float emb = expm1_j(-o.b);
-  const float S1 = e0 * (1.f + emb) * ha.sinh;
-  const float S2 = -e0 * fmaf(emb, 1.f + ha.coshm1, ha.coshm1);
-  jet_bwd_apply(s0, S1, S2, g0, ga, gb, dz0, dP, dQ);
+  if (fmaxf(fabsf(o.a), fabsf(o.b)) <= SMALL) {       // always, when the forward took its main path
+    softplus_jet_bwd_small(o, offset, g0, ga, gb, dz0, dP, dQ);
+  } else {
+    const float sp0 = o.h0 + offset;
+    float s0, S1, S2;
+    softplus_jet_bwd_large(sp0, ex2a(-sp0 * LOG2E), o.a, o.b, &s0, &S1, &S2);
+    jet_bwd_apply(s0, S1, S2, g0, ga, gb, dz0, dP, dQ);
+  }
 }
 
 // ---- ELU (alpha = 1) --------------------------------------------------------------------------------------------------------
 // all three arguments in the linear region: a = P, b = Q exactly; all three in the exponential region:
 // a = e^{z0} e^Q sinh P, b = e^{z0} (expm1(Q) cosh P + cosh P - 1); otherwise the one-sided differences
 // elu(z0 + d) - elu(z0) (each cancellation-free) are combined directly.
-__device__ __forceinline__ Jet elu_jet_fwd(float z0, float P, float Q) {
+__device__ __noinline__ void elu_jet_fwd_large(float z0, float zp, float zm, Jet* out) {
+  const float e0 = z0 > 0.f ? z0 : expm1_j(z0), ep = zp > 0.f ? zp : expm1_j(zp), em = zm > 0.f ? zm : expm1_j(zm);
+  out->h0 = e0;
+  out->a = 0.5f * (ep - em);
+  out->b = 0.5f * ((ep - e0) + (em - e0));
+}
+__device__ __forceinline__ Jet elu_jet_fwd_small(float z0, float P, float Q) {
   const float zp = z0 + Q + P, zm = z0 + Q - P;
-  if (fmaxf(fabsf(P), fabsf(Q)) > 0.5f) {             // see softplus_jet_fwd
-    Jet o;
-    const float e0 = z0 > 0.f ? z0 : expm1_j(z0), ep = zp > 0.f ? zp : expm1_j(zp), em = zm > 0.f ? zm : expm1_j(zm);
-    o.h0 = e0;
-    o.a = 0.5f * (ep - em);
-    o.b = 0.5f * ((ep - e0) + (em - e0));
-    return o;
-  }
   const float em0 = expm1_j(fminf(z0, 0.f));          // elu(z0) where z0 <= 0
   const float e = 1.f + em0;                          // e^{min(z0, 0)}
   Jet o;
   o.h0 = z0 > 0.f ? z0 : em0;
-  const Hyp hp = hyp(P);
-  const float emq = expm1_j(Q), eq = 1.f + emq;
+  const Hyp hp = hyp<true>(P);
+  const float emq = expm1_s(Q), eq = 1.f + emq;
   const float ep = hp.em + emq + hp.em * emq, em = hp.emn + emq + hp.emn * emq;   // expm1(Q +- P)
   const bool pos = z0 > 0.f && zp > 0.f && zm > 0.f, neg = z0 <= 0.f && zp <= 0.f && zm <= 0.f;
   // one-sided differences for the mixed case
@@ -170,6 +196,14 @@ __device__ __forceinline__ Jet elu_jet_fwd(float z0, float P, float Q) {
   o.a = pos ? P : (neg ? e * eq * hp.sinh : 0.5f * (dp - dm));
   o.b = pos ? Q : (neg ? e * fmaf(emq, 1.f + hp.coshm1, hp.coshm1) : 0.5f * (dp + dm));
   return o;
+}
+__device__ __forceinline__ Jet elu_jet_fwd(float z0, float P, float Q) {
+  if (fmaxf(fabsf(P), fabsf(Q)) > SMALL) {            // see softplus_jet_fwd_large
+    Jet o;
+    elu_jet_fwd_large(z0, z0 + Q + P, z0 + Q - P, &o);
+    return o;
+  }
+  return elu_jet_fwd_small(z0, P, Q);
 }
 __device__ __forceinline__ void elu_jet_bwd(const Jet& o, float g0, float ga, float gb, float& dz0, float& dP, float& dQ) {
   const float hp = o.h0 + o.b + o.a, hm = o.h0 + o.b - o.a;
@@ -190,6 +224,55 @@ template <int ACT>
 __device__ __forceinline__ void jet_bwd(const Jet& o, float offset, float g0, float ga, float gb, float& dz0, float& dP, float& dQ) {
   if constexpr (ACT == JACT_ELU) elu_jet_bwd(o, g0, ga, gb, dz0, dP, dQ);
   else softplus_jet_bwd(o, offset, g0, ga, gb, dz0, dP, dQ);
+}
+
+// out-of-line single-element versions for the rare mixed case below (keeps the epilogue loops small)
+template <int ACT>
+__device__ __noinline__ void jet_fwd_any(float z0, float P, float Q, float offset, Jet* o) { *o = jet_fwd<ACT>(z0, P, Q, offset); }
+__device__ __noinline__ void softplus_jet_bwd_any(const Jet* o, float offset, float g0, float ga, float gb, float* d) {
+  softplus_jet_bwd(*o, offset, g0, ga, gb, d[0], d[1], d[2]);
+}
+
+// N independent elements at once: one test for the main path, then N straight-line evaluations the compiler can interleave
+// (the epilogues are latency-bound on a single element's dependency chain)
+template <int ACT, int N>
+__device__ __forceinline__ void jet_fwd_n(const float (&z0)[N], const float (&P)[N], const float (&Q)[N], float offset, Jet (&o)[N]) {
+  float m = 0.f;
+#pragma unroll
+  for (int n = 0; n < N; ++n) m = fmaxf(m, fmaxf(fabsf(P[n]), fabsf(Q[n])));
+  if (m <= SMALL) {
+#pragma unroll
+    for (int n = 0; n < N; ++n) {
+      if constexpr (ACT == JACT_ELU) o[n] = elu_jet_fwd_small(z0[n], P[n], Q[n]);
+      else o[n] = softplus_jet_fwd_small(z0[n], P[n], Q[n], offset);
+    }
+  } else {      // (fully unrolled as well: a runtime index would push the arrays into local memory on the main path too)
+#pragma unroll
+    for (int n = 0; n < N; ++n) jet_fwd_any<ACT>(z0[n], P[n], Q[n], offset, &o[n]);
+  }
+}
+template <int ACT, int N>
+__device__ __forceinline__ void jet_bwd_n(const Jet (&o)[N], float offset, const float (&g0)[N], const float (&ga)[N],
+                                          const float (&gb)[N], float (&dz0)[N], float (&dP)[N], float (&dQ)[N]) {
+  if constexpr (ACT == JACT_ELU) {
+#pragma unroll
+    for (int n = 0; n < N; ++n) elu_jet_bwd(o[n], g0[n], ga[n], gb[n], dz0[n], dP[n], dQ[n]);
+  } else {
+    float m = 0.f;
+#pragma unroll
+    for (int n = 0; n < N; ++n) m = fmaxf(m, fmaxf(fabsf(o[n].a), fabsf(o[n].b)));
+    if (m <= SMALL) {
+#pragma unroll
+      for (int n = 0; n < N; ++n) softplus_jet_bwd_small(o[n], offset, g0[n], ga[n], gb[n], dz0[n], dP[n], dQ[n]);
+    } else {
+#pragma unroll
+      for (int n = 0; n < N; ++n) {
+        float d[3];
+        softplus_jet_bwd_any(&o[n], offset, g0[n], ga[n], gb[n], d);
+        dz0[n] = d[0]; dP[n] = d[1]; dQ[n] = d[2];
+      }
+    }
+  }
 }
 
 }  // namespace jet
