@@ -321,7 +321,9 @@ def main():
                                       jet_passes=int(os.environ.get("FDSM_BENCH_JET_PASSES", "2")))
         if net.formulation == "jet":
             network = (f"fused difference-propagating chain (ours): Philox direction + tcgen05 forward / head / combine / dgrad in one "
-                       f"kernel (weights TF32 hi+lo, {net.jet_passes} pass), split-K tcgen05 weight gradients, clip + Adam; one "
+                       f"kernel (jet_passes={net.jet_passes}: " + {1: "TF32 weights", 2: "hidden-layer weights TF32 hi+lo, input layer TF32",
+                                                                      3: "all weights TF32 hi+lo"}[net.jet_passes] +
+                       "), split-K tcgen05 weight gradients, clip + Adam; one "
                        f"CUDA-graph replay per step")
         else:
             network = "fused tcgen05 3xTF32 MLP (ours): kernels (1)-(4) + clip + Adam, one CUDA-graph replay per step"

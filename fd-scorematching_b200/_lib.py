@@ -52,7 +52,15 @@ class JetArgs(C.Structure):
         ("params", _f32p), ("workspace", _f32p),
         ("c1", _f32), ("scale", _f32), ("mean", _i32),
         ("loss", _f32p), ("grads", _f32p), ("accumulate", _i32),
-        ("ev_chain_start", C.c_void_p), ("ev_chain_stop", C.c_void_p), ("trace", C.c_void_p),
+        ("ev_chain_start", C.c_void_p), ("ev_chain_stop", C.c_void_p), ("trace", C.c_void_p), ("update", C.c_void_p),
+    ]
+
+
+class JetUpdate(C.Structure):      # mirrors fdsm_jet_update
+    _fields_ = [
+        ("exp_avg", _f32p), ("exp_avg_sq", _f32p), ("lr", C.c_float), ("lr_dev", _f32p),
+        ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float), ("max_norm", C.c_float),
+        ("step_counter", C.c_void_p), ("scratch", _f32p),
     ]
 
 
@@ -73,7 +81,7 @@ class MlpDesc(C.Structure):
                 ("presplit", _i32)]
 
 
-ABI_VERSION = 5    # FDSM_ABI_VERSION of include/fdsm.h
+ABI_VERSION = 6    # FDSM_ABI_VERSION of include/fdsm.h
 
 # name -> (restype, argtypes); must list every symbol include/fdsm.h declares
 PROTOTYPES = {

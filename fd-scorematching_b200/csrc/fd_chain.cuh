@@ -20,8 +20,11 @@
 // ignores the 13 low mantissa bits, i.e. the raw tile IS the hi operand; once the hi MMAs of a slot have completed, the
 // epilogue warps -- idle during phase 0 -- overwrite the slot IN PLACE with lo = x - trunc(x) and the lo MMAs follow, one
 // k-block behind the hi MMAs.  Later phases stream under the epilogues, where the delivery rate is not the limit and the
-// epilogue warps are busy: there the weights come as two TMA copies, hi and lo (PASSES = 2; PASSES = 1 ships
-// round-to-nearest TF32 weights and issues the hi MMAs only).  With CL > 1 the CTAs of a cluster split each slot's TMA
+// epilogue warps are busy: there the weights come as two TMA copies, hi and lo.  That is PASSES = 3 (every GEMM as hi + lo).
+// PASSES = 2, the default, keeps hi + lo for the hidden layers and runs the input layer on round-to-nearest TF32 weights
+// alone: the rounding of W_0 moves loss / gradient by 2e-5 / 9e-5 (config 2, against fp64), the rounding of the hidden
+// weights by 1e-4 / 2e-4 (tests/tools/jet_accuracy_study.py), and phase 0 -- nothing to overlap it with -- is the one
+// place where the second pass costs its full time.  PASSES = 1 issues hi MMAs only, everywhere.  With CL > 1 the CTAs of a cluster split each slot's TMA
 // boxes and multicast them.
 //
 // Shared memory: A region NA x (3 S x 128 B) (NA = ceil32(H+1)/32 k-blocks; the TMA ring of phase 0, then the resident
@@ -60,7 +63,7 @@ struct alignas(64) ChainParams {
   const float* head_w;               // [w1(H) b1 | w2(H) b2 | wq(H) bq]  or  [w(H) b]
   float* loss_part;                  // [tiles]   sum over the tile's samples of the per-sample loss (unscaled)
   float* head_part;                  // [tiles][head_n]  head-parameter gradient of the tile
-  int B, Bp, S, H, L, npad, kpad0, kpadh, head;
+  int B, Bp, S, D, H, L, npad, kpad0, kpadh, head;
   int ablk, nraw;                    // bytes of one A k-block (3 S x 128), slots of the weight ring
   float act_offset;                  // ln 2 for the normalised softplus
   float c1, coef;                    // loss_b = dE^2/8 - sE + (c1 - 2) E0 ; dL/dloss_b = coef (= scale / B or scale)
@@ -314,7 +317,7 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
             tma_load_2d(a_base + as * ablk + S * 128, &p.t_in, a_full(as), kb * 32, p.Bp + tile * S);
           }
           // phase 0: one slot per k-block (fp32; lo is derived on chip);  later phases with PASSES = 2: hi slot, lo slot
-          const int ncopy = (PASSES == 2 && g > 0) ? 2 : 1;
+          const int ncopy = (PASSES >= 2 && g > 0) ? 2 : 1;
           const int kpad_l = layer == 0 ? p.kpad0 : p.kpadh;
           for (int ps = 0; ps < ncopy; ++ps) {
             mbar_wait_parked(w_empty(ws), wph ^ 1u);           // every CTA of the cluster has finished with this slot
@@ -350,9 +353,14 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
         const int nkb = fwd ? (g == 0 ? nkb0 : NA) : nbx;
         const uint32_t idesc = make_idesc_tf32(128, npad, tc::MAJOR_K, fwd ? tc::MAJOR_MN : tc::MAJOR_K);
         const uint32_t b_lbo = fwd ? 4096u : 16u, b_sbo = fwd ? 512u : 1024u, b_step = fwd ? 1024u : 32u, b_lay = fwd ? 1u : 2u;
-        auto mmas = [&](int as_, int slot, bool first) {
+        // contraction length that carries data: input columns + the ones column (forward), the layer's outputs (dgrad);
+        // 8-column steps of a k-block that lie entirely in the zero padding are not issued
+        const int kvalid = fwd ? (g == 0 ? p.D + 1 : H + 1) : H;
+        auto mmas = [&](int as_, int slot, bool first, int kb_) {
+          const int n8 = min(4, (kvalid - 32 * kb_ + 7) >> 3);
 #pragma unroll
           for (int k8 = 0; k8 < 4; ++k8) {
+            if (k8 >= n8) break;
             const uint64_t da = make_smem_desc(a_base + as_ * ablk + k8 * 32, 16u, 1024u, 2u);
             const uint64_t db = make_smem_desc(w_base + slot * WSLOT_BYTES + k8 * b_step, b_lbo, b_sbo, b_lay);
             mma_tf32_ss(tmem_base, da, db, idesc, (first && k8 == 0) ? 0u : 1u);
@@ -362,15 +370,15 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
           if (CL > 1) tc_commit_mc(w_empty(slot), CMASK);
           else tc_commit(w_empty(slot));
         };
-        if (g == 0 && PASSES == 2) {
+        if (g == 0 && PASSES == 3) {
           // phase 0: the lo MMAs of a k-block run one k-block behind its hi MMAs (the in-place conversion gets that long);
           // with a single A slot the operand of k-block kb must be released before kb + 1 can land: no lag then
           const bool lag = NA >= 2;
-          int pws = 0, pas = 0; uint32_t pph = 0;
+          int pws = 0, pas = 0, pkb = 0; uint32_t pph = 0;
           auto lo_mmas = [&]() {
             mbar_wait_parked(lo_full(pws), pph);
             tc_fence_after();
-            mmas(pas, pws, false);
+            mmas(pas, pws, false, pkb);
             release(pws);
             tc_commit(a_empty(pas));
           };
@@ -379,10 +387,10 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
             mbar_wait_parked(a_full(as), (kb / NA) & 1);
             mbar_wait_parked(w_full(ws), wph);
             tc_fence_after();
-            mmas(as, ws, kb == 0);
+            mmas(as, ws, kb == 0, kb);
             tc_commit(hi_done(ws));
             if (lag && kb > 0) lo_mmas();
-            pws = ws; pas = as; pph = wph;
+            pws = ws; pas = as; pph = wph; pkb = kb;
             if (!lag) lo_mmas();
             if (++ws == nraw) { ws = 0; wph ^= 1u; }
           }
@@ -396,10 +404,11 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
               mbar_wait_parked(a_ready(kb), (g - 1) & 1);      // the epilogue has finished this k-block of the operand
               store_block(g - 1, kb);
             }
-            for (int ps = 0; ps < PASSES; ++ps) {
+            const int nps = (PASSES >= 2 && g > 0) ? 2 : 1;
+            for (int ps = 0; ps < nps; ++ps) {
               mbar_wait_parked(w_full(ws), wph);
               tc_fence_after();
-              mmas(as, ws, kb == 0 && ps == 0);
+              mmas(as, ws, kb == 0 && ps == 0, kb);
               release(ws);
               if (++ws == nraw) { ws = 0; wph ^= 1u; }
             }
@@ -441,7 +450,7 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
       __syncwarp();
       if (lane == 0) mbar_arrive(a_ready(j));
     };
-    if (PASSES == 2) {
+    if (PASSES == 3) {
       // phase 0: these warps have nothing else to do -- they turn every weight slot into its lo part once its hi MMAs are done
       const int nvec = nbx * 256;                       // float4s of a slot
       int ws = 0; uint32_t wph = 0;
@@ -624,7 +633,7 @@ struct InputArgs {
   unsigned long long seed, offset, row0; const unsigned long long* offset_dev;
   float* xv; int B, Bp, D, kpad0;
 };
-__global__ void __launch_bounds__(256) jet_inputs_kernel(InputArgs a) {
+__global__ void __launch_bounds__(256, 4) jet_inputs_kernel(InputArgs a) {
   constexpr int G = 128, MAXC = 2;
   __shared__ float red[256 / 32];
   if (a.offset_dev) a.offset += __ldg(a.offset_dev);
@@ -652,9 +661,18 @@ __global__ void __launch_bounds__(256) jet_inputs_kernel(InputArgs a) {
     };
     // the draw stays in registers between the norm pass and the write pass when the row fits (D <= 4 MAXC G = 1024);
     // longer rows regenerate it (counter-based: identical numbers)
-    float4 dreg[MAXC];
+    float4 dreg[MAXC], xreg[MAXC];
     float ss = 0.f;
     if (active) {
+      // the sample row is requested BEFORE the Philox / Box-Muller arithmetic: the HBM latency hides under it
+      if (xvec) {
+#pragma unroll
+        for (int k = 0; k < MAXC; ++k) {
+          const int j = t + k * G;
+          xreg[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (j < nchunk) xreg[k] = ldg4(a.x + b * a.ldx + 4 * j);
+        }
+      }
 #pragma unroll
       for (int k = 0; k < MAXC; ++k) {
         const int j = t + k * G;
@@ -688,7 +706,7 @@ __global__ void __launch_bounds__(256) jet_inputs_kernel(InputArgs a) {
       if (k == 0) d = dreg[0];
       else if (k == 1) d = dreg[MAXC - 1];
       else d = raw(j);
-      if (xvec) xx = ldg4(xrow + e);
+      if (xvec) xx = k == 0 ? xreg[0] : k == 1 ? xreg[MAXC - 1] : ldg4(xrow + e);
       else xx = make_float4(e < D ? __ldg(xrow + e) : 0.f, e + 1 < D ? __ldg(xrow + e + 1) : 0.f, e + 2 < D ? __ldg(xrow + e + 2) : 0.f,
                             e + 3 < D ? __ldg(xrow + e + 3) : 0.f);
       float4 v;

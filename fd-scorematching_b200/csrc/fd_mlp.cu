@@ -20,6 +20,7 @@
 
 #include "tc_gemm_host.cuh"
 #include "fd_combine.cuh"
+#include <cooperative_groups.h>
 #include "fd_chain.cuh"
 
 namespace fdsm {

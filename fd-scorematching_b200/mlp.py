@@ -11,6 +11,7 @@ Two ways in:
 """
 import ctypes as C
 import math
+import os
 
 import numpy as np
 import torch
@@ -80,8 +81,9 @@ class FusedEnergyMLP(nn.Module):
                  presplit=False, formulation="auto", jet_passes=2):
         """formulation of the fused FD-SSM step (`fd_ssm_loss_and_grad` / `fd_ssm_step`): "jet" = the difference-
         propagating chain kernel (csrc/fd_chain.cuh; hidden <= 223, n_hidden <= 5), "stacked" = the reference's stacked batch
-        [x | x+v | x-v] through the 3xTF32 GEMM launches, "auto" = jet where supported.  `jet_passes`: 2 = weights as TF32
-        hi + lo (default), 1 = weights rounded to TF32.  `passes` / `presplit` configure the stacked path and `net(x)`."""
+        [x | x+v | x-v] through the 3xTF32 GEMM launches, "auto" = jet where supported.  `jet_passes`: 3 = every GEMM with
+        weights as TF32 hi + lo, 2 (default) = hi + lo for the hidden layers and round-to-nearest TF32 weights for the input
+        layer, 1 = weights rounded to TF32 everywhere (include/fdsm.h quotes the measured errors).  `passes` / `presplit` configure the stacked path and `net(x)`."""
         super().__init__()
         if act not in ACTS:
             raise ValueError(f"act must be one of {sorted(ACTS)}")
@@ -202,8 +204,9 @@ class FusedEnergyMLP(nn.Module):
         self._step_state = st
         return st
 
-    def _jet_loss_and_grad(self, x2, eps, scale, u, v, draw, c1, mean, offset_dev):
-        """The same loss and gradient through the difference-propagating chain kernel (fdsm_jet_fd_ssm)."""
+    def _jet_loss_and_grad(self, x2, eps, scale, u, v, draw, c1, mean, offset_dev, update=False):
+        """The same loss and gradient through the difference-propagating chain kernel (fdsm_jet_fd_ssm); `update`: the clipped
+        Adam step of configure_optimizer() in the same call (fdsm_jet_update: one fused launch for reduce + clip + Adam)."""
         lib = _lib.load()
         B, D = x2.shape
         st = self._jet_state(B, x2.device)
@@ -232,7 +235,20 @@ class FusedEnergyMLP(nn.Module):
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(); e1.record()        # creates the underlying cudaEvent_t handles
             a.ev_chain_start, a.ev_chain_stop = C.c_void_p(e0.cuda_event), C.c_void_p(e1.cuda_event)
-        ops._count(4 + 2 * self.n_hidden)     # prep, inputs, chain, finish + per layer: weight-gradient GEMM and its reduce
+        if update:
+            o = self._opt
+            if "update_scratch" not in o:
+                o["update_scratch"] = torch.zeros(1024, device=self.flat.device)
+            ju = _lib.JetUpdate()
+            ju.exp_avg, ju.exp_avg_sq = _ptr(o["m"]), _ptr(o["v"])
+            ju.lr, ju.lr_dev = o["lr"], _ptr(o["lr_dev"])
+            ju.beta1, ju.beta2, ju.eps, ju.max_norm = o["betas"][0], o["betas"][1], o["eps"], o["clip"]
+            ju.step_counter, ju.scratch = C.c_void_p(o["step"].data_ptr()), _ptr(o["update_scratch"])
+            a.update = C.cast(C.pointer(ju), C.c_void_p)
+            keep.append(ju)
+            ops._count(4 + self.n_hidden)     # prep, inputs, chain, weight-gradient GEMMs, fused reduce + clip + Adam
+        else:
+            ops._count(4 + 2 * self.n_hidden)     # prep, inputs, chain, finish + per layer: weight-gradient GEMM and its reduce
         check(lib.fdsm_jet_fd_ssm(C.byref(self.jet_desc), C.byref(a), _stream()), "fdsm_jet_fd_ssm")
         if hook is not None:
             hook.append((e0, e1))
@@ -345,11 +361,14 @@ class FusedEnergyMLP(nn.Module):
         """Learning-rate schedules (DeepEBM/ESM/inputs.py:75-90) write the device scalar the captured step reads."""
         self._opt["lr_dev"].fill_(float(lr))
 
-    def _loss_and_grad_captured(self, st, kind, cfg):
+    def _loss_and_grad_captured(self, st, kind, cfg, update=False):
         o = self._opt
         draw = (o["seed"], 0, o["rank"] * st["B"])      # offset = device step counter; rows keyed by the GLOBAL sample index
         if kind == "ssm":
             eps, scale = cfg
+            if update:
+                x2 = st["x"].reshape(st["x"].shape[0], -1)
+                return self._jet_loss_and_grad(x2, eps, scale, None, None, draw, 2.0, True, o["step"], update=True)
             return self.fd_ssm_loss_and_grad(st["x"], eps, scale, draw=draw, offset_dev=o["step"])
         eps, sigma02, loss_coe = cfg
         return self.fd_dsm_loss_and_grad(st["x"], st["sigma_b"], eps=eps, sigma02=sigma02, loss_coe=loss_coe, draw=draw,
@@ -399,7 +418,14 @@ class FusedEnergyMLP(nn.Module):
         peer = distributed and getattr(allreduce, "fused_sumsq", False)    # ddp.PeerAllReduce: capturable, emits the sumsq
         key = (st["B"], kind, cfg, bool(distributed), bool(peer))
 
+        # single GPU, difference-propagating path: the update rides in the same library call (one fused launch)
+        fused = (self.formulation == "jet" and kind == "ssm" and not distributed and
+                 os.environ.get("FDSM_JET_FUSED_UPDATE", "1") != "0")
+        key = key + (fused,)
+
         def exchange_and_update():
+            if fused:
+                return
             if peer:
                 allreduce(st["grad"], sumsq=self._opt["sumsq"], step=self._opt["step"])
                 ops._count(1)
@@ -408,7 +434,7 @@ class FusedEnergyMLP(nn.Module):
                 self._apply_update(st)
 
         if not self._opt["use_graph"]:
-            self._loss_and_grad_captured(st, kind, cfg)
+            self._loss_and_grad_captured(st, kind, cfg, update=fused)
             if distributed and allreduce is not None and not peer:
                 allreduce(st["grad"])
             exchange_and_update()
@@ -418,15 +444,13 @@ class FusedEnergyMLP(nn.Module):
             side = torch.cuda.Stream()
             side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):
-                step0 = self._opt["step"].clone()
-                self._loss_and_grad_captured(st, kind, cfg)
-                self._opt["step"].copy_(step0)
+                self._loss_and_grad_captured(st, kind, cfg)           # (no update: parameters and step counter untouched)
             torch.cuda.current_stream().wait_stream(side)
             launches0 = ops.LAUNCHES
             g1, g2 = torch.cuda.CUDAGraph(), None
             one_graph = not distributed or peer
             with torch.cuda.graph(g1):
-                self._loss_and_grad_captured(st, kind, cfg)
+                self._loss_and_grad_captured(st, kind, cfg, update=fused)
                 if one_graph:
                     exchange_and_update()
             if not one_graph:
@@ -461,13 +485,16 @@ class FusedEnergyMLP(nn.Module):
             fwd = 2.0 * (2 * B * D * H + 3 * B * H * H * (L - 1))          # layer 0 on the 2B rows [x | v], the rest on 3B
             dgrad = 2.0 * 3 * B * H * H * (L - 1)
             flops = fwd + dgrad
+            fwd0 = 2.0 * 2 * B * D * H
+            executed = {1: flops, 2: fwd0 + 2 * (flops - fwd0), 3: 2 * flops}[self.jet_passes]
             ach = flops / (avg * 1e-3) / 1e12
             peak = peaks["bf16_tflops"] / 2.0
-            return {"kernel": f"fdsm::jet::chain_kernel (tcgen05 kind::tf32, TMA-fed, weights as TF32 hi+lo = {self.jet_passes} MMA "
-                              f"pass(es); all {L} forward layers + head + combine + {L - 1} dgrad GEMMs in one launch)",
+            wdesc = {1: "TF32 weights, 1 MMA pass", 2: "hidden-layer weights as TF32 hi+lo (2 MMA passes), input layer 1 pass",
+                     3: "all weights as TF32 hi+lo, 2 MMA passes"}[self.jet_passes]
+            return {"kernel": f"fdsm::jet::chain_kernel (tcgen05 kind::tf32, TMA-fed, {wdesc}; all {L} forward layers + head + combine + {L - 1} dgrad GEMMs in one launch)",
                     "bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": None,
                     "peak_kind": f"{peaks_kind} dense bf16 burst / 2 (TF32 kind)", "passes": self.jet_passes,
-                    "executed_tf32_tflops": ach * self.jet_passes, "executed_frac": ach * self.jet_passes / peak,
+                    "executed_tf32_tflops": ach * executed / flops, "executed_frac": ach * executed / flops / peak,
                     "algorithmic_flops_per_launch": flops, "avg_launch_us": avg * 1e3, "launches_timed": len(ms),
                     "stacked_formulation_flops": 2.0 * 3 * B * (D * H + (L - 1) * H * H) + dgrad,
                     "note": "achieved counts the 2*M*N*K of OUR formulation (layer 0 contracts the 2B rows [x | v]); the "

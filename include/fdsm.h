@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define FDSM_ABI_VERSION 5
+#define FDSM_ABI_VERSION 6
 
 #define FDSM_OK 0
 #define FDSM_ERR_INVALID_ARGUMENT (-1)
@@ -247,11 +247,25 @@ int fdsm_mlp_backward_fd_dsm(const fdsm_mlp_desc* desc, const float* x_hi, const
  * the per-sample loss and all data-gradient GEMMs for a tile of samples; the weight gradients follow as split-K GEMMs.
  *   *loss = scale * mean_b|sum_b [ (E+ - E-)^2/8 - (E+ + E- - 2 E0) + (c1 - 2) E0 ]
  *   grads (+)= dloss/dparams   (flat, the layout of fdsm_mlp_*)
- * desc->passes: 1 = weights rounded to TF32 (one MMA pass); any other value = weights as TF32 hi + lo (two passes,
- * default).  desc->presplit is ignored.  Supported: hidden <= 223, n_hidden <= 5 (fdsm_jet_supported).
+ * desc->passes: 3 = every GEMM with its weights as TF32 hi + lo (two MMA passes; the input layer's weights travel once as
+ * fp32 and lo is derived on chip); 1 = weights rounded to TF32, one pass everywhere; any other value (default, 2) = hi + lo
+ * for the hidden layers, round-to-nearest TF32 weights for the input layer (config 2 against fp64: loss / gradient within
+ * 2e-5 / 9e-5, passes = 3: 2e-6 / 6e-5, passes = 1: 1e-4 / 2e-4).  desc->presplit is ignored.  Supported: hidden <= 223, n_hidden <= 5 (fdsm_jet_supported).
  * Deterministic: fixed-order tile, split-K and head reductions.  Graph-capturable (uses internal side streams by
  * event fork/join).
  * ------------------------------------------------------------------------------------------ */
+/* Optional fused tail of the single-GPU training step (DeepEBM/train_ssm.py:65-70: clip_grad_norm_ + Adam.step): the
+ * fixed-order sums of the split-K partials and of the per-tile head records, the squared gradient norm, the clip
+ * coefficient and the Adam update run as ONE launch (with a grid-wide barrier) after the weight-gradient GEMMs (instead of n_hidden
+ * reduces + finish + fdsm_grad_sumsq + fdsm_adam_step).  `grads` is still written.  The arithmetic is fdsm_adam_step's;
+ * *step_counter is read at entry and incremented by one at the end, as fdsm_grad_sumsq does. */
+typedef struct fdsm_jet_update {
+  float* exp_avg; float* exp_avg_sq;               /* Adam moments, n_params each                                         */
+  float lr; const float* lr_dev;                   /* learning rate: *lr_dev if non-NULL (schedules write it), else lr    */
+  float beta1, beta2, eps, max_norm;               /* max_norm <= 0: no clipping                                          */
+  int64_t* step_counter;                           /* device scalar                                                       */
+  float* scratch;                                  /* >= 1024 floats, zeroed once by the caller, then owned by the library */
+} fdsm_jet_update;
 typedef struct fdsm_jet_args {
   const float* x; int64_t ldx; int64_t B;   /* samples (B, D)                                                          */
   const float* dir; int64_t lddir;          /* injected direction (B, D) or NULL => Philox stream 0 (as fdsm_stack)     */
@@ -265,6 +279,8 @@ typedef struct fdsm_jet_args {
                                                       (measurement: bench.py's roofline of the dominant kernel)         */
   void* trace;                                     /* optional debug buffer: tiles x 38 uint64 %globaltimer stamps of the chain
                                                       kernel's phases (scripts/chain_trace.py); NULL in production      */
+  const fdsm_jet_update* update;                   /* NULL: loss + gradient only.  Non-NULL: the parameters (`params`, written
+                                                      in place) take the clipped Adam step in the same call              */
 } fdsm_jet_args;
 int fdsm_jet_supported(const fdsm_mlp_desc* desc);
 /* offsets (optional, >= 8 + 4 * n_hidden entries): test view of the workspace -- [0] samples per tile S, [1] padded rows per
