@@ -66,12 +66,13 @@ class ClockSampler:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "20"], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
-            self.t = threading.Thread(target=lambda: [self.lines.append(l) for l in self.proc.stdout], daemon=True)
+            self.t = threading.Thread(target=lambda: [self.lines.append((time.monotonic(), l)) for l in self.proc.stdout], daemon=True)
             self.t.start()
         except Exception:
             self.proc = None
 
-    def stop(self):
+    def stop(self, t0=None, t1=None):
+        """Median SM clock / throttle reasons of the samples taken in [t0, t1] (time.monotonic) -- the loaded window."""
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -81,7 +82,9 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for l in self.lines:
+        for ts, l in self.lines:
+            if (t0 is not None and ts < t0) or (t1 is not None and ts > t1):
+                continue
             f = [x.strip() for x in l.split(",")]
             if len(f) < 7:
                 continue
@@ -349,20 +352,29 @@ def main():
         torch.cuda.synchronize()
 
     # ---- value: device-resident inputs ---------------------------------------------------------------
-    for i in range(args.warmup):
-        tr.step(pool[i % POOL])
-    barrier()
+    # nvidia-smi -lms 20 needs ~0.2 s before its first sample: it starts before the warm-up, and the load of the timed
+    # steps is held for SUSTAIN more (untimed) steps after them so that samples fall inside the loaded window even at
+    # --steps 20; `clocks.samples` counts the samples of that window only
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    SUSTAIN = 2500
+    for i in range(args.warmup):
+        tr.step(pool[i % POOL])
+    barrier()
+    tr.step(pool[0])         # one untimed step: the ranks leave the host barrier skewed; the first exchange re-aligns them
     l0 = ops.LAUNCHES if hasattr(ops, "LAUNCHES") else 0
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_load0 = time.monotonic()
     e0.record()
     for i in range(args.steps):
         tr.step(pool[i % POOL])
     e1.record()
-    barrier()
     launches = (ops.LAUNCHES - l0) if hasattr(ops, "LAUNCHES") else None
+    for i in range(max(0, SUSTAIN - args.steps)):
+        tr.step(pool[i % POOL])
+    barrier()
+    t_load1 = time.monotonic()
     ms = e0.elapsed_time(e1)
     t = torch.tensor([ms], device=dev)
     if world > 1:
@@ -374,6 +386,7 @@ def main():
     for i in range(max(3, args.warmup // 2)):
         tr.step_from_host(host[i % 4], loss_host)
     barrier()
+    tr.step_from_host(host[0], loss_host)
     e0.record()
     for i in range(args.steps):
         tr.step_from_host(host[i % 4], loss_host)
@@ -383,8 +396,95 @@ def main():
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_ms = float(t)
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop(t_load0, t_load1) if rank == 0 else None
     final_loss = float(loss_host)
+    # what the end-to-end step waits for: the pinned-host -> device copy of the batch, alone and under the step's load
+    h2d_bytes = B_PER_GPU * D * 4
+    dst = [torch.empty_like(pool[0]) for _ in range(2)]
+    cs = torch.cuda.Stream()
+    def h2d_gbs(loaded, reps=20):
+        torch.cuda.synchronize()
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(cs):
+            c0.record(cs)
+            for i in range(reps):
+                dst[i % 2].copy_(host[i % 4], non_blocking=True)
+            c1.record(cs)
+        if loaded:
+            for i in range(reps * 2):
+                tr.step(pool[i % POOL])
+        torch.cuda.synchronize()
+        return h2d_bytes * reps / (c0.elapsed_time(c1) * 1e-3) / 1e9
+    h2d_alone, h2d_loaded = h2d_gbs(False), h2d_gbs(True)
+
+    # ---- N > 1: the exchange alone, and the parity checks of the data-parallel path ---------------------
+    exchange_us, ddp_check = None, None
+    if world > 1 and use_fused:
+        from fdsm_b200 import ddp
+        ar = tr._allreduce
+        n = net.flat.numel()
+        peer = isinstance(ar, ddp.PeerAllReduce)
+        gx = torch.Generator(device=dev).manual_seed(4242 + rank)
+        x = torch.randn(n, device=dev, generator=gx)
+        parts = [torch.empty_like(x) for _ in range(world)]
+        dist.all_gather(parts, x)
+        want = parts[0].clone()
+        for q in parts[1:]:
+            want += q
+        want *= 1.0 / world
+        nccl = x * (1.0 / world)
+        dist.all_reduce(nccl)
+        ddp_check = {"backend": "fdsm_peer_allreduce (NVLink peer memory, one kernel)" if peer else "ncclAllReduce"}
+        if peer:
+            got = ar(x.clone())
+            torch.cuda.synchronize()
+            ddp_check["peer_equals_rank_order_sum_bitwise"] = bool(torch.equal(got, want))
+            ddp_check["peer_equals_nccl_all_reduce_bitwise"] = bool(torch.equal(got, nccl))
+            ddp_check["peer_vs_nccl_max_abs_diff"] = float((got - nccl).abs().max())
+            ddp_check["peer_timed_out"] = bool(ar.timed_out())
+        # replicas: the parameters after every step above, bit for bit against rank 0's
+        pr = [torch.empty_like(net.flat.data) for _ in range(world)]
+        dist.all_gather(pr, net.flat.data.contiguous())
+        ddp_check["params_bit_identical_across_ranks"] = all(bool(torch.equal(pr[0], q)) for q in pr[1:])
+        # sharding: this rank's Philox direction rows (row offset rank * B) = its slice of the unsharded draw
+        vs = ops.direction(B_PER_GPU, D, EPS, device=dev, draw=(1234, 7, rank * B_PER_GPU))
+        vf = ops.direction(B_PER_GPU * world, D, EPS, device=dev, draw=(1234, 7, 0))
+        ddp_check["sharded_philox_rows_equal_unsharded"] = bool(torch.equal(vs, vf[rank * B_PER_GPU:(rank + 1) * B_PER_GPU]))
+        flags = torch.tensor([int(all(v for k, v in ddp_check.items() if isinstance(v, bool) and k not in
+                                      ("peer_timed_out", "peer_equals_nccl_all_reduce_bitwise")) and not ddp_check.get("peer_timed_out", False))],
+                             device=dev)
+        dist.all_reduce(flags, op=dist.ReduceOp.MIN)
+        ddp_check["all_ranks_ok"] = bool(int(flags))
+        # the exchange alone: 20 launches in one graph (the peer kernel is capturable; NCCL is timed eagerly)
+        buf = torch.randn(n, device=dev, generator=gx)
+        if peer:
+            ssq, stp = torch.zeros(32, device=dev), torch.zeros((), dtype=torch.int64, device=dev)
+            gs2 = torch.cuda.Stream()
+            gs2.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(gs2):
+                ar(buf, sumsq=ssq, step=stp)
+                gx20 = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(gx20, stream=gs2):
+                    for _ in range(20):
+                        ar(buf, sumsq=ssq, step=stp)
+            torch.cuda.current_stream().wait_stream(gs2)
+            run20 = gx20.replay
+        else:
+            def run20():
+                for _ in range(20):
+                    ar(buf)
+        run20()
+        barrier()
+        run20()
+        x0, x1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        x0.record()
+        for _ in range(5):
+            run20()
+        x1.record()
+        barrier()
+        tt = torch.tensor([x0.elapsed_time(x1) * 1e3 / 100], device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        exchange_us = float(tt)
 
     # ---- roofline of the dominant kernel of OUR path, timed live with CUDA events ---------------------
     pk, pk_kind = peaks()
@@ -472,11 +572,16 @@ def main():
                        "parallelism": f"dp{world}"},
             "e2e": {"value": B_PER_GPU * world * args.steps / (e2e_ms * 1e-3), "unit": "samples/s",
                     "h2d_bytes_per_step": B_PER_GPU * D * 4, "d2h_bytes_per_step": 4,
-                    "ms_per_step": e2e_ms / args.steps, "api": "FDSSMTrainer.step_from_host (pinned host batch)"},
+                    "ms_per_step": e2e_ms / args.steps, "api": "FDSSMTrainer.step_from_host (pinned host batch)",
+                    "h2d_gbs_alone": h2d_alone, "h2d_gbs_overlapped": h2d_loaded,
+                    "h2d_us_per_step_at_overlapped_rate": B_PER_GPU * D * 4 / (h2d_loaded * 1e3)},
             "gpu_launches": launches, "final_loss": final_loss, "clocks": clocks, "roofline": roof,
         }
         if use_fused:
             out["roofline_fd_kernel"] = fd_roof
+        if world > 1:
+            out["exchange_us"] = exchange_us
+            out["ddp_check"] = ddp_check
         out["config"]["host_thread_cpus"] = ("gpu-local: " + str(len(tr.host_cpus))) if tr.host_cpus else "unbound"
         if world == 1 and not args.no_cpu_baseline:
             if affinity0 is not None:

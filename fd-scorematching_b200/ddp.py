@@ -127,14 +127,22 @@ class PeerAllReduce:
 
 def make_allreduce(n, device):
     """The exchange step for a flat fp32 gradient of n elements: the peer-memory kernel when the ranks share an NVLink
-    domain (FDSM_ALLREDUCE=nccl forces the NCCL library collective), else NCCL."""
+    domain (FDSM_ALLREDUCE=nccl forces the NCCL library collective), else NCCL.  The choice is collective: the ranks
+    all-reduce a success flag after trying to set the peer path up, so one rank without P2P / symmetric memory moves
+    EVERY rank to NCCL (mixed backends would deadlock in the first step)."""
     import os
     import sys
     if not is_distributed():
         return allreduce_mean_
-    if os.environ.get("FDSM_ALLREDUCE", "peer") != "nccl" and torch.device(device).type == "cuda":
+    peer, want = None, os.environ.get("FDSM_ALLREDUCE", "peer") != "nccl" and torch.device(device).type == "cuda"
+    if want:
         try:
-            return PeerAllReduce(n, device)
+            peer = PeerAllReduce(n, device)
         except Exception as e:   # no P2P / symmetric memory on this box: library collective
             print(f"[fdsm] peer all-reduce unavailable ({type(e).__name__}: {e}); using NCCL", file=sys.stderr)
+    ok = torch.tensor([1 if (peer is not None or not want) else 0], device=device, dtype=torch.int32)
+    if want:                     # FDSM_ALLREDUCE must be set identically on every rank (it decides whether this collective runs)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    if peer is not None and int(ok) == 1:
+        return peer
     return allreduce_mean_

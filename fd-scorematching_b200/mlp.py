@@ -384,17 +384,23 @@ class FusedEnergyMLP(nn.Module):
                                  o["betas"][0], o["betas"][1], o["eps"], o["clip"], _ptr(o["sumsq"]), _ptr(o["step"]), s),
               "fdsm_adam_step")
 
-    def fd_ssm_step(self, x, eps, allreduce=None, scale=None, distributed=False):
+    def fd_ssm_step(self, x, eps, allreduce=None, scale=None, distributed=False, borrow=False):
         """One optimisation step of DeepEBM/train_ssm.py:63-69 on a device batch x (B, ...).  Returns the loss (device
         scalar, persistent buffer).  The whole step is ONE CUDA-graph replay -- also for world > 1 when `allreduce` is the
-        peer-memory kernel (ddp.PeerAllReduce); with the NCCL library collective it is two replays around the all-reduce."""
+        peer-memory kernel (ddp.PeerAllReduce); with the NCCL library collective it is two replays around the all-reduce.
+        `borrow`: the step reads x where it lies instead of copying it into its own input buffer first -- for callers that
+        hand in one of a few long-lived buffers (the trainer's H2D staging pair): one captured graph per buffer address."""
         x2 = x.reshape(x.shape[0], -1)
         st = self._jet_state(x2.shape[0], x2.device) if self.formulation == "jet" else self._state(x2.shape[0], x2.device)
-        if "x" not in st:
-            st["x"] = torch.empty_like(x2)
         scale = 1.0 / eps ** 2 if scale is None else scale
-        st["x"].copy_(x2)
-        return self._train_step(st, "ssm", (float(eps), float(scale)), allreduce, distributed)
+        if borrow and x2.is_contiguous() and x2.dtype == torch.float32:
+            st["x"], xkey = x2, x2.data_ptr()
+        else:
+            if st.get("x_own") is None:
+                st["x_own"] = torch.empty_like(x2, memory_format=torch.contiguous_format)
+            st["x_own"].copy_(x2)
+            st["x"], xkey = st["x_own"], 0
+        return self._train_step(st, "ssm", (float(eps), float(scale)), allreduce, distributed, xkey)
 
     def mdsm_fd_step(self, x, sigmas, sigma02=0.01, eps=0.05, loss_coe=1e-4, allreduce=None, distributed=False):
         """One optimisation step of DeepEBM/train_dsm.py:62-71 with loss_func = mdsm_fd (loss_train.py:96-118): `sigmas`
@@ -414,14 +420,14 @@ class FusedEnergyMLP(nn.Module):
         st["sigma_b"].copy_(sigmas.reshape(-1))
         return self._train_step(st, "dsm", (float(eps), float(sigma02), float(loss_coe)), allreduce, distributed)
 
-    def _train_step(self, st, kind, cfg, allreduce, distributed):
+    def _train_step(self, st, kind, cfg, allreduce, distributed, xkey=0):
         peer = distributed and getattr(allreduce, "fused_sumsq", False)    # ddp.PeerAllReduce: capturable, emits the sumsq
         key = (st["B"], kind, cfg, bool(distributed), bool(peer))
 
         # single GPU, difference-propagating path: the update rides in the same library call (one fused launch)
         fused = (self.formulation == "jet" and kind == "ssm" and not distributed and
                  os.environ.get("FDSM_JET_FUSED_UPDATE", "1") != "0")
-        key = key + (fused,)
+        key = key + (fused, xkey)
 
         def exchange_and_update():
             if fused:

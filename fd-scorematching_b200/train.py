@@ -72,9 +72,23 @@ class FDSSMTrainer:
         self._rank = rank
         self._copy_stream = None
         self._staged = None
+        self._nstep = 0
+        self.peer_check_every = 256     # steps between host reads of the peer exchange's status word (one D2H sync each)
+
+    def check_exchange(self):
+        """Raises if the peer-memory all-reduce ever gave up waiting for a rank (fd_peer.cu: the launch then publishes NaN
+        squared norms and stops advancing the step counter).  Called every `peer_check_every` steps by step(); call it
+        before saving a checkpoint."""
+        timed_out = getattr(self._allreduce, "timed_out", None)
+        if timed_out is not None and timed_out():
+            raise RuntimeError("fdsm_b200: the gradient exchange timed out waiting for a peer rank; the parameters of this "
+                               "rank are no longer trustworthy -- restart from the last checkpoint")
 
     # -- one optimisation step on a device-resident batch ------------------------------------------
-    def step(self, x):
+    def step(self, x, borrow=False):
+        self._nstep += 1
+        if self._nstep % self.peer_check_every == 0:
+            self.check_exchange()
         B = x.shape[0]
         ops.set_row_offset(self._rank * B)
         sig = None
@@ -87,6 +101,8 @@ class FDSSMTrainer:
                 return self.net.mdsm_fd_step(x, sig, self.sigma02, self.eps, self.loss_coe, allreduce=self._allreduce,
                                              distributed=ddp.is_distributed())
             kw = {} if self.scale is None else {"scale": self.scale}
+            if borrow:
+                kw["borrow"] = True
             return self.net.fd_ssm_step(x, eps=self.eps, allreduce=self._allreduce, distributed=ddp.is_distributed(), **kw)
         self.flat.zero_grad()
         if sig is not None:
@@ -126,7 +142,8 @@ class FDSSMTrainer:
             self._bufs[i].copy_(x_host, non_blocking=True)
             self._evt[i].record(self._copy_stream)
         cur.wait_event(self._evt[i])
-        loss = self.step(self._bufs[i])
+        # the fused ssm_fd step reads the staging buffer where it lies (one captured graph per staging buffer): no D2D copy
+        loss = self.step(self._bufs[i], borrow=self.fused and self.loss_name == "ssm_fd")
         self._free[i].record(cur)
         loss_host.copy_(loss, non_blocking=True)
         return loss_host

@@ -313,8 +313,12 @@ int fdsm_adam_step(float* params, const float* grads, float* exp_avg, float* exp
  *
  * peer_buffers[r] = address, valid on THIS device, of rank r's receive buffer (fdsm_peer_buffer_bytes(n, world)
  * bytes, zero-filled once before the first call on any rank; e.g. torch symmetric memory or cudaIpc mappings).
- * scratch: >= 1024 bytes of LOCAL device memory, zero-filled once (words [192, 204): debug phase timestamps of block 0); scratch[2] != 0 after a
- * launch means a peer did not arrive within 20 s (the kernel gives up instead of hanging the GPU).
+ * scratch: >= 1024 bytes of LOCAL device memory, zero-filled once (words [192, 204): debug phase timestamps of block 0).
+ * scratch[2] != 0 after a launch means a peer did not arrive within 20 s: the kernel gives up instead of hanging the GPU,
+ * publishes NaN squared-norm partials (a clipped update then yields NaN parameters rather than a silently partial sum)
+ * and leaves the step counter alone; the status is sticky -- callers poll it (ddp.PeerAllReduce.timed_out) and abort.
+ * Wire format: 16-byte lines {g[2w], epoch, g[2w+1], epoch}; each 8-byte half is validated by its own flag (the store
+ * atomicity NCCL's LL protocol relies on), nothing is assumed about 16-byte stores as a unit.
  * out may alias grad.  Every rank must call it the same number of times with the same n.  Graph-capturable.
  * Results are bit-identical on every rank. */
 #define FDSM_PEER_MAX_WORLD 8

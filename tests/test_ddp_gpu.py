@@ -1,0 +1,28 @@
+"""The multi-GPU exchange on real GPUs (needs >= 2: skipped on a one-GPU box; `gpurun --gpus 2 -- python -m pytest
+tests/test_ddp_gpu.py -m gpu`).  The host-side logic of the N > 1 path is covered on CPU by tests/test_ddp_cpu.py (gloo)."""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+pytestmark = pytest.mark.gpu
+
+
+def _run(world, env_extra, timeout):
+    env = dict(os.environ, **env_extra)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
+           "--master-port", "29731", os.path.join(ROOT, "tests", "tools", "ddp_worker.py")]
+    return subprocess.run(cmd, env=env, cwd=ROOT, capture_output=True, text=True, timeout=timeout)
+
+
+@pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_peer_allreduce_bit_exact_10k_graph_replays_and_timeout():
+    """fdsm_peer_allreduce: bit-for-bit against the rank-order sum and ncclAllReduce; 10^4 back-to-back CUDA-graph replays
+    with alternately delayed ranks, every element checked on the device; the dead-peer path (NaN squared norm, step counter
+    untouched, sticky status)."""
+    world = min(torch.cuda.device_count(), 4)
+    r = _run(world, {"FDSM_PEER_TIMEOUT_MS": "300", "FDSM_DDP_REPLAYS": "10000"}, timeout=600)
+    assert r.returncode == 0 and "DDP_WORKER_OK" in r.stdout, (r.stdout[-3000:], r.stderr[-3000:])

@@ -163,7 +163,7 @@ def test_fused_combine_backward_equals_explicit_sequence(fdsm, D, H, L, act, hea
     from fdsm_b200 import _lib, ops
     from fdsm_b200.mlp import _ptr, _stream
     lib = _lib.load()
-    net = fdsm.mlp.FusedEnergyMLP(D, H, L, act=act, head=head, device=DEV, seed=5)
+    net = fdsm.mlp.FusedEnergyMLP(D, H, L, act=act, head=head, device=DEV, seed=5, formulation="stacked")
     x = torch.rand(B, D, device=DEV)
     u = torch.randn(B, D, device=DEV)
     eps, scale = 0.05, 1.0 / 0.05 ** 2
