@@ -53,6 +53,24 @@ def ncu_summary():
     return {}
 
 
+# The contract is ONE JSON line on stdout.  Libraries write banners there too (NCCL prints its version on the first
+# collective), so file descriptor 1 is pointed at stderr for the whole run and the line goes out through a saved duplicate.
+_JSON_FD = None
+
+
+def claim_stdout():
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit_json(obj):
+    line = (json.dumps(obj) + "\n").encode()
+    os.write(_JSON_FD if _JSON_FD is not None else 1, line)
+
+
 class ClockSampler:
     """nvidia-smi clocks/throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -162,7 +180,7 @@ def run_reference(args):
         step(i)
     dt = time.perf_counter() - t0
     v = B_PER_GPU * args.steps / dt
-    print(json.dumps({
+    emit_json(({
         "impl": "reference", "metric": "fd_ssm_train_samples_per_sec", "value": v, "unit": "samples/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -199,7 +217,7 @@ def run_other_config(args):
     if args.impl == "reference":
         if rank == 0:
             cb = bc.cpu_baseline(args.config, budget_s=20.0)
-            print(json.dumps({"impl": "reference", "metric": "fd_ssm_train_samples_per_sec", "value": cb["value"],
+            emit_json(({"impl": "reference", "metric": "fd_ssm_train_samples_per_sec", "value": cb["value"],
                               "unit": "samples/s", "n_gpus": args.gpus, "steps": steps, "warmup": warmup,
                               "ms_per_step": None, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                               "dtype": "f32", "data": "synthetic", "config": {"workload": cfgd["name"]}, "cpu_baseline": cb,
@@ -279,13 +297,14 @@ def run_other_config(args):
                "fd_kernels": fdk, "fd_kernel_share_of_step": fdk["total_us"] / step_us}
         if world == 1 and not args.no_cpu_baseline:
             out["cpu_baseline"] = bc.cpu_baseline(args.config)
-        print(json.dumps(out))
+        emit_json((out))
     if world > 1:
         dist.destroy_process_group()
 
 
 # ---------------------------------------------------------------------------------------------------
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
@@ -398,6 +417,24 @@ def main():
     e2e_ms = float(t)
     clocks = sampler.stop(t_load0, t_load1) if rank == 0 else None
     final_loss = float(loss_host)
+    # the same, shipping what the reference's loaders hold before ToTensor: uint8 pixels (1 byte each); x / 255 +
+    # ssm_eps * N(0,1) (DeepEBM/train_ssm.py:61-62) is built inside the step's input kernel
+    e2e_u8_ms = None
+    if use_fused and net.formulation == "jet":
+        host_u8 = [(p.clamp(0, 1) * 255.0).round().to(torch.uint8).cpu().pin_memory() for p in pool[:4]]
+        for i in range(max(3, args.warmup // 2)):
+            tr.step_from_host_u8(host_u8[i % 4], loss_host, 0.005)
+        barrier()
+        tr.step_from_host_u8(host_u8[0], loss_host, 0.005)
+        e0.record()
+        for i in range(args.steps):
+            tr.step_from_host_u8(host_u8[i % 4], loss_host, 0.005)
+        e1.record()
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_u8_ms = float(t)
     # what the end-to-end step waits for: the pinned-host -> device copy of the batch, alone and under the step's load
     h2d_bytes = B_PER_GPU * D * 4
     dst = [torch.empty_like(pool[0]) for _ in range(2)]
@@ -579,6 +616,10 @@ def main():
         }
         if use_fused:
             out["roofline_fd_kernel"] = fd_roof
+        if e2e_u8_ms is not None:
+            out["e2e_u8"] = {"value": B_PER_GPU * world * args.steps / (e2e_u8_ms * 1e-3), "unit": "samples/s",
+                             "h2d_bytes_per_step": B_PER_GPU * D, "d2h_bytes_per_step": 4, "ms_per_step": e2e_u8_ms / args.steps,
+                             "api": "FDSSMTrainer.step_from_host_u8 (pinned uint8 pixels; /255 + ssm_eps N(0,1) on the device)"}
         if world > 1:
             out["exchange_us"] = exchange_us
             out["ddp_check"] = ddp_check
@@ -587,7 +628,7 @@ def main():
             if affinity0 is not None:
                 os.sched_setaffinity(0, affinity0)   # the CPU baseline uses every host core the process may run on
             out["cpu_baseline"] = cpu_baseline()
-        print(json.dumps(out))
+        emit_json((out))
     if world > 1:
         dist.destroy_process_group()
 

@@ -629,6 +629,7 @@ namespace jet {
 // One group of 128 threads per sample.
 struct InputArgs {
   const float* x; long long ldx;
+  const unsigned char* x8; float x8_scale, x_noise;   // x8 != NULL: x = x8 * x8_scale + x_noise * N(0,1)  (Philox STREAM_NOISE)
   const float* dir; long long lddir; int normalize; float scale;
   unsigned long long seed, offset, row0; const unsigned long long* offset_dev;
   float* xv; int B, Bp, D, kpad0;
@@ -639,7 +640,8 @@ __global__ void __launch_bounds__(256, 4) jet_inputs_kernel(InputArgs a) {
   if (a.offset_dev) a.offset += __ldg(a.offset_dev);
   const int gid = threadIdx.x / G, t = threadIdx.x % G;
   const int D = a.D, nchunk = (D + 3) >> 2;
-  const bool xvec = (D & 3) == 0 && (a.ldx & 3) == 0 && aligned16(a.x);
+  const bool xvec = a.x8 ? ((D & 3) == 0 && (a.ldx & 3) == 0 && (reinterpret_cast<uintptr_t>(a.x8) & 3) == 0)
+                         : ((D & 3) == 0 && (a.ldx & 3) == 0 && aligned16(a.x));
   const bool dvec = a.dir && (D & 3) == 0 && (a.lddir & 3) == 0 && aligned16(a.dir);
   const long long ngroups = (a.Bp + 1) / 2;
   for (long long rg = blockIdx.x; rg < ngroups; rg += gridDim.x) {
@@ -659,19 +661,42 @@ __global__ void __launch_bounds__(256, 4) jet_inputs_kernel(InputArgs a) {
       if (e + 3 >= D) n.w = 0.f;
       return n;
     };
+    // the sample row: fp32, or uint8 pixels scaled (torchvision ToTensor: / 255) plus the on-device noise of
+    // DeepEBM/train_ssm.py:62 (x + ssm_eps * randn) drawn from Philox stream 1 -- the host ships 1 byte per pixel
+    auto load_x = [&](int j) -> float4 {
+      const int e = 4 * j;
+      if (a.x8) {
+        const unsigned char* r = a.x8 + b * a.ldx;
+        uchar4 q;
+        if (xvec) q = *reinterpret_cast<const uchar4*>(r + e);
+        else q = make_uchar4(e < D ? r[e] : 0, e + 1 < D ? r[e + 1] : 0, e + 2 < D ? r[e + 2] : 0, e + 3 < D ? r[e + 3] : 0);
+        float4 xx = make_float4(q.x * a.x8_scale, q.y * a.x8_scale, q.z * a.x8_scale, q.w * a.x8_scale);
+        if (a.x_noise != 0.f) {
+          const float4 n = philox_normal4(a.seed, a.offset, STREAM_NOISE, a.row0 + (unsigned long long)b, (uint32_t)j);
+          xx.x = fmaf(a.x_noise, n.x, xx.x); xx.y = fmaf(a.x_noise, n.y, xx.y); xx.z = fmaf(a.x_noise, n.z, xx.z);
+          xx.w = fmaf(a.x_noise, n.w, xx.w);
+        }
+        if (e + 1 >= D) xx.y = 0.f;
+        if (e + 2 >= D) xx.z = 0.f;
+        if (e + 3 >= D) xx.w = 0.f;
+        return xx;
+      }
+      const float* xrow = a.x + b * a.ldx;
+      if (xvec) return ldg4(xrow + e);
+      return make_float4(e < D ? __ldg(xrow + e) : 0.f, e + 1 < D ? __ldg(xrow + e + 1) : 0.f, e + 2 < D ? __ldg(xrow + e + 2) : 0.f,
+                         e + 3 < D ? __ldg(xrow + e + 3) : 0.f);
+    };
     // the draw stays in registers between the norm pass and the write pass when the row fits (D <= 4 MAXC G = 1024);
     // longer rows regenerate it (counter-based: identical numbers)
     float4 dreg[MAXC], xreg[MAXC];
     float ss = 0.f;
     if (active) {
       // the sample row is requested BEFORE the Philox / Box-Muller arithmetic: the HBM latency hides under it
-      if (xvec) {
 #pragma unroll
-        for (int k = 0; k < MAXC; ++k) {
-          const int j = t + k * G;
-          xreg[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (j < nchunk) xreg[k] = ldg4(a.x + b * a.ldx + 4 * j);
-        }
+      for (int k = 0; k < MAXC; ++k) {
+        const int j = t + k * G;
+        xreg[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (j < nchunk) xreg[k] = load_x(j);
       }
 #pragma unroll
       for (int k = 0; k < MAXC; ++k) {
@@ -699,16 +724,13 @@ __global__ void __launch_bounds__(256, 4) jet_inputs_kernel(InputArgs a) {
     }
     const bool exact = a.dir != nullptr;     // injected draws keep the reference's rounding sequence u / ||u|| * eps
     const float inv = a.normalize && !exact ? __fdiv_rn(a.scale, nrm) : 1.f;
-    const float* xrow = a.x + b * a.ldx;
     for (int j = t, k = 0; j < nchunk; j += G, ++k) {
       const int e = 4 * j;
       float4 d, xx;
       if (k == 0) d = dreg[0];
       else if (k == 1) d = dreg[MAXC - 1];
       else d = raw(j);
-      if (xvec) xx = k == 0 ? xreg[0] : k == 1 ? xreg[MAXC - 1] : ldg4(xrow + e);
-      else xx = make_float4(e < D ? __ldg(xrow + e) : 0.f, e + 1 < D ? __ldg(xrow + e + 1) : 0.f, e + 2 < D ? __ldg(xrow + e + 2) : 0.f,
-                            e + 3 < D ? __ldg(xrow + e + 3) : 0.f);
+      xx = k == 0 ? xreg[0] : k == 1 ? xreg[MAXC - 1] : load_x(j);
       float4 v;
       if (!a.normalize) v = d;
       else if (exact) v = make_float4(__fmul_rn(__fdiv_rn(d.x, nrm), a.scale), __fmul_rn(__fdiv_rn(d.y, nrm), a.scale),

@@ -204,16 +204,22 @@ class FusedEnergyMLP(nn.Module):
         self._step_state = st
         return st
 
-    def _jet_loss_and_grad(self, x2, eps, scale, u, v, draw, c1, mean, offset_dev, update=False):
+    def _jet_loss_and_grad(self, x2, eps, scale, u, v, draw, c1, mean, offset_dev, update=False, x_noise=0.0):
         """The same loss and gradient through the difference-propagating chain kernel (fdsm_jet_fd_ssm); `update`: the clipped
         Adam step of configure_optimizer() in the same call (fdsm_jet_update: one fused launch for reduce + clip + Adam)."""
         lib = _lib.load()
         B, D = x2.shape
         st = self._jet_state(B, x2.device)
-        x2 = ops._req(x2, "samples")
-        x2, ldx = ops._rows(x2, "samples")
         a = JetArgs()
-        a.x, a.ldx, a.B = _ptr(x2), ldx, B
+        if x2.dtype == torch.uint8:      # pixels: x = x_u8 / 255 + x_noise * N(0,1), built inside the input kernel
+            if not (x2.is_cuda and x2.is_contiguous()):
+                raise _lib.FdsmError("uint8 samples must be a contiguous CUDA tensor")
+            a.x_u8, a.ldx, a.B = C.c_void_p(x2.data_ptr()), D, B
+            a.x_u8_scale, a.x_noise_std = 1.0 / 255.0, float(x_noise)
+        else:
+            x2 = ops._req(x2, "samples")
+            x2, ldx = ops._rows(x2, "samples")
+            a.x, a.ldx, a.B = _ptr(x2), ldx, B
         keep = [x2]
         d = v if v is not None else u
         if d is not None:
@@ -366,9 +372,10 @@ class FusedEnergyMLP(nn.Module):
         draw = (o["seed"], 0, o["rank"] * st["B"])      # offset = device step counter; rows keyed by the GLOBAL sample index
         if kind == "ssm":
             eps, scale = cfg
-            if update:
+            if update or st["x"].dtype == torch.uint8:
                 x2 = st["x"].reshape(st["x"].shape[0], -1)
-                return self._jet_loss_and_grad(x2, eps, scale, None, None, draw, 2.0, True, o["step"], update=True)
+                return self._jet_loss_and_grad(x2, eps, scale, None, None, draw, 2.0, True, o["step"], update=update,
+                                               x_noise=st.get("x_noise", 0.0))
             return self.fd_ssm_loss_and_grad(st["x"], eps, scale, draw=draw, offset_dev=o["step"])
         eps, sigma02, loss_coe = cfg
         return self.fd_dsm_loss_and_grad(st["x"], st["sigma_b"], eps=eps, sigma02=sigma02, loss_coe=loss_coe, draw=draw,
@@ -384,16 +391,24 @@ class FusedEnergyMLP(nn.Module):
                                  o["betas"][0], o["betas"][1], o["eps"], o["clip"], _ptr(o["sumsq"]), _ptr(o["step"]), s),
               "fdsm_adam_step")
 
-    def fd_ssm_step(self, x, eps, allreduce=None, scale=None, distributed=False, borrow=False):
+    def fd_ssm_step(self, x, eps, allreduce=None, scale=None, distributed=False, borrow=False, x_noise=0.0):
         """One optimisation step of DeepEBM/train_ssm.py:63-69 on a device batch x (B, ...).  Returns the loss (device
         scalar, persistent buffer).  The whole step is ONE CUDA-graph replay -- also for world > 1 when `allreduce` is the
         peer-memory kernel (ddp.PeerAllReduce); with the NCCL library collective it is two replays around the all-reduce.
         `borrow`: the step reads x where it lies instead of copying it into its own input buffer first -- for callers that
-        hand in one of a few long-lived buffers (the trainer's H2D staging pair): one captured graph per buffer address."""
+        hand in one of a few long-lived buffers (the trainer's H2D staging pair): one captured graph per buffer address.
+        A uint8 x is a batch of PIXELS: the input kernel builds x / 255 + x_noise * N(0,1) (torchvision ToTensor and the
+        noise of DeepEBM/train_ssm.py:62) on the fly -- the host ships one byte per pixel."""
         x2 = x.reshape(x.shape[0], -1)
         st = self._jet_state(x2.shape[0], x2.device) if self.formulation == "jet" else self._state(x2.shape[0], x2.device)
         scale = 1.0 / eps ** 2 if scale is None else scale
-        if borrow and x2.is_contiguous() and x2.dtype == torch.float32:
+        if x2.dtype == torch.uint8:
+            if self.formulation != "jet":
+                raise NotImplementedError("uint8 pixel batches need the difference-propagating path (formulation='jet')")
+            if not borrow:
+                raise ValueError("uint8 pixel batches are read where they lie: pass borrow=True")
+            st["x"], st["x_noise"], xkey = x2, float(x_noise), (x2.data_ptr(), float(x_noise))
+        elif borrow and x2.is_contiguous() and x2.dtype == torch.float32:
             st["x"], xkey = x2, x2.data_ptr()
         else:
             if st.get("x_own") is None:

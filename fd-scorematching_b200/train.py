@@ -85,7 +85,7 @@ class FDSSMTrainer:
                                "rank are no longer trustworthy -- restart from the last checkpoint")
 
     # -- one optimisation step on a device-resident batch ------------------------------------------
-    def step(self, x, borrow=False):
+    def step(self, x, borrow=False, x_noise=0.0):
         self._nstep += 1
         if self._nstep % self.peer_check_every == 0:
             self.check_exchange()
@@ -103,6 +103,8 @@ class FDSSMTrainer:
             kw = {} if self.scale is None else {"scale": self.scale}
             if borrow:
                 kw["borrow"] = True
+            if x.dtype == torch.uint8:
+                kw["x_noise"] = x_noise
             return self.net.fd_ssm_step(x, eps=self.eps, allreduce=self._allreduce, distributed=ddp.is_distributed(), **kw)
         self.flat.zero_grad()
         if sig is not None:
@@ -122,7 +124,15 @@ class FDSSMTrainer:
         return loss.detach()
 
     # -- end-to-end: host batch in pinned memory -> loss on the host --------------------------------
-    def step_from_host(self, x_host, loss_host):
+    def step_from_host_u8(self, x_host_u8, loss_host, noise_std):
+        """The same end-to-end step for a pinned host batch of uint8 PIXELS (what the reference's loaders hold before
+        ToTensor): 1 byte per pixel over the link instead of 4; x / 255 + noise_std * N(0,1) (DeepEBM/train_ssm.py:61-62)
+        is built on the device inside the step's input kernel.  ssm_fd on the fused difference-propagating net only."""
+        if x_host_u8.dtype != torch.uint8:
+            raise ValueError("step_from_host_u8 takes a uint8 batch")
+        return self.step_from_host(x_host_u8, loss_host, x_noise=noise_std)
+
+    def step_from_host(self, x_host, loss_host, x_noise=0.0):
         """H2D copy of this step's batch (pinned -> device, on a side stream, double-buffered against the
         previous step's compute), the step, and an async D2H read of the loss into `loss_host` (pinned)."""
         cur = torch.cuda.current_stream()
@@ -143,7 +153,7 @@ class FDSSMTrainer:
             self._evt[i].record(self._copy_stream)
         cur.wait_event(self._evt[i])
         # the fused ssm_fd step reads the staging buffer where it lies (one captured graph per staging buffer): no D2D copy
-        loss = self.step(self._bufs[i], borrow=self.fused and self.loss_name == "ssm_fd")
+        loss = self.step(self._bufs[i], borrow=self.fused and self.loss_name == "ssm_fd", x_noise=x_noise)
         self._free[i].record(cur)
         loss_host.copy_(loss, non_blocking=True)
         return loss_host

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define FDSM_ABI_VERSION 6
+#define FDSM_ABI_VERSION 7
 
 #define FDSM_OK 0
 #define FDSM_ERR_INVALID_ARGUMENT (-1)
@@ -279,6 +279,12 @@ typedef struct fdsm_jet_args {
                                                       (measurement: bench.py's roofline of the dominant kernel)         */
   void* trace;                                     /* optional debug buffer: tiles x 38 uint64 %globaltimer stamps of the chain
                                                       kernel's phases (scripts/chain_trace.py); NULL in production      */
+  const uint8_t* x_u8; float x_u8_scale; float x_noise_std;
+                                                   /* x_u8 != NULL replaces x (ldx = its row stride in BYTES): the samples are
+                                                      x_u8 * x_u8_scale + x_noise_std * N(0,1) (Philox stream 1, row / offset as
+                                                      the direction) -- torchvision's ToTensor (1/255) and the on-device noise
+                                                      of DeepEBM/train_ssm.py:62 fused into the input build, so that the host
+                                                      ships one byte per pixel                                           */
   const fdsm_jet_update* update;                   /* NULL: loss + gradient only.  Non-NULL: the parameters (`params`, written
                                                       in place) take the clipped Adam step in the same call              */
 } fdsm_jet_args;

@@ -172,3 +172,26 @@ def test_jet_fused_update_matches_the_separate_kernels(fdsm, monkeypatch):
     assert np.allclose(la, lb, rtol=1e-5, atol=0)
     assert float((ga - gb).norm() / gb.norm()) <= 1e-5
     assert float((pa - pb).norm() / pb.norm()) <= 1e-6
+
+
+def test_jet_uint8_pixels_equal_the_explicit_float_batch(fdsm):
+    """x_u8 / 255 + ssm_eps * N(0,1) built inside the input kernel (fdsm_jet_args.x_u8; DeepEBM/train_ssm.py:61-62 on uint8
+    pixels) against the same batch built explicitly in fp32 from the same Philox stream: same loss and gradient up to the
+    one fused multiply-add per element."""
+    from fdsm_b200 import ops
+    B, D = 200, 64
+    net, _ = _pair(fdsm, D, 48, 3, "nsoftplus", "quadratic")
+    x8 = torch.randint(0, 256, (B, D), dtype=torch.uint8, device=DEV)
+    draw = (77, 5, 1000)
+    n = ops.philox_normal(B, D, 1, draw[0], draw[1], row0=draw[2], device=DEV)
+    xf = x8.float() * (1.0 / 255.0) + 0.005 * n
+    la, ga = net._jet_loss_and_grad(x8, 0.05, 400.0, None, None, draw, 2.0, True, None, x_noise=0.005)
+    la, ga = la.clone(), ga.clone()
+    lb, gb = net._jet_loss_and_grad(xf, 0.05, 400.0, None, None, draw, 2.0, True, None)
+    assert abs(float(la) - float(lb)) <= 1e-5 * max(abs(float(lb)), 1e-12) + 1e-9
+    assert _relv(ga, gb) <= 1e-4
+    # and through the training step (graph replay, borrowed staging buffer)
+    net.configure_optimizer(lr=1e-3, betas=(0.9, 0.95), clip=0.1, use_graph=True, seed=3)
+    l1 = float(net.fd_ssm_step(x8, eps=0.05, borrow=True, x_noise=0.005))
+    l2 = float(net.fd_ssm_step(x8, eps=0.05, borrow=True, x_noise=0.005))
+    assert np.isfinite(l1) and np.isfinite(l2) and int(net._opt["step"]) == 2
