@@ -616,6 +616,8 @@ def main():
         }
         if use_fused:
             out["roofline_fd_kernel"] = fd_roof
+            import bench_configs
+            out["roofline_fd_kernels"] = bench_configs.fd_kernel_rooflines(dev, pk)
         if e2e_u8_ms is not None:
             out["e2e_u8"] = {"value": B_PER_GPU * world * args.steps / (e2e_u8_ms * 1e-3), "unit": "samples/s",
                              "h2d_bytes_per_step": B_PER_GPU * D, "d2h_bytes_per_step": 4, "ms_per_step": e2e_u8_ms / args.steps,

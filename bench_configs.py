@@ -182,3 +182,56 @@ def cpu_baseline(cfg_id, budget_s=15.0):
             break
     return {"value": b * n / dt, "unit": "samples/s", "cores": cores, "kind": "port",
             "sample": f"{n} steps at B={b} (of the config's B={cfg['B']}) on the torch-CPU oracle port, {dt:.1f}s, {cores} threads"}
+
+
+def fd_kernel_rooflines(device, pk, shapes=((4096, 784, "cfg2"), (65536, 784, "saturating, 205 MB in"))):
+    """HBM rooflines of the three FD kernels of the generic mode -- the 3-row energy stack, the noised 2-row stack of the
+    score form and the fused score combine (forward + ds) -- graph-timed (20 launches per replay, no host gaps) on
+    rotating inputs AND outputs larger than L2.  Algorithmic bytes per sample: 16 D, 12 D, 20 D."""
+    from fdsm_b200 import ops
+    out = {}
+    for B, D, tag in shapes:
+        nbuf = max(3, min(8, int(300e6 // (B * D * 4)) + 1))
+        xs = [torch.rand(B, D, device=device) for _ in range(nbuf)]
+        o3 = [torch.empty(3 * B, D, device=device) for _ in range(max(2, nbuf // 2))]
+        o2 = [torch.empty(2 * B, D, device=device) for _ in range(max(2, nbuf // 2))]
+        sig = torch.exp(torch.linspace(3.9, -4.6, 232)).to(device)
+        labels = torch.randint(0, 232, (B,), device=device)
+        ss = [torch.randn(2 * B, D, device=device) for _ in range(max(2, nbuf // 2))]
+        v = torch.randn(B, D, device=device) * 0.01
+
+        def timed(fn, n=20, reps=3):
+            gs = torch.cuda.Stream()
+            gs.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(gs):
+                fn(0)
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=gs):
+                    for i in range(n):
+                        fn(i)
+                g.replay()
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(gs)
+                for _ in range(reps):
+                    g.replay()
+                e1.record(gs)
+                torch.cuda.synchronize()
+            torch.cuda.current_stream().wait_stream(gs)
+            return e0.elapsed_time(e1) * 1e3 / (n * reps)
+
+        kernels = {
+            "stack3_energy": (16.0, lambda i: ops.stack(xs[i % nbuf], row_mask=7, scale=0.05, out=o3[i % len(o3)], draw=(7, i, 0))),
+            "stack2_noised": (12.0, lambda i: ops.stack(xs[i % nbuf], row_mask=6, scale=0.1, sigma=sig, labels=labels, perturb=True,
+                                                        out=o2[i % len(o2)], draw=(7, i, 0))),
+            "combine_score_fused": (20.0, lambda i: ops.combine_score_fused(ss[i % len(ss)], v, k=D / 0.02, sigma=sig, labels=labels)),
+        }
+        for name, (bps, fn) in kernels.items():
+            us = timed(fn)
+            alg = bps * D * B
+            out[f"{name} B={B} D={D} ({tag})"] = {"bound": "hbm", "avg_launch_us": us, "algorithmic_bytes_per_launch": alg,
+                                                 "achieved": alg / us / 1e3, "peak": pk["hbm_gbs"], "unit": "GB/s",
+                                                 "frac": alg / us / 1e3 / pk["hbm_gbs"]}
+        del xs, o3, o2, ss
+        torch.cuda.empty_cache()
+    return out
