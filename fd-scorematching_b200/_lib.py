@@ -53,7 +53,7 @@ class JetArgs(C.Structure):
         ("c1", _f32), ("scale", _f32), ("mean", _i32),
         ("loss", _f32p), ("grads", _f32p), ("accumulate", _i32),
         ("ev_chain_start", C.c_void_p), ("ev_chain_stop", C.c_void_p), ("trace", C.c_void_p),
-        ("x_u8", C.c_void_p), ("x_u8_scale", _f32), ("x_noise_std", _f32), ("update", C.c_void_p),
+        ("x_u8", C.c_void_p), ("x_u8_scale", _f32), ("x_noise_std", _f32), ("mode", _i32), ("update", C.c_void_p),
     ]
 
 
@@ -82,7 +82,7 @@ class MlpDesc(C.Structure):
                 ("presplit", _i32)]
 
 
-ABI_VERSION = 7    # FDSM_ABI_VERSION of include/fdsm.h
+ABI_VERSION = 8    # FDSM_ABI_VERSION of include/fdsm.h
 
 # name -> (restype, argtypes); must list every symbol include/fdsm.h declares
 PROTOTYPES = {

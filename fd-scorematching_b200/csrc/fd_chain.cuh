@@ -98,13 +98,13 @@ __device__ __forceinline__ void sts(uint8_t* p, float v) { *reinterpret_cast<flo
 // ---- Columns >= H need no masking: their pre-activations are exact zeros (zero-padded weight columns, zero-filled by the
 // ---- dump beyond npad), everything computed from them is finite, and every consumer multiplies it by a zero weight row /
 // ---- column or ignores it -- except column H of a hidden layer's output, the ones column that carries the next bias.
-template <int ACT>
+template <int ACT, int MODE>
 __device__ __forceinline__ void epi_fwd_hidden(uint8_t* const (&e)[2], bool v1, int sst, bool ones, float off) {
   float z[2], P[2], Q[2];
   Jet o[2];
 #pragma unroll
   for (int n = 0; n < 2; ++n) { z[n] = lds(e[n]); P[n] = lds(e[n] + sst); Q[n] = lds(e[n] + 2 * sst); }
-  jet_fwd_n<ACT, 2>(z, P, Q, off, o);
+  jet_fwd_n<ACT, MODE, 2>(z, P, Q, off, o);
 #pragma unroll
   for (int n = 0; n < 2; ++n) {
     if (n == 0 || v1) {
@@ -116,7 +116,7 @@ __device__ __forceinline__ void epi_fwd_hidden(uint8_t* const (&e)[2], bool v1, 
 }
 
 // last forward layer, pass 1: jets (kept unrounded in place) and the head's nine sums per sample
-template <int ACT>
+template <int ACT, int MODE>
 __device__ __forceinline__ void epi_head_pass1(uint8_t* const (&e0)[2], bool v1, int sst, int ablk, int NA, int lane, const float* hw,
                                                bool quad, float off, float (&sum)[2][9]) {
 #pragma unroll
@@ -134,7 +134,7 @@ __device__ __forceinline__ void epi_head_pass1(uint8_t* const (&e0)[2], bool v1,
       const uint8_t* e = e0[n] + j * ablk;
       z[n] = lds(e); P[n] = lds(e + sst); Q[n] = lds(e + 2 * sst);
     }
-    jet_fwd_n<ACT, 2>(z, P, Q, off, o);
+    jet_fwd_n<ACT, MODE, 2>(z, P, Q, off, o);
 #pragma unroll
     for (int n = 0; n < 2; ++n) {
       uint8_t* e = e0[n] + j * ablk;
@@ -142,8 +142,13 @@ __device__ __forceinline__ void epi_head_pass1(uint8_t* const (&e0)[2], bool v1,
       sum[n][0] = fmaf(w1, o[n].h0, sum[n][0]); sum[n][1] = fmaf(w1, o[n].a, sum[n][1]); sum[n][2] = fmaf(w1, o[n].b, sum[n][2]);
       if (quad) {
         sum[n][3] = fmaf(w2, o[n].h0, sum[n][3]); sum[n][4] = fmaf(w2, o[n].a, sum[n][4]); sum[n][5] = fmaf(w2, o[n].b, sum[n][5]);
-        sum[n][6] = fmaf(wq, o[n].a * (o[n].b + o[n].h0), sum[n][6]);
-        sum[n][7] = fmaf(wq, fmaf(o[n].b, o[n].b, fmaf(o[n].a, o[n].a, 2.f * o[n].h0 * o[n].b)), sum[n][7]);
+        if constexpr (MODE == JMODE_TAYLOR) {
+          sum[n][6] = fmaf(wq, o[n].a * o[n].h0, sum[n][6]);
+          sum[n][7] = fmaf(wq, fmaf(o[n].a, o[n].a, 2.f * o[n].h0 * o[n].b), sum[n][7]);
+        } else {
+          sum[n][6] = fmaf(wq, o[n].a * (o[n].b + o[n].h0), sum[n][6]);
+          sum[n][7] = fmaf(wq, fmaf(o[n].b, o[n].b, fmaf(o[n].a, o[n].a, 2.f * o[n].h0 * o[n].b)), sum[n][7]);
+        }
         sum[n][8] = fmaf(wq, o[n].h0 * o[n].h0, sum[n][8]);
       }
     }
@@ -157,9 +162,37 @@ __device__ __forceinline__ void epi_head_pass1(uint8_t* const (&e0)[2], bool v1,
 
 // from the nine sums of a sample: its loss term and the coefficients of the head backward (oracle/jet.py quadratic_head_jet)
 //   cs[0..3] = G1h G1a G1b gd   cs[4..7] = G2h G2a G2b gs   cs[8] = ge
+template <int MODE>
 __device__ __forceinline__ float head_sample(const float (&sum)[9], bool quad, float b1, float b2, float bq, float c1, float cf,
                                              bool lane0, float* cs, float& gb1, float& gb2, float& gbq) {
   const float l1 = sum[0] + b1, A1 = sum[1], B1 = sum[2], l2 = sum[3] + b2, A2 = sum[4], B2 = sum[5];
+  if constexpr (MODE == JMODE_TAYLOR) {
+    // exact SSM: d1 = E', d2h = E''/2;  loss_b = d1^2 / 2 - 2 d2h;  gd = dL/dd1, gs = dL/dd2h, no E0 term
+    float d1, d2h;
+    if (quad) {
+      d1 = A1 * l2 + l1 * A2 + 2.f * sum[6];
+      d2h = B1 * l2 + A1 * A2 + l1 * B2 + sum[7];
+    } else {
+      d1 = A1; d2h = B1;
+    }
+    const float gd = cf * d1, gs = -2.f * cf;
+    float G1h, G2h, G1a, G2a, G1b, G2b;
+    if (quad) {
+      G1h = gd * A2 + gs * B2; G2h = gd * A1 + gs * B1;
+      G1a = gd * l2 + gs * A2; G2a = gd * l1 + gs * A1;
+      G1b = gs * l2;           G2b = gs * l1;
+    } else {
+      G1h = 0.f; G1a = gd; G1b = gs; G2h = G2a = G2b = 0.f;
+    }
+    gb1 += G1h; gb2 += G2h;
+    if (lane0) {
+      float4* c4 = reinterpret_cast<float4*>(cs);
+      c4[0] = make_float4(G1h, G1a, G1b, gd);
+      c4[1] = make_float4(G2h, G2a, G2b, gs);
+      c4[2] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    return 0.5f * d1 * d1 - 2.f * d2h;
+  }
   float dE, sE, E0;
   if (quad) {
     dE = 2.f * (A1 * (l2 + B2) + A2 * (l1 + B1)) + 4.f * sum[6];
@@ -188,7 +221,7 @@ __device__ __forceinline__ float head_sample(const float (&sum)[9], bool quad, f
 }
 
 // last forward layer, pass 2, one block: gradient w.r.t. the jets, head-weight gradient terms, activation backward -> dZ
-template <int ACT>
+template <int ACT, int MODE>
 __device__ __forceinline__ void epi_head_pass2(uint8_t* const (&e)[2], bool v1, int sst, float w1, float w2, float wq,
                                                const float* const (&cs)[2], bool quad, float off, float& gw1, float& gw2, float& gwq) {
   Jet o[2];
@@ -203,15 +236,22 @@ __device__ __forceinline__ void epi_head_pass2(uint8_t* const (&e)[2], bool v1, 
     const float use = (n == 0 || v1) ? 1.f : 0.f;      // the stand-in second sample adds nothing to the weight gradients
     gw1 += use * (G1h * o[n].h0 + G1a * o[n].a + G1b * o[n].b);
     if (quad) {
-      g0[n] += G2h * w2 + wq * (4.f * gd * o[n].a + 4.f * gs * o[n].b + 2.f * ge * o[n].h0);
-      ga[n] += G2a * w2 + wq * 4.f * (gd * (o[n].b + o[n].h0) + gs * o[n].a);
-      gb[n] += G2b * w2 + wq * 4.f * (gd * o[n].a + gs * (o[n].b + o[n].h0));
       gw2 += use * (G2h * o[n].h0 + G2a * o[n].a + G2b * o[n].b);
-      gwq += use * (4.f * gd * o[n].a * (o[n].b + o[n].h0) +
-                    2.f * gs * fmaf(o[n].b, o[n].b, fmaf(o[n].a, o[n].a, 2.f * o[n].h0 * o[n].b)) + ge * o[n].h0 * o[n].h0);
+      if constexpr (MODE == JMODE_TAYLOR) {
+        g0[n] += G2h * w2 + wq * 2.f * (gd * o[n].a + gs * o[n].b);
+        ga[n] += G2a * w2 + wq * 2.f * (gd * o[n].h0 + gs * o[n].a);
+        gb[n] += G2b * w2 + wq * 2.f * gs * o[n].h0;
+        gwq += use * (2.f * gd * o[n].h0 * o[n].a + gs * fmaf(o[n].a, o[n].a, 2.f * o[n].h0 * o[n].b));
+      } else {
+        g0[n] += G2h * w2 + wq * (4.f * gd * o[n].a + 4.f * gs * o[n].b + 2.f * ge * o[n].h0);
+        ga[n] += G2a * w2 + wq * 4.f * (gd * (o[n].b + o[n].h0) + gs * o[n].a);
+        gb[n] += G2b * w2 + wq * 4.f * (gd * o[n].a + gs * (o[n].b + o[n].h0));
+        gwq += use * (4.f * gd * o[n].a * (o[n].b + o[n].h0) +
+                      2.f * gs * fmaf(o[n].b, o[n].b, fmaf(o[n].a, o[n].a, 2.f * o[n].h0 * o[n].b)) + ge * o[n].h0 * o[n].h0);
+      }
     }
   }
-  jet_bwd_n<ACT, 2>(o, off, g0, ga, gb, dz0, dP, dQ);
+  jet_bwd_n<ACT, MODE, 2>(o, off, g0, ga, gb, dz0, dP, dQ);
 #pragma unroll
   for (int n = 0; n < 2; ++n)
     if (n == 0 || v1) { sts(e[n], tf32r(dz0[n])); sts(e[n] + sst, tf32r(dP[n])); sts(e[n] + 2 * sst, tf32r(dQ[n])); }
@@ -219,7 +259,7 @@ __device__ __forceinline__ void epi_head_pass2(uint8_t* const (&e)[2], bool v1, 
 
 // dgrad epilogue, one block: rows hold dL/dH_l as (g0, ga, gb); H_l (hp[n]: the sample's h0 element in HBM / L2; the a / b
 // streams `hstride` floats further) -> dZ_{l-1}
-template <int ACT>
+template <int ACT, int MODE>
 __device__ __forceinline__ void epi_dgrad(uint8_t* const (&e)[2], bool v1, int sst, const float* const (&hp)[2], long long hstride,
                                           float off) {
   Jet o[2];
@@ -228,13 +268,13 @@ __device__ __forceinline__ void epi_dgrad(uint8_t* const (&e)[2], bool v1, int s
   for (int n = 0; n < 2; ++n) o[n] = Jet{__ldcg(hp[n]), __ldcg(hp[n] + hstride), __ldcg(hp[n] + 2 * hstride)};
 #pragma unroll
   for (int n = 0; n < 2; ++n) { g0[n] = lds(e[n]); ga[n] = lds(e[n] + sst); gb[n] = lds(e[n] + 2 * sst); }
-  jet_bwd_n<ACT, 2>(o, off, g0, ga, gb, dz0, dP, dQ);
+  jet_bwd_n<ACT, MODE, 2>(o, off, g0, ga, gb, dz0, dP, dQ);
 #pragma unroll
   for (int n = 0; n < 2; ++n)
     if (n == 0 || v1) { sts(e[n], tf32r(dz0[n])); sts(e[n] + sst, tf32r(dP[n])); sts(e[n] + 2 * sst, tf32r(dQ[n])); }
 }
 
-template <int ACT, int PASSES, int CL>
+template <int ACT, int PASSES, int CL, int MODE>
 __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ ChainParams p) {
   using namespace ptx;
   extern __shared__ uint8_t smem_raw[];
@@ -512,7 +552,7 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
             const bool v1 = k0 + 1 < spw;
             uint8_t* e0 = ebase(warp + EPI_WARPS * k0) + j * ablk;
             uint8_t* e[2] = {e0, v1 ? e0 + EPI_WARPS * 128 : e0};     // 16 rows further: same row & 7, same swizzle term
-            epi_fwd_hidden<ACT>(e, v1, sst, ones, off);
+            epi_fwd_hidden<ACT, MODE>(e, v1, sst, ones, off);
           }
           publish(j);
         }
@@ -523,7 +563,7 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
         float gb1 = 0.f, gb2 = 0.f, gbq = 0.f, loss_acc = 0.f;
         auto sample_done = [&](const float (&sum)[9], int i) {
           const bool valid = tile * S + i < p.B;
-          const float l = head_sample(sum, quad, b1, b2, bq, p.c1, valid ? p.coef : 0.f, lane == 0, coef_s + i * NCOEF, gb1, gb2, gbq);
+          const float l = head_sample<MODE>(sum, quad, b1, b2, bq, p.c1, valid ? p.coef : 0.f, lane == 0, coef_s + i * NCOEF, gb1, gb2, gbq);
           if (valid) loss_acc += l;
         };
 #pragma unroll 1
@@ -533,7 +573,7 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
           uint8_t* e0 = ebase(i0);
           uint8_t* e[2] = {e0, v1 ? e0 + EPI_WARPS * 128 : e0};
           float sum[2][9];
-          epi_head_pass1<ACT>(e, v1, sst, ablk, NA, lane, hw, quad, off, sum);
+          epi_head_pass1<ACT, MODE>(e, v1, sst, ablk, NA, lane, hw, quad, off, sum);
           sample_done(sum[0], i0);
           if (v1) sample_done(sum[1], i0 + EPI_WARPS);
         }
@@ -553,7 +593,7 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
             uint8_t* e[2] = {e0, v1 ? e0 + EPI_WARPS * 128 : e0};
             const float* c0 = coef_s + i0 * NCOEF;
             const float* cs[2] = {c0, v1 ? c0 + EPI_WARPS * NCOEF : c0};
-            epi_head_pass2<ACT>(e, v1, sst, w1, w2, wq, cs, quad, off, s1, s2, sq);
+            epi_head_pass2<ACT, MODE>(e, v1, sst, w1, w2, wq, cs, quad, off, s1, s2, sq);
           }
           gw1[j] = s1; gw2[j] = s2; gwq[j] = sq;
           publish(j);
@@ -602,7 +642,7 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
             uint8_t* e[2] = {e0, v1 ? e0 + EPI_WARPS * 128 : e0};
             const float* h0 = hcol + i0 * ldh + 32 * j;
             const float* hp[2] = {h0, v1 ? h0 + EPI_WARPS * ldh : h0};
-            epi_dgrad<ACT>(e, v1, sst, hp, hstride, off);
+            epi_dgrad<ACT, MODE>(e, v1, sst, hp, hstride, off);
           }
           publish(j);
         }

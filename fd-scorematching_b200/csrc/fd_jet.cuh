@@ -233,10 +233,61 @@ __device__ __noinline__ void softplus_jet_bwd_any(const Jet* o, float offset, fl
   softplus_jet_bwd(*o, offset, g0, ga, gb, d[0], d[1], d[2]);
 }
 
+// ---- exact sliced score matching: the same three streams as an order-2 Taylor jet of tau -> h(x + tau u) --------------------
+// (h0, a, b) = (h, h', h''/2):  z0 = W h0 + bias, P = W a, Q = W b as before; the activation rule becomes
+//     a' = s1 P          b' = 1/2 s2 P^2 + s1 Q          (s1, s2, s3: first three derivatives of the activation at z0)
+// (the eps -> 0 limit of the finite-difference rule above), and the backward from the OUTPUTS needs no division:
+//     s2 P = (1 - s0) a' ,   1/2 s3 P^2 + s2 Q = (1 - s0)(b' - a'^2 / 2)         (softplus: s1 = s0 = sigmoid(z0))
+//     dz0 = s1 g0 + (s2 P) ga + (1/2 s3 P^2 + s2 Q) gb      dP = s1 ga + (s2 P) gb      dQ = s1 gb
+// Reference: SSM/losses/sliced_sm.py:7-34, DeepEBM/ESM/loss_train.py:173-189 (double backward); oracle/forward_mode.py.
+enum : int { JMODE_FD = 0, JMODE_TAYLOR = 1 };
+template <int ACT>
+__device__ __forceinline__ Jet taylor_fwd(float z0, float P, float Q, float offset) {
+  Jet o;
+  if constexpr (ACT == JACT_ELU) {
+    const float e = ex2a(fminf(z0, 0.f) * LOG2E);
+    const bool pos = z0 > 0.f;
+    o.h0 = pos ? z0 : expm1_j(z0);
+    o.a = pos ? P : e * P;
+    o.b = pos ? Q : e * fmaf(0.5f * P, P, Q);
+  } else {
+    const float t = ex2a(-fabsf(z0) * LOG2E);
+    const float r = rcp_a(1.f + t);
+    const float s0 = z0 >= 0.f ? r : t * r, e0 = z0 >= 0.f ? t * r : r;
+    o.h0 = fmaf(lg2a(1.f + t), LN2, fmaxf(z0, 0.f)) - offset;
+    o.a = s0 * P;
+    o.b = s0 * fmaf(0.5f * e0 * P, P, Q);
+  }
+  return o;
+}
+template <int ACT>
+__device__ __forceinline__ void taylor_bwd(const Jet& o, float offset, float g0, float ga, float gb, float& dz0, float& dP, float& dQ) {
+  float d1, S1, S2;
+  if constexpr (ACT == JACT_ELU) {
+    const bool pos = o.h0 > 0.f;
+    d1 = pos ? 1.f : o.h0 + 1.f;
+    S1 = pos ? 0.f : o.a;
+    S2 = pos ? 0.f : o.b;
+  } else {
+    const float e0 = ex2a(-(o.h0 + offset) * LOG2E);
+    d1 = 1.f - e0;
+    S1 = e0 * o.a;
+    S2 = e0 * fmaf(-0.5f * o.a, o.a, o.b);
+  }
+  dz0 = fmaf(d1, g0, fmaf(S1, ga, S2 * gb));
+  dP = fmaf(d1, ga, S1 * gb);
+  dQ = d1 * gb;
+}
+
 // N independent elements at once: one test for the main path, then N straight-line evaluations the compiler can interleave
 // (the epilogues are latency-bound on a single element's dependency chain)
-template <int ACT, int N>
+template <int ACT, int MODE, int N>
 __device__ __forceinline__ void jet_fwd_n(const float (&z0)[N], const float (&P)[N], const float (&Q)[N], float offset, Jet (&o)[N]) {
+  if constexpr (MODE == JMODE_TAYLOR) {
+#pragma unroll
+    for (int n = 0; n < N; ++n) o[n] = taylor_fwd<ACT>(z0[n], P[n], Q[n], offset);
+    return;
+  }
   float m = 0.f;
 #pragma unroll
   for (int n = 0; n < N; ++n) m = fmaxf(m, fmaxf(fabsf(P[n]), fabsf(Q[n])));
@@ -251,10 +302,13 @@ __device__ __forceinline__ void jet_fwd_n(const float (&z0)[N], const float (&P)
     for (int n = 0; n < N; ++n) jet_fwd_any<ACT>(z0[n], P[n], Q[n], offset, &o[n]);
   }
 }
-template <int ACT, int N>
+template <int ACT, int MODE, int N>
 __device__ __forceinline__ void jet_bwd_n(const Jet (&o)[N], float offset, const float (&g0)[N], const float (&ga)[N],
                                           const float (&gb)[N], float (&dz0)[N], float (&dP)[N], float (&dQ)[N]) {
-  if constexpr (ACT == JACT_ELU) {
+  if constexpr (MODE == JMODE_TAYLOR) {
+#pragma unroll
+    for (int n = 0; n < N; ++n) taylor_bwd<ACT>(o[n], offset, g0[n], ga[n], gb[n], dz0[n], dP[n], dQ[n]);
+  } else if constexpr (ACT == JACT_ELU) {
 #pragma unroll
     for (int n = 0; n < N; ++n) elu_jet_bwd(o[n], g0[n], ga[n], gb[n], dz0[n], dP[n], dQ[n]);
   } else {

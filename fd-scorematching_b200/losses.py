@@ -240,7 +240,8 @@ def anneal_ESM_scorenet_VR(scorenet, samples, sigmas, labels=None, anneal_power=
 # ------------------------------------------------------------------------------------------------
 # a17: the exact (Hessian-vector-product) sliced score matching losses the FD objectives are compared against
 # (BASELINE.json config 2 "FD-SSM vs exact SSM").  Generic mode only: the two autograd.grad(create_graph=True) passes
-# run through the caller's torch network (a fused forward-mode kernel for our MLP energies is SURVEY.md §8f row N2);
+# run through the caller's torch network; for our fused MLP energies `ssm` runs in forward mode inside the chain kernel
+# (mlp.FusedEnergyMLP.exact_ssm_loss_and_grad, no double backward);
 # the projection vectors come from kernel (1) (Philox normals; sign / sphere variants derived from the same draw).
 # ------------------------------------------------------------------------------------------------
 def _projection_vectors(x2, noise_type, u):
@@ -292,6 +293,8 @@ def ssm(energy, x, *, batch_size=None, u=None):
     """DeepEBM/ESM/loss_train.py:173-189 (Gaussian projections, x viewed as (FLAGS.batch_size, dim))."""
     bs = batch_size if batch_size is not None else (FLAGS.batch_size or x.shape[0])
     x2 = x.reshape(bs, -1)
+    if getattr(energy, "formulation", None) == "jet":      # mlp.FusedEnergyMLP: forward mode in the chain kernel (N2)
+        return energy.exact_ssm_loss(x2, u=u)
     per, _, _ = _ssm_hvp(energy, x2, _projection_vectors(x2, "gaussian", u), vr=False)
     return per.mean()
 

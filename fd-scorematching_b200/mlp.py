@@ -76,6 +76,22 @@ class _MlpFunction(torch.autograd.Function):
         return g, None, None
 
 
+class _ExactSsmFunction(torch.autograd.Function):
+    """loss = mean_b[(u.grad E)^2/2 - u' Hess E u] through FusedEnergyMLP.exact_ssm_loss_and_grad; the flat parameter vector
+    is the only differentiable input (the objective's derivatives w.r.t. x are carried forward inside the kernel)."""
+
+    @staticmethod
+    def forward(ctx, flat, x, u, net, draw, scale, noise_type):
+        loss, grad = net.exact_ssm_loss_and_grad(x, u=u, draw=draw, scale=scale, noise_type=noise_type)
+        ctx.save_for_backward(grad.clone())
+        return loss.clone()
+
+    @staticmethod
+    def backward(ctx, gout):
+        (grad,) = ctx.saved_tensors
+        return grad * gout, None, None, None, None, None, None
+
+
 class FusedEnergyMLP(nn.Module):
     def __init__(self, in_dim, hidden, n_hidden=3, act="nsoftplus", head="quadratic", device="cuda", seed=None, passes=3,
                  presplit=False, formulation="auto", jet_passes=2):
@@ -204,7 +220,8 @@ class FusedEnergyMLP(nn.Module):
         self._step_state = st
         return st
 
-    def _jet_loss_and_grad(self, x2, eps, scale, u, v, draw, c1, mean, offset_dev, update=False, x_noise=0.0):
+    def _jet_loss_and_grad(self, x2, eps, scale, u, v, draw, c1, mean, offset_dev, update=False, x_noise=0.0, mode=0,
+                           normalize=None):
         """The same loss and gradient through the difference-propagating chain kernel (fdsm_jet_fd_ssm); `update`: the clipped
         Adam step of configure_optimizer() in the same call (fdsm_jet_update: one fused launch for reduce + clip + Adam)."""
         lib = _lib.load()
@@ -226,7 +243,8 @@ class FusedEnergyMLP(nn.Module):
             d, ldd = ops._rows(ops._req(d.reshape(B, -1), "direction"), "direction")
             a.dir, a.lddir = _ptr(d), ldd
             keep.append(d)
-        a.normalize_dir, a.dir_scale = int(v is None), float(eps if v is None else 1.0)
+        norm = (v is None) if normalize is None else bool(normalize)
+        a.normalize_dir, a.dir_scale, a.mode = int(norm), float(eps if norm else 1.0), int(mode)
         seed, offset, row0 = draw if draw is not None else ops.next_draw()
         a.seed, a.offset, a.row0 = seed, offset, row0
         if offset_dev is not None:
@@ -260,6 +278,26 @@ class FusedEnergyMLP(nn.Module):
             hook.append((e0, e1))
         st["_keep"] = keep
         return st["loss"], st["grad"]
+
+    def exact_ssm_loss_and_grad(self, x, *, u=None, draw=None, scale=1.0, mean=True, noise_type="gaussian", offset_dev=None):
+        """EXACT sliced score matching, loss = scale * mean_b[(u.grad E)^2 / 2 - u' Hess E u] (SSM/losses/sliced_sm.py:7-34
+        single_sliced_score_matching; DeepEBM/ESM/loss_train.py:173-189 ssm), and its gradient w.r.t. the flat parameters --
+        in FORWARD mode through the chain kernel (fdsm_jet_args.mode = 1: the streams carry h, dh/dtau, 1/2 d2h/dtau2 of
+        tau -> h(x + tau u)), no double backward.  `u`: the projection vectors (B, D) as given, or None: Philox N(0,1) rows
+        ("gaussian"), scaled to norm sqrt(D) for noise_type "sphere" (sliced_sm.py:14-15)."""
+        if self.formulation != "jet":
+            raise NotImplementedError("exact SSM in forward mode needs the chain kernel (hidden <= 223, n_hidden <= 5)")
+        x2 = x.reshape(x.shape[0], -1)
+        if noise_type not in ("gaussian", "sphere"):
+            raise ValueError("noise_type must be 'gaussian' or 'sphere' (pass sign vectors as `u` for 'radermacher')")
+        sphere = u is None and noise_type == "sphere"
+        return self._jet_loss_and_grad(x2, math.sqrt(x2.shape[1]) if sphere else 1.0, scale, None, u, draw, 2.0, mean, offset_dev,
+                                       mode=1, normalize=sphere)
+
+    def exact_ssm_loss(self, x, *, u=None, draw=None, scale=1.0, noise_type="gaussian"):
+        """The exact-SSM loss as an autograd scalar (its backward feeds `self.flat.grad`): what losses.ssm returns for a
+        fused net."""
+        return _ExactSsmFunction.apply(self.flat, x, u, self, draw, float(scale), noise_type)
 
     def fd_ssm_loss_and_grad(self, x, eps, scale, *, u=None, v=None, draw=None, c1=2.0, mean=True, offset_dev=None):
         """loss = scale * mean_b[(E2-E3)^2/8 - E2 - E3 + c1 E1] on the stacked batch [x, x+v, x-v] and its gradient
@@ -372,6 +410,10 @@ class FusedEnergyMLP(nn.Module):
         draw = (o["seed"], 0, o["rank"] * st["B"])      # offset = device step counter; rows keyed by the GLOBAL sample index
         if kind == "ssm":
             eps, scale = cfg
+            if eps is None:        # exact SSM (ssm of loss_train.py:173-189): Gaussian projections, forward mode
+                x2 = st["x"].reshape(st["x"].shape[0], -1)
+                return self._jet_loss_and_grad(x2, 1.0, scale, None, None, draw, 2.0, True, o["step"], update=update, mode=1,
+                                               normalize=False, x_noise=st.get("x_noise", 0.0))
             if update or st["x"].dtype == torch.uint8:
                 x2 = st["x"].reshape(st["x"].shape[0], -1)
                 return self._jet_loss_and_grad(x2, eps, scale, None, None, draw, 2.0, True, o["step"], update=update,
@@ -397,11 +439,14 @@ class FusedEnergyMLP(nn.Module):
         peer-memory kernel (ddp.PeerAllReduce); with the NCCL library collective it is two replays around the all-reduce.
         `borrow`: the step reads x where it lies instead of copying it into its own input buffer first -- for callers that
         hand in one of a few long-lived buffers (the trainer's H2D staging pair): one captured graph per buffer address.
+        eps=None runs the EXACT sliced score matching objective instead (exact_ssm_loss_and_grad, Gaussian projections).
         A uint8 x is a batch of PIXELS: the input kernel builds x / 255 + x_noise * N(0,1) (torchvision ToTensor and the
         noise of DeepEBM/train_ssm.py:62) on the fly -- the host ships one byte per pixel."""
         x2 = x.reshape(x.shape[0], -1)
         st = self._jet_state(x2.shape[0], x2.device) if self.formulation == "jet" else self._state(x2.shape[0], x2.device)
-        scale = 1.0 / eps ** 2 if scale is None else scale
+        if eps is None and self.formulation != "jet":
+            raise NotImplementedError("the exact-SSM step (eps=None) needs the chain kernel")
+        scale = (1.0 if eps is None else 1.0 / eps ** 2) if scale is None else scale
         if x2.dtype == torch.uint8:
             if self.formulation != "jet":
                 raise NotImplementedError("uint8 pixel batches need the difference-propagating path (formulation='jet')")
@@ -415,7 +460,7 @@ class FusedEnergyMLP(nn.Module):
                 st["x_own"] = torch.empty_like(x2, memory_format=torch.contiguous_format)
             st["x_own"].copy_(x2)
             st["x"], xkey = st["x_own"], 0
-        return self._train_step(st, "ssm", (float(eps), float(scale)), allreduce, distributed, xkey)
+        return self._train_step(st, "ssm", (None if eps is None else float(eps), float(scale)), allreduce, distributed, xkey)
 
     def mdsm_fd_step(self, x, sigmas, sigma02=0.01, eps=0.05, loss_coe=1e-4, allreduce=None, distributed=False):
         """One optimisation step of DeepEBM/train_dsm.py:62-71 with loss_func = mdsm_fd (loss_train.py:96-118): `sigmas`

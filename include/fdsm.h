@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define FDSM_ABI_VERSION 7
+#define FDSM_ABI_VERSION 8
 
 #define FDSM_OK 0
 #define FDSM_ERR_INVALID_ARGUMENT (-1)
@@ -269,7 +269,7 @@ typedef struct fdsm_jet_update {
 typedef struct fdsm_jet_args {
   const float* x; int64_t ldx; int64_t B;   /* samples (B, D)                                                          */
   const float* dir; int64_t lddir;          /* injected direction (B, D) or NULL => Philox stream 0 (as fdsm_stack)     */
-  int32_t normalize_dir; float dir_scale;   /* 1: v = dir/||dir|| * dir_scale ; 0: v = dir as given (dir != NULL)       */
+  int32_t normalize_dir; float dir_scale;   /* 1: v = u/||u|| * dir_scale ; 0: v = u as given (u = dir, or the Philox rows) */
   uint64_t seed, offset, row0;              /* Philox key / draw counter / global index of local row 0                  */
   const uint64_t* offset_dev;               /* optional device counter added to `offset` (graph replay)                 */
   const float* params; float* workspace;    /* flat parameters ; fdsm_jet_sizes() floats, 16-byte aligned                */
@@ -285,6 +285,13 @@ typedef struct fdsm_jet_args {
                                                       the direction) -- torchvision's ToTensor (1/255) and the on-device noise
                                                       of DeepEBM/train_ssm.py:62 fused into the input build, so that the host
                                                       ships one byte per pixel                                           */
+  int32_t mode;                                    /* 0: the finite-difference objective above.  1: EXACT sliced score matching
+                                                      (SSM/losses/sliced_sm.py:7-34; DeepEBM/ESM/loss_train.py:173-189):
+                                                        *loss = scale * mean_b|sum_b [ (u.grad E)^2 / 2 - u' Hess E u ]
+                                                      with u = the direction as given (dir, or Philox N(0,1) rows when dir is
+                                                      NULL; normalize_dir / dir_scale apply as above), evaluated in forward
+                                                      mode: the three streams carry (h, dh/dtau, 1/2 d2h/dtau2) of
+                                                      tau -> h(x + tau u) through the same kernel; c1 is ignored           */
   const fdsm_jet_update* update;                   /* NULL: loss + gradient only.  Non-NULL: the parameters (`params`, written
                                                       in place) take the clipped Adam step in the same call              */
 } fdsm_jet_args;

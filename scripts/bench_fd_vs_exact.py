@@ -38,6 +38,10 @@ def timed(step, n=100, warm=10):
 fused = fdsm.mlp.FusedEnergyMLP(D, HID, NHID, act="nsoftplus", head="quadratic", device=dev, seed=1234)
 tr = FDSSMTrainer(fused, eps=EPS, lr=LR, betas=BETAS, clip=CLIP, seed=1234)
 res = {"FD-SSM fused (ours)": timed(tr.step)}
+# exact SSM on the same fused net, in forward mode inside the same chain kernel
+fused_x = fdsm.mlp.FusedEnergyMLP(D, HID, NHID, act="nsoftplus", head="quadratic", device=dev, seed=1234)
+fused_x.configure_optimizer(lr=LR, betas=BETAS, clip=CLIP, seed=1234)
+res["exact SSM fused, forward mode (ours)"] = timed(lambda x: fused_x.fd_ssm_step(x, eps=None))
 
 net = TorchQuadraticMLP(D, HID, NHID).to(dev)
 with torch.no_grad():   # same weights as the fused net
@@ -62,13 +66,27 @@ def torch_step(loss_fn):
 with torch.no_grad():
     pass
 x0 = pool[0]
+ux = torch.randn(B_PER_GPU, D, device=dev, generator=gen)
+fused_chk = fdsm.mlp.FusedEnergyMLP(D, HID, NHID, act="nsoftplus", head="quadratic", device=dev, seed=1234)
 vals = {"FD-SSM fused (ours)": float(fused.fd_ssm_loss_and_grad(x0, EPS, 1 / EPS ** 2)[0]),
+        "exact SSM fused, forward mode (ours)": float(fused_chk.exact_ssm_loss_and_grad(x0, u=ux)[0]),
         "FD-SSM generic (torch MLP)": float(fdsm.ssm_fd(net, x0, eps=EPS)),
         "exact SSM (torch double backward)": float(fdsm.ssm(net, x0.clone())),
         "exact SSM-VR (torch double backward)": float(fdsm.ssm_vr(net, x0.clone()))}
 res["FD-SSM generic (torch MLP)"] = timed(torch_step(lambda n, x: fdsm.ssm_fd(n, x, eps=EPS)), n=50)
 res["exact SSM (torch double backward)"] = timed(torch_step(lambda n, x: fdsm.ssm(n, x.clone())), n=50)
 res["exact SSM-VR (torch double backward)"] = timed(torch_step(lambda n, x: fdsm.ssm_vr(n, x.clone())), n=50)
+# same projections through the reference's double-backward form on the torch twin of the UNTRAINED net: the two exact losses
+with torch.no_grad():
+    v0 = fused_chk.named_views()
+    twin = TorchQuadraticMLP(D, HID, NHID).to(dev)
+    for l, fc in enumerate(twin.fcs):
+        fc.weight.copy_(v0[f"fc{l + 1}.weight"]); fc.bias.copy_(v0[f"fc{l + 1}.bias"])
+    for name in ("ln1", "ln2", "lq"):
+        getattr(twin, name).weight.copy_(v0[f"{name}.weight"]); getattr(twin, name).bias.copy_(v0[f"{name}.bias"])
+ref_exact = float(fdsm.ssm(twin, x0.clone(), u=ux))
+print(f"exact SSM on the same batch and projections, untrained net: forward mode (ours) {vals['exact SSM fused, forward mode (ours)']:+.6e}  "
+      f"torch double backward {ref_exact:+.6e}")
 print(f"config 2: MLP_Quadratic_MNIST(nsoftplus) {D}-{HID}x{NHID}, B={B_PER_GPU}, one B200, training step (loss+backward+clip+Adam)")
 for k, ms in res.items():
     print(f"  {k:40s} {ms * 1e3:9.1f} us/step  {B_PER_GPU / ms * 1e3 / 1e6:7.2f} M samples/s   loss on batch 0: {vals[k]:+.6e}")

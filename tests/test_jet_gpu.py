@@ -195,3 +195,55 @@ def test_jet_uint8_pixels_equal_the_explicit_float_batch(fdsm):
     l1 = float(net.fd_ssm_step(x8, eps=0.05, borrow=True, x_noise=0.005))
     l2 = float(net.fd_ssm_step(x8, eps=0.05, borrow=True, x_noise=0.005))
     assert np.isfinite(l1) and np.isfinite(l2) and int(net._opt["step"]) == 2
+
+
+@pytest.mark.parametrize("name", ["a17_ssm_d64", "a17_sliced_gmm11"])
+def test_exact_ssm_forward_mode_matches_reference_golden(fdsm, golden, name):
+    """exact sliced score matching on the fused MLP in FORWARD mode inside the chain kernel
+    (fdsm_jet_args.mode = 1) against the goldens generated from the unmodified reference's double-backward code
+    (DeepEBM/ESM/loss_train.py:173-189 ssm on MLP_Quadratic; SSM/losses/sliced_sm.py:7-34 on the Softplus MLP).
+    Tolerance against the reference's fp64 values: 2e-4 on the loss, 5e-4 on the gradient (activations and gradients travel
+    as TF32; at B = 32 / 48 their rounding averages over few terms: measured 2.5e-4; at config 2 the loss agrees with the
+    double-backward form to 4e-5, profiles/r02_fd_vs_exact_ssm.txt)."""
+    from oracle import cases
+    c = cases.build(name, torch.float64)
+    spec = cases.CASES[name]["net"]
+    if spec[0] == "quadratic_mlp":
+        net = fdsm.mlp.FusedEnergyMLP(spec[1], spec[2], spec[3], act=spec[4], head="quadratic", device=DEV, jet_passes=3)
+    else:
+        net = fdsm.mlp.FusedEnergyMLP(spec[1], spec[2], 2, act="softplus", head="linear", device=DEV, jet_passes=3)
+    net.load_reference_state_dict([p.detach().float() for p in c["net"].parameters()])
+    u = c["u"].reshape(c["B"], -1)
+    if c["fn"] == "a17_sliced":
+        u = u.sign()          # SSM/losses/sliced_sm.py:12 default noise_type
+    x = c["x"].reshape(c["B"], -1).float().to(DEV)
+    loss, grad = net.exact_ssm_loss_and_grad(x, u=u.float().to(DEV))
+    l64, g64 = float(golden[f"{name}/loss_f64"]), golden[f"{name}/grad_f64"]
+    assert abs(float(loss) - l64) <= 2e-4 * abs(l64), (float(loss), l64)
+    assert _relv(grad, torch.from_numpy(np.asarray(g64))) <= 5e-4
+    # the autograd route of the adapter (losses.ssm on a fused net) gives the same numbers
+    if c["fn"] == "a17_ssm":
+        net.flat.grad = None
+        l2 = fdsm.losses.ssm(net, x, batch_size=c["B"], u=u.float().to(DEV))
+        l2.backward()
+        assert float(l2) == float(loss) and torch.equal(net.flat.grad, grad)
+
+
+def test_exact_ssm_philox_projections_and_step(fdsm):
+    """In-kernel Gaussian projections (unnormalised Philox rows) = the same rows injected; the exact-SSM training step
+    (fd_ssm_step(eps=None)) replays from a graph and moves the parameters."""
+    from fdsm_b200 import ops
+    B, D = 96, 64
+    net, _ = _pair(fdsm, D, 48, 3, "nsoftplus", "quadratic")
+    x = nets.np_rand(3, B, D).float().to(DEV)
+    draw = (11, 2, 500)
+    la, ga = net.exact_ssm_loss_and_grad(x, draw=draw)
+    la, ga = la.clone(), ga.clone()
+    u = ops.philox_normal(B, D, 0, draw[0], draw[1], row0=draw[2], device=DEV)
+    lb, gb = net.exact_ssm_loss_and_grad(x, u=u)
+    assert abs(float(la) - float(lb)) <= 1e-6 * abs(float(lb)) and _relv(ga, gb) <= 1e-5
+    net.configure_optimizer(lr=1e-3, betas=(0.9, 0.95), clip=0.1, use_graph=True, seed=3)
+    p0 = net.flat.data.clone()
+    for _ in range(3):
+        l = net.fd_ssm_step(x, eps=None)
+    assert np.isfinite(float(l)) and int(net._opt["step"]) == 3 and not torch.equal(p0, net.flat.data)
