@@ -49,7 +49,9 @@ def _worker(rank, world, port, q):
         _fd_loss(net, X[lo:hi], U[lo:hi]).backward()
         ddp.allreduce_mean_(flat.grad)
         sig = ddp.shard_sigmas(torch.linspace(0.1, 0.8, 8))
-        q.put((rank, flat.flat.clone(), flat.grad.clone(), (lo, hi), sig.clone(), ddp.is_distributed()))
+        # numpy arrays travel by value: a torch tensor in an mp queue is a shared-memory handle that dies with this process
+        q.put((rank, flat.flat.detach().numpy().copy(), flat.grad.detach().numpy().copy(), (lo, hi), sig.numpy().copy(),
+               ddp.is_distributed()))
     finally:
         dist.destroy_process_group()
 
@@ -63,6 +65,7 @@ def test_two_rank_gloo_step_matches_single_process():
     for p in procs:
         p.start()
     got = sorted((q.get(timeout=100) for _ in range(2)), key=lambda t: t[0])
+    got = [tuple(torch.from_numpy(a) if hasattr(a, "dtype") else a for a in t) for t in got]
     for p in procs:
         p.join(30)
         assert p.exitcode == 0
