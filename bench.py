@@ -42,15 +42,22 @@ def peaks():
 
 
 def ncu_summary():
-    """DRAM bytes per launch of the two judged kernels from the committed `ncu --set full` capture of this command
-    (profiles/r01_ncu_full_summary.json, written by scripts/ncu_summary.py from the .ncu-rep)."""
-    p = os.path.join(ROOT, "profiles", "r01_ncu_full_summary.json")
-    if os.path.exists(p):
-        try:
-            return json.load(open(p))
-        except Exception:
-            pass
-    return {}
+    """DRAM bytes per launch of the judged kernels from the committed `ncu --set full` captures of this command
+    (profiles/r0N_ncu_full_summary.json, written by scripts/ncu_summary.py from the .ncu-rep): the chain kernel from the
+    newest capture, the stack kernel (not launched by the fused step any more) from the last capture that holds it."""
+    out = {}
+    for tag in ("r01", "r02"):
+        p = os.path.join(ROOT, "profiles", f"{tag}_ncu_full_summary.json")
+        if os.path.exists(p):
+            try:
+                d = json.load(open(p))
+            except Exception:
+                continue
+            src = d.pop("source", None)
+            out.update(d)
+            for k in d:
+                out[k + "_source"] = src
+    return out
 
 
 # The contract is ONE JSON line on stdout.  Libraries write banners there too (NCCL prints its version on the first
@@ -377,7 +384,7 @@ def main():
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    SUSTAIN = 2500
+    SUSTAIN = int(os.environ.get("FDSM_BENCH_SUSTAIN", "2500"))   # 0 under ncu (every launch is intercepted)
     for i in range(args.warmup):
         tr.step(pool[i % POOL])
     barrier()
@@ -540,9 +547,12 @@ def main():
         torch.cuda.synchronize()
         roof = net.roofline(kev, pk, pk_kind)
         ncu = ncu_summary()
-        if roof is not None and ncu.get("gemm_dram_bytes_per_launch") is not None:
-            roof["traffic"] = ncu["gemm_dram_bytes_per_launch"]
-            roof["traffic_source"] = ncu.get("source")
+        tkey = "chain_dram_bytes_per_launch" if net.formulation == "jet" else "gemm_dram_bytes_per_launch"
+        if roof is not None and ncu.get(tkey) is not None:
+            roof["traffic"] = ncu[tkey]
+            roof["traffic_source"] = ncu.get(tkey + "_source")
+            if net.formulation == "jet" and ncu.get("chain_sm__pipe_tensor_cycles_active_pct_avg") is not None:
+                roof["ncu_tensor_pipe_active_pct"] = ncu["chain_sm__pipe_tensor_cycles_active_pct_avg"]
         # north_star (2): the FD kernels against the HBM roofline -- the fused Philox direction + [x, x+v, x-v] build.
         # Kernel time = 20 launches on rotating batches inside one CUDA graph between two events (no host launch gaps);
         # the in-step eager launch of the un-graphed pass above is reported next to it.

@@ -44,7 +44,8 @@ with open(out_csv, "w", newline="") as f:
         name = r[col["Kernel Name"]]
         vals = [num(r, n) for n in want]
         w.writerow([r[col["ID"]], name[:100]] + vals)
-        key = "gemm" if "gemm_raw_kernel" in name else ("stack" if "stack_kernel" in name else None)
+        key = ("chain" if "chain_kernel" in name else "gemm" if "gemm_raw_kernel" in name else "wgrad_gemm" if "gemm_kernel" in name else
+               "stack" if "stack_kernel" in name else "jet_inputs" if "jet_inputs" in name else "jet_update" if "jet_update" in name else None)
         if key:
             d = dict(zip(want, vals))
             per.setdefault(key, []).append(d)
