@@ -82,7 +82,7 @@ class MlpDesc(C.Structure):
                 ("presplit", _i32)]
 
 
-ABI_VERSION = 8    # FDSM_ABI_VERSION of include/fdsm.h
+ABI_VERSION = 9    # FDSM_ABI_VERSION of include/fdsm.h
 
 # name -> (restype, argtypes); must list every symbol include/fdsm.h declares
 PROTOTYPES = {
@@ -99,6 +99,8 @@ PROTOTYPES = {
     "fdsm_combine_score": (C.c_int, [_f32p, _i64, _f32p, _i64, _f32p, C.c_void_p, _f32, _i64, _i64, _f32, _i32,
                                      _f32p, _f32p, _f32p, _f32p, _i64, _stream]),
     "fdsm_scale_unless_one": (C.c_int, [_f32p, _i64, _f32p, _stream]),
+    "fdsm_combine_score_static": (C.c_int, [_f32p, _i64, _f32p, _i64, _f32p, C.c_void_p, _f32, _i64, _i64, _f32, _i32,
+                                            _f32p, _f32p, _f32p, _i64, _stream]),
     "fdsm_tf32_split": (C.c_int, [_f32p, _i64, _i64, _i64, _f32p, _f32p, _i64, _i64, _i32, _stream]),
     "fdsm_tc_gemm": (C.c_int, [C.POINTER(GemmArgs), _stream]),
     "fdsm_grad_sumsq": (C.c_int, [_f32p, _i64, _f32p, C.c_void_p, _stream]),

@@ -5,6 +5,8 @@
 //   fixed-order mean kernel.
 #include "fd_combine.cuh"
 
+#include <mutex>
+
 namespace fdsm {
 namespace {
 
@@ -252,6 +254,86 @@ extern "C" int fdsm_combine_score(const float* s, int64_t lds, const float* v, i
     FDSM_LAUNCH_CHECK("fdsm_combine_score(mean)");
   }
   return FDSM_OK;
+}
+
+// ---- no-allocation variant of the score-form combine (include/fdsm.h: fdsm_combine_score_static) ---------------------
+// The per-sample terms that the mean kernel sums are the kernel's scratch; here they live in a file-scope device array
+// (one copy per GPU that loads the library, held until exit) instead of a caller buffer.  In host code the array's NAME
+// is a host-side stand-in for the symbol, not a device address: the address is resolved once per device, with that
+// device current, by cudaGetSymbolAddress and cached.
+static __device__ __align__(256) float g_score_static_scratch[FDSM_COMBINE_SCORE_STATIC_MAX_B];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+float* g_static_ptr[kMaxDevices] = {};
+
+int static_scratch(float** out) {
+  int dev = -1;
+  int rc = fdsm::cuda_status(cudaGetDevice(&dev), "fdsm_combine_score_static(cudaGetDevice)");
+  if (rc) return rc;
+  if (dev < 0 || dev >= kMaxDevices) {
+    fdsm::set_error("fdsm_combine_score_static: device ordinal %d outside [0, %d)", dev, kMaxDevices);
+    return FDSM_ERR_UNSUPPORTED;
+  }
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (!g_static_ptr[dev]) {
+    void* p = nullptr;
+    rc = fdsm::cuda_status(cudaGetSymbolAddress(&p, g_score_static_scratch), "fdsm_combine_score_static(cudaGetSymbolAddress)");
+    if (rc) return rc;
+    if (!p) {
+      fdsm::set_error("fdsm_combine_score_static: cudaGetSymbolAddress returned a null address");
+      return FDSM_ERR_UNSUPPORTED;
+    }
+    g_static_ptr[dev] = static_cast<float*>(p);
+  }
+  *out = g_static_ptr[dev];
+  return FDSM_OK;
+}
+}  // namespace
+
+extern "C" int fdsm_combine_score_static(const float* s, int64_t lds, const float* v, int64_t ldv, const float* sigma,
+                                         const int64_t* labels, float power, int64_t B, int64_t D, float k,
+                                         int32_t projected, const float* gout, float* loss, float* ds, int64_t ldds,
+                                         fdsm_stream_t stream) {
+  FDSM_REQUIRE(B >= 0 && D >= 0 && D < (1ll << 31), "fdsm_combine_score_static: bad shape");
+  FDSM_REQUIRE(B <= FDSM_COMBINE_SCORE_STATIC_MAX_B,
+               "fdsm_combine_score_static: B = %lld exceeds the static scratch (FDSM_COMBINE_SCORE_STATIC_MAX_B = %d samples); "
+               "use fdsm_combine_score with a caller-owned per_sample buffer",
+               (long long)B, FDSM_COMBINE_SCORE_STATIC_MAX_B);
+  FDSM_REQUIRE(!labels || sigma, "fdsm_combine_score_static: labels without sigma table");
+  float* per = nullptr;
+  int rc = static_scratch(&per);      // set-up = the first call on this device (B = 0 will do: warm up before a capture)
+  if (rc) return rc;
+  FDSM_REQUIRE(loss, "fdsm_combine_score_static: loss is NULL");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (B > 0 && D > 0) {
+    FDSM_REQUIRE(s && v, "fdsm_combine_score_static: NULL input");
+    FDSM_REQUIRE(lds >= D && ldv >= D && (!ds || ldds >= D), "fdsm_combine_score_static: leading dimension < D");
+    ScoreArgs a{s, lds, v, ldv, sigma, labels, power, B, (int)D, k, projected, gout, per, ds, ldds};
+    const bool vec = D % 4 == 0 && lds % 4 == 0 && ldv % 4 == 0 && aligned16(s) && aligned16(v) &&
+                     (!ds || (aligned16(ds) && ldds % 4 == 0));
+    const int64_t nchunk = (D + 3) / 4;
+    int G = 32;
+    while (G < kBlock && (int64_t)G * 4 < nchunk) G <<= 1;
+    const int64_t ngroups = (B + (kBlock / G) - 1) / (kBlock / G);
+    const int64_t cap = (int64_t)sm_count() * 8;
+    const int grid = (int)(ngroups < cap ? ngroups : cap);
+    switch (G) {
+      case 32: launch_score<32>(a, vec, grid, st); break;
+      case 64: launch_score<64>(a, vec, grid, st); break;
+      case 128: launch_score<128>(a, vec, grid, st); break;
+      default: launch_score<256>(a, vec, grid, st); break;
+    }
+    rc = cuda_status(cudaGetLastError(), "fdsm_combine_score_static");
+    if (rc) return rc;
+  } else if (B > 0) {
+    // D == 0: every per-sample term is an empty sum, but the scratch keeps the previous call's values: clear what is read
+    rc = cuda_status(cudaMemsetAsync(per, 0, (size_t)B * sizeof(float), st), "fdsm_combine_score_static(memset)");
+    if (rc) return rc;
+  }
+  mean_kernel<<<1, 1024, 0, st>>>(per, B, loss);
+  FDSM_LAUNCH_CHECK("fdsm_combine_score_static(mean)");
 }
 
 extern "C" int fdsm_scale_unless_one(float* data, int64_t n, const float* g, fdsm_stream_t stream) {

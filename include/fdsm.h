@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define FDSM_ABI_VERSION 8
+#define FDSM_ABI_VERSION 9
 
 #define FDSM_OK 0
 #define FDSM_ERR_INVALID_ARGUMENT (-1)
@@ -142,6 +142,25 @@ int fdsm_combine_score(const float* s, int64_t lds, const float* v, int64_t ldv,
  * gradient here: for the usual `loss.backward()` on the returned loss every block reads the scalar and exits, so the
  * score-form combine moves 20*D bytes per sample instead of the 32*D of a forward launch plus a backward launch. */
 int fdsm_scale_unless_one(float* data, int64_t n, const float* g, fdsm_stream_t stream);
+
+/* The score-form combine for callers that cannot provide (or allocate) the per-sample workspace: code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc.  NO COUNTERPART IN THE REFERENCE.
+ * Same arithmetic, kernels and launch configuration as fdsm_combine_score
+ * called with (per_sample = workspace, loss, ds): *loss (required) = mean_b per_b, `ds` (optional) = gout[0] * dloss/ds;
+ * the per-sample terms the mean reads live in a file-scope `static __device__` array of
+ * FDSM_COMBINE_SCORE_STATIC_MAX_B floats (256 KiB, present once on every GPU that loads the library, until exit) and
+ * are not returned.  It allocates nothing: no cudaMalloc / cudaFree / allocating library call, on any path.
+ *   - B > FDSM_COMBINE_SCORE_STATIC_MAX_B returns FDSM_ERR_INVALID_ARGUMENT (message names the limit); use
+ *     fdsm_combine_score with a caller-owned buffer for larger batches.
+ *   - The first call on each device resolves the array's device address (cudaGetSymbolAddress, that device current) and
+ *     caches it; make that first call (B = 0 is enough) before starting a stream capture.
+ *   - Every call on a device shares the one array and it keeps the previous call's contents (every entry a call reads is
+ *     written by that call first): calls that overlap on the GPU (different streams, concurrent graph branches) RACE.
+ *     Serialise them on one stream or use fdsm_combine_score.                                                          */
+#define FDSM_COMBINE_SCORE_STATIC_MAX_B 65536
+int fdsm_combine_score_static(const float* s, int64_t lds, const float* v, int64_t ldv, const float* sigma,
+                              const int64_t* labels, float power, int64_t B, int64_t D, float k, int32_t projected,
+                              const float* gout, float* loss, float* ds, int64_t ldds, fdsm_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------
  * Kernel (3) building blocks: TF32 hi/lo operand split and the tcgen05/TMEM GEMM fed by TMA.
