@@ -54,9 +54,9 @@ constexpr int CHAIN_MISC_BYTES = (3 * HWS + 4 * HREC + MAX_S * NCOEF) * 4 + NBAR
 
 struct alignas(64) ChainParams {
   CUtensorMap t_in;                  // [2 Bp x kpad0]  rows [x | v]                          (load, box {32, S})
-  CUtensorMap t_wf[MAXL];            // Wt_l [kpad_0 x npad] fp32 (l = 0) / [2 kpad_l x npad] hi rows, lo rows (l >= 1),
-                                     //   MN-major view                                      (load, box {32, 32})
-  CUtensorMap t_wb[MAXL];            // the same memory, K-major view for the dgrad          (load, box {32, 32})
+  CUtensorMap t_wf[MAXL];            // Wt_l = [hi rows | lo rows] [2 kpad_l x npad], MN-major, as (32 n, k, n-panel[, hi|lo]):
+                                     //   l = 0, PASSES != 3: 3-D, box {32, 64, nbx} ; otherwise 4-D, box {32, 32, nbx, HL}
+  CUtensorMap t_wb[MAXL];            // the same memory, K-major view for the dgrad: 3-D (n, k, hi|lo), box {32, 32 nbx, HL}
   CUtensorMap t_h[MAXL];             // H_l [3 Bp x kpadh], l = 1..L-1                       (store, box {32, S})
   CUtensorMap t_dz[MAXL];            // dZ_l [3 Bp x npad] (l = 0: 2 Bp rows)                (store, box {32, S})
   const float* h[MAXL];              // H_l again, for the backward's plain loads
@@ -295,8 +295,6 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
   auto a_empty = [&](int s) { return bars + 8u * (MAX_NA + s); };
   auto w_full = [&](int s) { return bars + 8u * (2 * MAX_NA + s); };
   auto w_empty = [&](int s) { return bars + 8u * (2 * MAX_NA + MAX_RAW + s); };
-  auto hi_done = [&](int s) { return bars + 8u * (2 * MAX_NA + 2 * MAX_RAW + s); };     // the slot's hi MMAs have completed
-  auto lo_full = [&](int s) { return bars + 8u * (2 * MAX_NA + 3 * MAX_RAW + s); };     // the slot now holds lo
   const uint32_t acc_full = bars + 8u * (2 * MAX_NA + 4 * MAX_RAW);
   auto a_ready = [&](int j) { return bars + 8u * (2 * MAX_NA + 4 * MAX_RAW + 1 + j); };
   volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(bars_gen + 8 * NBARS);
@@ -316,7 +314,7 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
   if (threadIdx.x == 0) {
     for (int s = 0; s < MAX_NA; ++s) { mbar_init(a_full(s), 1); mbar_init(a_empty(s), 1); mbar_init(a_ready(s), EPI_WARPS); }
     for (int s = 0; s < MAX_RAW; ++s) {
-      mbar_init(w_full(s), 1); mbar_init(w_empty(s), CL); mbar_init(hi_done(s), 1); mbar_init(lo_full(s), EPI_WARPS);
+      mbar_init(w_full(s), 1); mbar_init(w_empty(s), CL);
     }
     mbar_init(acc_full, 2);          // the MMAs' commit + the store thread (earlier TMA stores have left shared memory)
     fence_barrier_init();
@@ -339,10 +337,31 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
   const uint32_t tmem_base = *tmem_ptr_smem;
   stamp(p, 1);
 
+  // Weight stream: ONE TMA instruction per "unit" (measured, scripts/tma_ingest_bench.cu: what an SM can pull through TMA is
+  // set by the number of barrier phases / instructions, ~650 clk per ring slot + ~70 per box whatever their size, not by
+  // bytes -- 7 boxes of 4 KB per slot deliver 24 B/clk, one 56 KB box 85 B/clk).  A unit fills a double slot (2 x 28 KB):
+  //   phase 0, PASSES != 3:  two k-blocks of W_0 (TF32 hi)          3-D box {32 n, 64 k, nbx}      [nblk][64 k][32 n]
+  //   phase 0, PASSES == 3:  one k-block of W_0, hi and lo          4-D box {32 n, 32 k, nbx, 2}   [hi|lo][nblk][32 k][32 n]
+  //   forward l >= 1:        one k-block of W_l, hi (and lo)        4-D box {32 n, 32 k, nbx, HL}
+  //   dgrad l:               one k-block (32 outputs) of W_l        3-D box {32 n, 32 nbx rows k, HL}  [hi|lo][k][32 n]
+  constexpr int HL = PASSES >= 2 ? 2 : 1;            // copies of a hidden-layer unit: hi (+ lo)
+  constexpr int WK0 = PASSES == 3 ? 1 : 2;           // k-blocks of W_0 per unit
+  const int nunits = nraw >> 1;                      // ring depth in units
+  const uint32_t unit0_bytes = (uint32_t)nbx * 4096u * 2u;                 // both layouts of phase 0 fill 2 x nbx boxes
+  const uint32_t unith_bytes = (uint32_t)nbx * 4096u * (uint32_t)HL;
+  // phase 0's A operand arrives in groups of AG k-blocks per barrier (the same per-barrier cost): group slot g covers the
+  // A-region blocks [AG g, AG g + AG)
+  const int AG = NA >= 2 ? 2 : 1, nag = NA / AG;
+
   if (warp == PROD_WARP) {
     // ===== TMA producer (one thread): the weight stream of every phase back to back, plus phase 0's A operand ============
     if (lane == 0) {
-      int ws = 0; uint32_t wph = 0;
+      int wu = 0; uint32_t wph = 0; int useq = 0;
+      auto next_unit = [&]() -> uint32_t {          // waits for the ring slot, arms its barrier; returns its address (0: a peer issues)
+        mbar_wait_parked(w_empty(2 * wu), wph ^ 1u);                 // every CTA of the cluster has finished with this unit
+        return w_base + 2 * wu * WSLOT_BYTES;
+      };
+      auto advance = [&]() { if (++wu == nunits) { wu = 0; wph ^= 1u; } ++useq; };
       for (int g = 0; g < nphase; ++g) {
         const bool fwd = g < L;
         const int layer = fwd ? g : 2 * L - 1 - g;
@@ -350,35 +369,41 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
         const CUtensorMap* tw = fwd ? &p.t_wf[layer] : &p.t_wb[layer];
         for (int kb = 0; kb < nkb; ++kb) {
           if (g == 0) {
-            const int as = kb % NA;
-            mbar_wait_parked(a_empty(as), ((kb / NA) & 1) ^ 1u);
-            mbar_arrive_expect_tx(a_full(as), (uint32_t)(2 * S * 128));
-            tma_load_2d(a_base + as * ablk, &p.t_in, a_full(as), kb * 32, tile * S);
-            tma_load_2d(a_base + as * ablk + S * 128, &p.t_in, a_full(as), kb * 32, p.Bp + tile * S);
-          }
-          // phase 0: one slot per k-block (fp32; lo is derived on chip);  later phases with PASSES = 2: hi slot, lo slot
-          const int ncopy = (PASSES >= 2 && g > 0) ? 2 : 1;
-          const int kpad_l = layer == 0 ? p.kpad0 : p.kpadh;
-          for (int ps = 0; ps < ncopy; ++ps) {
-            mbar_wait_parked(w_empty(ws), wph ^ 1u);           // every CTA of the cluster has finished with this slot
-            mbar_arrive_expect_tx(w_full(ws), (uint32_t)nbx * 4096u);
-            const uint32_t dst = w_base + ws * WSLOT_BYTES;
-            for (int i = 0; i < nbx; ++i) {
-              if (CL > 1 && (uint32_t)(i % CL) != crank) continue;
-              // forward (W MN-major: box = 32 outputs x 32 k):  (32 i, k-block);  dgrad (K-major: 32 k x 32 rows): (k-block, 32 i)
-              const int c0 = fwd ? 32 * i : 32 * kb, c1 = ps * kpad_l + (fwd ? 32 * kb : 32 * i);
-              if (CL > 1) tma_load_2d_mc(dst + i * 4096, tw, w_full(ws), c0, c1, CMASK);
-              else tma_load_2d(dst + i * 4096, tw, w_full(ws), c0, c1);
+            if (kb % AG == 0) {
+              const int gs = (kb / AG) % nag, nk = min(AG, nkb - kb);
+              mbar_wait_parked(a_empty(gs), ((kb / AG / nag) & 1) ^ 1u);
+              mbar_arrive_expect_tx(a_full(gs), (uint32_t)(nk * 2 * S * 128));
+              for (int q = 0; q < nk; ++q) {
+                const uint32_t dst = a_base + (gs * AG + q) * ablk;
+                tma_load_2d(dst, &p.t_in, a_full(gs), (kb + q) * 32, tile * S);
+                tma_load_2d(dst + S * 128, &p.t_in, a_full(gs), (kb + q) * 32, p.Bp + tile * S);
+              }
             }
-            if (++ws == nraw) { ws = 0; wph ^= 1u; }
+            if (kb % WK0 != 0) continue;
           }
+          const uint32_t dst = next_unit();
+          const uint32_t bytes = g == 0 ? unit0_bytes : unith_bytes;
+          mbar_arrive_expect_tx(w_full(2 * wu), bytes);
+          if (CL == 1 || (uint32_t)(useq % CL) == crank) {          // clusters: the CTAs take turns and multicast the unit
+            if (g == 0 && PASSES != 3) {
+              if (CL > 1) tma_load_3d_mc(dst, tw, w_full(2 * wu), 0, 32 * kb, 0, CMASK);
+              else tma_load_3d(dst, tw, w_full(2 * wu), 0, 32 * kb, 0);
+            } else if (fwd) {
+              if (CL > 1) tma_load_4d_mc(dst, tw, w_full(2 * wu), 0, 32 * kb, 0, 0, CMASK);
+              else tma_load_4d(dst, tw, w_full(2 * wu), 0, 32 * kb, 0, 0);
+            } else {
+              if (CL > 1) tma_load_3d_mc(dst, tw, w_full(2 * wu), 32 * kb, 0, 0, CMASK);
+              else tma_load_3d(dst, tw, w_full(2 * wu), 32 * kb, 0, 0);
+            }
+          }
+          advance();
         }
       }
     }
   } else if (warp == MMA_WARP) {
     // ===== MMA issuer + TMA-store issuer (one thread) =====================================================================
     if (lane == 0) {
-      int ws = 0; uint32_t wph = 0;
+      int wu = 0; uint32_t wph = 0;
       // block kb of the output of epilogue `ge` leaves for HBM (operands of the weight-gradient GEMMs / of the backward)
       auto store_block = [&](int ge, int kb) {
         const CUtensorMap* tm;
@@ -392,67 +417,52 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
         const bool fwd = g < L;
         const int nkb = fwd ? (g == 0 ? nkb0 : NA) : nbx;
         const uint32_t idesc = make_idesc_tf32(128, npad, tc::MAJOR_K, fwd ? tc::MAJOR_MN : tc::MAJOR_K);
-        const uint32_t b_lbo = fwd ? 4096u : 16u, b_sbo = fwd ? 512u : 1024u, b_step = fwd ? 1024u : 32u, b_lay = fwd ? 1u : 2u;
+        // forward (MN-major B): n-blocks of a unit are 4 KB apart -- 8 KB in phase 0's two-k-block units
+        const uint32_t b_lbo = fwd ? ((g == 0 && WK0 == 2) ? 8192u : 4096u) : 16u;
+        const uint32_t b_sbo = fwd ? 512u : 1024u, b_step = fwd ? 1024u : 32u, b_lay = fwd ? 1u : 2u;
         // contraction length that carries data: input columns + the ones column (forward), the layer's outputs (dgrad);
         // 8-column steps of a k-block that lie entirely in the zero padding are not issued
         const int kvalid = fwd ? (g == 0 ? p.D + 1 : H + 1) : H;
-        auto mmas = [&](int as_, int slot, bool first, int kb_) {
+        auto mmas = [&](int as_, uint32_t bbase, bool first, int kb_) {
           const int n8 = min(4, (kvalid - 32 * kb_ + 7) >> 3);
 #pragma unroll
           for (int k8 = 0; k8 < 4; ++k8) {
             if (k8 >= n8) break;
             const uint64_t da = make_smem_desc(a_base + as_ * ablk + k8 * 32, 16u, 1024u, 2u);
-            const uint64_t db = make_smem_desc(w_base + slot * WSLOT_BYTES + k8 * b_step, b_lbo, b_sbo, b_lay);
+            const uint64_t db = make_smem_desc(bbase + k8 * b_step, b_lbo, b_sbo, b_lay);
             mma_tf32_ss(tmem_base, da, db, idesc, (first && k8 == 0) ? 0u : 1u);
           }
         };
-        auto release = [&](int slot) {
-          if (CL > 1) tc_commit_mc(w_empty(slot), CMASK);
-          else tc_commit(w_empty(slot));
+        auto release = [&]() {
+          if (CL > 1) tc_commit_mc(w_empty(2 * wu), CMASK);
+          else tc_commit(w_empty(2 * wu));
+          if (++wu == nunits) { wu = 0; wph ^= 1u; }
         };
-        if (g == 0 && PASSES == 3) {
-          // phase 0: the lo MMAs of a k-block run one k-block behind its hi MMAs (the in-place conversion gets that long);
-          // with a single A slot the operand of k-block kb must be released before kb + 1 can land: no lag then
-          const bool lag = NA >= 2;
-          int pws = 0, pas = 0, pkb = 0; uint32_t pph = 0;
-          auto lo_mmas = [&]() {
-            mbar_wait_parked(lo_full(pws), pph);
+        // the second copy (lo) of a unit follows the first: nbx boxes (forward) / 32 nbx rows of 128 bytes (dgrad) further
+        const uint32_t lo_off = (uint32_t)nbx * 4096u;
+        for (int kb = 0; kb < nkb; ++kb) {
+          const uint32_t ubase = w_base + 2 * wu * WSLOT_BYTES;
+          if (g == 0) {
+            const int gs = (kb / AG) % nag, as = gs * AG + kb % AG;
+            if (kb % AG == 0) mbar_wait_parked(a_full(gs), (kb / AG / nag) & 1);
+            if (kb % WK0 == 0) mbar_wait_parked(w_full(2 * wu), wph);
             tc_fence_after();
-            mmas(pas, pws, false, pkb);
-            release(pws);
-            tc_commit(a_empty(pas));
-          };
-          for (int kb = 0; kb < nkb; ++kb) {
-            const int as = kb % NA;
-            mbar_wait_parked(a_full(as), (kb / NA) & 1);
-            mbar_wait_parked(w_full(ws), wph);
-            tc_fence_after();
-            mmas(as, ws, kb == 0, kb);
-            tc_commit(hi_done(ws));
-            if (lag && kb > 0) lo_mmas();
-            pws = ws; pas = as; pph = wph; pkb = kb;
-            if (!lag) lo_mmas();
-            if (++ws == nraw) { ws = 0; wph ^= 1u; }
-          }
-          if (lag) lo_mmas();
-        } else {
-          for (int kb = 0; kb < nkb; ++kb) {
-            const int as = g == 0 ? kb % NA : kb;
-            if (g == 0) {
-              mbar_wait_parked(a_full(as), (kb / NA) & 1);
+            if (WK0 == 2) {
+              mmas(as, ubase + (kb & 1) * 4096u, kb == 0, kb);
             } else {
-              mbar_wait_parked(a_ready(kb), (g - 1) & 1);      // the epilogue has finished this k-block of the operand
-              store_block(g - 1, kb);
+              mmas(as, ubase, kb == 0, kb);
+              mmas(as, ubase + lo_off, false, kb);
             }
-            const int nps = (PASSES >= 2 && g > 0) ? 2 : 1;
-            for (int ps = 0; ps < nps; ++ps) {
-              mbar_wait_parked(w_full(ws), wph);
-              tc_fence_after();
-              mmas(as, ws, kb == 0 && ps == 0, kb);
-              release(ws);
-              if (++ws == nraw) { ws = 0; wph ^= 1u; }
-            }
-            if (g == 0) tc_commit(a_empty(as));
+            if (kb % AG == AG - 1 || kb == nkb - 1) tc_commit(a_empty(gs));
+            if (kb % WK0 == WK0 - 1 || kb == nkb - 1) release();
+          } else {
+            mbar_wait_parked(a_ready(kb), (g - 1) & 1);      // the epilogue has finished this k-block of the operand
+            store_block(g - 1, kb);
+            mbar_wait_parked(w_full(2 * wu), wph);
+            tc_fence_after();
+            mmas(kb, ubase, kb == 0, kb);
+            if (HL == 2) mmas(kb, ubase + lo_off, false, kb);
+            release();
           }
         }
         if (p.trace) stamp_now(p, 5 + 4 * g);            // phase g's MMAs issued
@@ -490,26 +500,6 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
       __syncwarp();
       if (lane == 0) mbar_arrive(a_ready(j));
     };
-    if (PASSES == 3) {
-      // phase 0: these warps have nothing else to do -- they turn every weight slot into its lo part once its hi MMAs are done
-      const int nvec = nbx * 256;                       // float4s of a slot
-      int ws = 0; uint32_t wph = 0;
-      for (int kb = 0; kb < nkb0; ++kb) {
-        mbar_wait_parked(w_full(ws), wph);              // (the TMA's writes, acquired by this thread too)
-        mbar_wait_parked(hi_done(ws), wph);
-        float4* slot = reinterpret_cast<float4*>(w_gen + ws * WSLOT_BYTES);
-        // lo = x - trunc(x): exact in fp32; the tensor core truncates it to TF32 (2^-21 of x)
-        auto lo = [](float x) { return x - __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); };
-        for (int v = threadIdx.x; v < nvec; v += EPI_T) {
-          const float4 x = slot[v];
-          slot[v] = make_float4(lo(x.x), lo(x.y), lo(x.z), lo(x.w));
-        }
-        fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(lo_full(ws));
-        if (++ws == nraw) { ws = 0; wph ^= 1u; }
-      }
-    }
     for (int g = 0; g < nphase; ++g) {
       const bool fwd = g < L;
       const int layer = fwd ? g : 2 * L - 1 - g;

@@ -53,6 +53,37 @@ inline int make_tmap(CUtensorMap* m, const float* ptr, long long rows, long long
   return FDSM_OK;
 }
 
+// General tiled map over fp32 data: dims / box innermost first (dims[0] contiguous), strides in BYTES for dims 1.. (need not be
+// monotonic: a later dimension may step by less than an earlier one -- e.g. the 32-column panels of a row-major matrix as
+// dimension 2 with a 128-byte stride, so that ONE box covers several panels in the [panel][row][32] order tcgen05 wants).
+inline int make_tmap_nd(CUtensorMap* m, const float* ptr, int rank, const long long* dims, const long long* strides_bytes,
+                        const int* box, bool mn_major, const char* what) {
+  auto fn = encode_fn();
+  if (!fn) {
+    set_error("cuTensorMapEncodeTiled entry point not available");
+    return FDSM_ERR_UNSUPPORTED;
+  }
+  FDSM_REQUIRE(ptr && aligned16(ptr), "%s: operand pointer must be non-NULL and 16-byte aligned", what);
+  FDSM_REQUIRE(rank >= 2 && rank <= 5, "%s: rank %d out of range", what, rank);
+  cuuint64_t d[5]; cuuint64_t st[4]; cuuint32_t bx[5]; cuuint32_t es[5];
+  for (int i = 0; i < rank; ++i) {
+    FDSM_REQUIRE(dims[i] >= 1 && box[i] >= 1 && box[i] <= 256, "%s: dimension %d: size %lld, box %d", what, i, dims[i], box[i]);
+    d[i] = (cuuint64_t)dims[i]; bx[i] = (cuuint32_t)box[i]; es[i] = 1;
+    if (i) {
+      FDSM_REQUIRE(strides_bytes[i - 1] > 0 && strides_bytes[i - 1] % 16 == 0, "%s: stride %lld of dimension %d", what, strides_bytes[i - 1], i);
+      st[i - 1] = (cuuint64_t)strides_bytes[i - 1];
+    }
+  }
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<float*>(ptr), d, st, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("%s: cuTensorMapEncodeTiled (rank %d) failed (CUresult %d)", what, rank, (int)r);
+    return FDSM_ERR_INVALID_ARGUMENT;
+  }
+  return FDSM_OK;
+}
+
 // debug hook (scripts/gemm_trace.py): when set, every raw-operand launch writes 8 %globaltimer stamps per CTA
 inline unsigned long long*& trace_buffer() {
   static unsigned long long* buf = nullptr;
