@@ -68,6 +68,8 @@ struct alignas(64) ChainParams {
   float act_offset;                  // ln 2 for the normalised softplus
   float c1, coef;                    // loss_b = dE^2/8 - sE + (c1 - 2) E0 ; dL/dloss_b = coef (= scale / B or scale)
   unsigned long long* trace;         // debug: per-CTA %globaltimer stamps [tile][TRACE_N] (NULL in production)
+  int trace_mode;                    // debug: what the free slots 22.. of a 3-layer trace hold (0: fwd1 k-block stamps of the MMA thread,
+                                     //   1: per-warp end of fwd1's epilogue, 2: per-warp end of block 1 of fwd1's epilogue)
 };
 constexpr int TRACE_N = 2 + 4 * (2 * MAXL - 1);
 __device__ __forceinline__ void stamp_now(const ChainParams& p, int slot) {
@@ -457,8 +459,10 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
             if (kb % WK0 == WK0 - 1 || kb == nkb - 1) release();
           } else {
             mbar_wait_parked(a_ready(kb), (g - 1) & 1);      // the epilogue has finished this k-block of the operand
+            if (p.trace && p.trace_mode == 0 && g == 1 && L == 3 && kb < 8) stamp_now(p, 22 + 2 * kb);      // (debug: free slots of a 3-layer trace)
             store_block(g - 1, kb);
             mbar_wait_parked(w_full(2 * wu), wph);
+            if (p.trace && p.trace_mode == 0 && g == 1 && L == 3 && kb < 8) stamp_now(p, 23 + 2 * kb);
             tc_fence_after();
             mmas(kb, ubase, kb == 0, kb);
             if (HL == 2) mmas(kb, ubase + lo_off, false, kb);
@@ -545,7 +549,9 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
             epi_fwd_hidden<ACT, MODE>(e, v1, sst, ones, off);
           }
           publish(j);
+          if (p.trace && p.trace_mode == 2 && g == 1 && L == 3 && j == 1 && lane == 0) stamp_now(p, 22 + warp);
         }
+        if (p.trace && p.trace_mode == 1 && g == 1 && L == 3 && lane == 0) stamp_now(p, 22 + warp);
       } else if (fwd) {
         // -- last forward layer: jets, head, per-sample loss and its gradient, activation backward -> dZ_{L-1} ---------------
         const bool quad = p.head != 0;

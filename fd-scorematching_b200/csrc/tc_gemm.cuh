@@ -271,5 +271,135 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
   }
 }
 
+
+// ---- weight-gradient GEMM, wide stages -----------------------------------------------------------------------------------
+// dWt[m][n] = sum_r In[r][m] dZ[r][n] over the batch rows r: both operands MN-major (the contraction index is the row of the
+// stored matrices), one pass of plain TF32, split-K partials (EPI_STORE).  What an SM can pull through TMA is set by the
+// number of instructions / barrier phases (~650 clk per pipeline stage + ~70 per box, whatever their size:
+// scripts/tma_ingest_bench.cu), so gemm_kernel's stage of 11 boxes of 32 x 32 (one 32-row k-block, 43 KB) costs as much as
+// this kernel's stage of TWO 3-D boxes covering 64 rows (86 KB): {32 m, 64 r, 4 panels} of In and {32 n, 64 r, BN/32 panels}
+// of dZ, landing as [panel][64 r][32] -- the k-blocks of a stage are 4 KB apart inside each 8 KB panel.
+constexpr int WIDE_BK = 64;
+constexpr int WIDE_A_BYTES = BM * WIDE_BK * 4;       // 32 KB
+constexpr int WIDE_B_BYTES = 256 * WIDE_BK * 4;      // 64 KB (max BN)
+constexpr int WIDE_STAGES = 2;
+constexpr int WIDE_SMEM = WIDE_STAGES * (WIDE_A_BYTES + WIDE_B_BYTES) + 1024 + 256;
+
+template <int VARIANT>      // (a template only so that the header may be included by several translation units)
+__global__ void __launch_bounds__(kThreads, 1) gemm_wide_kernel(const __grid_constant__ GemmParams p) {
+  using namespace ptx;
+  constexpr int STAGE_BYTES = WIDE_A_BYTES + WIDE_B_BYTES;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  uint8_t* gen = smem_raw + (base - raw);
+  const uint32_t bars = base + WIDE_STAGES * STAGE_BYTES;
+  volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(gen + WIDE_STAGES * STAGE_BYTES + 8 * (2 * WIDE_STAGES + 1));
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (WIDE_STAGES + s); };
+  const uint32_t tmem_full_bar = bars + 8u * (2 * WIDE_STAGES);
+
+  auto stamp = [&](int slot) {      // debug (scripts/wgrad_trace.py): %globaltimer stamps, 8 per CTA
+    if (p.trace) {
+      const int cta = blockIdx.x + gridDim.x * blockIdx.z;
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      if (cta < 160) p.trace[cta * 8 + slot] = t;
+    }
+  };
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * BM, n0 = blockIdx.y * p.BN;
+  if (threadIdx.x == 0) stamp(0);
+  const int kblocks = (p.K + WIDE_BK - 1) / WIDE_BK;          // 64-row blocks of the contraction
+  const int kb0 = (int)((long long)kblocks * blockIdx.z / gridDim.z);
+  const int kb1 = (int)((long long)kblocks * (blockIdx.z + 1) / gridDim.z);
+  const int nbp = (p.BN + 31) / 32;                           // 32-column panels of dZ per stage
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&p.ta_hi);
+    prefetch_tensormap(&p.tb_hi);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < WIDE_STAGES; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc(smem_u32((const void*)tmem_ptr_smem), TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  griddep_wait();      // (no-op unless launched programmatically: everything above overlaps the previous kernel's drain)
+  if (threadIdx.x == 0) stamp(1);
+
+  if (warp == 0) {
+    if (lane == 0) {
+      const uint32_t tx = (uint32_t)(WIDE_A_BYTES + nbp * 32 * WIDE_BK * 4);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(empty_bar(stage), phase ^ 1u);
+        const uint32_t sa = base + stage * STAGE_BYTES;
+        mbar_arrive_expect_tx(full_bar(stage), tx);
+        tma_load_3d(sa, &p.ta_hi, full_bar(stage), 0, kb * WIDE_BK, m0 >> 5);
+        tma_load_3d(sa + WIDE_A_BYTES, &p.tb_hi, full_bar(stage), 0, kb * WIDE_BK, n0 >> 5);
+        if (++stage == WIDE_STAGES) { stage = 0; phase ^= 1u; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_tf32(BM, p.BN, MAJOR_MN, MAJOR_MN);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(full_bar(stage), phase);
+        tc_fence_after();
+        if (kb == kb0) stamp(2);
+        if (kb == kb1 - 1) stamp(3);
+        const uint32_t sa = base + stage * STAGE_BYTES, sb = sa + WIDE_A_BYTES;
+        // rows beyond K (a ragged last block) arrive as zeros: issuing their MMAs is harmless
+#pragma unroll
+        for (int k8 = 0; k8 < WIDE_BK / UMMA_K; ++k8) {
+          // MN-major, 128-byte swizzle with 32-byte atoms: 8 rows of the contraction = 1 KB; panels 8 KB apart
+          const uint64_t da = make_smem_desc(sa + k8 * 1024u, 8192u, 512u, 1u);
+          const uint64_t db = make_smem_desc(sb + k8 * 1024u, 8192u, 512u, 1u);
+          mma_tf32_ss(tmem_base, da, db, idesc, (kb > kb0 || k8 > 0) ? 1u : 0u);
+        }
+        tc_commit(empty_bar(stage));
+        if (kb == kb1 - 1) tc_commit(tmem_full_bar);
+        if (++stage == WIDE_STAGES) { stage = 0; phase ^= 1u; }
+      }
+    }
+  }
+  __syncwarp();
+  {
+    const int q = warp & 3, part = warp >> 2;
+    const int row = m0 + q * 32 + lane;
+    const bool row_ok = row < p.M;
+    const bool have_acc = kb1 > kb0;
+    if (have_acc) {
+      mbar_wait(tmem_full_bar, 0);
+      tc_fence_after();
+    }
+    if (threadIdx.x == 128) stamp(4);
+    float l1 = 0.f, l2 = 0.f, lq = 0.f;
+    const int ncols_out = min(p.N - n0, p.BN);
+    const int nsteps = (ncols_out + CW - 1) / CW, sper = (nsteps + EPI_PARTS - 1) / EPI_PARTS;
+    const int c_begin = min(part * sper, nsteps) * CW, c_end = min((part + 1) * sper, nsteps) * CW;
+    epilogue_dispatch<EPI_STORE>(p, tmem_base + ((uint32_t)(q * 32) << 16), have_acc, row, row_ok, n0, c_begin, c_end, nullptr, l1, l2, lq);
+    if (threadIdx.x == 128) stamp(5);
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) stamp(6);
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
 }  // namespace tc
 }  // namespace fdsm

@@ -233,5 +233,47 @@ inline int launch_gemm(GemmParams& p, const Operand& A, const Operand& B, int M,
   FDSM_LAUNCH_CHECK("tc_gemm");
 }
 
+
+// dWt[M x N] partials = In^T dZ: In [rows x lda] (M of its columns), dZ [rows x ldb] (N <= 256 of its columns), both row-major
+// with the contraction over `rows`; split s is written at out + s * split_stride with leading dimension ldo.
+// FDSM_WGRAD_WIDE=0 routes the launch through the general kernel (A/B measurements).
+inline int launch_wgrad_wide(const float* In, long long lda, const float* dZ, long long ldb, int M, int N, long long rows, int splits,
+                             float* out, long long ldo, long long split_stride, cudaStream_t st, bool pdl = false) {
+  static const bool wide = [] { const char* e = getenv("FDSM_WGRAD_WIDE"); return !(e && e[0] == '0'); }();
+  if (!wide || N > 256) {
+    GemmParams gp = {};
+    gp.epi = EPI_STORE;
+    gp.out_hi = out; gp.ldo = ldo; gp.split_stride = split_stride;
+    Operand A{In, nullptr, lda, MAJOR_MN}, B{dZ, nullptr, ldb, MAJOR_MN};
+    return launch_gemm(gp, A, B, M, N, (int)rows, N, 1, splits, st);
+  }
+  FDSM_REQUIRE(M >= 1 && N >= 1 && rows >= 1 && splits >= 1, "wgrad: bad shape");
+  GemmParams p = {};
+  p.M = M; p.N = N; p.K = (int)rows; p.BN = (N + 15) / 16 * 16; p.a_major = MAJOR_MN; p.b_major = MAJOR_MN; p.passes = 1;
+  p.epi = EPI_STORE; p.out_hi = out; p.ldo = ldo; p.split_stride = split_stride;
+  {
+    // (32 columns, row, 32-column panel): a box of 4 (In) / BN/32 (dZ) panels x 64 rows lands as [panel][64 rows][32]
+    const long long da[3] = {32, rows, (lda + 31) / 32}, sa[2] = {4 * lda, 128};
+    const int ba[3] = {32, WIDE_BK, BM / 32};
+    int rc = make_tmap_nd(&p.ta_hi, In, 3, da, sa, ba, true, "wgrad In");
+    if (rc) return rc;
+    const int nbp = (p.BN + 31) / 32;
+    const long long db[3] = {32, rows, nbp}, sb[2] = {4 * ldb, 128};
+    const int bb[3] = {32, WIDE_BK, nbp};
+    rc = make_tmap_nd(&p.tb_hi, dZ, 3, db, sb, bb, true, "wgrad dZ");
+    if (rc) return rc;
+  }
+  p.trace = trace_buffer() ? trace_buffer() + (size_t)TRACE_STRIDE * trace_launch_index()++ : nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] { cudaFuncSetAttribute(gemm_wide_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, WIDE_SMEM); });
+  const long long kblocks = (rows + WIDE_BK - 1) / WIDE_BK;
+  if (splits > kblocks) splits = (int)kblocks;
+  dim3 grid((M + BM - 1) / BM, 1, splits);
+  // programmatic launch only where the stream predecessor is a kernel of ours that the caller vouches for (`pdl`)
+  if (pdl) return cuda_status(launch_pdl(gemm_wide_kernel<0>, grid, dim3(kThreads), (size_t)WIDE_SMEM, st, p), "tc_gemm(wgrad wide)");
+  gemm_wide_kernel<0><<<grid, kThreads, WIDE_SMEM, st>>>(p);
+  FDSM_LAUNCH_CHECK("tc_gemm(wgrad wide)");
+}
+
 }  // namespace tc
 }  // namespace fdsm

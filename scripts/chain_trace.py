@@ -38,3 +38,14 @@ for g, n in enumerate(names):
     print(f"{n:8s} {a.mean():10.2f} {(a - prev).mean():16.2f} {(d - a).mean():14.2f} {(j - d).mean():10.2f} {m.mean():16.2f}   | end max {j.max():.2f}")
     prev = j
 print(f"kernel span (first CTA start -> last epilogue done): {rel[:, 4 + 4 * (2 * L - 2)].max():.2f} us")
+mode = int(os.environ.get("FDSM_CHAIN_TRACE_MODE", "0"))
+if L == 3 and mode == 0:
+    a0 = rel[:, 2]          # fwd0 accumulator ready
+    print("fwd1, MMA thread, per k-block (us after fwd0's accumulator was ready; mean over CTAs):  operand block published | its weights landed")
+    print("   " + "  ".join(f"kb{kb}: {(rel[:, 22 + 2 * kb] - a0).mean():5.2f} | {(rel[:, 23 + 2 * kb] - a0).mean():5.2f}" for kb in range(7)))
+    print(f"   MMAs issued {(rel[:, 5 + 4] - a0).mean():5.2f}   accumulator ready {(rel[:, 2 + 4] - a0).mean():5.2f}")
+elif L == 3:
+    d0 = rel[:, 3]          # fwd0's accumulator dumped: the epilogue warps start together
+    what = "whole epilogue" if mode == 1 else "block 1 published"
+    print(f"fwd1's epilogue, per warp: {what} (us after the dump; mean / max over CTAs)")
+    print("   " + "  ".join(f"w{w}: {(rel[:, 22 + w] - d0).mean():4.2f}/{(rel[:, 22 + w] - d0).max():4.2f}" for w in range(16)))
