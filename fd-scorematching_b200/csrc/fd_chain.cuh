@@ -358,6 +358,7 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
   if (warp == PROD_WARP) {
     // ===== TMA producer (one thread): the weight stream of every phase back to back, plus phase 0's A operand ============
     if (lane == 0) {
+      pdl_wait();        // XV comes from the kernel before this one on the stream (programmatic launch: see launch_chain_cl)
       int wu = 0; uint32_t wph = 0; int useq = 0;
       auto next_unit = [&]() -> uint32_t {          // waits for the ring slot, arms its barrier; returns its address (0: a peer issues)
         mbar_wait_parked(w_empty(2 * wu), wph ^ 1u);                 // every CTA of the cluster has finished with this unit
@@ -670,51 +671,64 @@ struct InputArgs {
   unsigned long long seed, offset, row0; const unsigned long long* offset_dev;
   float* xv; int B, Bp, D, kpad0;
 };
+// FAST = compile-time specialisation of the two production configurations (the mode tests fold away and the compiler
+// interleaves the Philox chains of a thread's chunks, as for the stack kernel's MODE_ENERGY3): 1 = fp32 samples, 2 = uint8
+// pixels + Gaussian noise; both: Philox direction, normalised, 16-byte aligned rows, D <= 1024.  0 = everything else.
+// Bit-identical outputs (tests/test_jet_gpu.py compares against FDSM_JET_INPUTS_GENERAL=1).
+template <int FAST>
 __global__ void __launch_bounds__(256, 4) jet_inputs_kernel(InputArgs a) {
   constexpr int G = 128, MAXC = 2;
   __shared__ float red[256 / 32];
+  pdl_launch_dependents();      // the chain kernel behind this grid sets up (barriers, TMEM, head weights) as blocks here retire
   if (a.offset_dev) a.offset += __ldg(a.offset_dev);
+  if (FAST) { a.dir = nullptr; a.normalize = 1; }
+  if (FAST == 1) a.x8 = nullptr;
+  if (FAST == 2) a.x = nullptr;
   const int gid = threadIdx.x / G, t = threadIdx.x % G;
   const int D = a.D, nchunk = (D + 3) >> 2;
-  const bool xvec = a.x8 ? ((D & 3) == 0 && (a.ldx & 3) == 0 && (reinterpret_cast<uintptr_t>(a.x8) & 3) == 0)
-                         : ((D & 3) == 0 && (a.ldx & 3) == 0 && aligned16(a.x));
-  const bool dvec = a.dir && (D & 3) == 0 && (a.lddir & 3) == 0 && aligned16(a.dir);
+  const bool xvec = FAST ? true : a.x8 ? ((D & 3) == 0 && (a.ldx & 3) == 0 && (reinterpret_cast<uintptr_t>(a.x8) & 3) == 0)
+                                       : ((D & 3) == 0 && (a.ldx & 3) == 0 && aligned16(a.x));
+  const bool dvec = !FAST && a.dir && (D & 3) == 0 && (a.lddir & 3) == 0 && aligned16(a.dir);
   const long long ngroups = (a.Bp + 1) / 2;
   for (long long rg = blockIdx.x; rg < ngroups; rg += gridDim.x) {
     const long long b = rg * 2 + gid;
     const bool active = b < a.B;
     auto raw = [&](int j) -> float4 {
       const int e = 4 * j;
-      if (a.dir) {
+      if (!FAST && a.dir) {
         const float* r = a.dir + b * a.lddir;
         if (dvec) return ldg4(r + e);
         return make_float4(e < D ? __ldg(r + e) : 0.f, e + 1 < D ? __ldg(r + e + 1) : 0.f, e + 2 < D ? __ldg(r + e + 2) : 0.f,
                            e + 3 < D ? __ldg(r + e + 3) : 0.f);
       }
       float4 n = philox_normal4(a.seed, a.offset, STREAM_DIRECTION, a.row0 + (unsigned long long)b, (uint32_t)j);
-      if (e + 1 >= D) n.y = 0.f;
-      if (e + 2 >= D) n.z = 0.f;
-      if (e + 3 >= D) n.w = 0.f;
+      if (!FAST) {       // (FAST: D % 4 == 0, every chunk is whole)
+        if (e + 1 >= D) n.y = 0.f;
+        if (e + 2 >= D) n.z = 0.f;
+        if (e + 3 >= D) n.w = 0.f;
+      }
       return n;
     };
     // the sample row: fp32, or uint8 pixels scaled (torchvision ToTensor: / 255) plus the on-device noise of
     // DeepEBM/train_ssm.py:62 (x + ssm_eps * randn) drawn from Philox stream 1 -- the host ships 1 byte per pixel
     auto load_x = [&](int j) -> float4 {
       const int e = 4 * j;
-      if (a.x8) {
+      if (FAST == 2 || (!FAST && a.x8)) {
         const unsigned char* r = a.x8 + b * a.ldx;
         uchar4 q;
         if (xvec) q = *reinterpret_cast<const uchar4*>(r + e);
         else q = make_uchar4(e < D ? r[e] : 0, e + 1 < D ? r[e + 1] : 0, e + 2 < D ? r[e + 2] : 0, e + 3 < D ? r[e + 3] : 0);
         float4 xx = make_float4(q.x * a.x8_scale, q.y * a.x8_scale, q.z * a.x8_scale, q.w * a.x8_scale);
-        if (a.x_noise != 0.f) {
+        if (FAST == 2 || a.x_noise != 0.f) {
           const float4 n = philox_normal4(a.seed, a.offset, STREAM_NOISE, a.row0 + (unsigned long long)b, (uint32_t)j);
           xx.x = fmaf(a.x_noise, n.x, xx.x); xx.y = fmaf(a.x_noise, n.y, xx.y); xx.z = fmaf(a.x_noise, n.z, xx.z);
           xx.w = fmaf(a.x_noise, n.w, xx.w);
         }
-        if (e + 1 >= D) xx.y = 0.f;
-        if (e + 2 >= D) xx.z = 0.f;
-        if (e + 3 >= D) xx.w = 0.f;
+        if (!FAST) {
+          if (e + 1 >= D) xx.y = 0.f;
+          if (e + 2 >= D) xx.z = 0.f;
+          if (e + 3 >= D) xx.w = 0.f;
+        }
         return xx;
       }
       const float* xrow = a.x + b * a.ldx;
@@ -743,7 +757,7 @@ __global__ void __launch_bounds__(256, 4) jet_inputs_kernel(InputArgs a) {
           ss += dreg[k].x * dreg[k].x + dreg[k].y * dreg[k].y + dreg[k].z * dreg[k].z + dreg[k].w * dreg[k].w;
         }
       }
-      if (a.normalize)
+      if (!FAST && a.normalize)
         for (int j = t + MAXC * G; j < nchunk; j += G) {
           const float4 d = raw(j);
           ss += d.x * d.x + d.y * d.y + d.z * d.z + d.w * d.w;
@@ -758,7 +772,7 @@ __global__ void __launch_bounds__(256, 4) jet_inputs_kernel(InputArgs a) {
       for (int c = t; c < a.kpad0; c += G) { xr[c] = 0.f; vr[c] = 0.f; }
       continue;
     }
-    const bool exact = a.dir != nullptr;     // injected draws keep the reference's rounding sequence u / ||u|| * eps
+    const bool exact = !FAST && a.dir != nullptr;     // injected draws keep the reference's rounding sequence u / ||u|| * eps
     const float inv = a.normalize && !exact ? __fdiv_rn(a.scale, nrm) : 1.f;
     for (int j = t, k = 0; j < nchunk; j += G, ++k) {
       const int e = 4 * j;
@@ -774,9 +788,11 @@ __global__ void __launch_bounds__(256, 4) jet_inputs_kernel(InputArgs a) {
       else v = make_float4(d.x * inv, d.y * inv, d.z * inv, d.w * inv);
       // kpad0 is a multiple of 32 and the buffer is 16-byte aligned: the chunk store is always in range and aligned.
       // A partial last chunk (D % 4 != 0) carries the first padding columns itself: x gets the ones column at D, v zeros
-      if (D - e == 1) xx.y = 1.f;
-      if (D - e == 2) xx.z = 1.f;
-      if (D - e == 3) xx.w = 1.f;
+      if (!FAST) {
+        if (D - e == 1) xx.y = 1.f;
+        if (D - e == 2) xx.z = 1.f;
+        if (D - e == 3) xx.w = 1.f;
+      }
       *reinterpret_cast<float4*>(xr + e) = make_float4(tf32r(xx.x), tf32r(xx.y), tf32r(xx.z), tf32r(xx.w));
       *reinterpret_cast<float4*>(vr + e) = make_float4(tf32r(v.x), tf32r(v.y), tf32r(v.z), tf32r(v.w));
     }

@@ -285,7 +285,12 @@ constexpr int WIDE_B_BYTES = 256 * WIDE_BK * 4;      // 64 KB (max BN)
 constexpr int WIDE_STAGES = 2;
 constexpr int WIDE_SMEM = WIDE_STAGES * (WIDE_A_BYTES + WIDE_B_BYTES) + 1024 + 256;
 
-template <int VARIANT>      // (a template only so that the header may be included by several translation units)
+// CS > 1: the CTAs of a cluster (CS consecutive splits of one output tile, cluster dimension z) add their accumulators
+// through distributed shared memory before anything goes to HBM -- every CTA stages its 128 x BN tile in its own shared
+// memory (the pipeline's buffers, free by then), and CTA r of the cluster sums rows [128 r / CS, 128 (r + 1) / CS) over the
+// CS tiles in rank order (fixed order: deterministic) and writes them as partial blockIdx.z / CS: 1 / CS of the split-K
+// partial traffic, written as coalesced 16-byte row segments, and 1 / CS of what the reduce / update kernel reads back.
+template <int CS>
 __global__ void __launch_bounds__(kThreads, 1) gemm_wide_kernel(const __grid_constant__ GemmParams p) {
   using namespace ptx;
   constexpr int STAGE_BYTES = WIDE_A_BYTES + WIDE_B_BYTES;
@@ -385,11 +390,71 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_wide_kernel(const __grid_con
       tc_fence_after();
     }
     if (threadIdx.x == 128) stamp(4);
-    float l1 = 0.f, l2 = 0.f, lq = 0.f;
     const int ncols_out = min(p.N - n0, p.BN);
     const int nsteps = (ncols_out + CW - 1) / CW, sper = (nsteps + EPI_PARTS - 1) / EPI_PARTS;
     const int c_begin = min(part * sper, nsteps) * CW, c_end = min((part + 1) * sper, nsteps) * CW;
-    epilogue_dispatch<EPI_STORE>(p, tmem_base + ((uint32_t)(q * 32) << 16), have_acc, row, row_ok, n0, c_begin, c_end, nullptr, l1, l2, lq);
+    (void)row; (void)row_ok;
+    // stage: accumulator row (q, lane) -> shared [128][ldt] (ldt = BN + 4: the 16-byte row pieces of a warp's 32 rows fall
+    // on all eight bank groups); un-staged, every warp-wide 16-byte store touches 32 different rows and the epilogue of a
+    // 128 x 208 tile takes 4.5 us (profiles/r02_wgrad_trace_v1.txt)
+    const int ldt = p.BN + 4;
+    float* stage = reinterpret_cast<float*>(gen);
+    {
+      const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16);
+      float* srow = stage + (q * 32 + lane) * ldt;
+      for (int c = c_begin; c < c_end; c += CW) {
+        float v[8];
+        if (have_acc) {
+          tmem_ld_32x8(trow + (uint32_t)c, v);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) v[i] = 0.f;
+        }
+        *reinterpret_cast<float4*>(srow + c) = make_float4(v[0], v[1], v[2], v[3]);
+        *reinterpret_cast<float4*>(srow + c + 4) = make_float4(v[4], v[5], v[6], v[7]);
+      }
+    }
+    if constexpr (CS == 1) {
+      // coalesced row copies shared -> global (one asynchronous bulk copy per row when the rows are 16-byte aligned)
+      const bool vec = ((p.ldo | n0) & 3) == 0 && aligned16(p.out_hi) && (p.split_stride & 3) == 0;
+      __syncthreads();       // the tile is complete (every thread of the CTA runs this epilogue)
+      stage_store_tile(stage, ldt, p.out_hi + (long long)blockIdx.z * p.split_stride + (long long)m0 * p.ldo + n0, p.ldo,
+                       min(BM, p.M - m0), ncols_out, vec);
+    } else {
+      tc_fence_before();
+      cluster_sync_all();                       // every tile of the cluster is staged (release / acquire at cluster scope)
+      const uint32_t crank = cluster_ctarank();
+      constexpr int RPC = BM / CS;              // rows this CTA reduces
+      const int nc4 = (ncols_out + 3) >> 2;
+      const uint32_t stage_s = smem_u32(stage);
+      uint32_t peer[CS];
+#pragma unroll
+      for (int c = 0; c < CS; ++c)
+        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(peer[c]) : "r"(stage_s), "r"(c));
+      float* outp = p.out_hi + (long long)(blockIdx.z / CS) * p.split_stride;
+      for (int i = threadIdx.x; i < RPC * nc4; i += kThreads) {
+        const int r = crank * RPC + i / nc4, c4 = i % nc4;
+        if (m0 + r >= p.M) continue;
+        const uint32_t off = (uint32_t)(r * ldt + 4 * c4) * 4u;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int c = 0; c < CS; ++c) {
+          float4 v;
+          asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(peer[c] + off));
+          acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        }
+        float* o = outp + (long long)(m0 + r) * p.ldo + n0 + 4 * c4;
+        if (4 * c4 + 3 < ncols_out && aligned16(o)) {
+          *reinterpret_cast<float4*>(o) = acc;
+        } else {
+          if (4 * c4 < ncols_out) o[0] = acc.x;
+          if (4 * c4 + 1 < ncols_out) o[1] = acc.y;
+          if (4 * c4 + 2 < ncols_out) o[2] = acc.z;
+          if (4 * c4 + 3 < ncols_out) o[3] = acc.w;
+        }
+      }
+      cluster_sync_all();                       // no CTA leaves while a peer still reads its tile
+    }
     if (threadIdx.x == 128) stamp(5);
     tc_fence_before();
   }

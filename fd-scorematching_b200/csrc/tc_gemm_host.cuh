@@ -234,13 +234,37 @@ inline int launch_gemm(GemmParams& p, const Operand& A, const Operand& B, int M,
 }
 
 
+// Co-resident CTAs of gemm_wide_kernel when launched as clusters of `cs` along the split dimension (one CTA per SM by shared
+// memory; clusters must fit inside a GPC, so this is a little below the SM count for cs = 4).  0: not launchable.
+template <int CS>
+inline int wgrad_cluster_capacity_of() {
+  cudaFuncSetAttribute(gemm_wide_kernel<CS>, cudaFuncAttributeMaxDynamicSharedMemorySize, WIDE_SMEM);
+  if (CS == 1) return sm_count();
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(1, 1, (unsigned)(sm_count() / CS * CS)); cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = WIDE_SMEM;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 1; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = CS;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, gemm_wide_kernel<CS>, &cfg) != cudaSuccess) { (void)cudaGetLastError(); n = 0; }
+  return n * CS;
+}
+inline int wgrad_cluster_capacity(int cs) {
+  static const int c1 = wgrad_cluster_capacity_of<1>(), c2 = wgrad_cluster_capacity_of<2>(), c4 = wgrad_cluster_capacity_of<4>();
+  return cs == 4 ? c4 : cs == 2 ? c2 : c1;
+}
+
 // dWt[M x N] partials = In^T dZ: In [rows x lda] (M of its columns), dZ [rows x ldb] (N <= 256 of its columns), both row-major
-// with the contraction over `rows`; split s is written at out + s * split_stride with leading dimension ldo.
-// FDSM_WGRAD_WIDE=0 routes the launch through the general kernel (A/B measurements).
+// with the contraction over `rows`.  `cluster` (1, 2, 4; splits % cluster == 0) consecutive splits of an output tile add their
+// accumulators on chip (distributed shared memory): partial j = splits [cluster j, cluster (j + 1)) is written at
+// out + j * split_stride with leading dimension ldo -- splits / cluster partials in all.
+// FDSM_WGRAD_WIDE=0 routes the launch through the general kernel (A/B measurements; cluster must be 1 then).
 inline int launch_wgrad_wide(const float* In, long long lda, const float* dZ, long long ldb, int M, int N, long long rows, int splits,
-                             float* out, long long ldo, long long split_stride, cudaStream_t st, bool pdl = false) {
+                             int cluster, float* out, long long ldo, long long split_stride, cudaStream_t st, bool pdl = false) {
   static const bool wide = [] { const char* e = getenv("FDSM_WGRAD_WIDE"); return !(e && e[0] == '0'); }();
   if (!wide || N > 256) {
+    FDSM_REQUIRE(cluster == 1, "wgrad: the general kernel has no cluster reduction");
     GemmParams gp = {};
     gp.epi = EPI_STORE;
     gp.out_hi = out; gp.ldo = ldo; gp.split_stride = split_stride;
@@ -248,6 +272,7 @@ inline int launch_wgrad_wide(const float* In, long long lda, const float* dZ, lo
     return launch_gemm(gp, A, B, M, N, (int)rows, N, 1, splits, st);
   }
   FDSM_REQUIRE(M >= 1 && N >= 1 && rows >= 1 && splits >= 1, "wgrad: bad shape");
+  FDSM_REQUIRE((cluster == 1 || cluster == 2 || cluster == 4) && splits % cluster == 0, "wgrad: %d splits in clusters of %d", splits, cluster);
   GemmParams p = {};
   p.M = M; p.N = N; p.K = (int)rows; p.BN = (N + 15) / 16 * 16; p.a_major = MAJOR_MN; p.b_major = MAJOR_MN; p.passes = 1;
   p.epi = EPI_STORE; p.out_hi = out; p.ldo = ldo; p.split_stride = split_stride;
@@ -264,15 +289,27 @@ inline int launch_wgrad_wide(const float* In, long long lda, const float* dZ, lo
     if (rc) return rc;
   }
   p.trace = trace_buffer() ? trace_buffer() + (size_t)TRACE_STRIDE * trace_launch_index()++ : nullptr;
-  static std::once_flag once;
-  std::call_once(once, [] { cudaFuncSetAttribute(gemm_wide_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, WIDE_SMEM); });
-  const long long kblocks = (rows + WIDE_BK - 1) / WIDE_BK;
-  if (splits > kblocks) splits = (int)kblocks;
-  dim3 grid((M + BM - 1) / BM, 1, splits);
+  (void)wgrad_cluster_capacity(1);     // (sets the shared-memory attribute of every instantiation, once)
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((M + BM - 1) / BM, 1, splits); cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = WIDE_SMEM; cfg.stream = st;
+  cudaLaunchAttribute at[2];
+  int na = 0;
+  if (cluster > 1) {
+    at[na].id = cudaLaunchAttributeClusterDimension;
+    at[na].val.clusterDim.x = 1; at[na].val.clusterDim.y = 1; at[na].val.clusterDim.z = cluster;
+    ++na;
+  }
   // programmatic launch only where the stream predecessor is a kernel of ours that the caller vouches for (`pdl`)
-  if (pdl) return cuda_status(launch_pdl(gemm_wide_kernel<0>, grid, dim3(kThreads), (size_t)WIDE_SMEM, st, p), "tc_gemm(wgrad wide)");
-  gemm_wide_kernel<0><<<grid, kThreads, WIDE_SMEM, st>>>(p);
-  FDSM_LAUNCH_CHECK("tc_gemm(wgrad wide)");
+  if (pdl && pdl_enabled()) {
+    at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  cfg.attrs = at; cfg.numAttrs = na;
+  cudaError_t e = cluster == 4 ? cudaLaunchKernelEx(&cfg, gemm_wide_kernel<4>, p)
+                : cluster == 2 ? cudaLaunchKernelEx(&cfg, gemm_wide_kernel<2>, p)
+                               : cudaLaunchKernelEx(&cfg, gemm_wide_kernel<1>, p);
+  return cuda_status(e, "tc_gemm(wgrad wide)");
 }
 
 }  // namespace tc

@@ -103,6 +103,23 @@ def test_jet_philox_direction_is_the_stack_kernels(fdsm):
     assert float((XV[1, :50, :64].view(torch.int32) & 0x1FFF).abs().max()) == 0
 
 
+def test_jet_inputs_specialisation_is_bit_identical_to_the_general_kernel(fdsm):
+    """jet_inputs_kernel<1> (fp32 rows, 16-byte aligned, ld % 4 == 0: the production configuration) against the general
+    instantiation, reached with the same samples in a buffer whose row stride is not a multiple of 4: same XV bits."""
+    net, _ = _pair(fdsm, 64, 48, 3, "nsoftplus", "quadratic")
+    x = nets.np_rand(1, 50, 64).float().to(DEV)
+    def xv(xin):
+        net.fd_ssm_loss_and_grad(xin, 0.05, 400.0, draw=(99, 7, 1000))
+        o = net._step_state["offsets"]
+        return net._step_state["ws"][o[5]:o[5] + 2 * o[1] * o[3]].clone()
+    fast = xv(x)
+    wide = torch.zeros(50, 65, device=DEV)
+    wide[:, :64] = x
+    slow = xv(wide[:, :64])            # row stride 65 floats
+    assert wide[:, :64].stride(0) == 65
+    assert torch.equal(fast, slow)
+
+
 def test_jet_is_deterministic_and_shard_invariant(fdsm):
     """Same inputs -> bit-identical loss and gradient; a batch split in two halves (row0 offsets) gives the mean of the
     halves' gradients up to fp32 summation order."""
