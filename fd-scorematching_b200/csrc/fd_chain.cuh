@@ -313,6 +313,7 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
   constexpr uint16_t CMASK = (uint16_t)((1u << CL) - 1u);
 
   if (p.trace && threadIdx.x == 96) stamp_now(p, 0);
+  pdl_launch_dependents();           // the weight-gradient launch behind this kernel is processed while it runs
   if (threadIdx.x == 0) {
     for (int s = 0; s < MAX_NA; ++s) { mbar_init(a_full(s), 1); mbar_init(a_empty(s), 1); mbar_init(a_ready(s), EPI_WARPS); }
     for (int s = 0; s < MAX_RAW; ++s) {
@@ -676,10 +677,9 @@ struct InputArgs {
 // pixels + Gaussian noise; both: Philox direction, normalised, 16-byte aligned rows, D <= 1024.  0 = everything else.
 // Bit-identical outputs (tests/test_jet_gpu.py compares against FDSM_JET_INPUTS_GENERAL=1).
 template <int FAST>
-__global__ void __launch_bounds__(256, 4) jet_inputs_kernel(InputArgs a) {
+__device__ __forceinline__ void jet_inputs_body(InputArgs a, const int block, const int nblocks) {
   constexpr int G = 128, MAXC = 2;
   __shared__ float red[256 / 32];
-  pdl_launch_dependents();      // the chain kernel behind this grid sets up (barriers, TMEM, head weights) as blocks here retire
   if (a.offset_dev) a.offset += __ldg(a.offset_dev);
   if (FAST) { a.dir = nullptr; a.normalize = 1; }
   if (FAST == 1) a.x8 = nullptr;
@@ -690,7 +690,7 @@ __global__ void __launch_bounds__(256, 4) jet_inputs_kernel(InputArgs a) {
                                        : ((D & 3) == 0 && (a.ldx & 3) == 0 && aligned16(a.x));
   const bool dvec = !FAST && a.dir && (D & 3) == 0 && (a.lddir & 3) == 0 && aligned16(a.dir);
   const long long ngroups = (a.Bp + 1) / 2;
-  for (long long rg = blockIdx.x; rg < ngroups; rg += gridDim.x) {
+  for (long long rg = block; rg < ngroups; rg += nblocks) {
     const long long b = rg * 2 + gid;
     const bool active = b < a.B;
     auto raw = [&](int j) -> float4 {
@@ -798,6 +798,12 @@ __global__ void __launch_bounds__(256, 4) jet_inputs_kernel(InputArgs a) {
     }
     for (int c = 4 * nchunk + t; c < a.kpad0; c += G) { xr[c] = c == D ? 1.f : 0.f; vr[c] = 0.f; }
   }
+}
+
+template <int FAST>
+__global__ void __launch_bounds__(256, 4) jet_inputs_kernel(InputArgs a) {
+  pdl_launch_dependents();      // the chain kernel behind this grid sets up (barriers, TMEM, head weights) as blocks here retire
+  jet_inputs_body<FAST>(a, blockIdx.x, gridDim.x);
 }
 
 // ---- after the chain: loss and head-parameter gradient from the per-tile records (fixed order: deterministic) ------------

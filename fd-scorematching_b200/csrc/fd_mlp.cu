@@ -157,12 +157,11 @@ struct PrepArgs {
   int K[16], kpad[16];
   int H, npad;
 };
-__global__ void __launch_bounds__(256) prep_weights_kernel(const PrepArgs a) {
+__device__ __forceinline__ void prep_weights_body(const PrepArgs& a, const int bx, const int by, const int l) {
   // 32x32 tile transpose through shared memory: coalesced reads of W[n][k] (k fastest) and writes of Wt[k][n]
   __shared__ float tile[32][33];
-  const int l = blockIdx.z;
   const int K = a.K[l], kpad = a.kpad[l], H = a.H, npad = a.npad;
-  const int k0 = blockIdx.x * 32, n0 = blockIdx.y * 32;
+  const int k0 = bx * 32, n0 = by * 32;
   if (k0 >= kpad) return;   // uniform per block
   const float* __restrict__ W = a.W[l];
   const float* __restrict__ b = a.b[l];
@@ -191,6 +190,7 @@ __global__ void __launch_bounds__(256) prep_weights_kernel(const PrepArgs a) {
     }
   }
 }
+__global__ void __launch_bounds__(256) prep_weights_kernel(const PrepArgs a) { prep_weights_body(a, blockIdx.x, blockIdx.y, blockIdx.z); }
 
 // ---- head backward: dE -> dZ_L and the head parameter gradients --------------------------------------------
 // dH[r,j] = g (l2 w1[j] + l1 w2[j] + 2 wq[j] h)   (quadratic)   |   g w[j]   (linear);   dZ = dH * act'(h)

@@ -290,8 +290,16 @@ constexpr int WIDE_SMEM = WIDE_STAGES * (WIDE_A_BYTES + WIDE_B_BYTES) + 1024 + 2
 // memory (the pipeline's buffers, free by then), and CTA r of the cluster sums rows [128 r / CS, 128 (r + 1) / CS) over the
 // CS tiles in rank order (fixed order: deterministic) and writes them as partial blockIdx.z / CS: 1 / CS of the split-K
 // partial traffic, written as coalesced 16-byte row segments, and 1 / CS of what the reduce / update kernel reads back.
+// one CTA's job: output tile `m_tile` of dWt, split `split` of `nsplits` along the contraction
+struct WideJob {
+  const CUtensorMap* ta; const CUtensorMap* tb;      // (param space)
+  int M, N, K, BN;
+  float* out; long long ldo, split_stride;
+  unsigned long long* trace; int cta;
+  int m_tile, split, nsplits;
+};
 template <int CS>
-__global__ void __launch_bounds__(kThreads, 1) gemm_wide_kernel(const __grid_constant__ GemmParams p) {
+__device__ __forceinline__ void gemm_wide_body(const WideJob& p) {
   using namespace ptx;
   constexpr int STAGE_BYTES = WIDE_A_BYTES + WIDE_B_BYTES;
   extern __shared__ uint8_t smem_raw[];
@@ -306,23 +314,24 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_wide_kernel(const __grid_con
 
   auto stamp = [&](int slot) {      // debug (scripts/wgrad_trace.py): %globaltimer stamps, 8 per CTA
     if (p.trace) {
-      const int cta = blockIdx.x + gridDim.x * blockIdx.z;
+      const int cta = p.cta;
       unsigned long long t;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
       if (cta < 160) p.trace[cta * 8 + slot] = t;
     }
   };
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.x * BM, n0 = blockIdx.y * p.BN;
+  const int m0 = p.m_tile * BM, n0 = 0;
+  griddep_launch_dependents();      // the kernel behind this one (launched programmatically) may become resident and wait
   if (threadIdx.x == 0) stamp(0);
   const int kblocks = (p.K + WIDE_BK - 1) / WIDE_BK;          // 64-row blocks of the contraction
-  const int kb0 = (int)((long long)kblocks * blockIdx.z / gridDim.z);
-  const int kb1 = (int)((long long)kblocks * (blockIdx.z + 1) / gridDim.z);
+  const int kb0 = (int)((long long)kblocks * p.split / p.nsplits);
+  const int kb1 = (int)((long long)kblocks * (p.split + 1) / p.nsplits);
   const int nbp = (p.BN + 31) / 32;                           // 32-column panels of dZ per stage
 
   if (warp == 0 && lane == 0) {
-    prefetch_tensormap(&p.ta_hi);
-    prefetch_tensormap(&p.tb_hi);
+    prefetch_tensormap(p.ta);
+    prefetch_tensormap(p.tb);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < WIDE_STAGES; ++s) {
@@ -349,8 +358,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_wide_kernel(const __grid_con
         mbar_wait(empty_bar(stage), phase ^ 1u);
         const uint32_t sa = base + stage * STAGE_BYTES;
         mbar_arrive_expect_tx(full_bar(stage), tx);
-        tma_load_3d(sa, &p.ta_hi, full_bar(stage), 0, kb * WIDE_BK, m0 >> 5);
-        tma_load_3d(sa + WIDE_A_BYTES, &p.tb_hi, full_bar(stage), 0, kb * WIDE_BK, n0 >> 5);
+        tma_load_3d(sa, p.ta, full_bar(stage), 0, kb * WIDE_BK, m0 >> 5);
+        tma_load_3d(sa + WIDE_A_BYTES, p.tb, full_bar(stage), 0, kb * WIDE_BK, n0 >> 5);
         if (++stage == WIDE_STAGES) { stage = 0; phase ^= 1u; }
       }
     }
@@ -416,9 +425,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_wide_kernel(const __grid_con
     }
     if constexpr (CS == 1) {
       // coalesced row copies shared -> global (one asynchronous bulk copy per row when the rows are 16-byte aligned)
-      const bool vec = ((p.ldo | n0) & 3) == 0 && aligned16(p.out_hi) && (p.split_stride & 3) == 0;
+      const bool vec = ((p.ldo | n0) & 3) == 0 && aligned16(p.out) && (p.split_stride & 3) == 0;
       __syncthreads();       // the tile is complete (every thread of the CTA runs this epilogue)
-      stage_store_tile(stage, ldt, p.out_hi + (long long)blockIdx.z * p.split_stride + (long long)m0 * p.ldo + n0, p.ldo,
+      stage_store_tile(stage, ldt, p.out + (long long)p.split * p.split_stride + (long long)m0 * p.ldo + n0, p.ldo,
                        min(BM, p.M - m0), ncols_out, vec);
     } else {
       tc_fence_before();
@@ -431,7 +440,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_wide_kernel(const __grid_con
 #pragma unroll
       for (int c = 0; c < CS; ++c)
         asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(peer[c]) : "r"(stage_s), "r"(c));
-      float* outp = p.out_hi + (long long)(blockIdx.z / CS) * p.split_stride;
+      float* outp = p.out + (long long)(p.split / CS) * p.split_stride;
       for (int i = threadIdx.x; i < RPC * nc4; i += kThreads) {
         const int r = crank * RPC + i / nc4, c4 = i % nc4;
         if (m0 + r >= p.M) continue;
@@ -464,6 +473,34 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_wide_kernel(const __grid_con
     tc_fence_after();
     tmem_dealloc(tmem_base, TMEM_COLS);
   }
+}
+
+template <int CS>
+__global__ void __launch_bounds__(kThreads, 1) gemm_wide_kernel(const __grid_constant__ GemmParams p) {
+  WideJob j{&p.ta_hi, &p.tb_hi, p.M, p.N, p.K, p.BN, p.out_hi, p.ldo, p.split_stride, p.trace,
+            (int)(blockIdx.x + gridDim.x * blockIdx.z), (int)blockIdx.x, (int)blockIdx.z, (int)gridDim.z};
+  gemm_wide_body<CS>(j);
+}
+
+// Several weight-gradient GEMMs (the layers of one backward pass) as ONE launch: CTA b serves job l with
+// cta0[l] <= b < cta0[l + 1]; inside a job the M tiles vary fastest.  One graph node instead of one per layer on as many
+// streams (no fork / join around them, and a single stream predecessor for the kernel that follows).
+constexpr int WIDE_MAX_JOBS = 5;
+struct alignas(64) WideBatchParams {
+  CUtensorMap ta[WIDE_MAX_JOBS], tb[WIDE_MAX_JOBS];
+  int M[WIDE_MAX_JOBS], K[WIDE_MAX_JOBS], mt[WIDE_MAX_JOBS], splits[WIDE_MAX_JOBS], cta0[WIDE_MAX_JOBS + 1];
+  float* out[WIDE_MAX_JOBS]; long long split_stride[WIDE_MAX_JOBS];
+  int N, BN, njobs; long long ldo;
+  unsigned long long* trace;
+};
+template <int VARIANT>      // (a template only so that the header may be included by several translation units)
+__global__ void __launch_bounds__(kThreads, 1) gemm_wide_batch_kernel(const __grid_constant__ WideBatchParams p) {
+  int l = 0;
+  while (l + 1 < p.njobs && (int)blockIdx.x >= p.cta0[l + 1]) ++l;
+  const int local = (int)blockIdx.x - p.cta0[l];
+  WideJob j{&p.ta[l], &p.tb[l], p.M[l], p.N, p.K[l], p.BN, p.out[l], p.ldo, p.split_stride[l], p.trace,
+            (int)blockIdx.x, local % p.mt[l], local / p.mt[l], p.splits[l]};
+  gemm_wide_body<1>(j);
 }
 
 }  // namespace tc

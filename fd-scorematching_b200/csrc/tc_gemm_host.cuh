@@ -312,5 +312,38 @@ inline int launch_wgrad_wide(const float* In, long long lda, const float* dZ, lo
   return cuda_status(e, "tc_gemm(wgrad wide)");
 }
 
+// The same GEMMs for several layers in one launch (see gemm_wide_batch_kernel).  Job l: In_l [rows_l x lda_l] (M_l of its
+// columns), dZ_l [rows_l x ldb] (N of its columns, the same N and ldb for every job), splits_l partials at out_l.
+struct WgradJob { const float* In; long long lda; const float* dZ; int M; long long rows; int splits; float* out; long long split_stride; };
+inline int launch_wgrad_batch(const WgradJob* jobs, int njobs, int N, long long ldb, long long ldo, cudaStream_t st, bool pdl) {
+  FDSM_REQUIRE(njobs >= 1 && njobs <= WIDE_MAX_JOBS && N >= 1 && N <= 256, "wgrad batch: %d jobs, N = %d", njobs, N);
+  WideBatchParams p = {};
+  p.N = N; p.BN = (N + 15) / 16 * 16; p.njobs = njobs; p.ldo = ldo;
+  const int nbp = (p.BN + 31) / 32;
+  int ctas = 0;
+  for (int l = 0; l < njobs; ++l) {
+    const WgradJob& j = jobs[l];
+    FDSM_REQUIRE(j.M >= 1 && j.rows >= 1 && j.splits >= 1, "wgrad batch: bad shape in job %d", l);
+    const long long da[3] = {32, j.rows, (j.lda + 31) / 32}, sa[2] = {4 * j.lda, 128};
+    const int ba[3] = {32, WIDE_BK, BM / 32};
+    int rc = make_tmap_nd(&p.ta[l], j.In, 3, da, sa, ba, true, "wgrad In");
+    if (rc) return rc;
+    const long long db[3] = {32, j.rows, nbp}, sb[2] = {4 * ldb, 128};
+    const int bb[3] = {32, WIDE_BK, nbp};
+    rc = make_tmap_nd(&p.tb[l], j.dZ, 3, db, sb, bb, true, "wgrad dZ");
+    if (rc) return rc;
+    p.M[l] = j.M; p.K[l] = (int)j.rows; p.mt[l] = (j.M + BM - 1) / BM; p.splits[l] = j.splits;
+    p.out[l] = j.out; p.split_stride[l] = j.split_stride;
+    p.cta0[l] = ctas; ctas += p.mt[l] * j.splits;
+  }
+  p.cta0[njobs] = ctas;
+  p.trace = trace_buffer() ? trace_buffer() + (size_t)TRACE_STRIDE * trace_launch_index()++ : nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] { cudaFuncSetAttribute(gemm_wide_batch_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, WIDE_SMEM); });
+  if (pdl) return cuda_status(launch_pdl(gemm_wide_batch_kernel<0>, dim3(ctas), dim3(kThreads), (size_t)WIDE_SMEM, st, p), "tc_gemm(wgrad batch)");
+  gemm_wide_batch_kernel<0><<<ctas, kThreads, WIDE_SMEM, st>>>(p);
+  FDSM_LAUNCH_CHECK("tc_gemm(wgrad batch)");
+}
+
 }  // namespace tc
 }  // namespace fdsm
