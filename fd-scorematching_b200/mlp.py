@@ -270,9 +270,9 @@ class FusedEnergyMLP(nn.Module):
             ju.step_counter, ju.scratch = C.c_void_p(o["step"].data_ptr()), _ptr(o["update_scratch"])
             a.update = C.cast(C.pointer(ju), C.c_void_p)
             keep.append(ju)
-            ops._count(4 + self.n_hidden)     # prep, inputs, chain, weight-gradient GEMMs, fused reduce + clip + Adam
-        else:
-            ops._count(4 + 2 * self.n_hidden)     # prep, inputs, chain, finish + per layer: weight-gradient GEMM and its reduce
+        # launches of the default configuration: front (weight prep + input build), chain, batched weight-gradient GEMMs, and the
+        # fixed-order reduce (+ clip + Adam when `update`)
+        ops._count(4)
         check(lib.fdsm_jet_fd_ssm(C.byref(self.jet_desc), C.byref(a), _stream()), "fdsm_jet_fd_ssm")
         if hook is not None:
             hook.append((e0, e1))
