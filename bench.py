@@ -486,6 +486,13 @@ def main():
             ddp_check["peer_equals_nccl_all_reduce_bitwise"] = bool(torch.equal(got, nccl))
             ddp_check["peer_vs_nccl_max_abs_diff"] = float((got - nccl).abs().max())
             ddp_check["peer_timed_out"] = bool(ar.timed_out())
+            # the squared-norm partials the clip coefficient is computed from: bit for bit the same on every rank
+            ssq_c, stp_c = torch.zeros(32, device=dev), torch.zeros((), dtype=torch.int64, device=dev)
+            ar(x.clone(), sumsq=ssq_c, step=stp_c)
+            torch.cuda.synchronize()
+            sq = [torch.empty_like(ssq_c) for _ in range(world)]
+            dist.all_gather(sq, ssq_c)
+            ddp_check["peer_sumsq_partials_bit_identical_across_ranks"] = all(bool(torch.equal(sq[0], q)) for q in sq[1:])
         # replicas: the parameters after every step above, bit for bit against rank 0's
         pr = [torch.empty_like(net.flat.data) for _ in range(world)]
         dist.all_gather(pr, net.flat.data.contiguous())

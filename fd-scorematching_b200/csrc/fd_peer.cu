@@ -190,13 +190,22 @@ __global__ void __launch_bounds__(kPeerThreads) peer_allreduce2_kernel(const Pee
     }
   }
   if (stamp) stamps[1] = globaltimer();
-  float acc2 = 0.f;
+  // The squared norm must come out bit-identical on every rank (it sets the clip coefficient of the update: replicas whose
+  // norms differ in the last bit drift apart).  A thread visits the same words on every rank -- index i of every owner's
+  // range -- but in a rank-dependent ORDER (its own range first): it therefore keeps one partial per owner range and adds
+  // them in owner order at the end.
+  float acc_o[kMaxWorld];
+#pragma unroll
+  for (int q = 0; q < kMaxWorld; ++q) acc_o[q] = 0.f;
   unsigned long long t0 = 0;
-  auto emit = [&](long long w, float s0, float s1) {
+  auto emit = [&](int o, long long w, float s0, float s1) {
     const long long e = 2 * w;
     if (e < a.n) a.out[e] = s0; else s0 = 0.f;
     if (e + 1 < a.n) a.out[e + 1] = s1; else s1 = 0.f;
-    acc2 += s0 * s0 + s1 * s1;
+    const float v = s0 * s0 + s1 * s1;
+#pragma unroll
+    for (int q = 0; q < kMaxWorld; ++q)      // (compile-time indices: the partials stay in registers)
+      if (q == o) acc_o[q] += v;
   };
   // (2) my range: gather, reduce in rank order, broadcast the result
   for (long long i = gtid; i < nown; i += gsz) {
@@ -212,7 +221,7 @@ __global__ void __launch_bounds__(kPeerThreads) peer_allreduce2_kernel(const Pee
     uint4 r;
     r.x = __float_as_uint(s0); r.y = epoch; r.z = __float_as_uint(s1); r.w = epoch;
     for (int d = 1; d < W; ++d) st_16(a.slot[(me + d) % W] + offB + w, r);
-    emit(w, s0, s1);
+    emit(me, w, s0, s1);
   }
   // (3) the other ranges: wait for the owners' results
   for (int d = 1; d < W; ++d) {
@@ -221,10 +230,13 @@ __global__ void __launch_bounds__(kPeerThreads) peer_allreduce2_kernel(const Pee
       const long long w = (long long)o * nown + i;
       if (w >= a.n3) break;
       const uint4 x = poll_word(a.slot[me] + offB + w, epoch, t0, a);
-      emit(w, __uint_as_float(x.x), __uint_as_float(x.z));
+      emit(o, w, __uint_as_float(x.x), __uint_as_float(x.z));
     }
   }
   if (stamp) stamps[2] = globaltimer();
+  float acc2 = 0.f;
+#pragma unroll
+  for (int q = 0; q < kMaxWorld; ++q) acc2 += acc_o[q];
   acc2 = warp_sum(acc2);
   if ((tid & 31) == 0) red[tid >> 5] = acc2;
   __syncthreads();

@@ -26,3 +26,13 @@ def test_peer_allreduce_bit_exact_10k_graph_replays_and_timeout():
     world = min(torch.cuda.device_count(), 4)
     r = _run(world, {"FDSM_PEER_TIMEOUT_MS": "300", "FDSM_DDP_REPLAYS": "10000"}, timeout=600)
     assert r.returncode == 0 and "DDP_WORKER_OK" in r.stdout, (r.stdout[-3000:], r.stderr[-3000:])
+
+
+@pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_peer_allreduce_two_shot_protocol_on_two_gpus():
+    """The two-shot kernel (reduce-scatter to an owner + all-gather: the default beyond 4 ranks) forced at world 2: the same
+    checks, including that the squared-norm partials are bit-identical across ranks -- a thread of that kernel visits its
+    words in a rank-dependent order, and a per-thread running sum made the clip coefficient differ in the last bit between
+    replicas (found by bench.py's ddp_check at 8 GPUs: parameters no longer bit-identical across ranks)."""
+    r = _run(2, {"FDSM_PEER_TIMEOUT_MS": "300", "FDSM_DDP_REPLAYS": "2000", "FDSM_PEER_TWO_SHOT": "1"}, timeout=600)
+    assert r.returncode == 0 and "DDP_WORKER_OK" in r.stdout, (r.stdout[-3000:], r.stderr[-3000:])

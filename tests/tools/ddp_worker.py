@@ -52,6 +52,12 @@ def main():
             ss = float((got.double() ** 2).sum())
             if abs(float(sumsq.sum()) - ss) > 1e-5 * max(ss, 1e-30) or int(step) != it + 1:
                 fails.append(f"n={n} it={it}: squared norm / step counter")
+            # the partials set the clip coefficient: replicas stay bit-identical only if these are (both protocols;
+            # FDSM_PEER_TWO_SHOT=1 runs the two-shot kernel at world 2)
+            sq = [torch.empty_like(sumsq) for _ in range(world)]
+            dist.all_gather(sq, sumsq)
+            if not all(torch.equal(sq[0], q) for q in sq[1:]):
+                fails.append(f"n={n} it={it}: squared-norm partials differ across ranks")
 
     # (2) stress: `replays` back-to-back graph replays, no host sync in between, the two ranks alternately delayed so that
     #     either may run a full step ahead (the parity double buffer).  Data: small integers derived in-graph from the device
