@@ -53,18 +53,20 @@ constexpr int NBARS = 2 * MAX_NA + 4 * MAX_RAW + 1 + MAX_NA;
 constexpr int CHAIN_MISC_BYTES = (3 * HWS + 4 * HREC + MAX_S * NCOEF) * 4 + NBARS * 8 + 16 + EPI_WARPS * 4 + 64;
 
 struct alignas(64) ChainParams {
-  CUtensorMap t_in;                  // [2 Bp x kpad0]  rows [x | v]                          (load, box {32, S})
+  CUtensorMap t_in;                  // XV [2][Bp][kpad0] as (32 k, row, stream, k-block): box {32, S, 3, AG} -- the third stream is
+                                     //   out of bounds: the b rows of the input layer arrive as zeros        (load)
   CUtensorMap t_wf[MAXL];            // Wt_l = [hi rows | lo rows] [2 kpad_l x npad], MN-major, as (32 n, k, n-panel[, hi|lo]):
                                      //   l = 0, PASSES != 3: 3-D, box {32, 64, nbx} ; otherwise 4-D, box {32, 32, nbx, HL}
   CUtensorMap t_wb[MAXL];            // the same memory, K-major view for the dgrad: 3-D (n, k, hi|lo), box {32, 32 nbx, HL}
-  CUtensorMap t_h[MAXL];             // H_l [3 Bp x kpadh], l = 1..L-1                       (store, box {32, S})
-  CUtensorMap t_dz[MAXL];            // dZ_l [3 Bp x npad] (l = 0: 2 Bp rows)                (store, box {32, S})
+  CUtensorMap t_h[MAXL];             // H_l [3][Bp][kpadh], l = 1..L-1, as (column, row, stream)      (store, box {32, S, 3})
+  CUtensorMap t_dz[MAXL];            // dZ_l [3][Bp][npad] (l = 0: 2 streams)                         (store, box {32, S, 3 | 2})
   const float* h[MAXL];              // H_l again, for the backward's plain loads
   const float* head_w;               // [w1(H) b1 | w2(H) b2 | wq(H) bq]  or  [w(H) b]
   float* loss_part;                  // [tiles]   sum over the tile's samples of the per-sample loss (unscaled)
   float* head_part;                  // [tiles][head_n]  head-parameter gradient of the tile
   int B, Bp, S, D, H, L, npad, kpad0, kpadh, head;
   int ablk, nraw;                    // bytes of one A k-block (3 S x 128), slots of the weight ring
+  int ag;                            // k-blocks of phase 0's A operand per TMA instruction / barrier
   float act_offset;                  // ln 2 for the normalised softplus
   float c1, coef;                    // loss_b = dE^2/8 - sE + (c1 - 2) E0 ; dL/dloss_b = coef (= scale / B or scale)
   unsigned long long* trace;         // debug: per-CTA %globaltimer stamps [tile][TRACE_N] (NULL in production)
@@ -86,9 +88,9 @@ __host__ __device__ constexpr int chain_smem_bytes(int NA, int ablk, int nslots)
   return 1024 + NA * ablk + nslots * WSLOT_BYTES + CHAIN_MISC_BYTES;
 }
 
-__device__ __forceinline__ void tma_store_2d(const void* tmap, uint32_t src, int32_t c0, int32_t c1) {
-  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
-               ::"l"((uint64_t)tmap), "r"(src), "r"(c0), "r"(c1)
+__device__ __forceinline__ void tma_store_3d(const void* tmap, uint32_t src, int32_t c0, int32_t c1, int32_t c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+               ::"l"((uint64_t)tmap), "r"(src), "r"(c0), "r"(c1), "r"(c2)
                : "memory");
 }
 __device__ __forceinline__ float lds(const uint8_t* p) { return *reinterpret_cast<const float*>(p); }
@@ -352,9 +354,10 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
   const int nunits = nraw >> 1;                      // ring depth in units
   const uint32_t unit0_bytes = (uint32_t)nbx * 4096u * 2u;                 // both layouts of phase 0 fill 2 x nbx boxes
   const uint32_t unith_bytes = (uint32_t)nbx * 4096u * (uint32_t)HL;
-  // phase 0's A operand arrives in groups of AG k-blocks per barrier (the same per-barrier cost): group slot g covers the
-  // A-region blocks [AG g, AG g + AG)
-  const int AG = NA >= 2 ? 2 : 1, nag = NA / AG;
+  // phase 0's A operand arrives in groups of AG k-blocks, one 4-D instruction and one barrier phase each (the same
+  // per-barrier cost): group slot g covers the A-region blocks [AG g, AG g + AG); k-blocks past the end and the b stream are
+  // out of bounds of the tensor map, i.e. land as zeros
+  const int AG = p.ag, nag = NA / AG;
 
   if (warp == PROD_WARP) {
     // ===== TMA producer (one thread): the weight stream of every phase back to back, plus phase 0's A operand ============
@@ -374,14 +377,10 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
         for (int kb = 0; kb < nkb; ++kb) {
           if (g == 0) {
             if (kb % AG == 0) {
-              const int gs = (kb / AG) % nag, nk = min(AG, nkb - kb);
+              const int gs = (kb / AG) % nag;
               mbar_wait_parked(a_empty(gs), ((kb / AG / nag) & 1) ^ 1u);
-              mbar_arrive_expect_tx(a_full(gs), (uint32_t)(nk * 2 * S * 128));
-              for (int q = 0; q < nk; ++q) {
-                const uint32_t dst = a_base + (gs * AG + q) * ablk;
-                tma_load_2d(dst, &p.t_in, a_full(gs), (kb + q) * 32, tile * S);
-                tma_load_2d(dst + S * 128, &p.t_in, a_full(gs), (kb + q) * 32, p.Bp + tile * S);
-              }
+              mbar_arrive_expect_tx(a_full(gs), (uint32_t)(AG * ablk));
+              tma_load_4d(a_base + gs * AG * ablk, &p.t_in, a_full(gs), 0, tile * S, 0, kb);
             }
             if (kb % WK0 != 0) continue;
           }
@@ -410,12 +409,11 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
       int wu = 0; uint32_t wph = 0;
       // block kb of the output of epilogue `ge` leaves for HBM (operands of the weight-gradient GEMMs / of the backward)
       auto store_block = [&](int ge, int kb) {
-        const CUtensorMap* tm;
-        int nstream = 3;
+        const CUtensorMap* tm;          // (the map's box carries the stream count: 3, or 2 for dZ_0)
         if (ge < L - 1) tm = &p.t_h[ge + 1];
-        else if (ge == L - 1) { tm = &p.t_dz[L - 1]; nstream = L == 1 ? 2 : 3; }
-        else { const int lay = 2 * L - 1 - ge; tm = &p.t_dz[lay - 1]; nstream = lay == 1 ? 2 : 3; }
-        for (int s = 0; s < nstream; ++s) tma_store_2d(tm, a_base + kb * ablk + s * S * 128, kb * 32, s * p.Bp + tile * S);
+        else if (ge == L - 1) tm = &p.t_dz[L - 1];
+        else tm = &p.t_dz[2 * L - 2 - ge];
+        tma_store_3d(tm, a_base + kb * ablk, kb * 32, tile * S, 0);
       };
       for (int g = 0; g < nphase; ++g) {
         const bool fwd = g < L;
@@ -450,6 +448,7 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
             const int gs = (kb / AG) % nag, as = gs * AG + kb % AG;
             if (kb % AG == 0) mbar_wait_parked(a_full(gs), (kb / AG / nag) & 1);
             if (kb % WK0 == 0) mbar_wait_parked(w_full(2 * wu), wph);
+            if (p.trace && p.trace_mode == 3 && L == 3 && kb % 2 == 0 && kb < 32) stamp_now(p, 22 + kb / 2);   // (debug)
             tc_fence_after();
             if (WK0 == 2) {
               mmas(as, ubase + (kb & 1) * 4096u, kb == 0, kb);

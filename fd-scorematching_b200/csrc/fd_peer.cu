@@ -80,6 +80,8 @@ __device__ __forceinline__ uint4 poll_word(const uint4* src, unsigned epoch, uns
 __global__ void __launch_bounds__(kPeerThreads) peer_allreduce_kernel(const PeerArgs a) {
   __shared__ float red[kPeerThreads / 32];
   __shared__ int is_last;
+  pdl_launch_dependents();     // the optimizer kernel behind this one is launched while it runs
+  pdl_wait();                  // launched programmatically itself: the gradient comes from the kernel before it on the stream
   const int tid = threadIdx.x, blk = blockIdx.x, nblk = gridDim.x, W = a.world, me = a.rank;
   const unsigned epoch = *reinterpret_cast<volatile unsigned*>(a.scratch) + 1u;
   // phase stamps of block 0 (debug, u64 at scratch[192..]): start, pushed, reduced, done
@@ -164,6 +166,8 @@ __global__ void __launch_bounds__(kPeerThreads) peer_allreduce_kernel(const Peer
 __global__ void __launch_bounds__(kPeerThreads) peer_allreduce2_kernel(const PeerArgs a) {
   __shared__ float red[kPeerThreads / 32];
   __shared__ int is_last;
+  pdl_launch_dependents();     // the optimizer kernel behind this one is launched while it runs
+  pdl_wait();                  // launched programmatically itself: the gradient comes from the kernel before it on the stream
   const int tid = threadIdx.x, blk = blockIdx.x, nblk = gridDim.x, W = a.world, me = a.rank;
   const unsigned epoch = *reinterpret_cast<volatile unsigned*>(a.scratch) + 1u;
   unsigned long long* stamps = reinterpret_cast<unsigned long long*>(a.scratch + 192);
@@ -310,7 +314,7 @@ extern "C" int fdsm_peer_allreduce(const float* grad, float* out, int64_t n, voi
     return e ? (e[0] == '1' ? 1 : 0) : -1;
   }();
   const bool two_shot = world > 1 && (two_shot_env >= 0 ? two_shot_env == 1 : world > 4);
-  if (two_shot) peer_allreduce2_kernel<<<(int)nblk, kPeerThreads, 0, (cudaStream_t)stream>>>(a);
-  else peer_allreduce_kernel<<<(int)nblk, kPeerThreads, 0, (cudaStream_t)stream>>>(a);
-  FDSM_LAUNCH_CHECK("fdsm_peer_allreduce");
+  const cudaError_t e = two_shot ? launch_pdl(peer_allreduce2_kernel, dim3((unsigned)nblk), dim3(kPeerThreads), 0, (cudaStream_t)stream, a)
+                                 : launch_pdl(peer_allreduce_kernel, dim3((unsigned)nblk), dim3(kPeerThreads), 0, (cudaStream_t)stream, a);
+  return cuda_status(e, "fdsm_peer_allreduce");
 }

@@ -44,6 +44,10 @@ if L == 3 and mode == 0:
     print("fwd1, MMA thread, per k-block (us after fwd0's accumulator was ready; mean over CTAs):  operand block published | its weights landed")
     print("   " + "  ".join(f"kb{kb}: {(rel[:, 22 + 2 * kb] - a0).mean():5.2f} | {(rel[:, 23 + 2 * kb] - a0).mean():5.2f}" for kb in range(7)))
     print(f"   MMAs issued {(rel[:, 5 + 4] - a0).mean():5.2f}   accumulator ready {(rel[:, 2 + 4] - a0).mean():5.2f}")
+elif L == 3 and mode == 3:
+    s1 = rel[:, 1]          # set-up done
+    print("fwd0, MMA thread: operands of k-blocks 0, 2, 4, ... landed (us after set-up; mean over CTAs)")
+    print("   " + "  ".join(f"{(rel[:, 22 + u] - s1).mean():5.2f}" for u in range(13)))
 elif L == 3:
     d0 = rel[:, 3]          # fwd0's accumulator dumped: the epilogue warps start together
     what = "whole epilogue" if mode == 1 else "block 1 published"
