@@ -1,6 +1,7 @@
 """Callers either side of the hot path, with the reference's signatures:
-annealed Langevin dynamics (ncsnv2/models/__init__.py:19-56) on the fused update kernel, and the EMA helper
-(ncsnv2/models/ema.py:4-47) on the fused EMA kernel.  The score network is the caller's torch module (generic mode)."""
+annealed Langevin dynamics (ncsnv2/models/__init__.py:19-56) and DeepEBM's energy-model samplers
+(DeepEBM/ESM/sampling_mdsm.py:6-96) on the fused update kernel, and the EMA helper (ncsnv2/models/ema.py:4-47) on the
+fused EMA kernel.  The score / energy network is the caller's torch module (generic mode)."""
 import numpy as np
 import torch
 
@@ -37,6 +38,71 @@ def anneal_Langevin_dynamics(x_mod, scorenet, sigmas, n_steps_each=200, step_lr=
                 print("level: {}, step_size: {}, grad_norm: {}, image_norm: {}, snr: {}, grad_mean_norm: {}".format(
                     c, step_size, grad_norm.item(), image_norm.item(), snr.item(), grad_mean_norm.item()))
     return [x_mod.to("cpu")] if final_only else images
+
+
+# ---- DeepEBM's samplers for energy models (DeepEBM/ESM/sampling_mdsm.py) -------------------------------------------------------
+# Every step is  x <- x - sigma^2/2 * dE/dx + c * sigma * z  (c = 1, or sqrt(T_i) for the annealed sampler): the gradient is the
+# caller's network through torch autograd, the update is ONE kernel (fdsm_langevin_step with step_size = -sigma^2/2 and
+# noise_scale = c * sigma: the reference's rounding order), z from the in-kernel Philox noise stream or from `noises`.
+def _energy_grad(netE, x):
+    x = x.detach().requires_grad_()
+    E_values = netE(x)
+    grad = torch.autograd.grad(E_values.sum(), x)[0]
+    return E_values, grad
+
+
+def _mdsm_update(x, grad, sigma2, noise_scale, z):
+    if noise_scale is None:       # Langevin_E(noise=False): the drift alone
+        return x.detach() - 0.5 * sigma2 * grad
+    return ops.langevin_step(x.detach(), grad, -0.5 * sigma2, noise=z, noise_scale=float(noise_scale))
+
+
+def Langevin(netE, init_x, K, sigma, *, noises=None):
+    """DeepEBM/ESM/sampling_mdsm.py:6-29: K Langevin steps at temperature sigma; returns the final x."""
+    sigma2 = sigma ** 2
+    netE.eval()
+    it = iter(noises) if noises is not None else None
+    x = init_x
+    for _ in range(K):
+        _, grad = _energy_grad(netE, x)
+        x = _mdsm_update(x, grad, sigma2, sigma, next(it) if it is not None else None)
+    netE.train()
+    return x
+
+
+def Langevin_E(netE, init_x, K, sigma, noise=True, *, noises=None):
+    """DeepEBM/ESM/sampling_mdsm.py:32-60: as Langevin, also returning the (K, B) matrix of energies along the way."""
+    sigma2 = sigma ** 2
+    netE.eval()
+    it = iter(noises) if noises is not None else None
+    x = init_x
+    E_list = []
+    for _ in range(K):
+        E_values, grad = _energy_grad(netE, x)
+        E_list.append(E_values.squeeze().detach().cpu().numpy())
+        x = _mdsm_update(x, grad, sigma2, sigma if noise else None, next(it) if (it is not None and noise) else None)
+    netE.train()
+    return x.detach(), np.vstack(E_list)
+
+
+def Annealed_Langevin_E(netE, init_x, sigma, T_vect, Sample_every, *, noises=None):
+    """DeepEBM/ESM/sampling_mdsm.py:63-96: annealed Langevin sampling, noise scaled by sqrt(T_vect[i]); returns (list of CPU
+    samples taken every `Sample_every` steps, (B, K) energy matrix)."""
+    sigma2 = sigma ** 2
+    T_vect = np.sqrt(T_vect)
+    K = T_vect.shape[0]
+    netE.eval()
+    it = iter(noises) if noises is not None else None
+    E_list, x_list = [], []
+    x = init_x
+    for i in range(K):
+        E_values, grad = _energy_grad(netE, x)
+        E_list.append(E_values.squeeze().detach())
+        x = _mdsm_update(x, grad, sigma2, T_vect[i] * sigma, next(it) if it is not None else None)
+        if (i + 1) % Sample_every == 0:
+            x_list.append(x.detach().cpu())
+    netE.train()
+    return x_list, torch.stack(E_list, 1).cpu().numpy()
 
 
 class EMAHelper(object):

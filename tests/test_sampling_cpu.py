@@ -32,3 +32,22 @@ def test_ema_restatement_equals_reference(golden):
                     p.add_(nets.np_randn(4410 + 10 * i + j, *p.shape).to(dt) * 0.1)
             shadow = [sampling.ema_update(s, p.data, 0.9) for s, p in zip(shadow, lin.parameters())]
         np.testing.assert_array_equal(torch.cat([s.reshape(-1) for s in shadow]).double().numpy(), golden[f"n4_ema/shadow_{tag}"])
+
+
+def test_oracle_mdsm_sampler_matches_reference_golden():
+    """oracle.sampling.mdsm_annealed_langevin against outputs of the unmodified DeepEBM/ESM/sampling_mdsm.py
+    (tests/golden/deepebm_sampler.npz, oracle/make_golden_sampler.py)."""
+    import os
+    import numpy as np
+    import torch
+    from oracle import sampling as osamp
+    from oracle.make_golden_sampler import energy_net, inputs
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "deepebm_sampler.npz"))
+    for tag, dt in (("f32", torch.float32), ("f64", torch.float64)):
+        net = energy_net(dt)
+        x0, zs, T = inputs(dt)
+        x, E = osamp.mdsm_annealed_langevin(net, x0.clone(), 0.1, T, zs)
+        np.testing.assert_array_equal(x.double().numpy(), g[f"annealed/x_final_{tag}"])
+        np.testing.assert_array_equal(E.double().numpy(), g[f"annealed/E_{tag}"])
+        x, _ = osamp.mdsm_annealed_langevin(net, x0.clone(), 0.1, np.ones(4), zs[:4])
+        np.testing.assert_array_equal(x.double().numpy(), g[f"langevin/x_final_{tag}"])

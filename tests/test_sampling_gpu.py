@@ -64,3 +64,30 @@ def test_ema_helper_matches_reference(fdsm, golden):
     big_s, big_p = torch.randn(1 << 20, device=DEV), torch.randn(1 << 20, device=DEV)
     want = (1. - 0.999) * big_p + 0.999 * big_s
     assert torch.equal(fdsm.ops.ema_update(big_s.clone(), big_p, 0.999), want)
+
+
+def test_deepebm_samplers_match_reference(fdsm):
+    """DeepEBM/ESM/sampling_mdsm.py (Annealed_Langevin_E, Langevin, Langevin_E) behind the reference's signatures: the update
+    runs on fdsm_langevin_step; against outputs of the unmodified reference on replayed normal draws."""
+    import os
+    from oracle.make_golden_sampler import energy_net, inputs
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "deepebm_sampler.npz"))
+    net = energy_net(torch.float32).to(DEV)
+    x0, zs, T = inputs(torch.float32)
+    x0, zs = x0.to(DEV), [z.to(DEV) for z in zs]
+    xs, E = fdsm.sampling.Annealed_Langevin_E(net, x0.clone(), 0.1, T.copy(), 3, noises=zs)
+    assert len(xs) == 2 and xs[0].device.type == "cpu" and E.shape == (10, 6)
+    # the network runs on cuBLAS here and on MKL in the reference: fp32 rounding of the energy gradient
+    np.testing.assert_allclose(xs[0].double().numpy(), g["annealed/x_mid_f32"], rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(xs[1].double().numpy(), g["annealed/x_final_f32"], rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(xs[1].double().numpy(), g["annealed/x_final_f64"], rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(E.astype(np.float64), g["annealed/E_f32"], rtol=1e-4, atol=1e-5)
+    xl = fdsm.sampling.Langevin(net, x0.clone(), 4, 0.1, noises=zs[:4])
+    np.testing.assert_allclose(xl.double().cpu().numpy(), g["langevin/x_final_f32"], rtol=1e-5, atol=1e-6)
+    xe, Em = fdsm.sampling.Langevin_E(net, x0.clone(), 4, 0.1, noises=zs[:4])
+    assert torch.equal(xe, xl) and Em.shape == (4, 10)
+    xn, _ = fdsm.sampling.Langevin_E(net, x0.clone(), 2, 0.1, noise=False)
+    assert torch.isfinite(xn).all()
+    # in-kernel Philox noise: finite, and different from the drift-only path
+    xp = fdsm.sampling.Langevin(net, x0.clone(), 2, 0.1)
+    assert torch.isfinite(xp).all() and not torch.equal(xp, xn)
