@@ -22,6 +22,9 @@ namespace fdsm {
 namespace jet {
 
 constexpr float LOG2E = 1.4426950408889634f, LN2 = 0.69314718055994531f;
+#ifndef FDSM_JET_PACKED
+#define FDSM_JET_PACKED 1      // 0: scalar closed forms everywhere (A/B builds: make EXTRA=-DFDSM_JET_PACKED=0)
+#endif
 
 __device__ __forceinline__ float ex2a(float x) {
   float y;
@@ -74,6 +77,74 @@ __device__ __forceinline__ float log1p_j(float t) {
 __device__ __forceinline__ float tf32r(float x) { return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u); }
 
 struct Jet { float h0, a, b; };
+
+// ---- two elements per instruction: Blackwell's packed fp32 pipe (FFMA2 / FADD2 / FMUL2: fma.rn.f32x2 ...) -----------------------
+// The epilogues are bound by instruction issue and already work on two samples per lane; the polynomial parts of the closed
+// forms below (about two thirds of the arithmetic) run on both samples with one instruction each.  Every lane of a packed
+// instruction is the IEEE operation of its scalar form.
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) {
+  float2 d;
+  asm("{\n\t.reg .b64 ra, rb, rc, rd;\n\t"
+      "mov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\tmov.b64 rc, {%6, %7};\n\t"
+      "fma.rn.f32x2 rd, ra, rb, rc;\n\t"
+      "mov.b64 {%0, %1}, rd;\n\t}"
+      : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y), "f"(c.x), "f"(c.y));
+  return d;
+}
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) {
+  float2 d;
+  asm("{\n\t.reg .b64 ra, rb, rd;\n\t"
+      "mov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\t"
+      "mul.rn.f32x2 rd, ra, rb;\n\t"
+      "mov.b64 {%0, %1}, rd;\n\t}"
+      : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+  return d;
+}
+__device__ __forceinline__ float2 add2(float2 a, float2 b) {
+  float2 d;
+  asm("{\n\t.reg .b64 ra, rb, rd;\n\t"
+      "mov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\t"
+      "add.rn.f32x2 rd, ra, rb;\n\t"
+      "mov.b64 {%0, %1}, rd;\n\t}"
+      : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+  return d;
+}
+__device__ __forceinline__ float2 f2(float c) { return make_float2(c, c); }
+__device__ __forceinline__ float2 neg2(float2 a) { return make_float2(-a.x, -a.y); }
+__device__ __forceinline__ float2 sub2(float2 a, float2 b) { return add2(a, neg2(b)); }
+__device__ __forceinline__ float2 rcp2(float2 d) { return make_float2(rcp_a(d.x), rcp_a(d.y)); }
+// the polynomials of expm1_s / log1p_ratio, two arguments at once (same coefficients, same evaluation order)
+__device__ __forceinline__ float2 expm1_s2(float2 x) {
+  float2 p = f2(1.984127e-4f);
+  p = fma2(p, x, f2(1.3888889e-3f));
+  p = fma2(p, x, f2(8.3333333e-3f));
+  p = fma2(p, x, f2(4.1666667e-2f));
+  p = fma2(p, x, f2(1.6666667e-1f));
+  p = fma2(p, x, f2(0.5f));
+  return fma2(mul2(p, x), x, x);
+}
+__device__ __forceinline__ float2 log1p_ratio2(float2 n, float2 d) {
+  const float2 s = mul2(n, rcp2(fma2(f2(2.f), d, n)));
+  const float2 u = mul2(s, s);
+  float2 q = f2(0.076923077f);
+  q = fma2(q, u, f2(0.090909091f));
+  q = fma2(q, u, f2(0.11111111f));
+  q = fma2(q, u, f2(0.14285715f));
+  q = fma2(q, u, f2(0.2f));
+  q = fma2(q, u, f2(0.33333334f));
+  const float2 s2 = add2(s, s);
+  return fma2(mul2(s2, u), q, s2);
+}
+struct Hyp2 { float2 em, emn, sinh, coshm1; };
+__device__ __forceinline__ Hyp2 hyp_small2(float2 d) {
+  Hyp2 r;
+  r.em = expm1_s2(d);
+  const float2 inv = rcp2(add2(f2(1.f), r.em));     // e^-d
+  r.emn = neg2(mul2(r.em, inv));
+  r.sinh = mul2(f2(0.5f), sub2(r.em, r.emn));
+  r.coshm1 = mul2(mul2(mul2(f2(0.5f), r.em), r.em), inv);
+  return r;
+}
 
 // quantities of one small argument d shared by the closed forms: expm1(d), expm1(-d), sinh d, cosh d - 1
 struct Hyp { float em, emn, sinh, coshm1; };
@@ -164,6 +235,37 @@ __device__ __forceinline__ void softplus_jet_bwd(const Jet& o, float offset, flo
     softplus_jet_bwd_large(sp0, ex2a(-sp0 * LOG2E), o.a, o.b, &s0, &S1, &S2);
     jet_bwd_apply(s0, S1, S2, g0, ga, gb, dz0, dP, dQ);
   }
+}
+
+// the two main paths above on TWO elements (sample pair of a lane) with the packed pipe
+__device__ __forceinline__ void softplus_jet_fwd_small2(float2 z0, float2 P, float2 Q, float offset, Jet (&o)[2]) {
+  const float2 t = make_float2(ex2a(-fabsf(z0.x) * LOG2E), ex2a(-fabsf(z0.y) * LOG2E));      // e^-|z0|
+  const float2 t1 = add2(f2(1.f), t);
+  const float2 r = rcp2(t1), tr = mul2(t, r);
+  const float2 s0 = make_float2(z0.x >= 0.f ? r.x : tr.x, z0.y >= 0.f ? r.y : tr.y);
+  const float2 e0 = make_float2(z0.x >= 0.f ? tr.x : r.x, z0.y >= 0.f ? tr.y : r.y);
+  const float2 h0 = add2(fma2(make_float2(lg2a(t1.x), lg2a(t1.y)), f2(LN2), make_float2(fmaxf(z0.x, 0.f), fmaxf(z0.y, 0.f))), f2(-offset));
+  const Hyp2 hp = hyp_small2(P);
+  const float2 emq = expm1_s2(Q), eq = add2(f2(1.f), emq);
+  const float2 em = add2(add2(hp.emn, emq), mul2(hp.emn, emq));      // expm1(Q - P)
+  const float2 a = mul2(f2(0.5f), log1p_ratio2(mul2(mul2(mul2(f2(2.f), s0), eq), hp.sinh), fma2(s0, em, f2(1.f))));
+  const float2 S = mul2(f2(2.f), fma2(emq, add2(f2(1.f), hp.coshm1), hp.coshm1));
+  const float2 b = mul2(f2(0.5f), log1p_ratio2(mul2(s0, fma2(e0, S, mul2(mul2(s0, emq), add2(f2(2.f), emq)))), f2(1.f)));
+  o[0] = Jet{h0.x, a.x, b.x};
+  o[1] = Jet{h0.y, a.y, b.y};
+}
+__device__ __forceinline__ void softplus_jet_bwd_small2(const Jet (&o)[2], float offset, float2 g0, float2 ga, float2 gb, float2& dz0,
+                                                        float2& dP, float2& dQ) {
+  const float2 e0 = make_float2(ex2a(-(o[0].h0 + offset) * LOG2E), ex2a(-(o[1].h0 + offset) * LOG2E));
+  const Hyp2 ha = hyp_small2(make_float2(o[0].a, o[1].a));
+  const float2 emb = expm1_s2(make_float2(-o[0].b, -o[1].b));
+  const float2 d0 = sub2(f2(1.f), e0);
+  const float2 S1 = mul2(mul2(e0, add2(f2(1.f), emb)), ha.sinh);
+  const float2 S2 = neg2(mul2(e0, fma2(emb, add2(f2(1.f), ha.coshm1), ha.coshm1)));
+  const float2 Sm = add2(S2, d0);
+  dz0 = fma2(d0, g0, fma2(S2, gb, mul2(S1, ga)));
+  dP = fma2(Sm, ga, mul2(S1, gb));
+  dQ = fma2(Sm, gb, mul2(S1, ga));
 }
 
 // ---- ELU (alpha = 1) --------------------------------------------------------------------------------------------------------
@@ -292,10 +394,14 @@ __device__ __forceinline__ void jet_fwd_n(const float (&z0)[N], const float (&P)
 #pragma unroll
   for (int n = 0; n < N; ++n) m = fmaxf(m, fmaxf(fabsf(P[n]), fabsf(Q[n])));
   if (m <= SMALL) {
+    if constexpr (ACT != JACT_ELU && N == 2 && FDSM_JET_PACKED) {
+      softplus_jet_fwd_small2(make_float2(z0[0], z0[1]), make_float2(P[0], P[1]), make_float2(Q[0], Q[1]), offset, o);
+    } else {
 #pragma unroll
-    for (int n = 0; n < N; ++n) {
-      if constexpr (ACT == JACT_ELU) o[n] = elu_jet_fwd_small(z0[n], P[n], Q[n]);
-      else o[n] = softplus_jet_fwd_small(z0[n], P[n], Q[n], offset);
+      for (int n = 0; n < N; ++n) {
+        if constexpr (ACT == JACT_ELU) o[n] = elu_jet_fwd_small(z0[n], P[n], Q[n]);
+        else o[n] = softplus_jet_fwd_small(z0[n], P[n], Q[n], offset);
+      }
     }
   } else {      // (fully unrolled as well: a runtime index would push the arrays into local memory on the main path too)
 #pragma unroll
@@ -316,8 +422,14 @@ __device__ __forceinline__ void jet_bwd_n(const Jet (&o)[N], float offset, const
 #pragma unroll
     for (int n = 0; n < N; ++n) m = fmaxf(m, fmaxf(fabsf(o[n].a), fabsf(o[n].b)));
     if (m <= SMALL) {
+      if constexpr (N == 2 && FDSM_JET_PACKED) {
+        float2 z2, p2, q2;
+        softplus_jet_bwd_small2(o, offset, make_float2(g0[0], g0[1]), make_float2(ga[0], ga[1]), make_float2(gb[0], gb[1]), z2, p2, q2);
+        dz0[0] = z2.x; dz0[1] = z2.y; dP[0] = p2.x; dP[1] = p2.y; dQ[0] = q2.x; dQ[1] = q2.y;
+      } else {
 #pragma unroll
-      for (int n = 0; n < N; ++n) softplus_jet_bwd_small(o[n], offset, g0[n], ga[n], gb[n], dz0[n], dP[n], dQ[n]);
+        for (int n = 0; n < N; ++n) softplus_jet_bwd_small(o[n], offset, g0[n], ga[n], gb[n], dz0[n], dP[n], dQ[n]);
+      }
     } else {
 #pragma unroll
       for (int n = 0; n < N; ++n) {
