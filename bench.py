@@ -409,7 +409,9 @@ def main():
     value = B_PER_GPU * world * args.steps / (ms * 1e-3)
 
     # ---- e2e: host buffers through the public API, H2D + D2H inside the timed region -----------------
-    for i in range(max(3, args.warmup // 2)):
+    # (at least 50 untimed steps: the PCIe link leaves its idle state only under traffic, and the device-resident leg above
+    # sent none for a third of a second -- with 3 warm-up steps the first timed copies ran at a fraction of the link rate)
+    for i in range(max(50, args.warmup)):
         tr.step_from_host(host[i % 4], loss_host)
     barrier()
     tr.step_from_host(host[0], loss_host)
@@ -429,7 +431,7 @@ def main():
     e2e_u8_ms = None
     if use_fused and net.formulation == "jet":
         host_u8 = [(p.clamp(0, 1) * 255.0).round().to(torch.uint8).cpu().pin_memory() for p in pool[:4]]
-        for i in range(max(3, args.warmup // 2)):
+        for i in range(max(50, args.warmup)):
             tr.step_from_host_u8(host_u8[i % 4], loss_host, 0.005)
         barrier()
         tr.step_from_host_u8(host_u8[0], loss_host, 0.005)
