@@ -32,7 +32,7 @@
 namespace fdsm {
 namespace {
 
-constexpr int kPeerThreads = 256;
+constexpr int kPeerThreads = 1024;   // one 16-byte line per thread at config 2 (119 k lines on <= 160 blocks): every push is in flight before the first poll
 constexpr int kMaxWorld = FDSM_PEER_MAX_WORLD;
 constexpr int kMaxBlocks = FDSM_PEER_MAX_BLOCKS;
 
