@@ -76,10 +76,34 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
   }
 }
 
+// The step's result leaves for the host as a plain store into mapped pinned memory: a copy-engine D2H of 4 bytes between two
+// graph replays idles the stream on both sides of it (fdsm_publish_scalars).
+__global__ void publish_scalars_kernel(const float* __restrict__ src, volatile float* h_dst, int n) {
+  pdl_wait();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) h_dst[i] = __ldcg(src + i);
+  __threadfence_system();
+}
+
 }  // namespace
 }  // namespace fdsm
 
 using namespace fdsm;
+
+extern "C" int fdsm_publish_scalars(const float* src, float* h_dst, int64_t n, fdsm_stream_t stream) {
+  FDSM_REQUIRE(n >= 0 && n <= 4096, "fdsm_publish_scalars: n must be in [0, 4096] (a step's scalars, not a tensor copy)");
+  if (n == 0) return FDSM_OK;
+  FDSM_REQUIRE(src && h_dst, "fdsm_publish_scalars: NULL pointer");
+  cudaPointerAttributes at;
+  cudaError_t e = cudaPointerGetAttributes(&at, h_dst);
+  if (e != cudaSuccess || at.type != cudaMemoryTypeHost || at.devicePointer == nullptr) {
+    (void)cudaGetLastError();
+    set_error("fdsm_publish_scalars: h_dst must be pinned (page-locked, device-mapped) host memory");
+    return FDSM_ERR_INVALID_ARGUMENT;
+  }
+  return cuda_status(launch_pdl(publish_scalars_kernel, dim3((unsigned)((n + 127) / 128)), dim3(128), 0, (cudaStream_t)stream, src,
+                                (volatile float*)at.devicePointer, (int)n), "fdsm_publish_scalars");
+}
 
 extern "C" int fdsm_grad_sumsq(const float* g, int64_t n, float* sumsq, int64_t* step_counter, fdsm_stream_t stream) {
   FDSM_REQUIRE(n >= 0 && sumsq && (g || n == 0), "fdsm_grad_sumsq: bad arguments");

@@ -370,3 +370,18 @@ def ema_update(shadow, params, mu):
     _count(1)
     check(lib.fdsm_ema_update(_ptr(shadow), _ptr(params), shadow.numel(), 1.0 - float(mu), float(mu), _stream()), "fdsm_ema_update")
     return shadow
+
+
+def publish_scalars(src, host_dst):
+    """host_dst (pinned fp32 host tensor) <- src (device fp32), stored by a kernel on the current stream
+    (fdsm_publish_scalars): the host's read of a step's loss without a copy-engine operation between two graph replays.
+    The host reads host_dst after synchronising with the stream, as after a non-blocking copy_."""
+    lib = _lib.load()
+    _req(src, "src")
+    if host_dst.is_cuda or host_dst.dtype != torch.float32 or not host_dst.is_pinned() or not host_dst.is_contiguous():
+        raise ValueError("host_dst must be a contiguous pinned fp32 host tensor")
+    if src.numel() != host_dst.numel() or not src.is_contiguous():
+        raise ValueError("src must be contiguous and as long as host_dst")
+    _count(1)
+    check(lib.fdsm_publish_scalars(_ptr(src), C.c_void_p(host_dst.data_ptr()), src.numel(), _stream()), "fdsm_publish_scalars")
+    return host_dst

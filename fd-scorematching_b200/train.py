@@ -41,6 +41,18 @@ def bind_host_thread_to_gpu_node(device_index):
         return None
 
 
+def read_loss_to_host(loss, loss_host):
+    """Device scalar -> `loss_host`, ordered on the current stream.  A pinned fp32 destination is written by a kernel
+    (ops.publish_scalars: no copy-engine operation between two graph replays; FDSM_E2E_LOSS_MEMCPY=1 keeps the memcpy);
+    anything else takes torch's non-blocking copy."""
+    if (loss.is_cuda and loss.dtype == torch.float32 and loss_host.dtype == torch.float32 and loss_host.is_pinned()
+            and loss_host.is_contiguous() and loss.numel() == loss_host.numel()
+            and os.environ.get("FDSM_E2E_LOSS_MEMCPY") != "1"):
+        return ops.publish_scalars(loss.reshape(-1), loss_host)
+    loss_host.copy_(loss, non_blocking=True)
+    return loss_host
+
+
 class FDSSMTrainer:
     """loss = "ssm_fd" (train_ssm.py) or "mdsm_fd" (train_dsm.py: pass the (B_global, 1) per-batch-position noise
     schedule of train_dsm.py:50-57 as `sigmas`; each rank uses its own slice of it)."""
@@ -137,7 +149,10 @@ class FDSSMTrainer:
         previous step's compute), the step, and an async D2H read of the loss into `loss_host` (pinned)."""
         cur = torch.cuda.current_stream()
         if self._copy_stream is None:
-            self._copy_stream = torch.cuda.Stream()
+            # one copy stream per staging buffer: batch n + 1 is handed to the copy engines while batch n is still in
+            # flight, so the link never idles between two copies (FDSM_E2E_COPY_STREAMS=1: a single stream)
+            n = 1 if os.environ.get("FDSM_E2E_COPY_STREAMS") == "1" else 2
+            self._copy_stream = [torch.cuda.Stream() for _ in range(n)]
             self._staging = {}
         key = (tuple(x_host.shape), x_host.dtype)
         if key not in self._staging:      # one double buffer per batch shape (the last batch of an epoch may be shorter)
@@ -147,16 +162,16 @@ class FDSSMTrainer:
         self._bufs, self._evt, self._free = sg["bufs"], sg["evt"], sg["free"]
         i = sg["i"]
         sg["i"] ^= 1
-        with torch.cuda.stream(self._copy_stream):
-            self._copy_stream.wait_event(self._free[i])      # previous consumer of this buffer is done
+        cs = self._copy_stream[i % len(self._copy_stream)]
+        with torch.cuda.stream(cs):
+            cs.wait_event(self._free[i])      # previous consumer of this buffer is done
             self._bufs[i].copy_(x_host, non_blocking=True)
-            self._evt[i].record(self._copy_stream)
+            self._evt[i].record(cs)
         cur.wait_event(self._evt[i])
         # the fused ssm_fd step reads the staging buffer where it lies (one captured graph per staging buffer): no D2D copy
         loss = self.step(self._bufs[i], borrow=self.fused and self.loss_name == "ssm_fd", x_noise=x_noise)
         self._free[i].record(cur)
-        loss_host.copy_(loss, non_blocking=True)
-        return loss_host
+        return read_loss_to_host(loss, loss_host)
 
 
 class GenericFDTrainer:
@@ -199,8 +214,7 @@ class GenericFDTrainer:
         x = self._h2d.stage(x_host)
         loss = self.step(x)
         self._h2d.release()
-        loss_host.copy_(loss, non_blocking=True)
-        return loss_host
+        return read_loss_to_host(loss, loss_host)
 
 
 class HostStager:

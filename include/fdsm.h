@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define FDSM_ABI_VERSION 9
+#define FDSM_ABI_VERSION 10
 
 #define FDSM_OK 0
 #define FDSM_ERR_INVALID_ARGUMENT (-1)
@@ -336,6 +336,12 @@ int fdsm_grad_sumsq(const float* g, int64_t n, float* sumsq, int64_t* step_count
 int fdsm_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
                    const float* lr_dev, float beta1, float beta2, float eps, float max_norm, const float* sumsq,
                    const int64_t* step_counter, fdsm_stream_t stream);
+/* The host's read of the step's result (`tloss.item()`, DeepEBM/train_ssm.py:84; every `loss.item()` of the runners):
+ * n <= 4096 floats from device memory `src` stored by a kernel into `h_dst`, PINNED host memory (cudaHostAlloc /
+ * torch pin_memory: device-mapped under unified addressing; anything else is rejected), ordered on `stream` -- the host
+ * reads them after synchronising with the stream.  In place of cudaMemcpyAsync(D2H) of 4 bytes: a copy-engine operation
+ * between two graph replays idles the stream on both sides of it (bench.py e2e: 36 us per step at config 2). */
+int fdsm_publish_scalars(const float* src, float* h_dst, int64_t n, fdsm_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------
  * The step's single exchange over NVLink peer memory: all-reduce of the flat fp32 gradient
