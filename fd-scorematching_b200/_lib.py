@@ -117,6 +117,11 @@ PROTOTYPES = {
     "fdsm_langevin_step": (C.c_int, [_f32p, _i64, _f32p, _i64, _f32p, _i64, _f32p, _i64, _i64, _i64, _f32, _f32, _u64, _u64, _u64,
                                      _stream]),
     "fdsm_ema_update": (C.c_int, [_f32p, _f32p, _i64, _f32, _f32, _stream]),
+    "fdsm_inorm_plus_stats_floats": (C.c_int64, [_i64, _i64]),
+    "fdsm_inorm_plus_launches": (C.c_int64, [_i64, _i64, _i64, _i32, _i32, _i32]),
+    "fdsm_inorm_plus_fwd": (C.c_int, [_f32p, _i64, _i64, _i64, _f32p, _f32p, _f32p, _i64, _i32, _f32p, _f32p, _stream]),
+    "fdsm_inorm_plus_bwd": (C.c_int, [_f32p, _f32p, _f32p, _i64, _i64, _i64, _f32p, _f32p, _i64, _i32, _f32p, _f32p, _f32p, _f32p,
+                                      _f32p, _f32p, _stream]),
     "fdsm_peer_buffer_bytes": (C.c_int64, [_i64, _i32]),
     "fdsm_peer_allreduce": (C.c_int, [_f32p, _f32p, _i64, C.POINTER(C.c_void_p), _i32, _i32, _f32, _f32p, C.c_void_p,
                                       C.c_void_p, _stream]),

@@ -505,6 +505,8 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
       __syncwarp();
       if (lane == 0) mbar_arrive(a_ready(j));
     };
+    float gw1[MAX_NA], gw2[MAX_NA], gwq[MAX_NA];        // this warp's head-gradient partial sums (set in phase L - 1)
+    float gb1 = 0.f, gb2 = 0.f, gbq = 0.f, loss_acc = 0.f;
     for (int g = 0; g < nphase; ++g) {
       const bool fwd = g < L;
       const int layer = fwd ? g : 2 * L - 1 - g;
@@ -557,7 +559,6 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
         // -- last forward layer: jets, head, per-sample loss and its gradient, activation backward -> dZ_{L-1} ---------------
         const bool quad = p.head != 0;
         const float b1 = __ldg(p.head_w + H), b2 = quad ? __ldg(p.head_w + 2 * H + 1) : 0.f, bq = quad ? __ldg(p.head_w + 3 * H + 2) : 0.f;
-        float gb1 = 0.f, gb2 = 0.f, gbq = 0.f, loss_acc = 0.f;
         auto sample_done = [&](const float (&sum)[9], int i) {
           const bool valid = tile * S + i < p.B;
           const float l = head_sample<MODE>(sum, quad, b1, b2, bq, p.c1, valid ? p.coef : 0.f, lane == 0, coef_s + i * NCOEF, gb1, gb2, gbq);
@@ -575,8 +576,8 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
           if (v1) sample_done(sum[1], i0 + EPI_WARPS);
         }
         __syncwarp();
-        // pass 2, block by block (the per-column head-weight sums go to a runtime-indexed, i.e. local-memory, array)
-        float gw1[MAX_NA], gw2[MAX_NA], gwq[MAX_NA];
+        // pass 2, block by block (the per-column head-weight sums go to a runtime-indexed, i.e. local-memory, array; the tile
+        // sums over the warps wait until the last phase is over: see below the phase loop)
 #pragma unroll 1
         for (int j = 0; j < NA; ++j) {
           const int c = lane + 32 * j;
@@ -594,36 +595,6 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
           }
           gw1[j] = s1; gw2[j] = s2; gwq[j] = sq;
           publish(j);
-        }
-        // tile sums in a fixed order: four rounds of four warps add their partial sums into record (warp & 3)
-        if (lane == 0) red[warp] = loss_acc;
-        for (int r = 0; r < EPI_WARPS / 4; ++r) {
-          if ((warp >> 2) == r) {
-            float* rec = hrec + (warp & 3) * HREC;
-#pragma unroll 1
-            for (int j = 0; j < NA; ++j) {
-              const int c = lane + 32 * j;
-              if (r == 0) { rec[c] = gw1[j]; rec[HWS + c] = gw2[j]; rec[2 * HWS + c] = gwq[j]; }
-              else { rec[c] += gw1[j]; rec[HWS + c] += gw2[j]; rec[2 * HWS + c] += gwq[j]; }
-            }
-            if (lane == 0) {
-              if (r == 0) { rec[3 * HWS] = gb1; rec[3 * HWS + 1] = gb2; rec[3 * HWS + 2] = gbq; }
-              else { rec[3 * HWS] += gb1; rec[3 * HWS + 1] += gb2; rec[3 * HWS + 2] += gbq; }
-            }
-          }
-          named_bar_sync(1, EPI_T);
-        }
-        const int nh = quad ? 3 : 1, head_n = nh * (H + 1);
-        for (int o = threadIdx.x; o < head_n; o += EPI_T) {
-          const int h = o / (H + 1), c = o % (H + 1);
-          const int src = c < H ? h * HWS + c : 3 * HWS + h;
-          p.head_part[(long long)tile * head_n + o] = (hrec[src] + hrec[HREC + src]) + (hrec[2 * HREC + src] + hrec[3 * HREC + src]);
-        }
-        if (threadIdx.x == 0) {
-          float s = 0.f;
-#pragma unroll
-          for (int w = 0; w < EPI_WARPS; ++w) s += red[w];
-          p.loss_part[tile] = s;
         }
       } else {
         // -- dgrad epilogue of layer `layer`: rows hold dL/dH_layer as (g0, ga, gb); H_layer comes back from L2 --------------
@@ -645,6 +616,39 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
         }
       }
       stamp(p, 4 + 4 * g);         // this warp's part of the epilogue done
+    }
+    // -- head-parameter gradient and loss of the tile, behind the last phase instead of between the head epilogue and the
+    //    first data-gradient epilogue (4.5 us there, in front of every warp's next accumulator dump).  The weight ring is idle by
+    //    now (every slot was consumed by MMAs that completed before the last accumulator was handed over; nraw >= 2 slots =
+    //    56 KB >= 16 records): each warp parks its partial sums in a record of its own, then every output adds the sixteen in
+    //    the fixed order of the former four rounds: ((w + w4) + w8) + w12 for q = w & 3, then (q0 + q1) + (q2 + q3).
+    {
+      fence_proxy_async();
+      float* park = reinterpret_cast<float*>(w_gen) + warp * HREC;
+#pragma unroll 1
+      for (int j = 0; j < NA; ++j) {
+        const int c = lane + 32 * j;
+        park[c] = gw1[j]; park[HWS + c] = gw2[j]; park[2 * HWS + c] = gwq[j];
+      }
+      if (lane == 0) { park[3 * HWS] = gb1; park[3 * HWS + 1] = gb2; park[3 * HWS + 2] = gbq; park[3 * HWS + 3] = loss_acc; }
+      named_bar_sync(1, EPI_T);
+      const float* pk = reinterpret_cast<const float*>(w_gen);
+      const int nh = p.head != 0 ? 3 : 1, head_n = nh * (H + 1);
+      for (int o = threadIdx.x; o < head_n; o += EPI_T) {
+        const int h = o / (H + 1), c = o % (H + 1);
+        const int src = c < H ? h * HWS + c : 3 * HWS + h;
+        float r[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          r[q] = ((pk[q * HREC + src] + pk[(q + 4) * HREC + src]) + pk[(q + 8) * HREC + src]) + pk[(q + 12) * HREC + src];
+        p.head_part[(long long)tile * head_n + o] = (r[0] + r[1]) + (r[2] + r[3]);
+      }
+      if (threadIdx.x == 0) {
+        float sl = 0.f;
+#pragma unroll
+        for (int w = 0; w < EPI_WARPS; ++w) sl += pk[w * HREC + 3 * HWS + 3];
+        p.loss_part[tile] = sl;
+      }
     }
   }
   tc_fence_before();

@@ -1,6 +1,6 @@
 // SURVEY.md §8f row N1, first piece: InstanceNorm++ with the ELU that follows it in every block of the score networks, forward
 // and backward, as HBM-bound kernels (the reference runs it as ~10 ATen launches per direction:
-// ncsnv2/models/normalization.py:150-176, ncsn/models/cond_refinenet_dilated.py:304-333; ELU at ncsnv2/models/layers.py:447-451).
+// ncsnv2/models/normalization.py:150-176, ncsn/models/cond_refinenet_dilated.py:304-333; ELU at ncsnv2/models/layers.py:443-448).
 //
 //   mu[n,c], var[n,c] over the HW plane (biased, eps 1e-5: F.instance_norm);  m[n], v[n] = mean / UNBIASED variance of mu[n,:]
 //   mustd = (mu - m) / sqrt(v + 1e-5);   y = gamma * ((x - mu) * rstd + mustd * alpha) + beta;   out = act ? elu(y) : y
@@ -47,6 +47,7 @@ __device__ __forceinline__ float elu_bwd_from_out(float o) { return o > 0.f ? 1.
 struct NormDims {
   long long planes;   // N * C
   int C, HW;
+  long long p0, p1;   // the planes of this launch (a whole number of samples): see the chunking note at the entry points
 };
 
 // stats = [mu (N*C) | rstd (N*C) | mustd (N*C) | s (N)]
@@ -58,7 +59,7 @@ __global__ void __launch_bounds__(kThreads) inorm_stats_kernel(const float* __re
   const int nq = d.HW / VEC;
   const float inv = 1.f / (float)d.HW;
   pdl_wait();
-  for (long long p = (long long)blockIdx.x * GROUPS + grp; p < d.planes; p += (long long)gridDim.x * GROUPS) {
+  for (long long p = d.p0 + (long long)blockIdx.x * GROUPS + grp; p < d.p1; p += (long long)gridDim.x * GROUPS) {
     const float* xp = x + p * d.HW;
     float mean, ss = 0.f;
     if (nq <= LANES * HELD) {          // the plane stays in registers between the two passes
@@ -126,7 +127,7 @@ __global__ void __launch_bounds__(kThreads) inorm_apply_kernel(const float* __re
   const int lane = threadIdx.x % LANES, grp = threadIdx.x / LANES;
   const int nq = d.HW / VEC;
   pdl_wait();
-  for (long long p = (long long)blockIdx.x * GROUPS + grp; p < d.planes; p += (long long)gridDim.x * GROUPS) {
+  for (long long p = d.p0 + (long long)blockIdx.x * GROUPS + grp; p < d.p1; p += (long long)gridDim.x * GROUPS) {
     const long long n = p / d.C;
     const int c = (int)(p - n * d.C);
     float m, s;
@@ -166,7 +167,7 @@ __global__ void __launch_bounds__(kThreads) inorm_bwd_sums_kernel(const float* _
   const int lane = threadIdx.x % LANES, grp = threadIdx.x / LANES;
   const int nq = d.HW / VEC;
   pdl_wait();
-  for (long long p = (long long)blockIdx.x * GROUPS + grp; p < d.planes; p += (long long)gridDim.x * GROUPS) {
+  for (long long p = d.p0 + (long long)blockIdx.x * GROUPS + grp; p < d.p1; p += (long long)gridDim.x * GROUPS) {
     const float mu = __ldg(stats + p), rstd = __ldg(stats + d.planes + p);
     const float* xp = x + p * d.HW;
     const float* op = out + p * d.HW;
@@ -212,7 +213,7 @@ __global__ void __launch_bounds__(kThreads) inorm_bwd_apply_kernel(const float* 
   const int nq = d.HW / VEC;
   const float inv = 1.f / (float)d.HW;
   pdl_wait();
-  for (long long p = (long long)blockIdx.x * GROUPS + grp; p < d.planes; p += (long long)gridDim.x * GROUPS) {
+  for (long long p = d.p0 + (long long)blockIdx.x * GROUPS + grp; p < d.p1; p += (long long)gridDim.x * GROUPS) {
     const long long n = p / d.C;
     const int c = (int)(p - n * d.C);
     // d_k = dL/dmustd_k = gamma_k alpha_k S1_k;  D1 = mean_k d_k,  D2 = sum_k d_k mustd_k
@@ -256,10 +257,22 @@ inline unsigned grid_for(long long planes, int lanes) {
   return (unsigned)(want < cap ? (want > 0 ? want : 1) : cap);
 }
 
+// Samples per launch pair.  The two kernels of a direction read the same activations twice; samples are independent, so the
+// tensor is walked in chunks small enough for the second kernel to find the first one's reads in L2 (126 MB): HBM then sees
+// the algorithmic bytes once (8 B per element forward, 16 B backward) instead of 12 / 28.  FDSM_NORM_CHUNK_MB overrides the
+// chunk footprint (0 = one chunk).
+inline long long chunk_samples(long long N, long long C, long long HW, int tensors) {
+  static const long long mb = [] { const char* e = getenv("FDSM_NORM_CHUNK_MB"); return e ? atoll(e) : 48ll; }();
+  if (mb <= 0) return N;
+  const long long per_sample = C * HW * 4 * tensors;
+  long long n = (mb << 20) / (per_sample > 0 ? per_sample : 1);
+  return n < 1 ? 1 : (n > N ? N : n);
+}
+
 #define FDSM_NORM_DISPATCH(KERNEL, ...)                                                                                     \
   do {                                                                                                                      \
     cudaError_t e_;                                                                                                         \
-    const dim3 g_(grid_for(d.planes, lanes)), b_(kThreads);                                                                 \
+    const dim3 g_(grid_for(d.p1 - d.p0, lanes)), b_(kThreads);                                                                 \
     if (vec == 4) {                                                                                                         \
       if (lanes == 32) e_ = launch_pdl(KERNEL<32, 4>, g_, b_, 0, st, __VA_ARGS__);                                          \
       else if (lanes == 16) e_ = launch_pdl(KERNEL<16, 4>, g_, b_, 0, st, __VA_ARGS__);                                     \
@@ -281,6 +294,12 @@ using namespace fdsm;
 
 extern "C" int64_t fdsm_inorm_plus_stats_floats(int64_t N, int64_t C) { return N < 0 || C < 0 ? -1 : 3 * N * C + N; }
 
+extern "C" int64_t fdsm_inorm_plus_launches(int64_t N, int64_t C, int64_t HW, int32_t backward, int32_t act, int32_t with_dx) {
+  if (N <= 0 || C <= 0 || HW <= 0) return 0;
+  const long long step = backward ? (with_dx ? chunk_samples(N, C, HW, act ? 4 : 3) : N) : chunk_samples(N, C, HW, 2);
+  return (N + step - 1) / step * ((backward && !with_dx) ? 1 : 2);
+}
+
 extern "C" int fdsm_inorm_plus_fwd(const float* x, int64_t N, int64_t C, int64_t HW, const float* gamma, const float* alpha,
                                    const float* beta, int64_t param_stride, int32_t act, float* out, float* stats,
                                    fdsm_stream_t stream) {
@@ -289,14 +308,18 @@ extern "C" int fdsm_inorm_plus_fwd(const float* x, int64_t N, int64_t C, int64_t
   FDSM_REQUIRE(act == 0 || act == 1, "fdsm_inorm_plus_fwd: act must be 0 (none) or 1 (ELU)");
   if (N == 0) return FDSM_OK;
   FDSM_REQUIRE(x && gamma && alpha && out && stats, "fdsm_inorm_plus_fwd: NULL pointer");
-  NormDims d{N * C, (int)C, (int)HW};
+  NormDims d{N * C, (int)C, (int)HW, 0, 0};
   const int vec = (HW % 4 == 0 && aligned16(x) && aligned16(out)) ? 4 : 1;
   const int lanes = pick_lanes(HW / vec);
   cudaStream_t st = (cudaStream_t)stream;
-  int rc;
-  FDSM_NORM_DISPATCH(inorm_stats_kernel, x, d, stats);
-  if (rc) return rc;
-  FDSM_NORM_DISPATCH(inorm_apply_kernel, x, d, gamma, alpha, beta, (long long)param_stride, (int)act, stats, out);
+  const long long step = chunk_samples(N, C, HW, 2);      // x + out
+  int rc = FDSM_OK;
+  for (long long n0 = 0; n0 < N && !rc; n0 += step) {
+    d.p0 = n0 * C; d.p1 = (n0 + step < N ? n0 + step : N) * C;
+    FDSM_NORM_DISPATCH(inorm_stats_kernel, x, d, stats);
+    if (rc) return rc;
+    FDSM_NORM_DISPATCH(inorm_apply_kernel, x, d, gamma, alpha, beta, (long long)param_stride, (int)act, stats, out);
+  }
   return rc;
 }
 
@@ -309,16 +332,20 @@ extern "C" int fdsm_inorm_plus_bwd(const float* x, const float* out, const float
   if (N == 0) return FDSM_OK;
   FDSM_REQUIRE(x && gout && gamma && alpha && stats && scratch && dgamma && dalpha && dbeta && (out || !act),
                "fdsm_inorm_plus_bwd: NULL pointer (out is needed when act = 1; dx alone may be NULL)");
-  NormDims d{N * C, (int)C, (int)HW};
+  NormDims d{N * C, (int)C, (int)HW, 0, 0};
   const int vec = (HW % 4 == 0 && aligned16(x) && aligned16(gout) && (!act || aligned16(out)) && (!dx || aligned16(dx))) ? 4 : 1;
   const int lanes = pick_lanes(HW / vec);
   cudaStream_t st = (cudaStream_t)stream;
   const float* o = act ? out : x;      // never read when act = 0
-  int rc;
-  FDSM_NORM_DISPATCH(inorm_bwd_sums_kernel, x, o, gout, d, gamma, alpha, (long long)param_stride, (int)act, stats, scratch, dgamma,
-                     dalpha, dbeta);
-  if (rc || !dx) return rc;
-  FDSM_NORM_DISPATCH(inorm_bwd_apply_kernel, x, o, gout, d, gamma, alpha, (long long)param_stride, (int)act, stats,
-                     (const float*)dbeta, (const float*)scratch, dx);
+  const long long step = dx ? chunk_samples(N, C, HW, act ? 4 : 3) : N;      // x, gout, (out,) dx
+  int rc = FDSM_OK;
+  for (long long n0 = 0; n0 < N && !rc; n0 += step) {
+    d.p0 = n0 * C; d.p1 = (n0 + step < N ? n0 + step : N) * C;
+    FDSM_NORM_DISPATCH(inorm_bwd_sums_kernel, x, o, gout, d, gamma, alpha, (long long)param_stride, (int)act, stats, scratch, dgamma,
+                       dalpha, dbeta);
+    if (rc || !dx) continue;
+    FDSM_NORM_DISPATCH(inorm_bwd_apply_kernel, x, o, gout, d, gamma, alpha, (long long)param_stride, (int)act, stats,
+                       (const float*)dbeta, (const float*)scratch, dx);
+  }
   return rc;
 }

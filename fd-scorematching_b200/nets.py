@@ -12,24 +12,27 @@ The two RefineNets share one implementation here: a normaliser either owns (alph
 InstanceNorm++) or looks them up in a per-noise-level embedding table (ncsn's conditional variant).
 """
 import math
+import os
 
 import numpy as np
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
+from . import ops
+
 
 # ---------------------------------------------------------------------------------------------------------------------
 # InstanceNorm++ : instance norm plus a term that re-injects the (standardised) per-channel means
 # ---------------------------------------------------------------------------------------------------------------------
-def _inorm_plus(x, gamma, alpha, beta):
-    """x (N,C,H,W); gamma / alpha / beta broadcastable (N or 1, C).  ncsnv2/models/normalization.py:163-176."""
-    mu = x.mean(dim=(2, 3))                                         # (N, C) per-channel means
-    centred = mu - mu.mean(dim=1, keepdim=True)
-    mu_std = centred / torch.sqrt(mu.var(dim=1, keepdim=True) + 1e-5)
-    h = F.instance_norm(x) + (mu_std * alpha)[:, :, None, None]
-    h = gamma[:, :, None, None] * h
-    return h if beta is None else h + beta[:, :, None, None]
+def _inorm_plus(x, gamma, alpha, beta, act=False):
+    """x (N,C,H,W); gamma / alpha / beta (N or 1, C); act: the ELU that follows the normaliser in the residual blocks.
+    ncsnv2/models/normalization.py:163-176.  CUDA fp32 tensors go through our fused kernels (ops.inorm_plus: two launches
+    per direction); FDSM_NORM_KERNEL=0 keeps the ATen op sequence there too (A/B timing).
+    CPU tensors (the forward goldens of tests/test_nets_cpu.py) take the op sequence."""
+    if x.is_cuda and x.dtype == torch.float32 and os.environ.get("FDSM_NORM_KERNEL", "1") != "0":
+        return ops.inorm_plus(x, gamma, alpha, beta, act)
+    return ops.inorm_plus_reference(x, gamma, alpha, beta, act)
 
 
 class InstanceNormPlus(nn.Module):
@@ -41,8 +44,8 @@ class InstanceNormPlus(nn.Module):
         self.gamma = nn.Parameter(torch.empty(channels).normal_(1.0, 0.02))
         self.beta = nn.Parameter(torch.zeros(channels))
 
-    def forward(self, x, y=None):
-        return _inorm_plus(x, self.gamma[None], self.alpha[None], self.beta[None])
+    def forward(self, x, y=None, act=False):
+        return _inorm_plus(x, self.gamma[None], self.alpha[None], self.beta[None], act)
 
 
 class CondInstanceNormPlus(nn.Module):
@@ -56,9 +59,9 @@ class CondInstanceNormPlus(nn.Module):
             self.embed.weight[:, :2 * channels].normal_(1.0, 0.02)
             self.embed.weight[:, 2 * channels:].zero_()
 
-    def forward(self, x, y):
+    def forward(self, x, y, act=False):
         gamma, alpha, beta = self.embed(y).chunk(3, dim=1)
-        return _inorm_plus(x, gamma, alpha, beta)
+        return _inorm_plus(x, gamma, alpha, beta, act)
 
 
 def _conv(cin, cout, k=3, dilation=1, bias=True):
@@ -107,8 +110,8 @@ class _ScoreResBlock(nn.Module):
         self.normalize1 = norm(cin, n_classes)
 
     def forward(self, x, y):
-        h = self.conv1(F.elu(self.normalize1(x, y)))
-        h = self.conv2(F.elu(self.normalize2(h, y)))
+        h = self.conv1(self.normalize1(x, y, act=True))
+        h = self.conv2(self.normalize2(h, y, act=True))
         return h + (self.shortcut(x) if self.has_shortcut else x)
 
 
@@ -128,9 +131,8 @@ class _RCU(nn.Module):
         for b in range(1, self.n_blocks + 1):
             h = x
             for s in (1, 2):
-                if self.cond:
-                    h = getattr(self, f"{b}_{s}_norm")(h, y)
-                h = getattr(self, f"{b}_{s}_conv")(F.elu(h))
+                h = getattr(self, f"{b}_{s}_norm")(h, y, act=True) if self.cond else F.elu(h)
+                h = getattr(self, f"{b}_{s}_conv")(h)
             x = x + h
         return x
 
@@ -231,7 +233,7 @@ class _RefineNet(nn.Module):
         r = self.refine2([f3, r], y, f3.shape[2:])
         r = self.refine3([f2, r], y, f2.shape[2:])
         r = self.refine4([f1, r], y, f1.shape[2:])
-        return self.end_conv(F.elu(self.normalizer(r, y)))
+        return self.end_conv(self.normalizer(r, y, act=True))
 
 
 class CondRefineNetDilated(_RefineNet):

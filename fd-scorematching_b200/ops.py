@@ -385,3 +385,92 @@ def publish_scalars(src, host_dst):
     _count(1)
     check(lib.fdsm_publish_scalars(_ptr(src), C.c_void_p(host_dst.data_ptr()), src.numel(), _stream()), "fdsm_publish_scalars")
     return host_dst
+
+
+# --------------------------------------------------------------------------------------------
+# SURVEY.md §8f row N1 (first piece): InstanceNorm++ (+ ELU), forward and backward in two launches each
+# --------------------------------------------------------------------------------------------
+def _param_rows(t, N, C, name):
+    """(1 | N, C) fp32 rows with unit inner stride -> (tensor, row stride in floats; 0 = one shared row)."""
+    _req(t, name)
+    if t.dim() != 2 or t.shape[1] != C or t.shape[0] not in (1, N):
+        raise ValueError(f"{name} must have shape (1, {C}) or ({N}, {C}), got {tuple(t.shape)}")
+    if t.stride(1) != 1 and C > 1:
+        t = t.contiguous()
+    return t, (0 if t.shape[0] == 1 else (t.stride(0) if C > 1 or t.shape[0] > 1 else 1))
+
+
+def inorm_plus_reference(x, gamma, alpha, beta, act=False):
+    """The torch op sequence the kernel replaces (ncsnv2/models/normalization.py:163-176 + F.elu).  Used for CPU tensors
+    (the networks' CPU goldens) and, inside InormPlus.backward, when the caller differentiates the gradient itself
+    (create_graph=True: the exact-SSM comparison losses); never for a first-order CUDA step."""
+    mu = x.mean(dim=(2, 3))
+    centred = mu - mu.mean(dim=1, keepdim=True)
+    mu_std = centred / torch.sqrt(mu.var(dim=1, keepdim=True) + 1e-5)
+    h = torch.nn.functional.instance_norm(x) + (mu_std * alpha)[:, :, None, None]
+    h = gamma[:, :, None, None] * h
+    if beta is not None:
+        h = h + beta[:, :, None, None]
+    return torch.nn.functional.elu(h) if act else h
+
+
+class InormPlus(torch.autograd.Function):
+    """out = act(InstanceNorm++(x; gamma, alpha, beta)) on a contiguous (N, C, H, W) CUDA tensor."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, alpha, beta, act):
+        lib = _lib.load()
+        _req(x, "x")
+        if x.dim() != 4:
+            raise ValueError(f"x must be (N, C, H, W), got {tuple(x.shape)}")
+        if not x.is_contiguous():
+            raise ValueError("x must be contiguous (ops.inorm_plus makes it so)")
+        N, Cc, H, W = x.shape
+        g, ps = _param_rows(gamma, N, Cc, "gamma")
+        a, pa = _param_rows(alpha, N, Cc, "alpha")
+        b, pb = _param_rows(beta, N, Cc, "beta") if beta is not None else (None, ps)
+        if not (ps == pa == pb):         # one stride serves the three rows: the embedding's chunks or three plain vectors
+            g, a = g.expand(N, Cc).contiguous(), a.expand(N, Cc).contiguous()
+            b = b.expand(N, Cc).contiguous() if b is not None else None
+            ps = Cc
+        out = torch.empty_like(x)
+        stats = torch.empty(max(int(lib.fdsm_inorm_plus_stats_floats(N, Cc)), 1), device=x.device, dtype=torch.float32)
+        _count(int(lib.fdsm_inorm_plus_launches(N, Cc, H * W, 0, int(bool(act)), 1)))
+        check(lib.fdsm_inorm_plus_fwd(_ptr(x), N, Cc, H * W, _ptr(g), _ptr(a), _ptr(b), ps, int(bool(act)), _ptr(out), _ptr(stats),
+                                      _stream()), "fdsm_inorm_plus_fwd")
+        ctx.save_for_backward(x, out if act else None, gamma, alpha, beta, stats, g, a)
+        ctx.act, ctx.ps, ctx.shared = bool(act), ps, (gamma.shape[0] == 1, alpha.shape[0] == 1, beta is not None and beta.shape[0] == 1)
+        return out
+
+    @staticmethod
+    def backward(ctx, gout):
+        x, out, gamma, alpha, beta, stats, g, a = ctx.saved_tensors
+        if torch.is_grad_enabled():
+            # gradient of the gradient requested (create_graph=True): differentiate the torch op sequence instead
+            with torch.enable_grad():
+                y = inorm_plus_reference(x, gamma, alpha, beta, ctx.act)
+                ins = [t for t in (x, gamma, alpha, beta) if t is not None and t.requires_grad]
+                grads = iter(torch.autograd.grad(y, ins, gout, create_graph=True))
+            res = [next(grads) if (t is not None and t.requires_grad) else None for t in (x, gamma, alpha, beta)]
+            return res[0], res[1], res[2], res[3], None
+        lib = _lib.load()
+        N, Cc, H, W = x.shape
+        gout = _req(gout, "grad_out").contiguous()
+        need_dx = ctx.needs_input_grad[0]
+        dx = torch.empty_like(x) if need_dx else None
+        dpar = torch.empty(4, N, Cc, device=x.device, dtype=torch.float32)     # dgamma, dalpha, dbeta, scratch
+        _count(int(lib.fdsm_inorm_plus_launches(N, Cc, H * W, 1, int(ctx.act), int(need_dx))))
+        check(lib.fdsm_inorm_plus_bwd(_ptr(x), _ptr(out), _ptr(gout), N, Cc, H * W, _ptr(g), _ptr(a), ctx.ps, int(ctx.act), _ptr(stats),
+                                      _ptr(dpar[3]), _ptr(dx), _ptr(dpar[0]), _ptr(dpar[1]), _ptr(dpar[2]), _stream()),
+              "fdsm_inorm_plus_bwd")
+
+        def rows(i, shared):
+            return dpar[i].sum(0, keepdim=True) if shared else dpar[i]
+        return (dx, rows(0, ctx.shared[0]) if ctx.needs_input_grad[1] else None,
+                rows(1, ctx.shared[1]) if ctx.needs_input_grad[2] else None,
+                rows(2, ctx.shared[2]) if (beta is not None and ctx.needs_input_grad[3]) else None, None)
+
+
+def inorm_plus(x, gamma, alpha, beta=None, act=False):
+    """InstanceNorm++ (+ ELU when act) of x (N, C, H, W) with parameter rows gamma / alpha / beta of shape (1 | N, C)."""
+    return InormPlus.apply(x.contiguous(), gamma, alpha, beta, act)

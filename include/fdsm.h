@@ -379,6 +379,33 @@ int fdsm_langevin_step(const float* x, int64_t ldx, const float* score, int64_t 
                        uint64_t offset, uint64_t row0, fdsm_stream_t stream);
 int fdsm_ema_update(float* shadow, const float* params, int64_t n, float one_minus_mu, float mu, fdsm_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------
+ * SURVEY.md §8f row N1, first piece: InstanceNorm++ fused with the ELU that follows it, forward and backward
+ * (InstanceNorm2dPlus.forward, ncsnv2/models/normalization.py:163-176; the conditional variant whose
+ * [gamma | alpha | beta] rows come from an embedding of the noise level, ncsn/models/cond_refinenet_dilated.py:304-333
+ * = ncsn/models/normalization.py ConditionalInstanceNorm2dPlus; `act(normalize(x))` of the residual blocks,
+ * ncsnv2/models/layers.py:401-456).  The convolutions between them stay on cuDNN.
+ *
+ *   mu, var  = mean / biased variance of each (n, c) plane of HW elements;  rstd = 1/sqrt(var + 1e-5)
+ *   m, v     = mean / UNBIASED variance over c of mu[n, :];                 mustd = (mu - m)/sqrt(v + 1e-5)
+ *   out      = act(gamma * ((x - mu) * rstd + mustd * alpha) + beta),       act = identity (0) or ELU (1)
+ *
+ * x, out, gout, dx: contiguous (N, C, HW) fp32.  gamma / alpha / beta: rows of C floats, row n at `+ n * param_stride`
+ * (param_stride = 0: one shared row, the unconditional module); beta may be NULL (bias=False).
+ * stats: fdsm_inorm_plus_stats_floats(N, C) floats written by the forward ([mu | rstd | mustd | 1/sqrt(v + eps)]) and read
+ * by the backward.  Backward: per-sample parameter gradients dgamma, dalpha, dbeta (N, C each; the caller sums over n for
+ * a shared row), dx (may be NULL: parameters only), scratch = N * C floats.  `out` is read only when act = 1.
+ * ------------------------------------------------------------------------------------------ */
+int64_t fdsm_inorm_plus_stats_floats(int64_t N, int64_t C);
+/* Kernel launches one call makes (two per chunk of samples: a direction's second kernel re-reads what its first one read, so
+ * the tensor is walked in chunks that stay in L2; FDSM_NORM_CHUNK_MB, default 48, 0 = one chunk) -- for launch counters. */
+int64_t fdsm_inorm_plus_launches(int64_t N, int64_t C, int64_t HW, int32_t backward, int32_t act, int32_t with_dx);
+int fdsm_inorm_plus_fwd(const float* x, int64_t N, int64_t C, int64_t HW, const float* gamma, const float* alpha,
+                        const float* beta, int64_t param_stride, int32_t act, float* out, float* stats, fdsm_stream_t stream);
+int fdsm_inorm_plus_bwd(const float* x, const float* out, const float* gout, int64_t N, int64_t C, int64_t HW,
+                        const float* gamma, const float* alpha, int64_t param_stride, int32_t act, const float* stats,
+                        float* scratch, float* dx, float* dgamma, float* dalpha, float* dbeta, fdsm_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
