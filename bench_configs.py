@@ -48,6 +48,9 @@ def build(cfg_id, device, fdsm):
     from fdsm_b200.train import FDSSMTrainer, GenericFDTrainer
     cfg = dict(CONFIGS[cfg_id], id=cfg_id)
     torch.manual_seed(1234)
+    if cfg_id in (3, 4, 5) and os.environ.get("FDSM_BENCH_CUDNN_BENCHMARK", "1") != "0":
+        # as the reference's runners run (DeepEBM/train_ssm.py:23, ncsn/main.py:96, ncsnv2/main.py:193)
+        torch.backends.cudnn.benchmark = True
     if cfg_id == 1:
         net = fdsm.mlp.FusedEnergyMLP(11, 128, 2, act="softplus", head="linear", device=device, seed=1234)
         tr = FDSSMTrainer(net, eps=0.1, lr=1e-3, betas=(0.9, 0.999), clip=None, seed=1234, scale=11 / 0.1 ** 2)
@@ -65,12 +68,12 @@ def build(cfg_id, device, fdsm):
             labels = torch.randint(0, 10, (x.shape[0],), device=x.device)       # anneal_runner.py:144
             return losses.ncsn_anneal_ESM_scorenet_VR(m, x, labels, sig, 1, 0.1)
         tr = GenericFDTrainer(net, loss4, lr=1e-3, betas=(0.9, 0.999))
-        cfg["network"] = "torch CondRefineNetDilated (cuDNN) between our FD kernels"
+        cfg["network"] = "torch CondRefineNetDilated: cuDNN convolutions, our InstanceNorm++ / ELU kernels, between our FD kernels"
     elif cfg_id == 5:
         net = nets.NCSNv2(3, 128, 232).to(device)
         tr = GenericFDTrainer(net, lambda m, x: losses.anneal_ESM_scorenet_VR(m, x, m.sigmas, None, 2.0, None, 1, 0.1),
                               lr=1e-4, betas=(0.9, 0.999), ema_rate=0.999)
-        cfg["network"] = "torch NCSNv2 (cuDNN) between our FD kernels"
+        cfg["network"] = "torch NCSNv2: cuDNN convolutions, our InstanceNorm++ / ELU kernels, between our FD kernels"
     else:
         raise SystemExit(f"unknown --config {cfg_id}")
     return cfg, net, tr
