@@ -257,12 +257,13 @@ inline unsigned grid_for(long long planes, int lanes) {
   return (unsigned)(want < cap ? (want > 0 ? want : 1) : cap);
 }
 
-// Samples per launch pair.  The two kernels of a direction read the same activations twice; samples are independent, so the
-// tensor is walked in chunks small enough for the second kernel to find the first one's reads in L2 (126 MB): HBM then sees
-// the algorithmic bytes once (8 B per element forward, 16 B backward) instead of 12 / 28.  FDSM_NORM_CHUNK_MB overrides the
-// chunk footprint (0 = one chunk).
+// Samples per launch pair (FDSM_NORM_CHUNK_MB > 0; default 0 = the whole tensor in one pair).  The two kernels of a direction read
+// the same activations twice, and samples are independent, so the tensor could be walked in chunks small enough for the second
+// kernel to find the first one's reads in L2.  Measured on B200 (profiles/r02_norm_kernels_chunk_sweep.txt), it does not pay:
+// at (256, 128, 32, 32) the forward takes 87 us unchunked, 105 / 108 / 126 / 143 / 189 us with 96 / 64 / 48 / 32 / 16 MB
+// chunks -- the short launches lose more to ramps and tails than the L2 hits return.  The knob stays for other shapes.
 inline long long chunk_samples(long long N, long long C, long long HW, int tensors) {
-  static const long long mb = [] { const char* e = getenv("FDSM_NORM_CHUNK_MB"); return e ? atoll(e) : 48ll; }();
+  static const long long mb = [] { const char* e = getenv("FDSM_NORM_CHUNK_MB"); return e ? atoll(e) : 0ll; }();
   if (mb <= 0) return N;
   const long long per_sample = C * HW * 4 * tensors;
   long long n = (mb << 20) / (per_sample > 0 ? per_sample : 1);

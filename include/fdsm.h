@@ -397,8 +397,8 @@ int fdsm_ema_update(float* shadow, const float* params, int64_t n, float one_min
  * a shared row), dx (may be NULL: parameters only), scratch = N * C floats.  `out` is read only when act = 1.
  * ------------------------------------------------------------------------------------------ */
 int64_t fdsm_inorm_plus_stats_floats(int64_t N, int64_t C);
-/* Kernel launches one call makes (two per chunk of samples: a direction's second kernel re-reads what its first one read, so
- * the tensor is walked in chunks that stay in L2; FDSM_NORM_CHUNK_MB, default 48, 0 = one chunk) -- for launch counters. */
+/* Kernel launches one call makes (two per chunk of samples; one chunk unless FDSM_NORM_CHUNK_MB > 0 asks for L2-sized
+ * chunks -- measured slower on B200, see csrc/fd_norm.cu) -- for launch counters. */
 int64_t fdsm_inorm_plus_launches(int64_t N, int64_t C, int64_t HW, int32_t backward, int32_t act, int32_t with_dx);
 int fdsm_inorm_plus_fwd(const float* x, int64_t N, int64_t C, int64_t HW, const float* gamma, const float* alpha,
                         const float* beta, int64_t param_stride, int32_t act, float* out, float* stats, fdsm_stream_t stream);
