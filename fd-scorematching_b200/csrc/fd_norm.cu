@@ -40,7 +40,9 @@ template <> struct Pack<1> {
   __device__ __forceinline__ float& at(int) { return v; }
 };
 
-__device__ __forceinline__ float elu_fwd(float y) { return y > 0.f ? y : expm1f(y); }
+// exp(y) - 1 as ATen's CUDA ELU forms it (exp, then the subtraction), on the MUFU pipe: expm1f's ~25 instructions made the apply
+// kernel issue-bound (ncu: sm throughput 70 %, DRAM 48 %; profiles/r02e_norm_fwd_ncu_full_summary.csv)
+__device__ __forceinline__ float elu_fwd(float y) { return y > 0.f ? y : __expf(y) - 1.f; }
 // d elu / dy from the OUTPUT: 1 where out > 0, else exp(y) = out + 1
 __device__ __forceinline__ float elu_bwd_from_out(float o) { return o > 0.f ? 1.f : o + 1.f; }
 
@@ -53,7 +55,7 @@ struct NormDims {
 // stats = [mu (N*C) | rstd (N*C) | mustd (N*C) | s (N)]
 // ---- forward 1: plane mean and 1/sqrt(var + eps) -----------------------------------------------------------------------------
 template <int LANES, int VEC>
-__global__ void __launch_bounds__(kThreads) inorm_stats_kernel(const float* __restrict__ x, NormDims d, float* __restrict__ stats) {
+__global__ void __launch_bounds__(kThreads, 4) inorm_stats_kernel(const float* __restrict__ x, NormDims d, float* __restrict__ stats) {
   constexpr int GROUPS = kThreads / LANES, HELD = 8;
   const int lane = threadIdx.x % LANES, grp = threadIdx.x / LANES;
   const int nq = d.HW / VEC;

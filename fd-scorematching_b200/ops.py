@@ -464,8 +464,11 @@ class InormPlus(torch.autograd.Function):
                                       _ptr(dpar[3]), _ptr(dx), _ptr(dpar[0]), _ptr(dpar[1]), _ptr(dpar[2]), _stream()),
               "fdsm_inorm_plus_bwd")
 
+        if any(ctx.shared):       # shared rows: ONE reduction over the samples for the three parameters
+            summed = dpar[:3].sum(1, keepdim=True)
+
         def rows(i, shared):
-            return dpar[i].sum(0, keepdim=True) if shared else dpar[i]
+            return summed[i] if shared else dpar[i]
         return (dx, rows(0, ctx.shared[0]) if ctx.needs_input_grad[1] else None,
                 rows(1, ctx.shared[1]) if ctx.needs_input_grad[2] else None,
                 rows(2, ctx.shared[2]) if (beta is not None and ctx.needs_input_grad[3]) else None, None)

@@ -22,6 +22,8 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --c
   python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $out/${tag}_ncu_launches.log 2>&1; echo "ncu list rc=$?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:'chain_kernel|jet_|gemm' -c 24 -f -o $out/${tag}_chain_full \
   python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $out/${tag}_ncu_full.log 2>&1; echo "ncu full rc=$?"
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:'inorm_' -c 8 -f -o $out/${tag}_norm_full \
-  python scripts/bench_norm.py --kernels-only > $out/${tag}_ncu_norm.log 2>&1; echo "ncu norm rc=$?"
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:'inorm_(stats|apply)' -c 4 -f -o $out/${tag}_norm_fwd_full \
+  python scripts/bench_norm.py --kernels-only > $out/${tag}_ncu_norm.log 2>&1; echo "ncu norm fwd rc=$?"
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:'inorm_bwd' -c 4 -f -o $out/${tag}_norm_bwd_full \
+  python scripts/bench_norm.py --kernels-only >> $out/${tag}_ncu_norm.log 2>&1; echo "ncu norm bwd rc=$?"
 ls -la $out
