@@ -347,11 +347,12 @@ def main():
     if use_fused:
         net = fdsm.mlp.FusedEnergyMLP(D, HID, NHID, act=ACT, head="quadratic", device=dev, seed=1234,
                                       formulation=os.environ.get("FDSM_BENCH_FORMULATION", "auto"),
-                                      jet_passes=int(os.environ.get("FDSM_BENCH_JET_PASSES", "2")))
+                                      jet_passes=int(os.environ.get("FDSM_BENCH_JET_PASSES", "4")))     # pixel data in [0, 1]: fp16 input layer
         if net.formulation == "jet":
             network = (f"fused difference-propagating chain (ours): Philox direction + tcgen05 forward / head / combine / dgrad in one "
                        f"kernel (jet_passes={net.jet_passes}: " + {1: "TF32 weights", 2: "hidden-layer weights TF32 hi+lo, input layer TF32",
-                                                                      3: "all weights TF32 hi+lo"}[net.jet_passes] +
+                                                                      3: "all weights TF32 hi+lo",
+                                                                      4: "hidden-layer weights TF32 hi+lo, input layer fp16 operands (kind::f16)"}[net.jet_passes] +
                        "), split-K tcgen05 weight gradients, clip + Adam; one "
                        f"CUDA-graph replay per step")
         else:

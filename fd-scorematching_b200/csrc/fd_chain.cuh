@@ -34,6 +34,7 @@
 // mod 32; two samples at a time for instruction-level parallelism); warp 16 lane 0 = TMA producer, warp 17 lane 0 = MMA +
 // TMA-store issuer; warp 2 also allocates TMEM.
 #pragma once
+#include <cuda_fp16.h>
 #include "fd_jet.cuh"
 
 namespace fdsm {
@@ -67,6 +68,11 @@ struct alignas(64) ChainParams {
   int B, Bp, S, D, H, L, npad, kpad0, kpadh, head;
   int ablk, nraw;                    // bytes of one A k-block (3 S x 128), slots of the weight ring
   int ag;                            // k-blocks of phase 0's A operand per TMA instruction / barrier
+  // input layer in kind::f16 (fdsm_mlp_desc.passes = 4): fp16 carries TF32's 11 significant bits in half the bytes, and phase 0 is
+  // the L2 -> shared-memory stream of W_0 and [x | v].  Both operands K-major, k-blocks of 64:
+  CUtensorMap t_in16;                // XV16 [2][Bp][kpad16] halfs as (64 k, row, stream, k-block): box {64, S, 3, AG}
+  CUtensorMap t_w16;                 // W16 [npad][kpad16] halfs (W_0 | b_0 | 0) as (64 k, n, k-block): box {64, npad, 2} = one unit
+  int in16, nkb16;
   float act_offset;                  // ln 2 for the normalised softplus
   float c1, coef;                    // loss_b = dE^2/8 - sE + (c1 - 2) E0 ; dL/dloss_b = coef (= scale / B or scale)
   unsigned long long* trace;         // debug: per-CTA %globaltimer stamps [tile][TRACE_N] (NULL in production)
@@ -309,7 +315,8 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
   const int S = p.S, H = p.H, L = p.L, npad = p.npad;
   const int nbx = (npad + 31) >> 5;                 // 32-wide blocks of the layer's outputs: boxes per W k-block (forward),
                                                     // k-blocks of a dgrad GEMM, blocks of a dZ store
-  const int nkb0 = p.kpad0 >> 5;
+  constexpr bool in16 = PASSES == 4;      // input layer in kind::f16 (hidden layers as PASSES = 2)
+  const int nkb0 = in16 ? p.nkb16 : p.kpad0 >> 5;
   const int nphase = 2 * L - 1;
   const uint32_t crank = CL > 1 ? cluster_ctarank() : 0u;
   constexpr uint16_t CMASK = (uint16_t)((1u << CL) - 1u);
@@ -349,10 +356,11 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
   //   phase 0, PASSES == 3:  one k-block of W_0, hi and lo          4-D box {32 n, 32 k, nbx, 2}   [hi|lo][nblk][32 k][32 n]
   //   forward l >= 1:        one k-block of W_l, hi (and lo)        4-D box {32 n, 32 k, nbx, HL}
   //   dgrad l:               one k-block (32 outputs) of W_l        3-D box {32 n, 32 nbx rows k, HL}  [hi|lo][k][32 n]
-  constexpr int HL = PASSES >= 2 ? 2 : 1;            // copies of a hidden-layer unit: hi (+ lo)
+  constexpr int HL = PASSES >= 2 ? 2 : 1;            // copies of a hidden-layer unit: hi (+ lo)   (PASSES = 4: as 2)
   constexpr int WK0 = PASSES == 3 ? 1 : 2;           // k-blocks of W_0 per unit
   const int nunits = nraw >> 1;                      // ring depth in units
-  const uint32_t unit0_bytes = (uint32_t)nbx * 4096u * 2u;                 // both layouts of phase 0 fill 2 x nbx boxes
+  const uint32_t unit0_bytes = in16 ? (uint32_t)npad * 256u                // fp16 input layer: two k-blocks of npad rows x 128 B
+                                    : (uint32_t)nbx * 4096u * 2u;          // both layouts of phase 0 fill 2 x nbx boxes
   const uint32_t unith_bytes = (uint32_t)nbx * 4096u * (uint32_t)HL;
   // phase 0's A operand arrives in groups of AG k-blocks, one 4-D instruction and one barrier phase each (the same
   // per-barrier cost): group slot g covers the A-region blocks [AG g, AG g + AG); k-blocks past the end and the b stream are
@@ -380,7 +388,7 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
               const int gs = (kb / AG) % nag;
               mbar_wait_parked(a_empty(gs), ((kb / AG / nag) & 1) ^ 1u);
               mbar_arrive_expect_tx(a_full(gs), (uint32_t)(AG * ablk));
-              tma_load_4d(a_base + gs * AG * ablk, &p.t_in, a_full(gs), 0, tile * S, 0, kb);
+              tma_load_4d(a_base + gs * AG * ablk, in16 ? &p.t_in16 : &p.t_in, a_full(gs), 0, tile * S, 0, kb);
             }
             if (kb % WK0 != 0) continue;
           }
@@ -388,7 +396,10 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
           const uint32_t bytes = g == 0 ? unit0_bytes : unith_bytes;
           mbar_arrive_expect_tx(w_full(2 * wu), bytes);
           if (CL == 1 || (uint32_t)(useq % CL) == crank) {          // clusters: the CTAs take turns and multicast the unit
-            if (g == 0 && PASSES != 3) {
+            if (g == 0 && in16) {
+              if (CL > 1) tma_load_3d_mc(dst, &p.t_w16, w_full(2 * wu), 0, 0, kb, CMASK);
+              else tma_load_3d(dst, &p.t_w16, w_full(2 * wu), 0, 0, kb);
+            } else if (g == 0 && PASSES != 3) {
               if (CL > 1) tma_load_3d_mc(dst, tw, w_full(2 * wu), 0, 32 * kb, 0, CMASK);
               else tma_load_3d(dst, tw, w_full(2 * wu), 0, 32 * kb, 0);
             } else if (fwd) {
@@ -435,6 +446,19 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
             mma_tf32_ss(tmem_base, da, db, idesc, (first && k8 == 0) ? 0u : 1u);
           }
         };
+        // fp16 input layer (PASSES = 4, phase 0): both operands K-major (the data-gradient phases' descriptor form), k-blocks
+        // of 64 columns, 16 per MMA
+        auto mmas16 = [&](int as_, uint32_t bbase, bool first, int kb_) {
+          const uint32_t idesc16 = make_idesc_f16(128, npad, tc::MAJOR_K, tc::MAJOR_K);
+          const int n16 = min(4, (kvalid - 64 * kb_ + 15) >> 4);
+#pragma unroll
+          for (int k16 = 0; k16 < 4; ++k16) {
+            if (k16 >= n16) break;
+            const uint64_t da = make_smem_desc(a_base + as_ * ablk + k16 * 32, 16u, 1024u, 2u);
+            const uint64_t db = make_smem_desc(bbase + k16 * 32, 16u, 1024u, 2u);
+            mma_f16_ss(tmem_base, da, db, idesc16, (first && k16 == 0) ? 0u : 1u);
+          }
+        };
         auto release = [&]() {
           if (CL > 1) tc_commit_mc(w_empty(2 * wu), CMASK);
           else tc_commit(w_empty(2 * wu));
@@ -450,7 +474,9 @@ __global__ void __launch_bounds__(CT, 1) chain_kernel(const __grid_constant__ Ch
             if (kb % WK0 == 0) mbar_wait_parked(w_full(2 * wu), wph);
             if (p.trace && p.trace_mode == 3 && L == 3 && kb % 2 == 0 && kb < 32) stamp_now(p, 22 + kb / 2);   // (debug)
             tc_fence_after();
-            if (WK0 == 2) {
+            if (in16) {
+              mmas16(as, ubase + (kb & 1) * (uint32_t)npad * 128u, kb == 0, kb);
+            } else if (WK0 == 2) {
               mmas(as, ubase + (kb & 1) * 4096u, kb == 0, kb);
             } else {
               mmas(as, ubase, kb == 0, kb);
@@ -674,12 +700,13 @@ struct InputArgs {
   const float* dir; long long lddir; int normalize; float scale;
   unsigned long long seed, offset, row0; const unsigned long long* offset_dev;
   float* xv; int B, Bp, D, kpad0;
+  __half* xv16; int kpad16;          // optional fp16 copy of the rows for the chain's kind::f16 input layer (NULL: none)
 };
 // FAST = compile-time specialisation of the two production configurations (the mode tests fold away and the compiler
 // interleaves the Philox chains of a thread's chunks, as for the stack kernel's MODE_ENERGY3): 1 = fp32 samples, 2 = uint8
 // pixels + Gaussian noise; both: Philox direction, normalised, 16-byte aligned rows, D <= 1024.  0 = everything else.
 // Bit-identical outputs (tests/test_jet_gpu.py compares against FDSM_JET_INPUTS_GENERAL=1).
-template <int FAST>
+template <int FAST, bool IN16 = false>
 __device__ __forceinline__ void jet_inputs_body(InputArgs a, const int block, const int nblocks) {
   constexpr int G = 128, MAXC = 2;
   __shared__ float red[256 / 32];
@@ -771,8 +798,11 @@ __device__ __forceinline__ void jet_inputs_body(InputArgs a, const int block, co
     if (b >= a.Bp) continue;
     float* xr = a.xv + b * (long long)a.kpad0;
     float* vr = a.xv + ((long long)a.Bp + b) * a.kpad0;
+    __half* xr16 = IN16 ? a.xv16 + b * (long long)a.kpad16 : nullptr;
+    __half* vr16 = IN16 ? a.xv16 + ((long long)a.Bp + b) * a.kpad16 : nullptr;
     if (!active) {          // rows of the padded tail: zeros (finite everywhere downstream, masked out of every sum)
       for (int c = t; c < a.kpad0; c += G) { xr[c] = 0.f; vr[c] = 0.f; }
+      if (IN16) for (int c = t; c < a.kpad16; c += G) { xr16[c] = __float2half_rn(0.f); vr16[c] = __float2half_rn(0.f); }
       continue;
     }
     const bool exact = !FAST && a.dir != nullptr;     // injected draws keep the reference's rounding sequence u / ||u|| * eps
@@ -798,8 +828,18 @@ __device__ __forceinline__ void jet_inputs_body(InputArgs a, const int block, co
       }
       *reinterpret_cast<float4*>(xr + e) = make_float4(tf32r(xx.x), tf32r(xx.y), tf32r(xx.z), tf32r(xx.w));
       *reinterpret_cast<float4*>(vr + e) = make_float4(tf32r(v.x), tf32r(v.y), tf32r(v.z), tf32r(v.w));
+      if (IN16) {           // (kpad16 is a multiple of 64: the 8-byte chunk store is in range and aligned)
+        const __half2 x01 = __floats2half2_rn(xx.x, xx.y), x23 = __floats2half2_rn(xx.z, xx.w);
+        const __half2 v01 = __floats2half2_rn(v.x, v.y), v23 = __floats2half2_rn(v.z, v.w);
+        uint2 px, pv;
+        px.x = *reinterpret_cast<const unsigned*>(&x01); px.y = *reinterpret_cast<const unsigned*>(&x23);
+        pv.x = *reinterpret_cast<const unsigned*>(&v01); pv.y = *reinterpret_cast<const unsigned*>(&v23);
+        *reinterpret_cast<uint2*>(xr16 + e) = px;
+        *reinterpret_cast<uint2*>(vr16 + e) = pv;
+      }
     }
     for (int c = 4 * nchunk + t; c < a.kpad0; c += G) { xr[c] = c == D ? 1.f : 0.f; vr[c] = 0.f; }
+    if (IN16) for (int c = 4 * nchunk + t; c < a.kpad16; c += G) { xr16[c] = __float2half_rn(c == D ? 1.f : 0.f); vr16[c] = __float2half_rn(0.f); }
   }
 }
 

@@ -56,8 +56,8 @@ inline int make_tmap(CUtensorMap* m, const float* ptr, long long rows, long long
 // General tiled map over fp32 data: dims / box innermost first (dims[0] contiguous), strides in BYTES for dims 1.. (need not be
 // monotonic: a later dimension may step by less than an earlier one -- e.g. the 32-column panels of a row-major matrix as
 // dimension 2 with a 128-byte stride, so that ONE box covers several panels in the [panel][row][32] order tcgen05 wants).
-inline int make_tmap_nd(CUtensorMap* m, const float* ptr, int rank, const long long* dims, const long long* strides_bytes,
-                        const int* box, bool mn_major, const char* what) {
+inline int make_tmap_nd(CUtensorMap* m, const void* ptr, int rank, const long long* dims, const long long* strides_bytes,
+                        const int* box, bool mn_major, const char* what, bool f16 = false) {
   auto fn = encode_fn();
   if (!fn) {
     set_error("cuTensorMapEncodeTiled entry point not available");
@@ -74,7 +74,8 @@ inline int make_tmap_nd(CUtensorMap* m, const float* ptr, int rank, const long l
       st[i - 1] = (cuuint64_t)strides_bytes[i - 1];
     }
   }
-  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<float*>(ptr), d, st, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+  CUresult r = fn(m, f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<void*>(ptr), d, st, bx,
+                  es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                   mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {

@@ -105,6 +105,15 @@ __device__ __forceinline__ void mma_tf32_ss(uint32_t tmem_d, uint64_t adesc, uin
       : "memory");
 }
 
+__device__ __forceinline__ void mma_f16_ss(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
 // ---- cluster multicast: one L2 read lands at the same shared-memory offset of every CTA in `mask`, and signals the
 // ---- mbarrier at `bar`'s offset in each of them; the commit form arrives on every CTA's barrier likewise ----------
 __device__ __forceinline__ void tma_load_2d_mc(uint32_t dst, const void* tmap, uint32_t bar, int32_t c0, int32_t c1, uint16_t mask) {
@@ -264,6 +273,11 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_
 __host__ __device__ constexpr uint32_t make_idesc_tf32(int M, int N, int a_major, int b_major) {
   return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)a_major << 15) | ((uint32_t)b_major << 16) |
          ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// The same for kind::f16 with fp16 operands (a_format = b_format = 0), fp32 accumulate: K = 16 per instruction.
+__host__ __device__ constexpr uint32_t make_idesc_f16(int M, int N, int a_major, int b_major) {
+  return (1u << 4) | ((uint32_t)a_major << 15) | ((uint32_t)b_major << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
 // round-to-nearest TF32 split: x = hi + lo (+ O(2^-22 |x|)), both exactly representable in TF32

@@ -99,7 +99,10 @@ class FusedEnergyMLP(nn.Module):
         propagating chain kernel (csrc/fd_chain.cuh; hidden <= 223, n_hidden <= 5), "stacked" = the reference's stacked batch
         [x | x+v | x-v] through the 3xTF32 GEMM launches, "auto" = jet where supported.  `jet_passes`: 3 = every GEMM with
         weights as TF32 hi + lo, 2 (default) = hi + lo for the hidden layers and round-to-nearest TF32 weights for the input
-        layer, 1 = weights rounded to TF32 everywhere (include/fdsm.h quotes the measured errors).  `passes` / `presplit` configure the stacked path and `net(x)`."""
+        layer, 1 = weights rounded to TF32 everywhere (include/fdsm.h quotes the measured errors); 4 = as 2 with the input layer
+        in kind::f16 (fp16 copies of W_0 and of the rows [x | v]: the same 11 significant bits as TF32 in half the bytes, which is
+        what phase 0 of the kernel is bound by; needs |x|, |W_0| < 65504, else the loss turns NaN).  `passes` / `presplit`
+        configure the stacked path and `net(x)`."""
         super().__init__()
         if act not in ACTS:
             raise ValueError(f"act must be one of {sorted(ACTS)}")
@@ -552,11 +555,12 @@ class FusedEnergyMLP(nn.Module):
             dgrad = 2.0 * 3 * B * H * H * (L - 1)
             flops = fwd + dgrad
             fwd0 = 2.0 * 2 * B * D * H
-            executed = {1: flops, 2: fwd0 + 2 * (flops - fwd0), 3: 2 * flops}[self.jet_passes]
+            executed = {1: flops, 2: fwd0 + 2 * (flops - fwd0), 3: 2 * flops, 4: fwd0 + 2 * (flops - fwd0)}[self.jet_passes]
             ach = flops / (avg * 1e-3) / 1e12
             peak = peaks["bf16_tflops"] / 2.0
             wdesc = {1: "TF32 weights, 1 MMA pass", 2: "hidden-layer weights as TF32 hi+lo (2 MMA passes), input layer 1 pass",
-                     3: "all weights as TF32 hi+lo, 2 MMA passes"}[self.jet_passes]
+                     3: "all weights as TF32 hi+lo, 2 MMA passes",
+                     4: "hidden-layer weights as TF32 hi+lo (2 MMA passes), input layer in kind::f16 (fp16 operands, 1 pass)"}[self.jet_passes]
             return {"kernel": f"fdsm::jet::chain_kernel (tcgen05 kind::tf32, TMA-fed, {wdesc}; all {L} forward layers + head + combine + {L - 1} dgrad GEMMs in one launch)",
                     "bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": None,
                     "peak_kind": f"{peaks_kind} dense bf16 burst / 2 (TF32 kind)", "passes": self.jet_passes,

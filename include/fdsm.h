@@ -269,7 +269,10 @@ int fdsm_mlp_backward_fd_dsm(const fdsm_mlp_desc* desc, const float* x_hi, const
  * desc->passes: 3 = every GEMM with its weights as TF32 hi + lo (two MMA passes; the input layer's weights travel once as
  * fp32 and lo is derived on chip); 1 = weights rounded to TF32, one pass everywhere; any other value (default, 2) = hi + lo
  * for the hidden layers, round-to-nearest TF32 weights for the input layer (config 2 against fp64: loss / gradient within
- * 2e-5 / 9e-5, passes = 3: 2e-6 / 6e-5, passes = 1: 1e-4 / 2e-4).  desc->presplit is ignored.  Supported: hidden <= 223, n_hidden <= 5 (fdsm_jet_supported).
+ * 2e-5 / 9e-5, passes = 3: 2e-6 / 6e-5, passes = 1: 1e-4 / 2e-4); 4 = as 2 with the input layer in kind::f16: fp16 copies of
+ * W_0 and of the rows [x | v] carry TF32's 11 significant bits in half the bytes (the input layer is bound by that stream;
+ * same measured errors as 2), valid while |x| and |W_0| stay below 65504 -- beyond that the loss turns NaN, never silently
+ * wrong.  desc->presplit is ignored.  Supported: hidden <= 223, n_hidden <= 5 (fdsm_jet_supported).
  * Deterministic: fixed-order tile, split-K and head reductions.  Graph-capturable (uses internal side streams by
  * event fork/join).
  * ------------------------------------------------------------------------------------------ */

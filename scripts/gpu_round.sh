@@ -12,7 +12,7 @@ timeout 600 python bench.py --steps 20 --warmup 5 > $out/${tag}_bench_n1_driver_
 timeout 600 python bench.py --no-cpu-baseline > $out/${tag}_bench_n1.json 2> $out/${tag}_bench_n1.err; echo "bench(200) rc=$?"
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > $out/${tag}_bench_reference_arm.json 2> $out/${tag}_bench_reference_arm.err; echo "ref rc=$?"
 timeout 600 python -c "import __graft_entry__ as g; g.smoke()" > $out/${tag}_smoke.txt 2>&1; echo "smoke rc=$?"
-timeout 300 python scripts/chain_trace.py > $out/${tag}_chain_trace.txt 2>&1; echo "chain trace rc=$?"
+timeout 300 python scripts/chain_trace.py 4096 4 > $out/${tag}_chain_trace.txt 2>&1; echo "chain trace rc=$?"
 timeout 300 python scripts/update_trace.py > $out/${tag}_update_trace.txt 2>&1; echo "update trace rc=$?"
 timeout 300 python scripts/bench_fd_vs_exact.py > $out/${tag}_fd_vs_exact.txt 2>&1; echo "fd vs exact rc=$?"
 for c in 1 3 4 5; do timeout 600 python bench.py --config $c --no-cpu-baseline > $out/${tag}_bench_cfg$c.json 2> $out/${tag}_bench_cfg$c.err; echo "cfg$c rc=$?"; done

@@ -58,7 +58,7 @@ CASES = [
 
 
 @pytest.mark.parametrize("D,H,L,act,head,B,eps,data", CASES)
-@pytest.mark.parametrize("passes", [3, 2, 1])
+@pytest.mark.parametrize("passes", [3, 2, 1, 4])
 def test_jet_loss_and_grad_match_fp64(fdsm, D, H, L, act, head, B, eps, data, passes):
     net, ref = _pair(fdsm, D, H, L, act, head, passes=passes)
     x = nets.np_rand(1, B, D) if data == "unit" else nets.np_randn(1, B, D) + 5.0 * ((nets.np_rand(3, B, 1) < 0.8).double() * 2 - 1)
@@ -66,7 +66,7 @@ def test_jet_loss_and_grad_match_fp64(fdsm, D, H, L, act, head, B, eps, data, pa
     scale = (D if head == "linear" else 1.0) / eps ** 2
     want, gwant = _oracle(ref, x, fd_losses.sphere_direction(u, eps), scale)
     loss, grad = net.fd_ssm_loss_and_grad(x.float().to(DEV), eps, scale, u=u.float().to(DEV))
-    tol_l, tol_g = {3: (2e-4, 2e-4), 2: (2e-4, 5e-4), 1: (1e-3, 1e-3)}[passes]
+    tol_l, tol_g = {3: (2e-4, 2e-4), 2: (2e-4, 5e-4), 1: (1e-3, 1e-3), 4: (2e-4, 5e-4)}[passes]     # 4: input layer in fp16 = TF32's 11 bits
     if act == "elu":
         tol_g = 5e-2
     # the loss is a signed mean: measure its error against the mean |per-sample term| when the mean itself nearly cancels

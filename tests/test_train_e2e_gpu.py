@@ -74,3 +74,27 @@ def test_step_from_host_u8_equals_device_u8_step(fdsm):
         torch.cuda.synchronize()
         assert float(loss_host) == want, f"step {i}"
     assert torch.equal(tr_dev.flat.flat, tr_host.flat.flat)
+
+
+def test_fp16_input_layer_on_pixel_batches(fdsm):
+    """jet_passes = 4 (input layer in kind::f16) through both input kernels -- fp32 rows and uint8 pixels + noise: the gradient
+    stays within TF32 rounding of the jet_passes = 2 gradient (same draws), and a training step runs through it."""
+    B, D, H = 256, 784, 200
+    nets_ = [fdsm.mlp.FusedEnergyMLP(D, H, 3, act="nsoftplus", head="quadratic", device=torch.device(DEV), seed=7, jet_passes=p)
+             for p in (2, 4)]
+    if nets_[0].formulation != "jet":
+        pytest.skip("needs the chain kernel")
+    pix = torch.randint(0, 256, (B, D), dtype=torch.uint8, device=DEV)
+    xf = pix.float() / 255.0
+    for x, kw in ((xf, {}), (pix, {"x_noise": 0.005})):
+        grads = []
+        for net in nets_:
+            _, g = net._jet_loss_and_grad(x, 0.05, 400.0, None, None, (5, 3, 0), 2.0, True, None, **kw)
+            grads.append(g.clone())
+        rel = float((grads[1] - grads[0]).norm() / grads[0].norm())
+        assert rel <= 5e-4, rel
+    from fdsm_b200.train import FDSSMTrainer
+    tr = FDSSMTrainer(nets_[1], eps=0.05, lr=1e-3, betas=(0.9, 0.95), clip=0.1, seed=99)
+    l0 = float(tr.step(xf))
+    l1 = float(tr.step(pix, borrow=True, x_noise=0.005))
+    assert np.isfinite(l0) and np.isfinite(l1)
