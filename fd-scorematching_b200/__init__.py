@@ -4,7 +4,15 @@ Import as ``fdsm_b200`` (see the ``fdsm_b200.py`` shim at the repo root; the dir
 contains a hyphen).  Public surface = the reference's loss-function signatures (``losses``), the
 kernel-level ops (``ops``) and the fused energy MLPs (``mlp``).
 """
-from . import _lib, losses, mlp, nets, ops, sampling  # noqa: F401
+import os as _os
+
+# The end-to-end step keeps several streams busy at once (two H2D copy streams, the step, the weight-gradient side streams).
+# With the CUDA default of 8 hardware queues, two of them can land on one queue and serialise (measured on B200: the fp32 e2e
+# step then takes copy + step = 380 us instead of the copy's 236 us, in some processes and not in others).  Read by the driver
+# when the context is created, so it only has an effect when this package is imported before CUDA is initialised.
+_os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
+from . import _lib, losses, mlp, nets, ops, sampling  # noqa: F401,E402
 from .losses import (FLAGS, MLE_efficient_score_matching_conjugate, anneal_ESM_scorenet_VR,  # noqa: F401
                      anneal_sliced_score_estimation_vr, deepebm_exact_score_matching, dsm_fd, exact_score_matching,
                      mdsm_baseline, mdsm_tracetrick,

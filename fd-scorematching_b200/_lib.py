@@ -82,7 +82,7 @@ class MlpDesc(C.Structure):
                 ("presplit", _i32)]
 
 
-ABI_VERSION = 10   # FDSM_ABI_VERSION of include/fdsm.h
+ABI_VERSION = 11   # FDSM_ABI_VERSION of include/fdsm.h
 
 # name -> (restype, argtypes); must list every symbol include/fdsm.h declares
 PROTOTYPES = {
@@ -107,6 +107,8 @@ PROTOTYPES = {
     "fdsm_adam_step": (C.c_int, [_f32p, _f32p, _f32p, _f32p, _i64, _f32, _f32p, _f32, _f32, _f32, _f32, _f32p, C.c_void_p,
                                  _stream]),
     "fdsm_publish_scalars": (C.c_int, [_f32p, _f32p, _i64, _stream]),
+    "fdsm_stage_h2d": (C.c_int, [C.c_void_p, C.c_void_p, _i64, _stream, C.c_void_p, C.c_void_p, _stream]),
+    "fdsm_publish_scalars_record": (C.c_int, [_f32p, _f32p, _i64, _stream, C.c_void_p]),
     "fdsm_mlp_sizes": (C.c_int, [C.POINTER(MlpDesc), _i64, C.POINTER(_i64), C.POINTER(_i64), C.POINTER(_i64)]),
     "fdsm_mlp_prepare": (C.c_int, [C.POINTER(MlpDesc), _i64, _f32p, _f32p, _stream]),
     "fdsm_mlp_forward": (C.c_int, [C.POINTER(MlpDesc), _f32p, _f32p, _i64, _f32p, _f32p, _f32p, _stream]),

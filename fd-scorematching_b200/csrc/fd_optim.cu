@@ -90,6 +90,29 @@ __global__ void publish_scalars_kernel(const float* __restrict__ src, volatile f
 
 using namespace fdsm;
 
+// Host plumbing of the end-to-end step in ONE call each (the step loop is host-bound on a busy host long before it is
+// link- or device-bound when every stream / event operation is a separate Python call): the batch's way in ...
+extern "C" int fdsm_stage_h2d(void* dst, const void* h_src, int64_t nbytes, fdsm_stream_t copy_stream, void* ev_free, void* ev_ready,
+                              fdsm_stream_t main_stream) {
+  FDSM_REQUIRE(nbytes >= 0 && (nbytes == 0 || (dst && h_src)) && ev_ready, "fdsm_stage_h2d: bad arguments");
+  cudaStream_t cs = (cudaStream_t)copy_stream, ms = (cudaStream_t)main_stream;
+  int rc;
+  if (ev_free && (rc = cuda_status(cudaStreamWaitEvent(cs, (cudaEvent_t)ev_free, 0), "fdsm_stage_h2d(wait)"))) return rc;
+  if (nbytes && (rc = cuda_status(cudaMemcpyAsync(dst, h_src, (size_t)nbytes, cudaMemcpyHostToDevice, cs), "fdsm_stage_h2d(copy)"))) return rc;
+  if ((rc = cuda_status(cudaEventRecord((cudaEvent_t)ev_ready, cs), "fdsm_stage_h2d(record)"))) return rc;
+  return cuda_status(cudaStreamWaitEvent(ms, (cudaEvent_t)ev_ready, 0), "fdsm_stage_h2d(join)");
+}
+
+extern "C" int fdsm_publish_scalars(const float* src, float* h_dst, int64_t n, fdsm_stream_t stream);
+// ... and the result's way out: `ev` (may be NULL) is recorded on `stream` first -- the consumer of the staged batch is done
+extern "C" int fdsm_publish_scalars_record(const float* src, float* h_dst, int64_t n, fdsm_stream_t stream, void* ev) {
+  if (ev) {
+    const int rc = cuda_status(cudaEventRecord((cudaEvent_t)ev, (cudaStream_t)stream), "fdsm_publish_scalars_record");
+    if (rc) return rc;
+  }
+  return fdsm_publish_scalars(src, h_dst, n, stream);
+}
+
 extern "C" int fdsm_publish_scalars(const float* src, float* h_dst, int64_t n, fdsm_stream_t stream) {
   FDSM_REQUIRE(n >= 0 && n <= 4096, "fdsm_publish_scalars: n must be in [0, 4096] (a step's scalars, not a tensor copy)");
   if (n == 0) return FDSM_OK;

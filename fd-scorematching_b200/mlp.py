@@ -484,6 +484,7 @@ class FusedEnergyMLP(nn.Module):
         return self._train_step(st, "dsm", (float(eps), float(sigma02), float(loss_coe)), allreduce, distributed)
 
     def _train_step(self, st, kind, cfg, allreduce, distributed, xkey=0):
+        self._last_graphs = None
         peer = distributed and getattr(allreduce, "fused_sumsq", False)    # ddp.PeerAllReduce: capturable, emits the sumsq
         key = (st["B"], kind, cfg, bool(distributed), bool(peer))
 
@@ -529,6 +530,7 @@ class FusedEnergyMLP(nn.Module):
             self._graphs[key] = (g1, g2, ops.LAUNCHES - launches0)
             ops.LAUNCHES = launches0
         g1, g2, nlaunch = self._graphs[key]
+        self._last_graphs = self._graphs[key]        # train.FDSSMTrainer's lean host path replays it directly next time
         g1.replay()
         if g2 is not None:
             if allreduce is not None:

@@ -145,8 +145,12 @@ class FDSSMTrainer:
         return self.step_from_host(x_host_u8, loss_host, x_noise=noise_std)
 
     def step_from_host(self, x_host, loss_host, x_noise=0.0):
-        """H2D copy of this step's batch (pinned -> device, on a side stream, double-buffered against the
-        previous step's compute), the step, and an async D2H read of the loss into `loss_host` (pinned)."""
+        """H2D copy of this step's batch (pinned -> device, one copy stream per staging buffer, double-buffered against the
+        previous step's compute), the step, and the loss into `loss_host` (pinned: stored by a kernel).  After the first two
+        calls for a batch shape (which capture the step's graph for each staging buffer) a call is two library calls and
+        one graph replay: `fdsm_stage_h2d` (wait for the buffer, copy, record, make the step wait), the replay,
+        `fdsm_publish_scalars_record` -- the host loop stays well under the 100 us of a device step also on a busy host."""
+        import ctypes as C
         cur = torch.cuda.current_stream()
         if self._copy_stream is None:
             # one copy stream per staging buffer: batch n + 1 is handed to the copy engines while batch n is still in
@@ -154,14 +158,34 @@ class FDSSMTrainer:
             n = 1 if os.environ.get("FDSM_E2E_COPY_STREAMS") == "1" else 2
             self._copy_stream = [torch.cuda.Stream() for _ in range(n)]
             self._staging = {}
-        key = (tuple(x_host.shape), x_host.dtype)
-        if key not in self._staging:      # one double buffer per batch shape (the last batch of an epoch may be shorter)
-            self._staging[key] = dict(bufs=[torch.empty_like(x_host, device="cuda") for _ in range(2)],
-                                      evt=[torch.cuda.Event() for _ in range(2)], free=[torch.cuda.Event() for _ in range(2)], i=0)
-        sg = self._staging[key]
-        self._bufs, self._evt, self._free = sg["bufs"], sg["evt"], sg["free"]
+        key = (tuple(x_host.shape), x_host.dtype, float(x_noise))
+        sg = self._staging.get(key)
+        if sg is None:      # one double buffer per batch shape (the last batch of an epoch may be shorter)
+            sg = self._staging[key] = dict(bufs=[torch.empty_like(x_host, device="cuda") for _ in range(2)],
+                                           evt=[torch.cuda.Event() for _ in range(2)], free=[torch.cuda.Event() for _ in range(2)], i=0,
+                                           lean=[None, None])
+            for e in sg["evt"] + sg["free"]:
+                e.record(cur)                        # creates the cudaEvent_t handles the lean path passes to the library
         i = sg["i"]
         sg["i"] ^= 1
+        lean = sg["lean"][i]
+        if lean is not None and x_host.is_pinned() and x_host.is_contiguous():
+            lib, g1, nlaunch, dst, nbytes, cs, ev_free, ev_ready, loss_dev, loss_ptr = lean
+            if loss_host.data_ptr() == loss_ptr:
+                main = C.c_void_p(cur.cuda_stream)
+                rc = lib.fdsm_stage_h2d(dst, C.c_void_p(x_host.data_ptr()), nbytes, cs, ev_free, ev_ready, main)
+                if rc == 0:
+                    g1.replay()
+                    rc = lib.fdsm_publish_scalars_record(loss_dev, C.c_void_p(loss_ptr), 1, main, ev_free)
+                if rc:
+                    from ._lib import check
+                    check(rc, "step_from_host")
+                ops._count(nlaunch + 1)
+                self._nstep += 1
+                if self._nstep % self.peer_check_every == 0:
+                    self.check_exchange()
+                return loss_host
+        self._bufs, self._evt, self._free = sg["bufs"], sg["evt"], sg["free"]
         cs = self._copy_stream[i % len(self._copy_stream)]
         with torch.cuda.stream(cs):
             cs.wait_event(self._free[i])      # previous consumer of this buffer is done
@@ -169,8 +193,20 @@ class FDSSMTrainer:
             self._evt[i].record(cs)
         cur.wait_event(self._evt[i])
         # the fused ssm_fd step reads the staging buffer where it lies (one captured graph per staging buffer): no D2D copy
-        loss = self.step(self._bufs[i], borrow=self.fused and self.loss_name == "ssm_fd", x_noise=x_noise)
+        fast = self.fused and self.loss_name == "ssm_fd"
+        loss = self.step(self._bufs[i], borrow=fast, x_noise=x_noise)
         self._free[i].record(cur)
+        # remember what a later call for this buffer replays: the single graph of the step just taken (none if the step ran
+        # eagerly or needs a library collective between two graphs), the staging pointers and event handles
+        graphs = getattr(self.net, "_last_graphs", None) if fast else None
+        if (graphs is not None and graphs[1] is None and loss_host.is_pinned() and loss_host.dtype == torch.float32
+                and loss_host.numel() == 1 and loss.dtype == torch.float32 and os.environ.get("FDSM_E2E_LEAN", "1") != "0"
+                and os.environ.get("FDSM_E2E_LOSS_MEMCPY") != "1"):
+            from . import _lib
+            sg["lean"][i] = (_lib.load(), graphs[0], graphs[2], C.c_void_p(self._bufs[i].data_ptr()),
+                             self._bufs[i].numel() * self._bufs[i].element_size(), C.c_void_p(cs.cuda_stream),
+                             C.c_void_p(self._free[i].cuda_event), C.c_void_p(self._evt[i].cuda_event),
+                             C.c_void_p(loss.data_ptr()), loss_host.data_ptr())
         return read_loss_to_host(loss, loss_host)
 
 

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define FDSM_ABI_VERSION 10
+#define FDSM_ABI_VERSION 11
 
 #define FDSM_OK 0
 #define FDSM_ERR_INVALID_ARGUMENT (-1)
@@ -345,6 +345,14 @@ int fdsm_adam_step(float* params, const float* grads, float* exp_avg, float* exp
  * reads them after synchronising with the stream.  In place of cudaMemcpyAsync(D2H) of 4 bytes: a copy-engine operation
  * between two graph replays idles the stream on both sides of it (bench.py e2e: 36 us per step at config 2). */
 int fdsm_publish_scalars(const float* src, float* h_dst, int64_t n, fdsm_stream_t stream);
+/* Host plumbing of the end-to-end step (`x_real = itr.__next__().to(device)`, DeepEBM/train_ssm.py:61), one call each instead of
+ * four stream / event operations from the host language -- on a busy host the step loop is otherwise host-bound:
+ * fdsm_stage_h2d: copy_stream waits for the cudaEvent_t ev_free (may be NULL: the previous consumer of dst), copies nbytes from
+ *   PINNED host memory h_src to dst, records the cudaEvent_t ev_ready; main_stream (where the step follows) waits for it.
+ * fdsm_publish_scalars_record: records the cudaEvent_t ev (may be NULL) on stream, then fdsm_publish_scalars. */
+int fdsm_stage_h2d(void* dst, const void* h_src, int64_t nbytes, fdsm_stream_t copy_stream, void* ev_free, void* ev_ready,
+                   fdsm_stream_t main_stream);
+int fdsm_publish_scalars_record(const float* src, float* h_dst, int64_t n, fdsm_stream_t stream, void* ev);
 
 /* ------------------------------------------------------------------------------------------
  * The step's single exchange over NVLink peer memory: all-reduce of the flat fp32 gradient
