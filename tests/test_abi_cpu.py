@@ -86,3 +86,20 @@ def test_product_never_imports_oracle():
                 txt = open(os.path.join(dp, fn)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", txt, flags=re.M), f"{fn} imports oracle/"
                 assert "/root/reference" not in txt
+
+
+def test_integration_md_names_every_entry_point():
+    """INTEGRATION.md is the maintainer's map from C entry point to the reference code it replaces: every function
+    include/fdsm.h declares appears there (the `a/b` and `_fwd/bwd` shorthands of its table are expanded)."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hdr = open(os.path.join(root, "include", "fdsm.h")).read()
+    doc = open(os.path.join(root, "INTEGRATION.md")).read()
+    names = sorted(set(re.findall(r"\b(fdsm_[a-z0-9_]+)\s*\(", hdr)))
+    mentioned = set(re.findall(r"fdsm_[a-z0-9_]+", doc))
+    for m in re.findall(r"`(fdsm_[a-z0-9_]+(?:/[a-z0-9_]+)+)`", doc):      # `fdsm_mlp_sizes/prepare/forward/backward`, `..._fwd/bwd`
+        head, *rest = m.split("/")
+        stem = head[:head.rfind("_") + 1]
+        mentioned.update(stem + r for r in rest)
+    missing = [n for n in names if n not in mentioned]
+    assert not missing, missing
