@@ -55,3 +55,27 @@ def test_fd_adapters_refuse_cpu_tensors(fdsm):
     for nt in ("sphere", "radermacher"):
         with pytest.raises(fdsm._lib.FdsmError):
             fdsm.losses.single_efficient_score_matching(c["net"], c["x"], eps=0.01, noise_type=nt, u=c["u"])
+
+
+def test_read_loss_to_host_takes_the_copy_path_for_pageable_destinations(fdsm):
+    """train.read_loss_to_host: only a pinned fp32 destination on a CUDA loss goes through fdsm_publish_scalars; everything
+    else (here: CPU tensors) is torch's copy -- same value either way."""
+    import torch
+    from fdsm_b200.train import read_loss_to_host
+    loss, dst = torch.tensor(1.25), torch.zeros(())
+    assert read_loss_to_host(loss, dst) is dst and float(dst) == 1.25
+    dst64 = torch.zeros((), dtype=torch.float64)
+    read_loss_to_host(torch.tensor(-3.5), dst64)
+    assert float(dst64) == -3.5
+
+
+def test_inorm_plus_op_sequence_second_order_on_cpu(fdsm):
+    """The op sequence InormPlus.backward differentiates when the caller asks for the gradient of the gradient
+    (create_graph=True) is an ordinary differentiable torch function: gradcheck in float64, first and second order."""
+    import torch
+    torch.manual_seed(0)
+    x = torch.randn(2, 3, 4, 4, dtype=torch.float64, requires_grad=True)
+    g, a, b = (torch.randn(1, 3, dtype=torch.float64, requires_grad=True) for _ in range(3))
+    f = lambda x, g, a, b: fdsm.ops.inorm_plus_reference(x, g, a, b, act=True)
+    assert torch.autograd.gradcheck(f, (x, g, a, b), eps=1e-6, atol=1e-6)
+    assert torch.autograd.gradgradcheck(f, (x, g, a, b), eps=1e-6, atol=1e-5)
